@@ -1,0 +1,162 @@
+"""ctypes wrapper of oracle/tsdf_oracle.c -- TEST INFRASTRUCTURE, NOT PRODUCT.
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline /
+--impl reference legs may import this module.  Parity status: pinned for the
+global volume by tests/golden (fixtures made from the unmodified reference).
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = os.path.join(_HERE, "liboracle.so")
+_SRCS = ["tsdf_oracle.c", "local_oracle.c", "mc_oracle.c"]
+
+
+def build(force=False):
+    srcs = [os.path.join(_HERE, s) for s in _SRCS if os.path.exists(os.path.join(_HERE, s))]
+    if not force and os.path.exists(_LIB) and all(
+        os.path.getmtime(_LIB) >= os.path.getmtime(s) for s in srcs
+    ):
+        return _LIB
+    cmd = ["gcc", "-O2", "-ffp-contract=off", "-fno-fast-math", "-fPIC", "-shared",
+           "-o", _LIB] + srcs + ["-lm"]
+    subprocess.check_call(cmd)
+    return _LIB
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        build()
+        L = C.CDLL(_LIB)
+        L.orc_create.restype = C.c_void_p
+        L.orc_create.argtypes = [C.c_double] * 4
+        L.orc_destroy.argtypes = [C.c_void_p]
+        L.orc_integrate_f32.restype = C.c_int64
+        L.orc_integrate_f32.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                        C.c_int64, C.c_double]
+        L.orc_integrate_f64.restype = C.c_int64
+        L.orc_integrate_f64.argtypes = L.orc_integrate_f32.argtypes
+        L.orc_num_voxels.restype = C.c_uint64
+        L.orc_num_voxels.argtypes = [C.c_void_p]
+        L.orc_num_events.restype = C.c_uint64
+        L.orc_num_events.argtypes = [C.c_void_p]
+        L.orc_export.restype = C.c_uint64
+        L.orc_export.argtypes = [C.c_void_p] * 5
+        L.orc_stats.argtypes = [C.c_void_p] * 3
+        L.orc_query.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int64,
+                                C.c_void_p, C.c_void_p, C.c_void_p]
+        L.orc_sim3_act_f32.argtypes = [C.c_void_p] * 3
+        L.orc_stage_keyframe.restype = C.c_int64
+        L.orc_stage_keyframe.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                         C.c_int, C.c_int, C.c_int, C.c_int, C.c_float,
+                                         C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        _lib = L
+    return _lib
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p) if a is not None else None
+
+
+class OracleVolume:
+    """CPU restatement of reference TSDFVolume (global_volume.py:15-140)."""
+
+    def __init__(self, voxel_size, truncation, max_weight=100.0, min_weight=1.0e-3):
+        self.voxel_size = float(voxel_size)
+        self.truncation = float(truncation)
+        self.max_weight = float(max_weight)
+        self.min_weight = float(min_weight)
+        self._h = lib().orc_create(self.voxel_size, self.truncation, self.max_weight,
+                                   self.min_weight)
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            lib().orc_destroy(self._h)
+            self._h = None
+
+    def integrate(self, points_world, confidences, cam_origin, step_scale=0.5):
+        pts = np.asarray(points_world)
+        if pts.size == 0:
+            return 0
+        conf = np.ascontiguousarray(confidences, dtype=np.float64).reshape(-1)
+        if pts.dtype == np.float32:
+            pts = np.ascontiguousarray(pts, dtype=np.float32).reshape(-1, 3)
+            org = np.ascontiguousarray(cam_origin, dtype=np.float32).reshape(3)
+            fn = lib().orc_integrate_f32
+        else:
+            pts = np.ascontiguousarray(pts, dtype=np.float64).reshape(-1, 3)
+            org = np.ascontiguousarray(cam_origin, dtype=np.float64).reshape(3)
+            fn = lib().orc_integrate_f64
+        return int(fn(self._h, _p(pts), _p(conf), _p(org), pts.shape[0], float(step_scale)))
+
+    def export(self):
+        n = int(lib().orc_num_voxels(self._h))
+        keys = np.zeros((n, 3), np.int64)
+        tsdf = np.zeros(n, np.float64)
+        w = np.zeros(n, np.float64)
+        cnt = np.zeros(n, np.uint32)
+        lib().orc_export(self._h, _p(keys), _p(tsdf), _p(w), _p(cnt))
+        return keys, tsdf, w, cnt
+
+    @property
+    def events(self):
+        return int(lib().orc_num_events(self._h))
+
+    def stats(self):
+        a = C.c_int64()
+        b = C.c_int64()
+        lib().orc_stats(self._h, C.byref(a), C.byref(b))
+        return {"valid_voxels": a.value, "total_voxels": b.value}
+
+    def query_batch(self, pts):
+        pts = np.asarray(pts)
+        f64 = pts.dtype != np.float32
+        pts = np.ascontiguousarray(pts, dtype=np.float64 if f64 else np.float32).reshape(-1, 3)
+        m = pts.shape[0]
+        t = np.zeros(m, np.float64)
+        g = np.zeros((m, 3), np.float64)
+        fl = np.zeros(m, np.uint8)
+        lib().orc_query(self._h, _p(pts), int(f64), m, _p(t), _p(g), _p(fl))
+        return t, g, fl
+
+    def query(self, point_world):
+        t, g, fl = self.query_batch(np.asarray(point_world).reshape(1, 3))
+        if not fl[0] & 1:
+            return None, None
+        return float(t[0]), (g[0].copy() if fl[0] & 2 else None)
+
+
+def sim3_act(pose, x):
+    pose = np.ascontiguousarray(pose, np.float32).reshape(8)
+    x = np.ascontiguousarray(x, np.float32).reshape(-1, 3)
+    y = np.zeros_like(x)
+    for i in range(x.shape[0]):
+        lib().orc_sim3_act_f32(_p(pose), _p(x[i]), _p(y[i]))
+    return y
+
+
+def stage_keyframe(X, Cf, pose, q_grid, H, W, min_conf):
+    """Returns pts_world f32 (n,3), conf f64 (n,), conf_q f64 (n,), cam_origin f32 (3,)."""
+    X = np.ascontiguousarray(X, np.float32).reshape(-1, 3)
+    Cf = np.ascontiguousarray(Cf, np.float32).reshape(-1)
+    pose = np.ascontiguousarray(pose, np.float32).reshape(8)
+    n = H * W
+    pts = np.zeros((n, 3), np.float32)
+    conf = np.zeros(n, np.float64)
+    confq = np.zeros(n, np.float64)
+    org = np.zeros(3, np.float32)
+    gh = gw = 0
+    qg = None
+    if q_grid is not None:
+        qg = np.ascontiguousarray(q_grid, np.float32)
+        gh, gw = qg.shape
+    k = int(lib().orc_stage_keyframe(_p(X), _p(Cf), _p(pose), _p(qg), gh, gw, H, W,
+                                     float(min_conf), _p(pts), _p(conf), _p(confq), _p(org)))
+    return pts[:k].copy(), conf[:k].copy(), confq[:k].copy(), org
