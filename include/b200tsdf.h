@@ -1,0 +1,158 @@
+/*
+ * b200tsdf.h -- C ABI of libb200tsdf.so, the sm_100a replacement for the
+ * dual-TSDF fusion hot path of MASt3R-SLAM-Quality-dualTSDF.
+ *
+ * This is the drop-in boundary: plain pointers and sizes, no torch types.
+ * Every entry point cites the reference interface it replaces (paths relative
+ * to the reference tree).  The reference-side binding (ctypes) is shown in
+ * INTEGRATION.md and implemented in mast3r_slam_quality_dualtsdf_b200/_ffi.py.
+ *
+ * Conventions
+ *  - every function returns 0 on success, <0 on error (B200TSDF_E_*); the
+ *    message of the last error of the calling thread: b200tsdf_last_error().
+ *  - pointers named *_dev are DEVICE pointers borrowed for the duration of the
+ *    stream-ordered call; *_host are host pointers.  `stream` is a
+ *    cudaStream_t passed as void* (NULL = legacy default stream).
+ *  - calls are asynchronous w.r.t. the host unless they return host data.
+ *  - the handle owns all volume memory (voxel-block hash + block payload).
+ *  - there is NO CPU fallback: every compute call needs a CUDA device.
+ */
+#ifndef B200TSDF_H_
+#define B200TSDF_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200TSDF_ABI_VERSION 1
+
+enum {
+  B200TSDF_OK = 0,
+  B200TSDF_E_INVALID = -1,  /* bad argument */
+  B200TSDF_E_CUDA = -2,     /* CUDA runtime error (message has the detail) */
+  B200TSDF_E_CAPACITY = -3, /* voxel-block hash full: raise capacity_log2 */
+  B200TSDF_E_NOMEM = -4
+};
+
+enum { B200TSDF_F32 = 0, B200TSDF_F64 = 1 };
+
+typedef struct b200tsdf b200tsdf_t;
+
+/* Replaces TSDFVolume.__init__ (mast3r_slam/tsdf/global_volume.py:18-30) and
+ * the tsdf_global config keys (config/base.yaml:110-125). */
+typedef struct {
+  double voxel_size;  /* tsdf_global.voxel_size   */
+  double truncation;  /* tsdf_global.trunc_dist   */
+  double max_weight;  /* tsdf_global.max_weight   */
+  double min_weight;  /* tsdf_global.min_tsdf_weight */
+  /* voxel-block hash: 2^capacity_log2 slots, each slot owns one 8x8x8 voxel
+   * block (payload indexed by slot).  Keep load factor <= ~0.6. */
+  int32_t capacity_log2;
+  /* optional bound in integer VOXEL keys (key = floor(p / voxel_size)):
+   * updates whose key is outside [key_min, key_max) are dropped.  The z range
+   * doubles as the z-slab of a rank in multi-GPU runs.  bounded = 0: the
+   * volume is unbounded like the reference dict. */
+  int32_t bounded;
+  int64_t key_min[3];
+  int64_t key_max[3];
+  int32_t device; /* CUDA device ordinal */
+  int32_t reserved;
+} b200tsdf_config;
+
+const char *b200tsdf_last_error(void);
+int b200tsdf_abi_version(void);
+
+int b200tsdf_create(const b200tsdf_config *cfg, b200tsdf_t **out);
+int b200tsdf_destroy(b200tsdf_t *h);
+/* Forget every voxel (keeps the allocation). */
+int b200tsdf_reset(b200tsdf_t *h, void *stream);
+
+/* Replaces TSDFVolume.integrate (global_volume.py:35-72) with the
+ * _update_voxel fold (:74-88) for BOTH volumes in one pass.
+ *  pts_dev    M x 3 world points, dtype B200TSDF_F32 or _F64 (the arithmetic
+ *             follows the dtype exactly as numpy >= 2 does in the reference)
+ *  conf_dev   M float64 confidences of the primary volume
+ *  conf_q_dev M float64 confidences of the quality-weighted volume (C*q), or
+ *             NULL: the second volume is then left untouched
+ *  origin_host 3 values of pts dtype (camera centre)
+ *  rays_fused_host (nullable) receives the reference's return value; passing
+ *             it makes the call synchronise the stream. */
+int b200tsdf_integrate_points(b200tsdf_t *h, const void *pts_dev, int dtype,
+                              const double *conf_dev, const double *conf_q_dev,
+                              const void *origin_host, int64_t m,
+                              double step_scale, int64_t *rays_fused_host,
+                              void *stream);
+
+/* Replaces TSDFGlobalIntegrator._integrate_single
+ * (mast3r_slam/tsdf/global_manager.py:81-106) for a batch of B keyframes:
+ * staging (confidence filter, Sim3 act, quality upsample), voxel-block
+ * allocation and the dual fold in one launch.  No random subsample: every
+ * pixel with C > min_conf is fused, in pixel order.
+ *  X_dev     B x H*W x 3 float32 camera-frame pointmaps (frame.py:242)
+ *  C_dev     B x H*W     float32 summed confidences     (frame.py:243)
+ *  q_grid_dev B x gh x gw float32 per-patch quality weights, or NULL (q = 1)
+ *  pose_dev  B x 8 float32 Sim3 [t(3), q(xyzw), s]       (frame.py:241)
+ *  H % gh == 0 and W % gw == 0 are required when q_grid_dev != NULL. */
+int b200tsdf_integrate_keyframes(b200tsdf_t *h, const float *X_dev,
+                                 const float *C_dev, const float *q_grid_dev,
+                                 const float *pose_dev, int32_t B, int32_t H,
+                                 int32_t W, int32_t gh, int32_t gw,
+                                 float min_conf, double step_scale,
+                                 void *stream);
+
+/* Same call with HOST buffers (pinned or pageable): copies H2D on `stream`
+ * into an internal staging area, then fuses.  This is the entry the
+ * reference-facing plugin uses when keyframes live on the host. */
+int b200tsdf_integrate_keyframes_host(b200tsdf_t *h, const float *X_host,
+                                      const float *C_host,
+                                      const float *q_grid_host,
+                                      const float *pose_host, int32_t B,
+                                      int32_t H, int32_t W, int32_t gh,
+                                      int32_t gw, float min_conf,
+                                      double step_scale, void *stream);
+
+/* Counters since create/reset (synchronises the stream).
+ *  out[0] rays fused        out[1] voxel updates, primary volume
+ *  out[2] voxel updates, quality volume   out[3] allocated voxel blocks
+ *  out[4] updates dropped (outside bounds) out[5] hash overflow events */
+int b200tsdf_counters(b200tsdf_t *h, int64_t out_host[6], void *stream);
+
+/* Replaces TSDFVolume.stats (global_volume.py:136-140); which = 0 primary,
+ * 1 quality volume.  Synchronises. */
+int b200tsdf_stats(b200tsdf_t *h, int which, int64_t *valid_host,
+                   int64_t *total_host, void *stream);
+
+/* Replaces TSDFVolume.query + _estimate_gradient (global_volume.py:93-128),
+ * batched.  flags bit0 = value present, bit1 = gradient present. */
+int b200tsdf_query(b200tsdf_t *h, int which, const void *pts_dev, int dtype,
+                   int64_t m, double *tsdf_dev, double *grad_dev,
+                   uint8_t *flags_dev, void *stream);
+
+/* Dump every voxel of one volume (parity tests, checkpoints): two-call
+ * protocol -- cap = 0 returns the count in *n_host.  Order is unspecified;
+ * keys are integer voxel coordinates like the reference dict keys.
+ * tsdf/weight are what the reference VoxelData holds, count = number of
+ * _update_voxel hits.  Synchronises. */
+int b200tsdf_export_voxels(b200tsdf_t *h, int which, int64_t *keys_dev,
+                           float *tsdf_dev, float *weight_dev,
+                           uint32_t *count_dev, int64_t cap, int64_t *n_host,
+                           void *stream);
+
+/* Block keys (integer block coordinates = voxel key >> 3) of all allocated
+ * voxel blocks; same two-call protocol. */
+int b200tsdf_export_blocks(b200tsdf_t *h, int64_t *bkeys_dev, int64_t cap,
+                           int64_t *n_host, void *stream);
+
+/* Marching cubes over the voxel blocks (no reference counterpart; SURVEY 8(a)
+ * A11).  A cube is emitted only if all 8 corners hold weight >= min_weight.
+ * Two-call protocol: verts_dev == NULL returns the triangle count only.
+ * verts_dev receives 3 vertices (9 floats) per triangle. */
+int b200tsdf_extract_mesh(b200tsdf_t *h, int which, float *verts_dev,
+                          int64_t tri_cap, int64_t *n_tris_host, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200TSDF_H_ */

@@ -1,0 +1,78 @@
+"""ctypes binding of libb200tsdf.so (include/b200tsdf.h).
+
+This is the binding a maintainer of the reference would add.
+There is no CPU fallback: if the library is missing or no CUDA device is
+present, calls raise.
+"""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libb200tsdf.so")
+
+F32, F64 = 0, 1
+
+# every symbol include/b200tsdf.h declares (tests check the .so exports all)
+SYMBOLS = [
+    "b200tsdf_last_error", "b200tsdf_abi_version", "b200tsdf_create", "b200tsdf_destroy",
+    "b200tsdf_reset", "b200tsdf_integrate_points", "b200tsdf_integrate_keyframes",
+    "b200tsdf_integrate_keyframes_host", "b200tsdf_counters", "b200tsdf_stats",
+    "b200tsdf_query", "b200tsdf_export_voxels", "b200tsdf_export_blocks",
+    "b200tsdf_extract_mesh",
+]
+
+
+class Config(C.Structure):
+    _fields_ = [
+        ("voxel_size", C.c_double), ("truncation", C.c_double),
+        ("max_weight", C.c_double), ("min_weight", C.c_double),
+        ("capacity_log2", C.c_int32), ("bounded", C.c_int32),
+        ("key_min", C.c_int64 * 3), ("key_max", C.c_int64 * 3),
+        ("device", C.c_int32), ("reserved", C.c_int32),
+    ]
+
+
+class B200TSDFError(RuntimeError):
+    pass
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise B200TSDFError(
+            f"{LIB_PATH} is missing: build it with "
+            "`python -m mast3r_slam_quality_dualtsdf_b200.build` (there is no CPU fallback)")
+    L = C.CDLL(LIB_PATH)
+    vp, i32, i64, dbl = C.c_void_p, C.c_int32, C.c_int64, C.c_double
+    L.b200tsdf_last_error.restype = C.c_char_p
+    L.b200tsdf_last_error.argtypes = []
+    L.b200tsdf_abi_version.restype = C.c_int
+    L.b200tsdf_create.argtypes = [C.POINTER(Config), C.POINTER(vp)]
+    L.b200tsdf_destroy.argtypes = [vp]
+    L.b200tsdf_reset.argtypes = [vp, vp]
+    L.b200tsdf_integrate_points.argtypes = [vp, vp, C.c_int, vp, vp, vp, i64, dbl, vp, vp]
+    L.b200tsdf_integrate_keyframes.argtypes = [vp, vp, vp, vp, vp, i32, i32, i32, i32, i32,
+                                               C.c_float, dbl, vp]
+    L.b200tsdf_integrate_keyframes_host.argtypes = L.b200tsdf_integrate_keyframes.argtypes
+    L.b200tsdf_counters.argtypes = [vp, vp, vp]
+    L.b200tsdf_stats.argtypes = [vp, C.c_int, vp, vp, vp]
+    L.b200tsdf_query.argtypes = [vp, C.c_int, vp, C.c_int, i64, vp, vp, vp, vp]
+    L.b200tsdf_export_voxels.argtypes = [vp, C.c_int, vp, vp, vp, vp, i64, vp, vp]
+    L.b200tsdf_export_blocks.argtypes = [vp, vp, i64, vp, vp]
+    L.b200tsdf_extract_mesh.argtypes = [vp, C.c_int, vp, i64, vp, vp]
+    for s in SYMBOLS:
+        if s != "b200tsdf_last_error":
+            getattr(L, s).restype = C.c_int
+    _lib = L
+    return L
+
+
+def check(rc, what=""):
+    if rc != 0:
+        msg = lib().b200tsdf_last_error().decode("utf-8", "replace")
+        raise B200TSDFError(f"{what} failed (rc={rc}): {msg}")

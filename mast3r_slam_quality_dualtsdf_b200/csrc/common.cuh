@@ -1,0 +1,153 @@
+// common.cuh -- shared device/host definitions of libb200tsdf (sm_100a only).
+//
+// Data layout in HBM (DESIGN.md "Data layout"):
+//   keys  [cap]        u64   packed block key, EMPTY = ~0     (open addressing)
+//   vox   [cap * 512]  float4 {S_p, W_p, S_q, W_q}             (16 B / voxel)
+//   cnt   [cap * 512]  u64   lo32 = hits primary, hi32 = hits quality volume
+//   list  [cap]        u32   slots in allocation order (n_blocks entries)
+// A block is 8x8x8 voxels; the payload of hash slot s is vox[s*512 ...].
+// S = sum(tsdf_i * w_i), W = sum(w_i): the reference running average
+// (global_volume.py:74-88) is exactly tsdf = S / W_eff with
+// W_eff = (hits == 1 ? W : min(W, max_weight)) -- see DESIGN.md "the fold".
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/b200tsdf.h"
+
+#define B200_BLOCK_LOG2 3
+#define B200_BLOCK_EDGE 8
+#define B200_BLOCK_VOX 512
+#define B200_EMPTY_KEY 0xFFFFFFFFFFFFFFFFull
+#define B200_KEY_BIAS (1 << 20) /* block coords in [-2^20, 2^20) */
+#define B200_MAX_PROBE 4096
+
+enum {
+  CTR_RAYS = 0,
+  CTR_EV_P = 1,
+  CTR_EV_Q = 2,
+  CTR_BLOCKS = 3,
+  CTR_DROPPED = 4,
+  CTR_OVERFLOW = 5,
+  CTR_COUNT = 8
+};
+
+struct VolumeDev {
+  unsigned long long *keys;
+  float4 *vox;
+  unsigned long long *cnt;
+  uint32_t *list;
+  unsigned long long *ctr; // CTR_COUNT counters
+  uint32_t cap_mask;
+  int bounded;
+  int kmin[3], kmax[3]; // voxel-key bounds (clamped to int32 range)
+  float max_weight, min_weight;
+};
+
+struct b200tsdf {
+  b200tsdf_config cfg;
+  VolumeDev d;
+  uint64_t cap;
+  // host staging for the *_host entry points
+  void *stage_dev;
+  size_t stage_bytes;
+  unsigned long long *scratch; // small device scratch (counters for sweeps)
+};
+
+// ---------------------------------------------------------------- hashing
+__host__ __device__ __forceinline__ unsigned long long pack_block_key(int bx, int by,
+                                                                      int bz) {
+  return (unsigned long long)(uint32_t)(bx + B200_KEY_BIAS) |
+         ((unsigned long long)(uint32_t)(by + B200_KEY_BIAS) << 21) |
+         ((unsigned long long)(uint32_t)(bz + B200_KEY_BIAS) << 42);
+}
+__host__ __device__ __forceinline__ void unpack_block_key(unsigned long long k, int &bx,
+                                                          int &by, int &bz) {
+  bx = (int)(k & 0x1FFFFF) - B200_KEY_BIAS;
+  by = (int)((k >> 21) & 0x1FFFFF) - B200_KEY_BIAS;
+  bz = (int)((k >> 42) & 0x1FFFFF) - B200_KEY_BIAS;
+}
+__host__ __device__ __forceinline__ bool block_in_range(int bx, int by, int bz) {
+  return bx >= -B200_KEY_BIAS && bx < B200_KEY_BIAS && by >= -B200_KEY_BIAS &&
+         by < B200_KEY_BIAS && bz >= -B200_KEY_BIAS && bz < B200_KEY_BIAS;
+}
+__host__ __device__ __forceinline__ uint32_t hash_block_key(unsigned long long k) {
+  k ^= k >> 33;
+  k *= 0xff51afd7ed558ccdull;
+  k ^= k >> 33;
+  k *= 0xc4ceb9fe1a85ec53ull;
+  k ^= k >> 33;
+  return (uint32_t)k;
+}
+
+#ifdef __CUDACC__
+// Lookup only.  Returns slot or 0xFFFFFFFF.
+__device__ __forceinline__ uint32_t hash_find(const VolumeDev &v, unsigned long long key) {
+  uint32_t s = hash_block_key(key) & v.cap_mask;
+  for (int p = 0; p < B200_MAX_PROBE; ++p) {
+    unsigned long long k = __ldcg(v.keys + s);
+    if (k == key) return s;
+    if (k == B200_EMPTY_KEY) return 0xFFFFFFFFu;
+    s = (s + 1) & v.cap_mask;
+  }
+  return 0xFFFFFFFFu;
+}
+
+// Insert-if-absent.  Payload is indexed by slot, so a successful CAS is the
+// whole allocation; the winner appends the slot to the block list.
+// *fresh is set when this call allocated the block.
+__device__ __forceinline__ uint32_t hash_insert(const VolumeDev &v, unsigned long long key,
+                                                bool *fresh) {
+  uint32_t s = hash_block_key(key) & v.cap_mask;
+  *fresh = false;
+  for (int p = 0; p < B200_MAX_PROBE; ++p) {
+    unsigned long long k = __ldcg(v.keys + s);
+    if (k == key) return s;
+    if (k == B200_EMPTY_KEY) {
+      unsigned long long old = atomicCAS(v.keys + s, B200_EMPTY_KEY, key);
+      if (old == B200_EMPTY_KEY) {
+        *fresh = true;
+        return s;
+      }
+      if (old == key) return s;
+    }
+    s = (s + 1) & v.cap_mask;
+  }
+  return 0xFFFFFFFFu;
+}
+
+// 128-bit vector reduction into the packed voxel (sm_90+: red.global.v4.f32).
+__device__ __forceinline__ void red_add_v4(float4 *p, float a, float b, float c, float d) {
+  asm volatile("red.relaxed.gpu.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p),
+               "f"(a), "f"(b), "f"(c), "f"(d)
+               : "memory");
+}
+__device__ __forceinline__ void red_add_u64(unsigned long long *p, unsigned long long x) {
+  asm volatile("red.relaxed.gpu.global.add.u64 [%0], %1;" ::"l"(p), "l"(x) : "memory");
+}
+
+// Reference view of one packed voxel: VoxelData{tsdf, weight} of volume
+// `which` (global_volume.py:9-12, :84-88).  hits == 0 -> absent.
+__device__ __forceinline__ bool voxel_view(const float4 &a, unsigned long long c, int which,
+                                           float max_weight, float &tsdf, float &w,
+                                           uint32_t &hits) {
+  float S = which ? a.z : a.x, W = which ? a.w : a.y;
+  hits = which ? (uint32_t)(c >> 32) : (uint32_t)c;
+  if (hits == 0) return false;
+  w = (hits == 1) ? W : fminf(W, max_weight);
+  tsdf = S / fmaxf(1.0e-9f, w);
+  return true;
+}
+#endif
+
+// ---------------------------------------------------------------- errors
+void b200_set_error(const char *fmt, ...);
+#define B200_CUDA(call)                                                          \
+  do {                                                                           \
+    cudaError_t e__ = (call);                                                    \
+    if (e__ != cudaSuccess) {                                                    \
+      b200_set_error("%s:%d %s -> %s", __FILE__, __LINE__, #call,                \
+                     cudaGetErrorString(e__));                                   \
+      return B200TSDF_E_CUDA;                                                    \
+    }                                                                            \
+  } while (0)

@@ -1,0 +1,218 @@
+// sweep.cu -- streaming passes over the allocated voxel blocks: stats, voxel /
+// block export, batched query.
+// Replaces TSDFVolume.stats (mast3r_slam/tsdf/global_volume.py:136-140),
+// TSDFVolume.query + _estimate_gradient (:93-128); export has no reference
+// counterpart (it dumps what TSDFVolume._voxels holds, for parity tests).
+#include "common.cuh"
+#include "ray.cuh"
+
+// One CTA per allocated block, 128 threads x 4 voxels, 128-bit loads.
+__global__ void __launch_bounds__(128)
+    stats_kernel(VolumeDev v, int which, unsigned long long *out /* [valid,total] */) {
+  uint32_t nb = (uint32_t)v.ctr[CTR_BLOCKS];
+  uint32_t valid = 0, total = 0;
+  for (uint32_t b = blockIdx.x; b < nb; b += gridDim.x) {
+    size_t base = (size_t)v.list[b] * B200_BLOCK_VOX;
+    for (int i = threadIdx.x; i < B200_BLOCK_VOX; i += blockDim.x) {
+      float4 a = v.vox[base + i];
+      unsigned long long c = v.cnt[base + i];
+      float t, w;
+      uint32_t hits;
+      if (voxel_view(a, c, which, v.max_weight, t, w, hits)) {
+        total++;
+        if (w >= v.min_weight) valid++;
+      }
+    }
+  }
+  valid = __reduce_add_sync(0xFFFFFFFFu, valid);
+  total = __reduce_add_sync(0xFFFFFFFFu, total);
+  if ((threadIdx.x & 31) == 0) {
+    if (valid) atomicAdd(out, (unsigned long long)valid);
+    if (total) atomicAdd(out + 1, (unsigned long long)total);
+  }
+}
+
+extern "C" int b200tsdf_stats(b200tsdf_t *h, int which, int64_t *valid_host, int64_t *total_host,
+                              void *stream) {
+  if (!h || !valid_host || !total_host || (which != 0 && which != 1)) return B200TSDF_E_INVALID;
+  cudaStream_t st = (cudaStream_t)stream;
+  B200_CUDA(cudaSetDevice(h->cfg.device));
+  B200_CUDA(cudaMemsetAsync(h->scratch, 0, 16, st));
+  stats_kernel<<<148 * 8, 128, 0, st>>>(h->d, which, h->scratch);
+  B200_CUDA(cudaGetLastError());
+  unsigned long long r[2];
+  B200_CUDA(cudaMemcpyAsync(r, h->scratch, 16, cudaMemcpyDeviceToHost, st));
+  B200_CUDA(cudaStreamSynchronize(st));
+  *valid_host = (int64_t)r[0];
+  *total_host = (int64_t)r[1];
+  return B200TSDF_OK;
+}
+
+// Export: warp-scan compaction (ballot + popc), one atomicAdd per warp.
+__global__ void __launch_bounds__(128)
+    export_kernel(VolumeDev v, int which, long long *keys, float *tsdf, float *weight,
+                  uint32_t *count, long long cap, unsigned long long *n_out) {
+  uint32_t nb = (uint32_t)v.ctr[CTR_BLOCKS];
+  const int lane = threadIdx.x & 31;
+  for (uint32_t b = blockIdx.x; b < nb; b += gridDim.x) {
+    uint32_t slot = v.list[b];
+    int bx, by, bz;
+    unpack_block_key(v.keys[slot], bx, by, bz);
+    size_t base = (size_t)slot * B200_BLOCK_VOX;
+    for (int i = threadIdx.x; i < B200_BLOCK_VOX; i += blockDim.x) {
+      float4 a = v.vox[base + i];
+      unsigned long long c = v.cnt[base + i];
+      float t, w;
+      uint32_t hits;
+      bool on = voxel_view(a, c, which, v.max_weight, t, w, hits);
+      unsigned mask = __ballot_sync(0xFFFFFFFFu, on);
+      if (mask == 0) continue;
+      unsigned long long start = 0;
+      if (lane == 0) start = atomicAdd(n_out, (unsigned long long)__popc(mask));
+      start = __shfl_sync(0xFFFFFFFFu, start, 0);
+      if (on && keys) {
+        long long o = (long long)start + __popc(mask & ((1u << lane) - 1));
+        if (o < cap) {
+          keys[3 * o + 0] = (long long)bx * 8 + (i & 7);
+          keys[3 * o + 1] = (long long)by * 8 + ((i >> 3) & 7);
+          keys[3 * o + 2] = (long long)bz * 8 + (i >> 6);
+          tsdf[o] = t;
+          weight[o] = w;
+          count[o] = hits;
+        }
+      }
+    }
+  }
+}
+
+extern "C" int b200tsdf_export_voxels(b200tsdf_t *h, int which, int64_t *keys_dev, float *tsdf_dev,
+                                      float *weight_dev, uint32_t *count_dev, int64_t cap,
+                                      int64_t *n_host, void *stream) {
+  if (!h || !n_host || (which != 0 && which != 1)) return B200TSDF_E_INVALID;
+  if (cap > 0 && (!keys_dev || !tsdf_dev || !weight_dev || !count_dev)) return B200TSDF_E_INVALID;
+  cudaStream_t st = (cudaStream_t)stream;
+  B200_CUDA(cudaSetDevice(h->cfg.device));
+  B200_CUDA(cudaMemsetAsync(h->scratch, 0, 8, st));
+  export_kernel<<<148 * 8, 128, 0, st>>>(h->d, which, cap > 0 ? (long long *)keys_dev : nullptr,
+                                         tsdf_dev, weight_dev, count_dev, (long long)cap,
+                                         h->scratch);
+  B200_CUDA(cudaGetLastError());
+  unsigned long long n;
+  B200_CUDA(cudaMemcpyAsync(&n, h->scratch, 8, cudaMemcpyDeviceToHost, st));
+  B200_CUDA(cudaStreamSynchronize(st));
+  *n_host = (int64_t)n;
+  return B200TSDF_OK;
+}
+
+__global__ void export_blocks_kernel(VolumeDev v, long long *bkeys, long long cap) {
+  uint32_t nb = (uint32_t)v.ctr[CTR_BLOCKS];
+  for (long long b = (long long)blockIdx.x * blockDim.x + threadIdx.x; b < nb && b < cap;
+       b += (long long)gridDim.x * blockDim.x) {
+    int bx, by, bz;
+    unpack_block_key(v.keys[v.list[b]], bx, by, bz);
+    bkeys[3 * b] = bx, bkeys[3 * b + 1] = by, bkeys[3 * b + 2] = bz;
+  }
+}
+
+extern "C" int b200tsdf_export_blocks(b200tsdf_t *h, int64_t *bkeys_dev, int64_t cap,
+                                      int64_t *n_host, void *stream) {
+  if (!h || !n_host || (cap > 0 && !bkeys_dev)) return B200TSDF_E_INVALID;
+  cudaStream_t st = (cudaStream_t)stream;
+  B200_CUDA(cudaSetDevice(h->cfg.device));
+  unsigned long long n;
+  B200_CUDA(cudaMemcpyAsync(&n, h->d.ctr + CTR_BLOCKS, 8, cudaMemcpyDeviceToHost, st));
+  B200_CUDA(cudaStreamSynchronize(st));
+  *n_host = (int64_t)n;
+  if (cap > 0 && n > 0) {
+    export_blocks_kernel<<<296, 256, 0, st>>>(h->d, (long long *)bkeys_dev, (long long)cap);
+    B200_CUDA(cudaGetLastError());
+    B200_CUDA(cudaStreamSynchronize(st));
+  }
+  return B200TSDF_OK;
+}
+
+// ------------------------------------------------------------------ query
+__device__ __forceinline__ bool fetch(const VolumeDev &v, int which, int kx, int ky, int kz,
+                                      float &t, float &w) {
+  int bx = kx >> 3, by = ky >> 3, bz = kz >> 3;
+  if (!block_in_range(bx, by, bz)) return false;
+  uint32_t s = hash_find(v, pack_block_key(bx, by, bz));
+  if (s == 0xFFFFFFFFu) return false;
+  size_t off = (size_t)s * B200_BLOCK_VOX + (((kz & 7) << 6) | ((ky & 7) << 3) | (kx & 7));
+  uint32_t hits;
+  return voxel_view(v.vox[off], v.cnt[off], which, v.max_weight, t, w, hits);
+}
+
+template <typename T>
+__global__ void query_kernel(VolumeDev v, int which, const T *__restrict__ pts, long long m,
+                             T vs, double voxel_size, double *tsdf, double *grad,
+                             uint8_t *flags) {
+  using R = Real<T>;
+  long long p = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= m) return;
+  int k[3];
+  for (int d = 0; d < 3; ++d) { // global_volume.py:133-134
+    T f = R::flr(R::div(pts[3 * p + d], vs));
+    f = f < (T)-2.0e9 ? (T)-2.0e9 : (f > (T)2.0e9 ? (T)2.0e9 : f);
+    k[d] = (int)f;
+  }
+  uint8_t fl = 0;
+  double tv = 0.0, g[3] = {0.0, 0.0, 0.0};
+  float t, w;
+  if (isfinite((double)pts[3 * p]) && fetch(v, which, k[0], k[1], k[2], t, w) &&
+      w >= v.min_weight) { // :98-100
+    fl = 1;
+    tv = (double)t;
+    int denom = 0;
+    for (int ax = 0; ax < 3; ++ax) { // :112-123
+      int kp[3] = {k[0], k[1], k[2]}, kn[3] = {k[0], k[1], k[2]};
+      kp[ax] += 1;
+      kn[ax] -= 1;
+      float tp, wp, tn, wn;
+      if (!fetch(v, which, kp[0], kp[1], kp[2], tp, wp)) continue;
+      if (!fetch(v, which, kn[0], kn[1], kn[2], tn, wn)) continue;
+      if (wp < v.min_weight || wn < v.min_weight) continue;
+      g[ax] = ((double)tp - (double)tn) / (2.0 * voxel_size);
+      denom++;
+    }
+    if (denom) {
+      double nrm = sqrt(fma(g[2], g[2], fma(g[1], g[1], g[0] * g[0])));
+      if (nrm >= 1.0e-9) { // :126-128
+        g[0] /= nrm, g[1] /= nrm, g[2] /= nrm;
+        fl = 3;
+      } else {
+        g[0] = g[1] = g[2] = 0.0;
+      }
+    }
+  }
+  tsdf[p] = tv;
+  grad[3 * p] = (fl & 2) ? g[0] : 0.0;
+  grad[3 * p + 1] = (fl & 2) ? g[1] : 0.0;
+  grad[3 * p + 2] = (fl & 2) ? g[2] : 0.0;
+  flags[p] = fl;
+}
+
+extern "C" int b200tsdf_query(b200tsdf_t *h, int which, const void *pts_dev, int dtype, int64_t m,
+                              double *tsdf_dev, double *grad_dev, uint8_t *flags_dev,
+                              void *stream) {
+  if (!h || m < 0 || (which != 0 && which != 1) ||
+      (m > 0 && (!pts_dev || !tsdf_dev || !grad_dev || !flags_dev)) ||
+      (dtype != B200TSDF_F32 && dtype != B200TSDF_F64)) {
+    b200_set_error("b200tsdf_query: invalid argument");
+    return B200TSDF_E_INVALID;
+  }
+  if (m == 0) return B200TSDF_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  B200_CUDA(cudaSetDevice(h->cfg.device));
+  unsigned grid = (unsigned)((m + 127) / 128);
+  if (dtype == B200TSDF_F32)
+    query_kernel<float><<<grid, 128, 0, st>>>(h->d, which, (const float *)pts_dev, (long long)m,
+                                              (float)h->cfg.voxel_size, h->cfg.voxel_size,
+                                              tsdf_dev, grad_dev, flags_dev);
+  else
+    query_kernel<double><<<grid, 128, 0, st>>>(h->d, which, (const double *)pts_dev, (long long)m,
+                                               h->cfg.voxel_size, h->cfg.voxel_size, tsdf_dev,
+                                               grad_dev, flags_dev);
+  B200_CUDA(cudaGetLastError());
+  return B200TSDF_OK;
+}

@@ -1,0 +1,128 @@
+// volume.cu -- handle lifetime, counters, error strings of libb200tsdf.
+// Replaces TSDFVolume.__init__ (mast3r_slam/tsdf/global_volume.py:18-30).
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <new>
+
+#include "common.cuh"
+
+static thread_local char g_err[512] = "";
+
+void b200_set_error(const char *fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+extern "C" const char *b200tsdf_last_error(void) { return g_err; }
+extern "C" int b200tsdf_abi_version(void) { return B200TSDF_ABI_VERSION; }
+
+static int clamp_i32(int64_t v) {
+  if (v < -2000000000ll) return -2000000000;
+  if (v > 2000000000ll) return 2000000000;
+  return (int)v;
+}
+
+extern "C" int b200tsdf_create(const b200tsdf_config *cfg, b200tsdf_t **out) {
+  if (!cfg || !out) {
+    b200_set_error("b200tsdf_create: null argument");
+    return B200TSDF_E_INVALID;
+  }
+  if (!(cfg->voxel_size > 0.0) || !(cfg->truncation > 0.0) || cfg->capacity_log2 < 4 ||
+      cfg->capacity_log2 > 30) {
+    b200_set_error("b200tsdf_create: bad config (voxel_size %g truncation %g capacity_log2 %d)",
+                   cfg->voxel_size, cfg->truncation, cfg->capacity_log2);
+    return B200TSDF_E_INVALID;
+  }
+  int ndev = 0;
+  B200_CUDA(cudaGetDeviceCount(&ndev));
+  if (ndev <= 0) {
+    b200_set_error("b200tsdf_create: no CUDA device (there is no CPU fallback)");
+    return B200TSDF_E_CUDA;
+  }
+  B200_CUDA(cudaSetDevice(cfg->device));
+  b200tsdf *h = new (std::nothrow) b200tsdf();
+  if (!h) return B200TSDF_E_NOMEM;
+  memset(h, 0, sizeof(*h));
+  h->cfg = *cfg;
+  h->cap = 1ull << cfg->capacity_log2;
+  VolumeDev &d = h->d;
+  cudaError_t e;
+  e = cudaMalloc(&d.keys, h->cap * sizeof(unsigned long long));
+  if (e == cudaSuccess) e = cudaMalloc(&d.vox, h->cap * B200_BLOCK_VOX * sizeof(float4));
+  if (e == cudaSuccess) e = cudaMalloc(&d.cnt, h->cap * B200_BLOCK_VOX * sizeof(unsigned long long));
+  if (e == cudaSuccess) e = cudaMalloc(&d.list, h->cap * sizeof(uint32_t));
+  if (e == cudaSuccess) e = cudaMalloc(&d.ctr, CTR_COUNT * sizeof(unsigned long long));
+  if (e == cudaSuccess) e = cudaMalloc(&h->scratch, 64 * sizeof(unsigned long long));
+  if (e != cudaSuccess) {
+    b200_set_error("b200tsdf_create: cudaMalloc failed for 2^%d blocks (%s)", cfg->capacity_log2,
+                   cudaGetErrorString(e));
+    b200tsdf_destroy(h);
+    return B200TSDF_E_NOMEM;
+  }
+  d.cap_mask = (uint32_t)(h->cap - 1);
+  d.bounded = cfg->bounded;
+  for (int i = 0; i < 3; ++i) {
+    d.kmin[i] = clamp_i32(cfg->key_min[i]);
+    d.kmax[i] = clamp_i32(cfg->key_max[i]);
+  }
+  d.max_weight = (float)cfg->max_weight;
+  d.min_weight = (float)cfg->min_weight;
+  int rc = b200tsdf_reset(h, nullptr);
+  if (rc != 0) {
+    b200tsdf_destroy(h);
+    return rc;
+  }
+  B200_CUDA(cudaStreamSynchronize(nullptr));
+  *out = h;
+  return B200TSDF_OK;
+}
+
+extern "C" int b200tsdf_destroy(b200tsdf_t *h) {
+  if (!h) return B200TSDF_OK;
+  cudaSetDevice(h->cfg.device);
+  cudaFree(h->d.keys);
+  cudaFree(h->d.vox);
+  cudaFree(h->d.cnt);
+  cudaFree(h->d.list);
+  cudaFree(h->d.ctr);
+  cudaFree(h->scratch);
+  cudaFree(h->stage_dev);
+  delete h;
+  return B200TSDF_OK;
+}
+
+extern "C" int b200tsdf_reset(b200tsdf_t *h, void *stream) {
+  if (!h) return B200TSDF_E_INVALID;
+  cudaStream_t st = (cudaStream_t)stream;
+  B200_CUDA(cudaSetDevice(h->cfg.device));
+  B200_CUDA(cudaMemsetAsync(h->d.keys, 0xFF, h->cap * sizeof(unsigned long long), st));
+  B200_CUDA(cudaMemsetAsync(h->d.vox, 0, h->cap * B200_BLOCK_VOX * sizeof(float4), st));
+  B200_CUDA(cudaMemsetAsync(h->d.cnt, 0, h->cap * B200_BLOCK_VOX * sizeof(unsigned long long), st));
+  B200_CUDA(cudaMemsetAsync(h->d.ctr, 0, CTR_COUNT * sizeof(unsigned long long), st));
+  return B200TSDF_OK;
+}
+
+extern "C" int b200tsdf_counters(b200tsdf_t *h, int64_t out_host[6], void *stream) {
+  if (!h || !out_host) return B200TSDF_E_INVALID;
+  cudaStream_t st = (cudaStream_t)stream;
+  unsigned long long tmp[CTR_COUNT];
+  B200_CUDA(cudaMemcpyAsync(tmp, h->d.ctr, sizeof(tmp), cudaMemcpyDeviceToHost, st));
+  B200_CUDA(cudaStreamSynchronize(st));
+  for (int i = 0; i < 6; ++i) out_host[i] = (int64_t)tmp[i];
+  return B200TSDF_OK;
+}
+
+// Grow the device staging area used by the *_host entry points.
+int b200_ensure_stage(b200tsdf *h, size_t bytes) {
+  if (h->stage_bytes >= bytes) return B200TSDF_OK;
+  if (h->stage_dev) B200_CUDA(cudaFree(h->stage_dev));
+  h->stage_dev = nullptr;
+  h->stage_bytes = 0;
+  B200_CUDA(cudaMalloc(&h->stage_dev, bytes));
+  h->stage_bytes = bytes;
+  return B200TSDF_OK;
+}

@@ -1,0 +1,247 @@
+"""B200 drop-in for the reference `mast3r_slam/tsdf/global_volume.py`.
+
+Same class name, constructor, `integrate` / `query` / `stats` signatures and
+attributes as the reference TSDFVolume (global_volume.py:15-140); storage is a
+device voxel-block hash owned by libb200tsdf.so, reached through the C ABI in
+include/b200tsdf.h.  New on top of the reference: a second, quality-weighted
+volume fused in the same pass (`confidences_q`, `integrate_keyframes`),
+`query_batch`, `export`, `extract_mesh`.  No CPU fallback.
+"""
+import ctypes as C
+import threading
+from typing import Dict, Optional, Tuple
+
+import numpy as np
+import torch
+
+from .. import _ffi
+
+
+def _stream_ptr(device):
+    return C.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+
+
+class TSDFVolume:
+    """Sparse dual TSDF volume (voxel-block hash on the GPU)."""
+
+    def __init__(
+        self,
+        voxel_size: float,
+        truncation: float,
+        max_weight: float = 100.0,
+        min_weight: float = 1.0e-3,
+        *,
+        capacity_log2: int = 17,
+        bounds=None,
+        device="cuda:0",
+    ) -> None:
+        self.voxel_size = float(voxel_size)
+        self.truncation = float(truncation)
+        self.max_weight = float(max_weight)
+        self.min_weight = float(min_weight)
+        self._lock = threading.RLock()  # reference: global_volume.py:30
+        self.device = torch.device(device)
+        if self.device.type != "cuda" or not torch.cuda.is_available():
+            raise _ffi.B200TSDFError("TSDFVolume needs a CUDA device (no CPU fallback)")
+        cfg = _ffi.Config()
+        cfg.voxel_size, cfg.truncation = self.voxel_size, self.truncation
+        cfg.max_weight, cfg.min_weight = self.max_weight, self.min_weight
+        cfg.capacity_log2 = int(capacity_log2)
+        cfg.bounded = 0
+        if bounds is not None:  # ((x0,y0,z0),(x1,y1,z1)) integer voxel keys, half-open
+            cfg.bounded = 1
+            for i in range(3):
+                cfg.key_min[i] = int(bounds[0][i])
+                cfg.key_max[i] = int(bounds[1][i])
+        cfg.device = self.device.index or 0
+        self.bounds = bounds
+        self._h = C.c_void_p()
+        _ffi.check(_ffi.lib().b200tsdf_create(C.byref(cfg), C.byref(self._h)), "b200tsdf_create")
+
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h:
+            _ffi.lib().b200tsdf_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def reset(self):
+        with self._lock:
+            _ffi.check(_ffi.lib().b200tsdf_reset(self._h, _stream_ptr(self.device)), "reset")
+
+    # ------------------------------------------------------------------
+    # Integration
+    # ------------------------------------------------------------------
+    def integrate(
+        self,
+        points_world: np.ndarray,
+        confidences: np.ndarray,
+        cam_origin: np.ndarray,
+        step_scale: float = 0.5,
+        confidences_q: Optional[np.ndarray] = None,
+    ) -> int:
+        """Reference signature (global_volume.py:35-41).  float32 points use
+        float32 ray arithmetic, anything else float64 -- as numpy >= 2 does
+        inside the reference."""
+        points_world = np.asarray(points_world)
+        if points_world.size == 0:  # :42-43
+            return 0
+        f32 = points_world.dtype == np.float32
+        dt, tdt = (np.float32, _ffi.F32) if f32 else (np.float64, _ffi.F64)
+        pts = torch.from_numpy(np.ascontiguousarray(points_world, dtype=dt).reshape(-1, 3))
+        conf = torch.from_numpy(np.ascontiguousarray(confidences, dtype=np.float64).reshape(-1))
+        org = np.ascontiguousarray(np.asarray(cam_origin).reshape(3), dtype=dt)
+        m = pts.shape[0]
+        if conf.shape[0] < m:  # zip() in the reference stops at the shorter one
+            m = conf.shape[0]
+        pts_d = pts.to(self.device)
+        conf_d = conf.to(self.device)
+        cq_d = None
+        if confidences_q is not None:
+            cq_d = torch.from_numpy(
+                np.ascontiguousarray(confidences_q, dtype=np.float64).reshape(-1)).to(self.device)
+        fused = C.c_int64(0)
+        with self._lock:
+            _ffi.check(_ffi.lib().b200tsdf_integrate_points(
+                self._h, pts_d.data_ptr(), tdt, conf_d.data_ptr(),
+                cq_d.data_ptr() if cq_d is not None else None,
+                org.ctypes.data_as(C.c_void_p), m, float(step_scale), C.byref(fused),
+                _stream_ptr(self.device)), "integrate_points")
+        return int(fused.value)
+
+    def integrate_keyframes(self, X, Cf, poses, q_grid=None, min_conf=0.05, H=None, W=None,
+                            step_scale=0.5):
+        """Fused staging + allocation + dual fold for a batch of keyframes
+        (replaces global_manager.py:81-106 per keyframe).  Tensors may live on
+        the device (zero-copy) or on the host (copied inside the call).
+        X (B,H*W,3) f32 camera-frame pointmap, Cf (B,H*W[,1]) f32, poses (B,8)
+        f32 Sim3 [t,q,s], q_grid (B,gh,gw) f32 or None."""
+        X = X if X.dim() == 3 else X.unsqueeze(0)
+        B, N = X.shape[0], X.shape[1]
+        if H is None or W is None:
+            raise ValueError("integrate_keyframes needs H and W")
+        if H * W != N:
+            raise ValueError(f"H*W = {H * W} does not match the pointmap ({N} pixels)")
+        gh = gw = 0
+        if q_grid is not None:
+            q_grid = q_grid.reshape(B, q_grid.shape[-2], q_grid.shape[-1])
+            gh, gw = q_grid.shape[-2], q_grid.shape[-1]
+        on_dev = X.is_cuda
+        ts = [X, Cf.reshape(B, N), poses.reshape(B, 8)] + ([q_grid] if q_grid is not None else [])
+        for t in ts:
+            if t.dtype != torch.float32 or not t.is_contiguous() or t.is_cuda != on_dev:
+                raise ValueError("keyframe tensors must be contiguous float32 on one device")
+        Xc, Cc, Pc = ts[0], ts[1], ts[2]
+        fn = (_ffi.lib().b200tsdf_integrate_keyframes if on_dev
+              else _ffi.lib().b200tsdf_integrate_keyframes_host)
+        with self._lock:
+            _ffi.check(fn(self._h, Xc.data_ptr(), Cc.data_ptr(),
+                          q_grid.data_ptr() if q_grid is not None else None, Pc.data_ptr(),
+                          B, H, W, gh, gw, float(min_conf), float(step_scale),
+                          _stream_ptr(self.device)), "integrate_keyframes")
+
+    # ------------------------------------------------------------------
+    # Query helpers
+    # ------------------------------------------------------------------
+    def query_batch(self, points, which: int = 0):
+        """Batched query: returns (tsdf f64 (M,), grad f64 (M,3), flags u8 (M,))
+        device tensors; flags bit0 = value present, bit1 = gradient present."""
+        if isinstance(points, np.ndarray):
+            dt = np.float32 if points.dtype == np.float32 else np.float64
+            points = torch.from_numpy(np.ascontiguousarray(points, dtype=dt))
+        pts = points.reshape(-1, 3).to(self.device).contiguous()
+        if pts.dtype not in (torch.float32, torch.float64):
+            pts = pts.double()
+        m = pts.shape[0]
+        t = torch.zeros(m, dtype=torch.float64, device=self.device)
+        g = torch.zeros(m, 3, dtype=torch.float64, device=self.device)
+        fl = torch.zeros(m, dtype=torch.uint8, device=self.device)
+        with self._lock:
+            _ffi.check(_ffi.lib().b200tsdf_query(
+                self._h, which, pts.data_ptr(), _ffi.F32 if pts.dtype == torch.float32 else _ffi.F64,
+                m, t.data_ptr(), g.data_ptr(), fl.data_ptr(), _stream_ptr(self.device)), "query")
+        return t, g, fl
+
+    def query(self, point_world: np.ndarray) -> Tuple[Optional[float], Optional[np.ndarray]]:
+        """Reference signature (global_volume.py:93-105)."""
+        t, g, fl = self.query_batch(np.asarray(point_world).reshape(1, 3))
+        f = int(fl.cpu()[0])
+        if not f & 1:
+            return None, None
+        return float(t.cpu()[0]), (g.cpu().numpy()[0].copy() if f & 2 else None)
+
+    # ------------------------------------------------------------------
+    # Utility
+    # ------------------------------------------------------------------
+    def stats(self, which: int = 0) -> Dict[str, float]:
+        """Reference signature (global_volume.py:136-140)."""
+        a, b = C.c_int64(), C.c_int64()
+        with self._lock:
+            _ffi.check(_ffi.lib().b200tsdf_stats(self._h, which, C.byref(a), C.byref(b),
+                                                 _stream_ptr(self.device)), "stats")
+        return {"valid_voxels": a.value, "total_voxels": b.value}
+
+    def counters(self) -> Dict[str, int]:
+        out = (C.c_int64 * 6)()
+        with self._lock:
+            _ffi.check(_ffi.lib().b200tsdf_counters(self._h, out, _stream_ptr(self.device)),
+                       "counters")
+        names = ["rays", "updates_primary", "updates_quality", "blocks", "dropped", "overflow"]
+        d = dict(zip(names, [int(x) for x in out]))
+        if d["overflow"]:
+            raise _ffi.B200TSDFError(
+                f"voxel-block hash overflow ({d['overflow']} updates lost): raise capacity_log2")
+        return d
+
+    def export(self, which: int = 0):
+        """All voxels of one volume, sorted by key: (keys i64 (n,3), tsdf f32,
+        weight f32, count u32) numpy arrays -- what reference _voxels holds."""
+        n = C.c_int64()
+        L = _ffi.lib()
+        with self._lock:
+            _ffi.check(L.b200tsdf_export_voxels(self._h, which, None, None, None, None, 0,
+                                                C.byref(n), _stream_ptr(self.device)), "export")
+            cap = n.value
+            keys = torch.zeros(max(cap, 1), 3, dtype=torch.int64, device=self.device)
+            t = torch.zeros(max(cap, 1), dtype=torch.float32, device=self.device)
+            w = torch.zeros(max(cap, 1), dtype=torch.float32, device=self.device)
+            c = torch.zeros(max(cap, 1), dtype=torch.int32, device=self.device)
+            if cap:
+                _ffi.check(L.b200tsdf_export_voxels(
+                    self._h, which, keys.data_ptr(), t.data_ptr(), w.data_ptr(), c.data_ptr(),
+                    cap, C.byref(n), _stream_ptr(self.device)), "export")
+        k = keys[:cap].cpu().numpy()
+        order = np.lexsort((k[:, 2], k[:, 1], k[:, 0]))
+        return (k[order], t[:cap].cpu().numpy()[order], w[:cap].cpu().numpy()[order],
+                c[:cap].cpu().numpy().astype(np.uint32)[order])
+
+    def block_keys(self):
+        n = C.c_int64()
+        L = _ffi.lib()
+        with self._lock:
+            _ffi.check(L.b200tsdf_export_blocks(self._h, None, 0, C.byref(n),
+                                                _stream_ptr(self.device)), "export_blocks")
+            bk = torch.zeros(max(n.value, 1), 3, dtype=torch.int64, device=self.device)
+            if n.value:
+                _ffi.check(L.b200tsdf_export_blocks(self._h, bk.data_ptr(), n.value, C.byref(n),
+                                                    _stream_ptr(self.device)), "export_blocks")
+        k = bk[:n.value].cpu().numpy()
+        return k[np.lexsort((k[:, 2], k[:, 1], k[:, 0]))]
+
+    def extract_mesh(self, which: int = 0):
+        """Marching cubes; returns verts f32 (3T,3) device tensor (triangle soup)."""
+        n = C.c_int64()
+        L = _ffi.lib()
+        with self._lock:
+            _ffi.check(L.b200tsdf_extract_mesh(self._h, which, None, 0, C.byref(n),
+                                               _stream_ptr(self.device)), "extract_mesh")
+            verts = torch.zeros(max(n.value, 1) * 3, 3, dtype=torch.float32, device=self.device)
+            if n.value:
+                _ffi.check(L.b200tsdf_extract_mesh(self._h, which, verts.data_ptr(), n.value,
+                                                   C.byref(n), _stream_ptr(self.device)),
+                           "extract_mesh")
+        return verts[: n.value * 3]

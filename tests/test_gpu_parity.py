@@ -1,0 +1,151 @@
+"""GPU parity: CUDA path (through the C ABI) vs the CPU oracle on the same
+seeded inputs.  Bit-exact: voxel key set, voxel-block key set, per-voxel update
+counts, rays fused, update totals.  Tolerance: tsdf 1e-5 (normalised), weight
+1e-5 relative."""
+import numpy as np
+import pytest
+import torch
+
+from mast3r_slam_quality_dualtsdf_b200 import synth
+from oracle import oracle as orc
+from tests.util import assert_volume_matches, block_set, oracle_dual
+
+pytestmark = pytest.mark.gpu
+
+
+def _vol(dev, voxel, trunc, **kw):
+    from mast3r_slam_quality_dualtsdf_b200.tsdf import TSDFVolume
+
+    return TSDFVolume(voxel, trunc, device=dev, **kw)
+
+
+@pytest.mark.parametrize("scene,voxel", [("plane", 0.03), ("sphere", 0.03), ("room", 0.01),
+                                         ("plane", 0.005)])
+@pytest.mark.parametrize("n_kf", [1, 3])
+def test_keyframes_match_oracle(cuda_device, scene, voxel, n_kf):
+    trunc = 4 * voxel
+    kf = synth.make_keyframes(synth.SCENES[scene], n_kf, H=48, W=64, seed=1, f=50.0, total=12)
+    vp, vq, rays = oracle_dual(kf, voxel, trunc)
+    vol = _vol(cuda_device, voxel, trunc)
+    vol.integrate_keyframes(torch.from_numpy(kf["X"]).to(cuda_device),
+                            torch.from_numpy(kf["C"]).to(cuda_device),
+                            torch.from_numpy(kf["pose"]).to(cuda_device),
+                            torch.from_numpy(kf["q"]).to(cuda_device), 0.05, 48, 64)
+    c = vol.counters()
+    assert c["rays"] == rays
+    assert c["updates_primary"] == vp.events and c["updates_quality"] == vq.events
+    assert c["dropped"] == 0
+    assert_volume_matches(vol.export(0), vp.export(), "primary")
+    assert_volume_matches(vol.export(1), vq.export(), "quality")
+    assert np.array_equal(vol.block_keys(), block_set(vp.export()[0]))
+    assert vol.stats(0) == vp.stats() and vol.stats(1) == vq.stats()
+
+
+def test_host_entry_matches_device_entry(cuda_device):
+    kf = synth.make_keyframes(synth.SCENES["sphere"], 2, H=48, W=64, seed=3, f=50.0)
+    a, b = _vol(cuda_device, 0.02, 0.08), _vol(cuda_device, 0.02, 0.08)
+    t = {k: torch.from_numpy(kf[k]) for k in ("X", "C", "pose", "q")}
+    a.integrate_keyframes(t["X"].pin_memory(), t["C"].pin_memory(), t["pose"].pin_memory(),
+                          t["q"].pin_memory(), 0.05, 48, 64)
+    b.integrate_keyframes(*(t[k].to(cuda_device) for k in ("X", "C", "pose")),
+                          t["q"].to(cuda_device), 0.05, 48, 64)
+    for which in (0, 1):
+        assert_volume_matches(a.export(which), tuple(np.asarray(x, np.float64) if x.dtype.kind == "f"
+                                                     else x for x in b.export(which)), "host")
+
+
+@pytest.mark.parametrize("dtype", [np.float32, np.float64])
+def test_integrate_points_reference_signature(cuda_device, dtype):
+    """TSDFVolume.integrate(points_world, confidences, cam_origin) as the SLAM
+    loop calls it (global_manager.py:106), float32 and float64 arithmetic."""
+    rng = np.random.default_rng(7)
+    pts = (rng.normal(size=(3000, 3)) * 0.4 + np.array([0.2, -0.1, 1.4])).astype(dtype)
+    pts[5] = np.nan                  # non-finite ray: skipped (global_volume.py:56)
+    pts[6] = [0.01, 0.02, 0.03]      # zero-length ray after origin subtraction
+    org = np.array([0.01, 0.02, 0.03], dtype)
+    conf = 0.5 + rng.random(3000)
+    conf[10] = 0.0                   # weight <= 0: no voxel update but the ray counts
+    conf[11] = -1.0
+    vo = orc.OracleVolume(0.03, 0.12)
+    n_ref = vo.integrate(pts, conf, org)
+    vol = _vol(cuda_device, 0.03, 0.12)
+    n = vol.integrate(pts, conf, org)
+    assert n == n_ref
+    assert vol.counters()["updates_primary"] == vo.events
+    assert_volume_matches(vol.export(0), vo.export(), f"points {dtype.__name__}")
+    assert vol.stats(1) == {"valid_voxels": 0, "total_voxels": 0}
+
+
+def test_empty_and_all_filtered(cuda_device):
+    vol = _vol(cuda_device, 0.03, 0.12)
+    assert vol.integrate(np.zeros((0, 3), np.float32), np.zeros(0), np.zeros(3, np.float32)) == 0
+    kf = synth.make_keyframes(synth.SCENES["plane"], 1, H=16, W=16, seed=0, f=20.0)
+    vol.integrate_keyframes(torch.from_numpy(kf["X"]).to(cuda_device),
+                            torch.zeros(1, 256, device=cuda_device),
+                            torch.from_numpy(kf["pose"]).to(cuda_device), None, 0.05, 16, 16)
+    assert vol.stats() == {"valid_voxels": 0, "total_voxels": 0}
+    assert vol.counters()["rays"] == 0
+    assert vol.query(np.zeros(3)) == (None, None)
+
+
+def test_max_weight_clamp_and_order_quirk(cuda_device):
+    """Reference quirk (global_volume.py:84-88): divide by the CLAMPED weight.
+    Drive voxels far past max_weight and compare with the sequential oracle."""
+    kf = synth.make_keyframes(synth.SCENES["plane"], 1, H=32, W=32, seed=5, f=40.0)
+    kf["C"] *= 4.0
+    vol = _vol(cuda_device, 0.03, 0.12, )
+    vol2 = orc.OracleVolume(0.03, 0.12, 5.0)
+    from mast3r_slam_quality_dualtsdf_b200.tsdf import TSDFVolume
+    vol = TSDFVolume(0.03, 0.12, 5.0, device=cuda_device)
+    pts, conf, confq, org = orc.stage_keyframe(kf["X"][0], kf["C"][0], kf["pose"][0], None, 32, 32,
+                                               0.05)
+    for _ in range(6):
+        vol2.integrate(pts, conf, org)
+        vol.integrate(pts, conf, org)
+    k, t, w, c = vol2.export()
+    assert (w >= 5.0 - 1e-9).sum() > 100, "test must saturate many voxels"
+    assert_volume_matches(vol.export(0), (k, t, w, c), "clamped")
+
+
+def test_query_matches_oracle(cuda_device):
+    kf = synth.make_keyframes(synth.SCENES["sphere"], 3, H=48, W=64, seed=2, f=50.0, total=12)
+    vp, vq, _ = oracle_dual(kf, 0.03, 0.12)
+    vol = _vol(cuda_device, 0.03, 0.12)
+    vol.integrate_keyframes(*(torch.from_numpy(kf[k]).to(cuda_device) for k in ("X", "C", "pose")),
+                            torch.from_numpy(kf["q"]).to(cuda_device), 0.05, 48, 64)
+    keys = vp.export()[0]
+    rng = np.random.default_rng(0)
+    probe = (keys[rng.integers(0, len(keys), 4000)] + rng.random((4000, 3))) * 0.03
+    probe = np.concatenate([probe, rng.normal(size=(500, 3)) * 3])
+    for dtype in (np.float32, np.float64):
+        p = probe.astype(dtype)
+        for which, vo in ((0, vp), (1, vq)):
+            t, g, fl = vo.query_batch(p)
+            tt, gg, ff = (x.cpu().numpy() for x in vol.query_batch(p, which))
+            assert np.array_equal(fl, ff)
+            assert np.abs(t - tt).max() <= 1e-5
+            # unit gradients of tsdf differences: f32 storage => looser, still tight
+            assert np.abs(g - gg).max() <= 2e-3
+    tv, gv = vol.query(probe[0])
+    tr, gr = vp.query(probe[0])
+    assert abs(tv - tr) <= 1e-5 and (gv is None) == (gr is None)
+
+
+def test_bounds_drop_outside(cuda_device):
+    kf = synth.make_keyframes(synth.SCENES["plane"], 1, H=48, W=64, seed=1, f=50.0)
+    vp, _, _ = oracle_dual(kf, 0.03, 0.12)
+    keys, t, w, c = vp.export()
+    lo, hi = keys.min(0), keys.max(0) + 1
+    mid = int((lo[2] + hi[2]) // 2)
+    parts = []
+    for z0, z1 in ((int(lo[2]), mid), (mid, int(hi[2]))):
+        vol = _vol(cuda_device, 0.03, 0.12, bounds=((int(lo[0]), int(lo[1]), z0),
+                                                    (int(hi[0]), int(hi[1]), z1)))
+        vol.integrate_keyframes(*(torch.from_numpy(kf[k]).to(cuda_device)
+                                  for k in ("X", "C", "pose")),
+                                torch.from_numpy(kf["q"]).to(cuda_device), 0.05, 48, 64)
+        parts.append(vol.export(0))
+    gk = np.concatenate([p[0] for p in parts])
+    order = np.lexsort((gk[:, 2], gk[:, 1], gk[:, 0]))
+    got = tuple(np.concatenate([p[i] for p in parts])[order] for i in range(4))
+    assert_volume_matches(got, (keys, t, w, c), "z-slab union")

@@ -1,0 +1,39 @@
+"""Shared helpers of the parity tests (oracle = checker only)."""
+import numpy as np
+
+from oracle import oracle as orc
+
+TSDF_TOL = 1.0e-5   # normalised tsdf units = 1e-5 of the truncation distance (north_star)
+W_TOL = 1.0e-5      # |dw| <= 1e-5 * max(1, w)
+
+
+def oracle_dual(kf, voxel, trunc, min_conf=0.05, max_weight=100.0, use_q=True, idx=None):
+    """Reference semantics for a keyframe batch: two oracle volumes, the second
+    fed confidences C*q."""
+    vp = orc.OracleVolume(voxel, trunc, max_weight)
+    vq = orc.OracleVolume(voxel, trunc, max_weight)
+    rays = 0
+    for b in (idx if idx is not None else range(kf["X"].shape[0])):
+        pts, conf, confq, org = orc.stage_keyframe(
+            kf["X"][b], kf["C"][b], kf["pose"][b], kf["q"][b] if use_q else None,
+            kf["H"], kf["W"], min_conf)
+        rays += vp.integrate(pts, conf, org)
+        vq.integrate(pts, confq, org)
+    return vp, vq, rays
+
+
+def assert_volume_matches(got, want, what=""):
+    """got/want = (keys, tsdf, weight, count) sorted by key."""
+    gk, gt, gw, gc = got
+    wk, wt, ww, wc = want
+    assert gk.shape == wk.shape, f"{what}: voxel key set size {gk.shape[0]} != {wk.shape[0]}"
+    assert np.array_equal(gk, wk), f"{what}: voxel key sets differ"
+    assert np.array_equal(gc.astype(np.int64), wc.astype(np.int64)), f"{what}: update counts differ"
+    dt = np.abs(gt.astype(np.float64) - wt)
+    assert dt.max(initial=0.0) <= TSDF_TOL, f"{what}: max |dtsdf| = {dt.max()}"
+    dw = np.abs(gw.astype(np.float64) - ww) / np.maximum(1.0, np.abs(ww))
+    assert dw.max(initial=0.0) <= W_TOL, f"{what}: max rel |dw| = {dw.max()}"
+
+
+def block_set(keys):
+    return np.unique(keys >> 3, axis=0)
