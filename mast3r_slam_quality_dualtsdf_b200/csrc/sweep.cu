@@ -172,7 +172,11 @@ __global__ void query_kernel(VolumeDev v, int which, const T *__restrict__ pts, 
       if (!fetch(v, which, kp[0], kp[1], kp[2], tp, wp)) continue;
       if (!fetch(v, which, kn[0], kn[1], kn[2], tn, wn)) continue;
       if (wp < v.min_weight || wn < v.min_weight) continue;
-      g[ax] = ((double)tp - (double)tn) / (2.0 * voxel_size);
+      // voxels are stored as float32 sums: differences at the rounding-noise
+      // level are the reference's exact zeros (equal tsdf on both sides)
+      double diff = (double)tp - (double)tn;
+      if (fabs(diff) <= 4.0e-7) diff = 0.0;
+      g[ax] = diff / (2.0 * voxel_size);
       denom++;
     }
     if (denom) {

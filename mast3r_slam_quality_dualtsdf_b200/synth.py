@@ -101,7 +101,7 @@ def render(scene, R, t, s, H, W, f=400.0):
 
 
 def make_keyframes(scene, n_kf, H=384, W=512, seed=0, f=400.0, orbit_radius=0.6, gh=None,
-                   gw=None, start=0, total=None):
+                   gw=None, start=0, total=None, up_axis="y"):
     """n_kf keyframes on a closed orbit of `total` poses (default n_kf),
     starting at pose index `start`.  Returns dict of float32 arrays:
     X (B,H*W,3), C (B,H*W), q (B,gh,gw), pose (B,8)."""
@@ -120,10 +120,12 @@ def make_keyframes(scene, n_kf, H=384, W=512, seed=0, f=400.0, orbit_radius=0.6,
             eye = np.array([orbit_radius * np.cos(ang), 0.1 * np.sin(3 * ang),
                             orbit_radius * np.sin(ang)])
             tgt = eye + np.array([np.cos(ang), 0.25 * np.sin(2 * ang), np.sin(ang)])
+            if up_axis == "z":  # orbit in the xy plane, z vertical (z-slabs cut every view)
+                eye, tgt = eye[[0, 2, 1]], tgt[[0, 2, 1]]
         else:
             eye = np.array([0.15 * np.cos(ang), 0.1 * np.sin(ang), 0.05 * np.sin(2 * ang)])
             tgt = np.array([0.05 * np.sin(ang), 0.05 * np.cos(ang), 1.5])
-        R = look_at(eye, tgt)
+        R = look_at(eye, tgt, (0.0, 0.0, 1.0) if up_axis == "z" else (0.0, 1.0, 0.0))
         s = 1.0 + 0.05 * np.sin(ang + 0.3)
         q = quat_from_R(R)
         Rq = R_from_quat(q.astype(np.float32).astype(np.float64))

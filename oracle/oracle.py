@@ -77,8 +77,8 @@ class OracleVolume:
                                    self.min_weight)
 
     def __del__(self):
-        if getattr(self, "_h", None):
-            lib().orc_destroy(self._h)
+        if getattr(self, "_h", None) and _lib is not None:
+            _lib.orc_destroy(self._h)
             self._h = None
 
     def integrate(self, points_world, confidences, cam_origin, step_scale=0.5):
