@@ -11,6 +11,7 @@
 // (DESIGN.md "the fold"), so no ordering between rays is needed.
 #include "common.cuh"
 #include "ray.cuh"
+#include "march_fast.cuh"
 
 struct Acc {
   int kx, ky, kz;
@@ -125,23 +126,48 @@ __device__ __forceinline__ void commit_counters(const VolumeDev &v, uint32_t ray
 }
 
 // ------------------------------------------------------------ points entry
-template <typename T>
+// float64 inputs: the generic march (every intermediate float64, as numpy
+// does for float64 arrays); float32 inputs: the fast march.
 __global__ void __launch_bounds__(256)
-    integrate_points_kernel(VolumeDev v, const T *__restrict__ pts,
-                            const double *__restrict__ conf, const double *__restrict__ conf_q,
-                            T ox, T oy, T oz, long long m, T step, T trunc, T vs) {
+    integrate_points_f64_kernel(VolumeDev v, const double *__restrict__ pts,
+                                const double *__restrict__ conf,
+                                const double *__restrict__ conf_q, double ox, double oy,
+                                double oz, long long m, double step, double trunc, double vs) {
   long long p = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   uint32_t rays = 0, ev_p = 0, ev_q = 0, dropped = 0, overflow = 0;
   if (p < m) {
-    Ray<T> r;
-    if (ray_setup<T>(r, pts[3 * p], pts[3 * p + 1], pts[3 * p + 2], ox, oy, oz, step, trunc)) {
+    Ray<double> r;
+    if (ray_setup<double>(r, pts[3 * p], pts[3 * p + 1], pts[3 * p + 2], ox, oy, oz, step,
+                          trunc)) {
       rays = 1; // global_volume.py:71
       float c = (float)conf[p];
       float cq = conf_q ? (float)conf_q[p] : 0.f;
-      march_ray<T>(v, r, trunc, vs, c, cq, conf_q != nullptr, ev_p, ev_q, dropped, overflow);
+      march_ray<double>(v, r, trunc, vs, c, cq, conf_q != nullptr, ev_p, ev_q, dropped,
+                        overflow);
     }
   }
   commit_counters(v, rays, ev_p, ev_q, dropped, overflow);
+}
+
+template <bool BOUNDED>
+__global__ void __launch_bounds__(256)
+    integrate_points_f32_kernel(VolumeDev v, const float *__restrict__ pts,
+                                const double *__restrict__ conf,
+                                const double *__restrict__ conf_q, float ox, float oy, float oz,
+                                long long m, float step, MarchConst mc) {
+  long long p = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  Tally tl = {0, 0, 0, 0, 0};
+  if (p < m) {
+    Ray<float> r;
+    if (ray_setup<float>(r, pts[3 * p], pts[3 * p + 1], pts[3 * p + 2], ox, oy, oz, step,
+                         mc.trunc)) {
+      tl.rays = 1; // global_volume.py:71
+      float c = (float)conf[p];
+      float cq = conf_q ? (float)conf_q[p] : 0.f;
+      march_ray_fast<BOUNDED>(v, r, mc, c, cq, conf_q != nullptr, tl);
+    }
+  }
+  commit_tally(v, tl);
 }
 
 // ---------------------------------------------------------- keyframe entry
@@ -165,15 +191,16 @@ __device__ __forceinline__ void sim3_act(const float *__restrict__ P, float x0, 
   y2 = __fadd_rn(__fmul_rn(a2, s), P[2]);
 }
 
+template <bool BOUNDED>
 __global__ void __launch_bounds__(256)
     integrate_keyframes_kernel(VolumeDev v, const float *__restrict__ X,
                                const float *__restrict__ C, const float *__restrict__ qg,
                                const float *__restrict__ poses, int H, int W, int gh, int gw,
-                               float min_conf, float step, float trunc, float vs) {
+                               float min_conf, float step, MarchConst mc) {
   const int kf = blockIdx.y;
   const long long npix = (long long)H * W;
   long long pix = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  uint32_t rays = 0, ev_p = 0, ev_q = 0, dropped = 0, overflow = 0;
+  Tally tl = {0, 0, 0, 0, 0};
   if (pix < npix) {
     const float *P = poses + 8 * kf;
     float c = C[kf * npix + pix];
@@ -182,23 +209,31 @@ __global__ void __launch_bounds__(256)
       float wx, wy, wz;
       sim3_act(P, x[0], x[1], x[2], wx, wy, wz);
       Ray<float> r;
-      if (ray_setup<float>(r, wx, wy, wz, P[0], P[1], P[2], step, trunc)) {
-        rays = 1;
+      if (ray_setup<float>(r, wx, wy, wz, P[0], P[1], P[2], step, mc.trunc)) {
+        tl.rays = 1;
         float q = 1.0f;
         if (qg) {
           int y = (int)(pix / W), xx = (int)(pix % W);
           int gy = min(y / (H / gh), gh - 1), gx = min(xx / (W / gw), gw - 1);
           q = qg[((long long)kf * gh + gy) * gw + gx];
         }
-        march_ray<float>(v, r, trunc, vs, c, c * q, true, ev_p, ev_q, dropped, overflow);
+        march_ray_fast<BOUNDED>(v, r, mc, c, c * q, true, tl);
       }
     }
   }
-  commit_counters(v, rays, ev_p, ev_q, dropped, overflow);
+  commit_tally(v, tl);
 }
 
 // ------------------------------------------------------------------ C ABI
-static int check_overflow_hint(b200tsdf *h) { return B200TSDF_OK; }
+static MarchConst make_consts(const b200tsdf *h) {
+  MarchConst mc;
+  mc.trunc = (float)h->cfg.truncation;
+  mc.vs = (float)h->cfg.voxel_size;
+  mc.inv_vs = 1.0f / mc.vs;
+  mc.inv_trunc = 1.0f / mc.trunc;
+  mc.nl2e_inv_trunc = -1.4426950408889634f / mc.trunc;
+  return mc;
+}
 
 extern "C" int b200tsdf_integrate_points(b200tsdf_t *h, const void *pts_dev, int dtype,
                                          const double *conf_dev, const double *conf_q_dev,
@@ -222,12 +257,17 @@ extern "C" int b200tsdf_integrate_points(b200tsdf_t *h, const void *pts_dev, int
     unsigned grid = (unsigned)((m + 255) / 256);
     if (dtype == B200TSDF_F32) {
       const float *o = (const float *)origin_host;
-      integrate_points_kernel<float><<<grid, 256, 0, st>>>(
-          h->d, (const float *)pts_dev, conf_dev, conf_q_dev, o[0], o[1], o[2], (long long)m,
-          (float)step_d, (float)h->cfg.truncation, (float)h->cfg.voxel_size);
+      if (h->d.bounded)
+        integrate_points_f32_kernel<true><<<grid, 256, 0, st>>>(
+            h->d, (const float *)pts_dev, conf_dev, conf_q_dev, o[0], o[1], o[2], (long long)m,
+            (float)step_d, make_consts(h));
+      else
+        integrate_points_f32_kernel<false><<<grid, 256, 0, st>>>(
+            h->d, (const float *)pts_dev, conf_dev, conf_q_dev, o[0], o[1], o[2], (long long)m,
+            (float)step_d, make_consts(h));
     } else {
       const double *o = (const double *)origin_host;
-      integrate_points_kernel<double><<<grid, 256, 0, st>>>(
+      integrate_points_f64_kernel<<<grid, 256, 0, st>>>(
           h->d, (const double *)pts_dev, conf_dev, conf_q_dev, o[0], o[1], o[2], (long long)m,
           step_d, h->cfg.truncation, h->cfg.voxel_size);
     }
@@ -239,7 +279,7 @@ extern "C" int b200tsdf_integrate_points(b200tsdf_t *h, const void *pts_dev, int
     B200_CUDA(cudaStreamSynchronize(st));
     *rays_fused_host = (int64_t)(after - before);
   }
-  return check_overflow_hint(h);
+  return B200TSDF_OK;
 }
 
 extern "C" int b200tsdf_integrate_keyframes(b200tsdf_t *h, const float *X_dev, const float *C_dev,
@@ -263,9 +303,14 @@ extern "C" int b200tsdf_integrate_keyframes(b200tsdf_t *h, const float *X_dev, c
   if (step_d < 1.0e-4) step_d = 1.0e-4;
   long long npix = (long long)H * W;
   dim3 grid((unsigned)((npix + 255) / 256), (unsigned)B);
-  integrate_keyframes_kernel<<<grid, 256, 0, st>>>(
-      h->d, X_dev, C_dev, q_grid_dev, pose_dev, H, W, gh, gw, min_conf, (float)step_d,
-      (float)h->cfg.truncation, (float)h->cfg.voxel_size);
+  if (h->d.bounded)
+    integrate_keyframes_kernel<true><<<grid, 256, 0, st>>>(
+        h->d, X_dev, C_dev, q_grid_dev, pose_dev, H, W, gh, gw, min_conf, (float)step_d,
+        make_consts(h));
+  else
+    integrate_keyframes_kernel<false><<<grid, 256, 0, st>>>(
+        h->d, X_dev, C_dev, q_grid_dev, pose_dev, H, W, gh, gw, min_conf, (float)step_d,
+        make_consts(h));
   B200_CUDA(cudaGetLastError());
   return B200TSDF_OK;
 }

@@ -142,6 +142,8 @@ SCENES = {
     "plane": {"kind": "plane", "n": [0.1, -0.2, 1.0], "d": 1.2},
     "sphere": {"kind": "sphere", "c": [0.0, 0.0, 1.5], "r": 0.5},
     "room": {"kind": "room", "half": 1.2437},
+    # walls exactly on voxel faces for 5 mm / 1 cm voxels: stresses floor() exactness
+    "room_aligned": {"kind": "room", "half": 1.25},
 }
 
 

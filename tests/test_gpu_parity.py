@@ -20,7 +20,8 @@ def _vol(dev, voxel, trunc, **kw):
 
 
 @pytest.mark.parametrize("scene,voxel", [("plane", 0.03), ("sphere", 0.03), ("room", 0.01),
-                                         ("plane", 0.005)])
+                                         ("plane", 0.005), ("room_aligned", 0.005),
+                                         ("room_aligned", 0.01)])
 @pytest.mark.parametrize("n_kf", [1, 3])
 def test_keyframes_match_oracle(cuda_device, scene, voxel, n_kf):
     trunc = 4 * voxel
