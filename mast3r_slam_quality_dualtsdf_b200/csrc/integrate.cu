@@ -9,9 +9,12 @@
 // voxel with ONE 128-bit vector reduction (red.global.add.v4.f32) plus one
 // 64-bit reduction for the two hit counters.  The fold is commutative
 // (DESIGN.md "the fold"), so no ordering between rays is needed.
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "ray.cuh"
 #include "march_fast.cuh"
+#include "fuse.cuh"
 
 struct Acc {
   int kx, ky, kz;
@@ -155,18 +158,24 @@ __global__ void __launch_bounds__(256)
                                 const double *__restrict__ conf,
                                 const double *__restrict__ conf_q, float ox, float oy, float oz,
                                 long long m, float step, MarchConst mc) {
+  __shared__ WarpCache wcs[8];
+  WarpCache &wc = wcs[threadIdx.x >> 5];
+  warp_cache_init(wc);
   long long p = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   Tally tl = {0, 0, 0, 0, 0};
+  Ray<float> r = {};
+  bool have = false;
+  float c = 0.f, cq = 0.f;
   if (p < m) {
-    Ray<float> r;
-    if (ray_setup<float>(r, pts[3 * p], pts[3 * p + 1], pts[3 * p + 2], ox, oy, oz, step,
-                         mc.trunc)) {
+    have = ray_setup<float>(r, pts[3 * p], pts[3 * p + 1], pts[3 * p + 2], ox, oy, oz, step,
+                            mc.trunc);
+    if (have) {
       tl.rays = 1; // global_volume.py:71
-      float c = (float)conf[p];
-      float cq = conf_q ? (float)conf_q[p] : 0.f;
-      march_ray_fast<BOUNDED>(v, r, mc, c, cq, conf_q != nullptr, tl);
+      c = (float)conf[p];
+      cq = conf_q ? (float)conf_q[p] : 0.f;
     }
   }
+  march_warp<BOUNDED>(v, wc, mc, have, r, c, cq, conf_q != nullptr, tl);
   commit_tally(v, tl);
 }
 
@@ -197,30 +206,41 @@ __global__ void __launch_bounds__(256)
                                const float *__restrict__ C, const float *__restrict__ qg,
                                const float *__restrict__ poses, int H, int W, int gh, int gw,
                                float min_conf, float step, MarchConst mc) {
-  const int kf = blockIdx.y;
+  // CTA = 32 x 8 pixel tile, warp = 8 x 4 sub-tile: rays of a warp stay close
+  // in the volume, so their reductions share 32-byte sectors.
+  __shared__ WarpCache wcs[8];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  WarpCache &wc = wcs[warp];
+  warp_cache_init(wc);
+  const int kf = blockIdx.z;
+  const int px = blockIdx.x * 32 + (warp & 3) * 8 + (lane & 7);
+  const int py = blockIdx.y * 8 + (warp >> 2) * 4 + (lane >> 3);
   const long long npix = (long long)H * W;
-  long long pix = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   Tally tl = {0, 0, 0, 0, 0};
-  if (pix < npix) {
+  Ray<float> r = {};
+  bool have = false;
+  float c = 0.f, cq = 0.f;
+  if (px < W && py < H) {
+    const long long pix = (long long)py * W + px;
     const float *P = poses + 8 * kf;
-    float c = C[kf * npix + pix];
+    c = C[kf * npix + pix];
     if (c > min_conf) { // global_manager.py:92
       const float *x = X + (kf * npix + pix) * 3;
       float wx, wy, wz;
       sim3_act(P, x[0], x[1], x[2], wx, wy, wz);
-      Ray<float> r;
-      if (ray_setup<float>(r, wx, wy, wz, P[0], P[1], P[2], step, mc.trunc)) {
+      have = ray_setup<float>(r, wx, wy, wz, P[0], P[1], P[2], step, mc.trunc);
+      if (have) {
         tl.rays = 1;
         float q = 1.0f;
         if (qg) {
-          int y = (int)(pix / W), xx = (int)(pix % W);
-          int gy = min(y / (H / gh), gh - 1), gx = min(xx / (W / gw), gw - 1);
+          int gy = min(py / (H / gh), gh - 1), gx = min(px / (W / gw), gw - 1);
           q = qg[((long long)kf * gh + gy) * gw + gx];
         }
-        march_ray_fast<BOUNDED>(v, r, mc, c, c * q, true, tl);
+        cq = c * q;
       }
     }
   }
+  march_warp<BOUNDED>(v, wc, mc, have, r, c, cq, true, tl);
   commit_tally(v, tl);
 }
 
@@ -232,6 +252,8 @@ static MarchConst make_consts(const b200tsdf *h) {
   mc.inv_vs = 1.0f / mc.vs;
   mc.inv_trunc = 1.0f / mc.trunc;
   mc.nl2e_inv_trunc = -1.4426950408889634f / mc.trunc;
+  const char *e = getenv("B200TSDF_DEBUG");
+  mc.dbg = e ? atoi(e) : 0;
   return mc;
 }
 
@@ -302,7 +324,7 @@ extern "C" int b200tsdf_integrate_keyframes(b200tsdf_t *h, const float *X_dev, c
   double step_d = h->cfg.voxel_size * step_scale;
   if (step_d < 1.0e-4) step_d = 1.0e-4;
   long long npix = (long long)H * W;
-  dim3 grid((unsigned)((npix + 255) / 256), (unsigned)B);
+  dim3 grid((unsigned)((W + 31) / 32), (unsigned)((H + 7) / 8), (unsigned)B);
   if (h->d.bounded)
     integrate_keyframes_kernel<true><<<grid, 256, 0, st>>>(
         h->d, X_dev, C_dev, q_grid_dev, pose_dev, H, W, gh, gw, min_conf, (float)step_d,

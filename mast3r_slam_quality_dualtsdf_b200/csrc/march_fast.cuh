@@ -20,6 +20,7 @@
 
 struct MarchConst {
   float trunc, vs, inv_vs, inv_trunc, nl2e_inv_trunc; // -log2(e) / trunc
+  int dbg; // experiments only (B200TSDF_DEBUG): bit0 skip count red, bit1 skip voxel red
 };
 
 struct Tally {
@@ -37,7 +38,8 @@ struct VoxCache {
 template <bool BOUNDED>
 __device__ __forceinline__ void flush_fast(const VolumeDev &v, int kx, int ky, int kz, float su,
                                            float wu, uint32_t n, float conf, float conf_q,
-                                           uint32_t cp, uint32_t cq, VoxCache &bc, Tally &tl) {
+                                           uint32_t cp, uint32_t cq, VoxCache &bc, Tally &tl,
+                                           int dbg = 0) {
   if (BOUNDED) {
     bool in = (uint32_t)(kx - v.kmin[0]) < (uint32_t)(v.kmax[0] - v.kmin[0]) &&
               (uint32_t)(ky - v.kmin[1]) < (uint32_t)(v.kmax[1] - v.kmin[1]) &&
@@ -67,8 +69,8 @@ __device__ __forceinline__ void flush_fast(const VolumeDev &v, int kx, int ky, i
   }
   uint32_t li = ((kz & 7) << 6) | ((ky & 7) << 3) | (kx & 7);
   size_t off = (size_t)bc.slot * B200_BLOCK_VOX + li;
-  red_add_v4(v.vox + off, conf * su, conf * wu, conf_q * su, conf_q * wu);
-  red_add_u64(v.cnt + off, (unsigned long long)(n * cp) | ((unsigned long long)(n * cq) << 32));
+  if (!(dbg & 2)) red_add_v4(v.vox + off, conf * su, conf * wu, conf_q * su, conf_q * wu);
+  if (!(dbg & 1)) red_add_u64(v.cnt + off, (unsigned long long)(n * cp) | ((unsigned long long)(n * cq) << 32));
 }
 
 // global_volume.py:63-70 for one ray; conf / conf_q are the reference `conf`
@@ -120,7 +122,7 @@ __device__ __forceinline__ void march_ray_fast(const VolumeDev &v, const Ray<flo
       kx = (int)fx, ky = (int)fy, kz = (int)fz;
     }
     if (n && (kx != ax || ky != ay || kz != az)) {
-      flush_fast<BOUNDED>(v, ax, ay, az, su, wu, n, conf, conf_q, cp, cq, bc, tl);
+      flush_fast<BOUNDED>(v, ax, ay, az, su, wu, n, conf, conf_q, cp, cq, bc, tl, mc.dbg);
       su = wu = 0.f;
       n = 0;
     }
@@ -133,7 +135,7 @@ __device__ __forceinline__ void march_ray_fast(const VolumeDev &v, const Ray<flo
     n += 1;
     total += 1;
   }
-  if (n) flush_fast<BOUNDED>(v, ax, ay, az, su, wu, n, conf, conf_q, cp, cq, bc, tl);
+  if (n) flush_fast<BOUNDED>(v, ax, ay, az, su, wu, n, conf, conf_q, cp, cq, bc, tl, mc.dbg);
   tl.ev_p += total * cp;
   tl.ev_q += total * cq;
 }
