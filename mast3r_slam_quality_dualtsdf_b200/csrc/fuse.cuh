@@ -107,27 +107,39 @@ __device__ __forceinline__ void march_warp(const VolumeDev &v, WarpCache &wc, co
   const bool live = (cp | cq) != 0;
   if (!cp) conf = 0.0f;
   if (!cq) conf_q = 0.0f;
-  // |s / vs| bound along the ray -> integer-proximity threshold of the fast floor
-  float ex = fabsf(r.ox) + r.maxd * fabsf(r.dx), ey = fabsf(r.oy) + r.maxd * fabsf(r.dy),
-        ez = fabsf(r.oz) + r.maxd * fabsf(r.dz);
-  float qmax = fmaxf(ex, fmaxf(ey, ez)) * mc.inv_vs * 1.0001f + 2.0f;
-  const float lim = (qmax < 4.0e6f) ? 0.5f - qmax * 2.3841858e-7f : -1.0f; // 2^-22
-  // rays whose keys could leave the +-2^23 voxel range of the block hash are dropped whole
-  const bool far = !(qmax < 8.0e6f);
-  bool check_bounds = false;
-  if (BOUNDED) { // skip the per-voxel bound test when every ray's band is well inside
+  // |s / vs| bound along the ray -> integer-proximity threshold of the fast
+  // floor; rays whose keys could leave the +-2^23 voxel range of the block hash
+  // are dropped whole.  Bounded volumes: a ray whose band lies inside the
+  // bounds takes the launch-wide threshold and skips the per-voxel bound test.
+  float lim;
+  bool far = false, check_bounds = false;
+  bool inside = false;
+  if (BOUNDED) {
     float d0 = fmaxf(r.len - mc.trunc, 0.0f);
-    bool inside = true;
-    const float o[3] = {r.ox, r.oy, r.oz}, d[3] = {r.dx, r.dy, r.dz};
-#pragma unroll
-    for (int a = 0; a < 3; ++a) {
-      float q0 = (o[a] + d0 * d[a]) * mc.inv_vs, q1 = (o[a] + r.maxd * d[a]) * mc.inv_vs;
-      inside = inside && fminf(q0, q1) - 2.0f >= (float)v.kmin[a] &&
-               fmaxf(q0, q1) + 2.0f < (float)v.kmax[a];
-    }
+    float ax0 = fmaf(d0, r.dx, r.ox) * mc.inv_vs, ax1 = fmaf(r.maxd, r.dx, r.ox) * mc.inv_vs;
+    float ay0 = fmaf(d0, r.dy, r.oy) * mc.inv_vs, ay1 = fmaf(r.maxd, r.dy, r.oy) * mc.inv_vs;
+    float az0 = fmaf(d0, r.dz, r.oz) * mc.inv_vs, az1 = fmaf(r.maxd, r.dz, r.oz) * mc.inv_vs;
+    inside = fminf(ax0, ax1) >= mc.blo[0] && fmaxf(ax0, ax1) < mc.bhi[0] &&
+             fminf(ay0, ay1) >= mc.blo[1] && fmaxf(ay0, ay1) < mc.bhi[1] &&
+             fminf(az0, az1) >= mc.blo[2] && fmaxf(az0, az1) < mc.bhi[2];
     check_bounds = !__all_sync(0xFFFFFFFFu, inside || !live);
   }
-  const int cnt = (live && !far) ? (r.n - r.i_lo) : 0;
+  if (BOUNDED && inside) {
+    lim = mc.lim_bounded;
+  } else {
+    float ex = fabsf(r.ox) + r.maxd * fabsf(r.dx), ey = fabsf(r.oy) + r.maxd * fabsf(r.dy),
+          ez = fabsf(r.oz) + r.maxd * fabsf(r.dz);
+    float qmax = fmaxf(ex, fmaxf(ey, ez)) * mc.inv_vs * 1.0001f + 2.0f;
+    lim = (qmax < 4.0e6f) ? 0.5f - qmax * 2.3841858e-7f : -1.0f; // 2^-22
+    far = !(qmax < 8.0e6f);
+  }
+  // first in-band sample: i_lo is conservative (ray.cuh), advance it exactly
+  int i = r.i_lo;
+  if (live && !far) {
+#pragma unroll 1
+    while (i < r.n - 1 && fabsf(__fsub_rn(r.len, __fmul_rn((float)i, r.lstep))) > mc.trunc) ++i;
+  }
+  const int cnt = (live && !far) ? (r.n - i) : 0;
   const int J = __reduce_max_sync(0xFFFFFFFFu, cnt);
   if (live && far) tl.dropped += 1;
   const float MAGIC = 12582912.0f; // 1.5 * 2^23
@@ -135,8 +147,7 @@ __device__ __forceinline__ void march_warp(const VolumeDev &v, WarpCache &wc, co
   int ax = 0, ay = 0, az = 0;
   float su = 0.f, wu = 0.f;
   uint32_t n = 0, total = 0;
-  float fi = (float)r.i_lo;
-  int i = r.i_lo;
+  float fi = (float)i;
   for (int j = 0; j < J; ++j, ++i, fi += 1.0f) {
     float dist = (i == r.n - 1) ? last_dist : __fmul_rn(fi, r.lstep);
     float sdf = __fsub_rn(r.len, dist);

@@ -233,7 +233,10 @@ __global__ void __launch_bounds__(256)
         tl.rays = 1;
         float q = 1.0f;
         if (qg) {
-          int gy = min(py / (H / gh), gh - 1), gx = min(px / (W / gw), gw - 1);
+          const int ch = H / gh, cw = W / gw; // uniform; power-of-two cells avoid the division
+          int gy = (ch & (ch - 1)) ? py / ch : py >> (31 - __clz(ch));
+          int gx = (cw & (cw - 1)) ? px / cw : px >> (31 - __clz(cw));
+          gy = min(gy, gh - 1), gx = min(gx, gw - 1);
           q = qg[((long long)kf * gh + gy) * gw + gx];
         }
         cq = c * q;
@@ -252,6 +255,13 @@ static MarchConst make_consts(const b200tsdf *h) {
   mc.inv_vs = 1.0f / mc.vs;
   mc.inv_trunc = 1.0f / mc.trunc;
   mc.nl2e_inv_trunc = -1.4426950408889634f / mc.trunc;
+  float qb = 2.0f;
+  for (int a = 0; a < 3; ++a) {
+    mc.blo[a] = (float)h->d.kmin[a] + 2.0f;
+    mc.bhi[a] = (float)h->d.kmax[a] - 2.0f;
+    qb = fmaxf(qb, fmaxf(fabsf((float)h->d.kmin[a]), fabsf((float)h->d.kmax[a])) + 2.0f);
+  }
+  mc.lim_bounded = (qb < 4.0e6f) ? 0.5f - qb * 2.3841858e-7f : -1.0f;
   const char *e = getenv("B200TSDF_DEBUG");
   mc.dbg = e ? atoi(e) : 0;
   return mc;

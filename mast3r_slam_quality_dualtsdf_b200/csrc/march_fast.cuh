@@ -20,6 +20,8 @@
 
 struct MarchConst {
   float trunc, vs, inv_vs, inv_trunc, nl2e_inv_trunc; // -log2(e) / trunc
+  // bounded volumes: float key bounds shrunk by 2 voxels, launch-wide floor threshold
+  float blo[3], bhi[3], lim_bounded;
   int dbg; // experiments only (B200TSDF_DEBUG): bit0 skip count red, bit1 skip voxel red
 };
 

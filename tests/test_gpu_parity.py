@@ -154,3 +154,33 @@ def test_bounds_drop_outside(cuda_device):
     order = np.lexsort((gk[:, 2], gk[:, 1], gk[:, 0]))
     got = tuple(np.concatenate([p[i] for p in parts])[order] for i in range(4))
     assert_volume_matches(got, (keys, t, w, c), "z-slab union")
+
+
+@pytest.mark.parametrize("case", ["plane_v30_f32", "sphere_v30_f32", "sphere_v30_f64",
+                                  "room_v10_f32", "plane_clamp_f32"])
+def test_against_reference_golden(cuda_device, case):
+    """CUDA path vs vectors frozen from the UNMODIFIED reference TSDFVolume."""
+    import os
+
+    from tests.golden import make_golden as mg
+
+    g = np.load(os.path.join(mg.HERE, case + ".npz"))
+    scene, n_kf, H, W, f, voxel, trunc, mw, dtype, seed = mg.CASES[case]
+    kf, staged = mg.staged_inputs(case)
+    from mast3r_slam_quality_dualtsdf_b200.tsdf import TSDFVolume
+
+    vol = TSDFVolume(voxel, trunc, mw, device=cuda_device)
+    fused = sum(vol.integrate(s[0], s[1], s[3], confidences_q=s[2]) for s in staged)
+    assert fused == int(g["p_fused"])
+    c = vol.counters()
+    assert c["updates_primary"] == int(g["p_events"]) and c["updates_quality"] == int(g["q_events"])
+    for which, name in ((0, "p"), (1, "q")):
+        want = (g[f"{name}_keys"].astype(np.int64), g[f"{name}_tsdf"], g[f"{name}_w"],
+                g[f"{name}_count"])
+        assert_volume_matches(vol.export(which), want, f"{case}/{name}")
+        st = vol.stats(which)
+        assert [st["valid_voxels"], st["total_voxels"]] == list(g[f"{name}_stats"])
+        t, gr, fl = (x.cpu().numpy() for x in vol.query_batch(g[f"{name}_probe"], which))
+        assert np.array_equal(fl & 1, g[f"{name}_qfl"] & 1)
+        has = (fl & 1) > 0
+        assert np.abs(t[has] - g[f"{name}_qt"][has]).max() <= 1e-5
