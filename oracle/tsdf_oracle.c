@@ -33,6 +33,9 @@ typedef struct {
   uint32_t count; /* number of _update_voxel hits (not in the reference; an
                      integer the parity tests compare bit-exactly) */
   uint8_t used;
+  uint8_t t_f32; /* tsdf still holds the np.float32 scalar of the first insert
+                    (global_volume.py:80): numpy then does float32 arithmetic
+                    on it in _estimate_gradient (:122) */
 } orc_voxel;
 
 typedef struct {
@@ -112,7 +115,7 @@ static orc_voxel *orc_find(orc_volume *v, const int64_t k[3], int insert) {
  * the caller per :133-134).  Running average divides by the CLAMPED total
  * weight; the first insert stores tsdf / weight verbatim (no clamp). */
 static void orc_update_voxel(orc_volume *v, const int64_t key[3], double tsdf,
-                             double weight) {
+                             double weight, int t_is_f32) {
   if (weight <= 0.0) return; /* :75 */
   v->events++;
   if ((v->n + 1) * 10 > v->cap * 7) orc_grow(v);
@@ -122,6 +125,7 @@ static void orc_update_voxel(orc_volume *v, const int64_t key[3], double tsdf,
     e->tsdf = tsdf;
     e->weight = weight;
     e->count = 1;
+    e->t_f32 = (uint8_t)t_is_f32;
     return;
   }
   double total = e->weight + weight; /* :84 */
@@ -129,6 +133,7 @@ static void orc_update_voxel(orc_volume *v, const int64_t key[3], double tsdf,
   double den = total > 1.0e-9 ? total : 1.0e-9; /* :85-87 */
   e->tsdf = (e->tsdf * e->weight + tsdf * weight) / den;
   e->weight = total; /* :88 */
+  e->t_f32 = 0;      /* float32 * float64 -> float64 */
   e->count++;
 }
 
@@ -194,7 +199,7 @@ int64_t orc_integrate_f32(orc_volume *v, const float *pts, const double *conf,
       key[0] = (int64_t)floorf(sx / vs);
       key[1] = (int64_t)floorf(sy / vs);
       key[2] = (int64_t)floorf(sz / vs);
-      orc_update_voxel(v, key, (double)t, w); /* :70 */
+      orc_update_voxel(v, key, (double)t, w, 1); /* :70 */
     }
     fused++; /* :71 */
   }
@@ -251,7 +256,7 @@ int64_t orc_integrate_f64(orc_volume *v, const double *pts, const double *conf,
       key[0] = (int64_t)floor(sx / vs);
       key[1] = (int64_t)floor(sy / vs);
       key[2] = (int64_t)floor(sz / vs);
-      orc_update_voxel(v, key, t, w);
+      orc_update_voxel(v, key, t, w, 0);
     }
     fused++;
   }
@@ -338,7 +343,12 @@ void orc_query(orc_volume *v, const void *pts, int dtype_f64, int64_t m,
       orc_voxel *vp = orc_find(v, kp, 0), *vn = orc_find(v, kn, 0);
       if (!vp || !vn) continue;
       if (vp->weight < v->min_weight || vn->weight < v->min_weight) continue;
-      g[ax] = (vp->tsdf - vn->tsdf) / (2.0 * v->voxel_size);
+      if (vp->t_f32 && vn->t_f32) { /* np.float32 - np.float32, / weak python float */
+        float d32 = (float)vp->tsdf - (float)vn->tsdf;
+        g[ax] = (double)(d32 / (float)(2.0 * v->voxel_size));
+      } else {
+        g[ax] = (vp->tsdf - vn->tsdf) / (2.0 * v->voxel_size);
+      }
       denom++;
     }
     if (!denom) continue; /* :124-125 */

@@ -40,7 +40,7 @@ def test_oracle_matches_reference_golden(case):
         has = fl & 1 > 0
         assert np.array_equal(qt[has], g[f"{name}_qt"][has])
         hg = fl == 3
-        assert np.allclose(qg[hg], g[f"{name}_qg"][hg], rtol=0, atol=1e-12)
+        assert np.allclose(qg[hg], g[f"{name}_qg"][hg], rtol=0, atol=1e-15)
 
 
 def test_all_fixtures_have_cases():
