@@ -1,7 +1,146 @@
-// mc.cu -- marching-cubes extraction (placeholder until the kernel lands).
+// mc.cu -- marching-cubes extraction over the allocated voxel blocks.
+//
+// No reference counterpart (the reference has no mesh path):
+// semantics are stated in oracle/mc_oracle.c and checked against it.
+// One CTA per voxel block: the 9x9x9 corner lattice (block + one-voxel halo
+// from the +x/+y/+z neighbour blocks, found through the block hash) is staged
+// in shared memory with 128-bit loads; every thread classifies two cubes;
+// triangle slots are assigned by a warp-scan (shfl_up) + per-CTA offsets and
+// ONE atomicAdd per CTA on the global triangle counter (warp-scan compaction).
+#include <math.h>
+
 #include "common.cuh"
+
+#define MC_TABLE_QUAL __device__ const
+#include "mc_tables.h"
+
+#define MC_THREADS 256
+
+template <bool WRITE>
+__global__ void __launch_bounds__(MC_THREADS)
+    mc_kernel(VolumeDev v, int which, float vs, float *__restrict__ verts, long long tri_cap,
+              unsigned long long *n_tris) {
+  __shared__ float tv[9 * 9 * 9];
+  __shared__ uint32_t nslot[8];
+  __shared__ signed char s_tri[256 * 16];
+  __shared__ unsigned char s_num[256];
+  __shared__ uint32_t warp_tot[MC_THREADS / 32];
+  __shared__ unsigned long long s_base;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  for (int i = tid; i < 256 * 16; i += MC_THREADS) s_tri[i] = ((const signed char *)MC_TRI_TABLE)[i];
+  if (tid < 256) s_num[tid] = MC_NUM_TRIS[tid];
+  const uint32_t nb = (uint32_t)v.ctr[CTR_BLOCKS];
+  for (uint32_t b = blockIdx.x; b < nb; b += gridDim.x) {
+    __syncthreads();
+    const uint32_t slot = v.list[b];
+    int bx, by, bz;
+    unpack_block_key(v.keys[slot], bx, by, bz);
+    if (tid < 8) {
+      int nx = bx + (tid & 1), ny = by + ((tid >> 1) & 1), nz = bz + (tid >> 2);
+      nslot[tid] = tid == 0 ? slot
+                            : (block_in_range(nx, ny, nz) ? hash_find(v, pack_block_key(nx, ny, nz))
+                                                          : 0xFFFFFFFFu);
+    }
+    __syncthreads();
+    for (int i = tid; i < 729; i += MC_THREADS) {
+      int x = i % 9, y = (i / 9) % 9, z = i / 81;
+      int nbk = (x == 8) | ((y == 8) << 1) | ((z == 8) << 2);
+      uint32_t s = nslot[nbk];
+      float val = NAN;
+      if (s != 0xFFFFFFFFu) {
+        size_t off = (size_t)s * B200_BLOCK_VOX + (((z & 7) << 6) | ((y & 7) << 3) | (x & 7));
+        float t, w;
+        uint32_t hits;
+        if (voxel_view(v.vox[off], v.cnt[off], which, v.max_weight, t, w, hits) &&
+            w >= v.min_weight)
+          val = t;
+      }
+      tv[i] = val;
+    }
+    __syncthreads();
+    int mask[2], nt[2];
+#pragma unroll
+    for (int c2 = 0; c2 < 2; ++c2) {
+      int c = tid + c2 * MC_THREADS;
+      int x = c & 7, y = (c >> 3) & 7, z = c >> 6;
+      int m = 0;
+      bool ok = true;
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        float t = tv[(z + (k >> 2)) * 81 + (y + ((k >> 1) & 1)) * 9 + x + (k & 1)];
+        ok = ok && !isnan(t);
+        m |= (t < 0.0f) ? (1 << k) : 0;
+      }
+      mask[c2] = m;
+      nt[c2] = ok ? s_num[m] : 0;
+    }
+    // warp-scan compaction of the per-thread triangle counts
+    uint32_t mine = nt[0] + nt[1], incl = mine;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      uint32_t o = __shfl_up_sync(0xFFFFFFFFu, incl, d);
+      if (lane >= d) incl += o;
+    }
+    if (lane == 31) warp_tot[warp] = incl;
+    __syncthreads();
+    uint32_t wbase = 0, total = 0;
+#pragma unroll
+    for (int w = 0; w < MC_THREADS / 32; ++w) {
+      if (w < warp) wbase += warp_tot[w];
+      total += warp_tot[w];
+    }
+    if (tid == 0 && total) s_base = atomicAdd(n_tris, (unsigned long long)total);
+    __syncthreads();
+    if (WRITE && total) {
+      long long o = (long long)s_base + wbase + (incl - mine);
+#pragma unroll
+      for (int c2 = 0; c2 < 2; ++c2) {
+        int c = tid + c2 * MC_THREADS;
+        int x = c & 7, y = (c >> 3) & 7, z = c >> 6;
+        for (int q = 0; q < nt[c2]; ++q, ++o) {
+          if (o >= tri_cap) break;
+#pragma unroll
+          for (int vtx = 0; vtx < 3; ++vtx) {
+            int e = s_tri[mask[c2] * 16 + 3 * q + vtx];
+            int a = MC_EDGE_CORNERS[e][0], bb = MC_EDGE_CORNERS[e][1];
+            int ax = x + (a & 1), ay = y + ((a >> 1) & 1), az = z + (a >> 2);
+            int cx = x + (bb & 1), cy = y + ((bb >> 1) & 1), cz = z + (bb >> 2);
+            float ta = tv[az * 81 + ay * 9 + ax], tb = tv[cz * 81 + cy * 9 + cx];
+            float mu = __fdiv_rn(ta, __fsub_rn(ta, tb));
+            float pa[3] = {__fmul_rn((float)(bx * 8 + ax), vs), __fmul_rn((float)(by * 8 + ay), vs),
+                           __fmul_rn((float)(bz * 8 + az), vs)};
+            float pb[3] = {__fmul_rn((float)(bx * 8 + cx), vs), __fmul_rn((float)(by * 8 + cy), vs),
+                           __fmul_rn((float)(bz * 8 + cz), vs)};
+#pragma unroll
+            for (int d = 0; d < 3; ++d)
+              verts[o * 9 + vtx * 3 + d] =
+                  __fadd_rn(pa[d], __fmul_rn(__fsub_rn(pb[d], pa[d]), mu));
+          }
+        }
+      }
+    }
+  }
+}
+
 extern "C" int b200tsdf_extract_mesh(b200tsdf_t *h, int which, float *verts_dev, int64_t tri_cap,
                                      int64_t *n_tris_host, void *stream) {
-  b200_set_error("b200tsdf_extract_mesh: not built yet");
-  return B200TSDF_E_INVALID;
+  if (!h || !n_tris_host || (which != 0 && which != 1) || tri_cap < 0) {
+    b200_set_error("b200tsdf_extract_mesh: invalid argument");
+    return B200TSDF_E_INVALID;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  B200_CUDA(cudaSetDevice(h->cfg.device));
+  B200_CUDA(cudaMemsetAsync(h->scratch, 0, 8, st));
+  const float vs = (float)h->cfg.voxel_size;
+  if (verts_dev && tri_cap > 0)
+    mc_kernel<true><<<148 * 4, MC_THREADS, 0, st>>>(h->d, which, vs, verts_dev,
+                                                     (long long)tri_cap, h->scratch);
+  else
+    mc_kernel<false><<<148 * 4, MC_THREADS, 0, st>>>(h->d, which, vs, nullptr, 0, h->scratch);
+  B200_CUDA(cudaGetLastError());
+  unsigned long long n;
+  B200_CUDA(cudaMemcpyAsync(&n, h->scratch, 8, cudaMemcpyDeviceToHost, st));
+  B200_CUDA(cudaStreamSynchronize(st));
+  *n_tris_host = (int64_t)n;
+  return B200TSDF_OK;
 }

@@ -17,8 +17,10 @@ _SRCS = ["tsdf_oracle.c", "local_oracle.c", "mc_oracle.c"]
 
 def build(force=False):
     srcs = [os.path.join(_HERE, s) for s in _SRCS if os.path.exists(os.path.join(_HERE, s))]
+    deps = srcs + [os.path.join(_HERE, "..", "mast3r_slam_quality_dualtsdf_b200", "csrc",
+                                "mc_tables.h")]
     if not force and os.path.exists(_LIB) and all(
-        os.path.getmtime(_LIB) >= os.path.getmtime(s) for s in srcs
+        os.path.getmtime(_LIB) >= os.path.getmtime(s) for s in deps
     ):
         return _LIB
     cmd = ["gcc", "-O2", "-ffp-contract=off", "-fno-fast-math", "-fPIC", "-shared",
@@ -57,6 +59,9 @@ def lib():
         L.orc_stage_keyframe.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                          C.c_int, C.c_int, C.c_int, C.c_int, C.c_float,
                                          C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.orc_marching_cubes.restype = C.c_int64
+        L.orc_marching_cubes.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64,
+                                         C.c_double, C.c_double, C.c_void_p, C.c_int64]
         _lib = L
     return _lib
 
@@ -160,3 +165,19 @@ def stage_keyframe(X, Cf, pose, q_grid, H, W, min_conf):
     k = int(lib().orc_stage_keyframe(_p(X), _p(Cf), _p(pose), _p(qg), gh, gw, H, W,
                                      float(min_conf), _p(pts), _p(conf), _p(confq), _p(org)))
     return pts[:k].copy(), conf[:k].copy(), confq[:k].copy(), org
+
+
+def marching_cubes(keys, tsdf, weight, voxel_size, min_weight=1.0e-3):
+    """CPU marching cubes (oracle/mc_oracle.c; parity unpinned -- the reference
+    has no mesh path).  Returns verts float32 (T, 3, 3)."""
+    keys = np.ascontiguousarray(keys, np.int64).reshape(-1, 3)
+    tsdf = np.ascontiguousarray(tsdf, np.float32).reshape(-1)
+    weight = np.ascontiguousarray(weight, np.float32).reshape(-1)
+    n = keys.shape[0]
+    nt = int(lib().orc_marching_cubes(_p(keys), _p(tsdf), _p(weight), n, float(voxel_size),
+                                      float(min_weight), None, 0))
+    verts = np.zeros((max(nt, 1), 3, 3), np.float32)
+    if nt:
+        lib().orc_marching_cubes(_p(keys), _p(tsdf), _p(weight), n, float(voxel_size),
+                                 float(min_weight), _p(verts), nt)
+    return verts[:nt]
