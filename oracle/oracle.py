@@ -181,3 +181,56 @@ def marching_cubes(keys, tsdf, weight, voxel_size, min_weight=1.0e-3):
         lib().orc_marching_cubes(_p(keys), _p(tsdf), _p(weight), n, float(voxel_size),
                                  float(min_weight), _p(verts), nt)
     return verts[:nt]
+
+
+# ---------------------------------------------------------------- local ROI
+def _local_lib():
+    L = lib()
+    if not getattr(L, "_local_ready", False):
+        L.orc_local_dims.argtypes = [C.c_void_p, C.c_void_p, C.c_double, C.c_int, C.c_void_p]
+        L.orc_local_build.restype = C.c_int64
+        L.orc_local_build.argtypes = [C.c_void_p] * 5 + [C.c_int64, C.c_double, C.c_double, C.c_int,
+                                                         C.c_double, C.c_void_p, C.c_void_p,
+                                                         C.c_void_p]
+        L.orc_local_raycast.restype = C.c_int64
+        L.orc_local_raycast.argtypes = [C.c_void_p] * 6 + [C.c_int64, C.c_int, C.c_double,
+                                                           C.c_void_p, C.c_void_p]
+        L._local_ready = True
+    return L
+
+
+def local_build(X_canon, Cf, pose, xyz_min, xyz_max, voxel_size, trunc_dist, max_grid_dim,
+                min_confidence):
+    """tsdf_refine.py:837-940 -> (tsdf (nz,ny,nx) f32, weights, fused)."""
+    L = _local_lib()
+    X = np.ascontiguousarray(X_canon, np.float32).reshape(-1, 3)
+    Cf = np.ascontiguousarray(Cf, np.float32).reshape(-1)
+    pose = np.ascontiguousarray(pose, np.float32).reshape(8)
+    lo = np.ascontiguousarray(xyz_min, np.float32).reshape(3)
+    hi = np.ascontiguousarray(xyz_max, np.float32).reshape(3)
+    dims = np.zeros(3, np.int32)
+    L.orc_local_dims(_p(lo), _p(hi), float(voxel_size), int(max_grid_dim), _p(dims))
+    nx, ny, nz = (int(v) for v in dims)
+    tsdf = np.zeros((nz, ny, nx), np.float32)
+    w = np.zeros((nz, ny, nx), np.float32)
+    fused = int(L.orc_local_build(_p(X), _p(Cf), _p(pose), _p(lo), _p(hi), X.shape[0],
+                                  float(voxel_size), float(trunc_dist), int(max_grid_dim),
+                                  float(min_confidence), _p(tsdf), _p(w), _p(dims)))
+    return tsdf, w, fused
+
+
+def local_raycast(tsdf, xyz_min, xyz_max, X_original, pix, n_samples, max_displacement):
+    """tsdf_refine.py:942-1021 for an explicit pixel list -> (X_refined, hits u8 (m,))."""
+    L = _local_lib()
+    tsdf = np.ascontiguousarray(tsdf, np.float32)
+    nz, ny, nx = tsdf.shape
+    dims = np.array([nx, ny, nz], np.int32)
+    lo = np.ascontiguousarray(xyz_min, np.float32).reshape(3)
+    hi = np.ascontiguousarray(xyz_max, np.float32).reshape(3)
+    X = np.ascontiguousarray(X_original, np.float32).reshape(-1, 3)
+    pix = np.ascontiguousarray(pix, np.int64).reshape(-1)
+    Xr = X.copy()
+    hits = np.zeros(len(pix), np.uint8)
+    L.orc_local_raycast(_p(tsdf), _p(dims), _p(lo), _p(hi), _p(X), _p(pix), len(pix),
+                        int(n_samples), float(max_displacement), _p(Xr), _p(hits))
+    return Xr, hits
