@@ -152,6 +152,42 @@ int b200tsdf_export_blocks(b200tsdf_t *h, int64_t *bkeys_dev, int64_t cap,
 int b200tsdf_extract_mesh(b200tsdf_t *h, int which, float *verts_dev,
                           int64_t tri_cap, int64_t *n_tris_host, void *stream);
 
+/* ---- local (per-ROI, dense) TSDF of the refiner: stateless calls ---------- */
+
+/* Replaces the config keys read by TSDFRefiner (mast3r_slam/tsdf_refine.py
+ * :839-841, :872, :953-955; config/base.yaml:84-101). */
+typedef struct {
+  double voxel_size;      /* tsdf_refine.voxel_size      */
+  double trunc_dist;      /* tsdf_refine.trunc_dist      */
+  double min_confidence;  /* tsdf_refine.min_confidence  */
+  double max_displacement;/* tsdf_refine.max_displacement*/
+  int32_t max_grid_dim;   /* tsdf_refine.max_grid_dim    */
+  int32_t ray_samples;    /* tsdf_refine.ray_samples     */
+} b200tsdf_local_cfg;
+
+/* Grid dims (nx, ny, nz) of an ROI box [min(3), max(3)] (tsdf_refine.py:844-846). */
+int b200tsdf_local_dims(const float *box6_host, const b200tsdf_local_cfg *cfg,
+                        int32_t dims3_host[3]);
+
+/* Replaces TSDFRefiner._build_tsdf_robust (tsdf_refine.py:837-940).
+ *  X_dev (N,3) f32 camera-frame pointmap, C_dev (N) f32, pose_dev 8 f32 Sim3,
+ *  tsdf_dev / weights_dev: (nz,ny,nx) f32 grids sized by b200tsdf_local_dims.
+ *  fused_host (nullable): number of points fused, -1 when fewer than 5 points
+ *  are valid (grids are then the initial 1 / 0); passing it synchronises. */
+int b200tsdf_local_build(const float *X_dev, const float *C_dev, const float *pose_dev,
+                         const float *box6_host, int64_t n_pts, const b200tsdf_local_cfg *cfg,
+                         float *tsdf_dev, float *weights_dev, int64_t *fused_host,
+                         void *stream);
+
+/* Replaces TSDFRefiner._extract_surface_safe + _sample_tsdf_trilinear
+ * (tsdf_refine.py:942-1064) for an explicit ordered pixel list (the caller
+ * makes the reference's random choice).  X_refined_dev must already hold a
+ * copy of X_dev; hits_dev has m bytes. */
+int b200tsdf_local_raycast(const float *tsdf_dev, const int32_t dims3_host[3],
+                           const float *box6_host, const float *X_dev, const int64_t *pix_dev,
+                           int64_t m, const b200tsdf_local_cfg *cfg, float *X_refined_dev,
+                           uint8_t *hits_dev, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

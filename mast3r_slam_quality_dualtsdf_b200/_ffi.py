@@ -18,7 +18,8 @@ SYMBOLS = [
     "b200tsdf_reset", "b200tsdf_integrate_points", "b200tsdf_integrate_keyframes",
     "b200tsdf_integrate_keyframes_host", "b200tsdf_counters", "b200tsdf_stats",
     "b200tsdf_query", "b200tsdf_export_voxels", "b200tsdf_export_blocks",
-    "b200tsdf_extract_mesh",
+    "b200tsdf_extract_mesh", "b200tsdf_local_dims", "b200tsdf_local_build",
+    "b200tsdf_local_raycast",
 ]
 
 
@@ -29,6 +30,13 @@ class Config(C.Structure):
         ("capacity_log2", C.c_int32), ("bounded", C.c_int32),
         ("key_min", C.c_int64 * 3), ("key_max", C.c_int64 * 3),
         ("device", C.c_int32), ("reserved", C.c_int32),
+    ]
+
+
+class LocalCfg(C.Structure):
+    _fields_ = [
+        ("voxel_size", C.c_double), ("trunc_dist", C.c_double), ("min_confidence", C.c_double),
+        ("max_displacement", C.c_double), ("max_grid_dim", C.c_int32), ("ray_samples", C.c_int32),
     ]
 
 
@@ -65,6 +73,9 @@ def lib():
     L.b200tsdf_export_voxels.argtypes = [vp, C.c_int, vp, vp, vp, vp, i64, vp, vp]
     L.b200tsdf_export_blocks.argtypes = [vp, vp, i64, vp, vp]
     L.b200tsdf_extract_mesh.argtypes = [vp, C.c_int, vp, i64, vp, vp]
+    L.b200tsdf_local_dims.argtypes = [vp, C.POINTER(LocalCfg), vp]
+    L.b200tsdf_local_build.argtypes = [vp, vp, vp, vp, i64, C.POINTER(LocalCfg), vp, vp, vp, vp]
+    L.b200tsdf_local_raycast.argtypes = [vp, vp, vp, vp, vp, i64, C.POINTER(LocalCfg), vp, vp, vp]
     for s in SYMBOLS:
         if s != "b200tsdf_last_error":
             getattr(L, s).restype = C.c_int
