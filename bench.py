@@ -324,6 +324,14 @@ def run_b200(args):
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0))
     achieved = alg_bytes_launch / (launch_ms * 1e-3) / 1e9
+    # DRAM traffic of the same kernel from the committed ncu --set full capture
+    traffic = None
+    try:
+        tr = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
+        if B == KF_PER_STEP and world == 1:
+            traffic = float(tr["integrate_keyframes_kernel"]["dram_bytes_per_launch"])
+    except Exception:
+        pass
 
     if rank != 0:
         if world > 1:
@@ -342,7 +350,7 @@ def run_b200(args):
                 "ms_per_step": e2e_ms / args.steps},
         "gpu_launches": args.steps,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                     "frac": achieved / peak, "traffic": None,
+                     "frac": achieved / peak, "traffic": traffic,
                      "kernel": "integrate_keyframes_kernel",
                      "peak_source": "measured (MEASURED_PEAKS.json hbm_gbs)" if peaks else "fallback",
                      "algorithmic_bytes_per_launch": alg_bytes_launch,
