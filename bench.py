@@ -294,8 +294,8 @@ def run_b200(args):
                     stage[k].copy_(host[s][k], non_blocking=True)
             bcast(stage)
             fuse(vol, stage)
-        vol.counters()  # the step's result (6 x int64) read back, synchronises
-        d2h[0] = 48
+        vol.counters()  # the step's result (8 x int64) read back, synchronises
+        d2h[0] = 64
 
     e2e_ms, e2e_updates, _, _, _ = timed(e2e_body, vol.reset)
     e2e_value = e2e_updates / (e2e_ms * 1e-3)

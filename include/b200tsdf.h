@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define B200TSDF_ABI_VERSION 1
+#define B200TSDF_ABI_VERSION 2
 
 enum {
   B200TSDF_OK = 0,
@@ -59,6 +59,17 @@ typedef struct {
   int64_t key_max[3];
   int32_t device; /* CUDA device ordinal */
   int32_t reserved;
+  /* multi-GPU partition: the world-z axis is cut into slabs of
+   * slab_width voxel layers (a power of two >= 8, measured from key_min[2] for a
+   * bounded volume, from 0 otherwise); slab s belongs to rank s mod
+   * slab_count.  This handle fuses only the voxels of rank slab_index and
+   * culls rays whose +-truncation band misses its slabs.  slab_count <= 1:
+   * the handle owns everything.  slab_count = R with slab_width = dim/R gives
+   * R contiguous z-slabs; a smaller width deals slabs round-robin (balanced
+   * when the surface is not uniform in z). */
+  int32_t slab_count;
+  int32_t slab_index;
+  int64_t slab_width;
 } b200tsdf_config;
 
 const char *b200tsdf_last_error(void);
@@ -116,8 +127,12 @@ int b200tsdf_integrate_keyframes_host(b200tsdf_t *h, const float *X_host,
 /* Counters since create/reset (synchronises the stream).
  *  out[0] rays fused        out[1] voxel updates, primary volume
  *  out[2] voxel updates, quality volume   out[3] allocated voxel blocks
- *  out[4] updates dropped (outside bounds) out[5] hash overflow events */
-int b200tsdf_counters(b200tsdf_t *h, int64_t out_host[6], void *stream);
+ *  out[4] updates dropped (outside bounds / foreign slab)
+ *  out[5] hash overflow events   out[6] rays culled (band misses this
+ *  rank's slabs)   out[7] reserved
+ * out[1], out[2] count APPLIED updates only, so the sum over the ranks of a
+ * sharded volume equals the single-volume count. */
+int b200tsdf_counters(b200tsdf_t *h, int64_t out_host[8], void *stream);
 
 /* Replaces TSDFVolume.stats (global_volume.py:136-140); which = 0 primary,
  * 1 quality volume.  Synchronises. */

@@ -30,6 +30,7 @@ class Config(C.Structure):
         ("capacity_log2", C.c_int32), ("bounded", C.c_int32),
         ("key_min", C.c_int64 * 3), ("key_max", C.c_int64 * 3),
         ("device", C.c_int32), ("reserved", C.c_int32),
+        ("slab_count", C.c_int32), ("slab_index", C.c_int32), ("slab_width", C.c_int64),
     ]
 
 

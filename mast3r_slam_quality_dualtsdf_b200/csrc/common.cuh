@@ -29,6 +29,7 @@ enum {
   CTR_BLOCKS = 3,
   CTR_DROPPED = 4,
   CTR_OVERFLOW = 5,
+  CTR_CULLED = 6, // rays skipped because their band misses this rank's slabs
   CTR_COUNT = 8
 };
 
@@ -42,12 +43,31 @@ struct VolumeDev {
   int bounded;
   int kmin[3], kmax[3]; // voxel-key bounds (clamped to int32 range)
   float max_weight, min_weight;
+  // bounded volumes: dense block -> slot directory, a CACHE of the hash
+  // (entries go EMPTY -> slot once; the hash stays the source of truth)
+  uint32_t *dir;
+  int dir_on, dir_b0[3], dir_n[3]; // first block coordinate, blocks per axis
+  // z-slab ownership (multi-GPU): slab s = (kz - slab_z0) >> slab_shift is
+  // owned iff s mod slab_count == slab_index
+  int slab_count, slab_index, slab_shift, slab_z0;
 };
+
+#define B200_NO_SLOT 0xFFFFFFFFu
+
+__host__ __device__ __forceinline__ int slab_owner_of(const VolumeDev &v, int s) {
+  int m = s % v.slab_count;
+  return m < 0 ? m + v.slab_count : m;
+}
+__host__ __device__ __forceinline__ bool slab_owns_z(const VolumeDev &v, int kz) {
+  if (v.slab_count <= 1) return true;
+  return slab_owner_of(v, (kz - v.slab_z0) >> v.slab_shift) == v.slab_index;
+}
 
 struct b200tsdf {
   b200tsdf_config cfg;
   VolumeDev d;
   uint64_t cap;
+  uint64_t dir_entries;
   // host staging for the *_host entry points
   void *stage_dev;
   size_t stage_bytes;

@@ -1,19 +1,25 @@
-// fuse.cuh -- warp-converged dual-volume ray march (float32).
+// fuse.cuh -- warp-converged dual-volume ray march (float32), v3.
 //
 // Same arithmetic as march_fast.cuh (exact voxel keys, tolerance-level tsdf /
-// weight), restructured so that the 32 rays of a warp run ONE converged
+// weight), structured so that the 32 rays of a warp run ONE converged
 // instruction stream:
-//   * warp-uniform trip count (max band length over the lanes), lanes that
-//     ran out of samples are predicated off -- no `continue`, no per-lane
-//     branches in the sample math;
-//   * the fold of a finished voxel (address, 128-bit vector reduction +
-//     64-bit counter reduction) is executed by the whole warp under a
-//     predicate whenever any lane leaves a voxel, instead of once per
-//     divergent lane group;
-//   * voxel-block slots come from a per-warp direct-mapped cache in shared
-//     memory; misses are de-duplicated with __match_any_sync so that one lane
-//     per distinct block probes / inserts into the global hash
-//     (warp-ballot allocation, one aggregated append to the block list).
+//   * the in-band sample range [i0, i1] of every ray is found ONCE with the
+//     reference's exact test (abs(sdf) > trunc, global_volume.py:66-67; the
+//     sdf sequence is monotone, so the band is contiguous) -- the loop itself
+//     carries no band test and no event counting;
+//   * warp-uniform trip count (longest band of the warp), finished lanes are
+//     predicated off;
+//   * the fold of a finished voxel (address, ONE 128-bit vector reduction +
+//     one 64-bit counter reduction) is executed by the whole warp under a
+//     predicate whenever any lane leaves a voxel;
+//   * voxel-block slots: bounded volumes read a dense block->slot directory
+//     (an L1/L2-resident cache of the block hash); unbounded volumes use a
+//     per-warp direct-mapped cache in shared memory.  Misses are
+//     de-duplicated with __match_any_sync so that one lane per distinct block
+//     probes / inserts into the global hash (warp-ballot allocation, one
+//     warp-aggregated append to the block list);
+//   * multi-GPU: rays whose band misses this rank's z-slabs are culled before
+//     the march; voxels of foreign slabs are dropped at the fold.
 // Reference semantics: TSDFVolume.integrate / _update_voxel
 // (mast3r_slam/tsdf/global_volume.py:53-88).
 #pragma once
@@ -23,7 +29,7 @@
 
 #define FUSE_CACHE_WAYS 32
 
-struct WarpCache { // one per warp, in shared memory
+struct WarpCache { // one per warp, in shared memory (unbounded volumes)
   unsigned long long key[FUSE_CACHE_WAYS];
   uint32_t slot[FUSE_CACHE_WAYS];
 };
@@ -40,8 +46,31 @@ __device__ __forceinline__ float ex2_ftz(float x) {
   return y;
 }
 
+// One lane per distinct missing block inserts into the hash; fresh slots are
+// appended to the block list with one aggregated atomicAdd.  `mm` = ballot of
+// the lanes that call this (all of them hold a valid `key`).
+__device__ __forceinline__ uint32_t alloc_blocks_warp(const VolumeDev &v, unsigned mm,
+                                                      unsigned long long key) {
+  const int lane = threadIdx.x & 31;
+  unsigned peers = __match_any_sync(mm, key);
+  int leader = __ffs(peers) - 1;
+  bool fresh = false;
+  uint32_t slot = B200_NO_SLOT;
+  if (lane == leader) slot = hash_insert(v, key, &fresh);
+  unsigned fm = __ballot_sync(mm, fresh);
+  if (fm) {
+    int first = __ffs(fm) - 1;
+    unsigned long long base = 0;
+    if (lane == first) base = atomicAdd(v.ctr + CTR_BLOCKS, (unsigned long long)__popc(fm));
+    base = __shfl_sync(mm, base, first);
+    if (fresh) v.list[base + __popc(fm & ((1u << lane) - 1))] = slot;
+  }
+  return __shfl_sync(peers, slot, leader);
+}
+
 // Converged fold: every lane runs this; only lanes with `pred` reduce.
-template <bool BOUNDED>
+// DIR: bounded volume with a block directory.
+template <bool BOUNDED, bool DIR>
 __device__ __forceinline__ void fold_warp(const VolumeDev &v, WarpCache &wc, bool pred, int kx,
                                           int ky, int kz, float su, float wu, uint32_t n,
                                           float conf, float conf_q, uint32_t cp, uint32_t cq,
@@ -51,69 +80,78 @@ __device__ __forceinline__ void fold_warp(const VolumeDev &v, WarpCache &wc, boo
     bool in = (uint32_t)(kx - v.kmin[0]) < (uint32_t)(v.kmax[0] - v.kmin[0]) &&
               (uint32_t)(ky - v.kmin[1]) < (uint32_t)(v.kmax[1] - v.kmin[1]) &&
               (uint32_t)(kz - v.kmin[2]) < (uint32_t)(v.kmax[2] - v.kmin[2]);
-    if (ok && !in) tl.dropped += n * (cp + cq);
+    if (v.slab_count > 1) in = in && slab_owns_z(v, kz);
+    if (ok && !in) {
+      tl.drop_p += n * cp;
+      tl.drop_q += n * cq;
+    }
     ok = ok && in;
   }
   const int bx = kx >> 3, by = ky >> 3, bz = kz >> 3;
-  const unsigned long long key = pack_block_key(bx, by, bz);
-  const int h = (bx + 3 * by + 5 * bz) & (FUSE_CACHE_WAYS - 1);
-  uint32_t slot = wc.slot[h];
-  bool miss = ok && (wc.key[h] != key);
-  unsigned mm = __ballot_sync(0xFFFFFFFFu, miss);
-  if (mm) { // rare once the warp's blocks are cached
-    if (miss) {
-      unsigned peers = __match_any_sync(mm, key);
-      int leader = __ffs(peers) - 1;
-      bool fresh = false;
-      if ((int)(threadIdx.x & 31) == leader) slot = hash_insert(v, key, &fresh);
-      // warp-aggregated append of the freshly allocated blocks
-      unsigned fm = __ballot_sync(mm, fresh);
-      if (fm) {
-        int first = __ffs(fm) - 1;
-        unsigned long long base = 0;
-        if ((int)(threadIdx.x & 31) == first)
-          base = atomicAdd(v.ctr + CTR_BLOCKS, (unsigned long long)__popc(fm));
-        base = __shfl_sync(mm, base, first);
-        if (fresh) v.list[base + __popc(fm & ((1u << (threadIdx.x & 31)) - 1))] = slot;
-      }
-      slot = __shfl_sync(peers, slot, leader);
-      unsigned same_way = __match_any_sync(mm, h); // one writer per cache way
-      if (slot == 0xFFFFFFFFu) {
-        tl.overflow += 1;
-        ok = false;
-      } else if ((int)(threadIdx.x & 31) == __ffs(same_way) - 1) {
-        wc.key[h] = key;
-        wc.slot[h] = slot;
+  uint32_t slot;
+  if (DIR) {
+    const int di = ((bz - v.dir_b0[2]) * v.dir_n[1] + (by - v.dir_b0[1])) * v.dir_n[0] +
+                   (bx - v.dir_b0[0]);
+    slot = ok ? v.dir[di] : 0u;
+    const bool miss = ok && slot == B200_NO_SLOT;
+    const unsigned mm = __ballot_sync(0xFFFFFFFFu, miss);
+    if (mm) { // only while the batch reaches fresh blocks
+      if (miss) {
+        slot = alloc_blocks_warp(v, mm, pack_block_key(bx, by, bz));
+        if (slot == B200_NO_SLOT) {
+          tl.overflow += 1;
+          ok = false;
+        } else {
+          v.dir[di] = slot; // every writer stores the same value
+        }
       }
     }
-    __syncwarp();
+  } else {
+    const unsigned long long key = pack_block_key(bx, by, bz);
+    const int h = (bx + 3 * by + 5 * bz) & (FUSE_CACHE_WAYS - 1);
+    slot = wc.slot[h];
+    const bool miss = ok && (wc.key[h] != key);
+    const unsigned mm = __ballot_sync(0xFFFFFFFFu, miss);
+    if (mm) { // rare once the warp's blocks are cached
+      if (miss) {
+        slot = alloc_blocks_warp(v, mm, key);
+        unsigned same_way = __match_any_sync(mm, h); // one writer per cache way
+        if (slot == B200_NO_SLOT) {
+          tl.overflow += 1;
+          ok = false;
+        } else if ((int)(threadIdx.x & 31) == __ffs(same_way) - 1) {
+          wc.key[h] = key;
+          wc.slot[h] = slot;
+        }
+      }
+      __syncwarp();
+    }
   }
-  const uint32_t li = ((kz & 7) << 6) | ((ky & 7) << 3) | (kx & 7);
-  const size_t off = (size_t)slot * B200_BLOCK_VOX + li;
   if (ok) {
+    const uint32_t li = ((kz & 7) << 6) | ((ky & 7) << 3) | (kx & 7);
+    const size_t off = (size_t)slot * B200_BLOCK_VOX + li;
     red_add_v4(v.vox + off, conf * su, conf * wu, conf_q * su, conf_q * wu);
-    red_add_u64(v.cnt + off, (unsigned long long)(n * cp) | ((unsigned long long)(n * cq) << 32));
+    red_add_u64(v.cnt + off, (unsigned long long)(cp ? n : 0u) |
+                                 ((unsigned long long)(cq ? n : 0u) << 32));
   }
 }
 
 // March the 32 rays of a warp in lockstep.  `have` = this lane holds a ray
 // (already counted in tl.rays by the caller).
-template <bool BOUNDED>
+template <bool BOUNDED, bool DIR>
 __device__ __forceinline__ void march_warp(const VolumeDev &v, WarpCache &wc, const MarchConst &mc,
                                            bool have, const Ray<float> &r, float conf,
                                            float conf_q, bool use_q, Tally &tl) {
-  const uint32_t cp = (have && conf > 0.0f) ? 1u : 0u; // :75  weight <= 0 -> return
-  const uint32_t cq = (have && use_q && conf_q > 0.0f) ? 1u : 0u;
-  const bool live = (cp | cq) != 0;
-  if (!cp) conf = 0.0f;
-  if (!cq) conf_q = 0.0f;
+  uint32_t cp = (have && conf > 0.0f) ? 1u : 0u; // :75  weight <= 0 -> return
+  uint32_t cq = (have && use_q && conf_q > 0.0f) ? 1u : 0u;
+  bool live = (cp | cq) != 0;
   // |s / vs| bound along the ray -> integer-proximity threshold of the fast
   // floor; rays whose keys could leave the +-2^23 voxel range of the block hash
-  // are dropped whole.  Bounded volumes: a ray whose band lies inside the
-  // bounds takes the launch-wide threshold and skips the per-voxel bound test.
+  // are skipped whole.  Bounded volumes: a ray whose band lies inside the
+  // bounds (and inside one owned slab) takes the launch-wide threshold and
+  // skips the per-voxel bound test.
   float lim;
-  bool far = false, check_bounds = false;
-  bool inside = false;
+  bool far = false, check_bounds = false, inside = false;
   if (BOUNDED) {
     float d0 = fmaxf(r.len - mc.trunc, 0.0f);
     float ax0 = fmaf(d0, r.dx, r.ox) * mc.inv_vs, ax1 = fmaf(r.maxd, r.dx, r.ox) * mc.inv_vs;
@@ -122,8 +160,28 @@ __device__ __forceinline__ void march_warp(const VolumeDev &v, WarpCache &wc, co
     inside = fminf(ax0, ax1) >= mc.blo[0] && fmaxf(ax0, ax1) < mc.bhi[0] &&
              fminf(ay0, ay1) >= mc.blo[1] && fmaxf(ay0, ay1) < mc.bhi[1] &&
              fminf(az0, az1) >= mc.blo[2] && fmaxf(az0, az1) < mc.bhi[2];
+    if (v.slab_count > 1 && live) {
+      float zl = fminf(az0, az1) - 2.0f, zh = fmaxf(az0, az1) + 2.0f;
+      bool any = true, all = false;
+      if (fabsf(zl) < 1.0e9f && fabsf(zh) < 1.0e9f) { // else: keep, per-voxel test decides
+        int s_lo = ((int)floorf(zl) - v.slab_z0) >> v.slab_shift;
+        int s_hi = ((int)floorf(zh) - v.slab_z0) >> v.slab_shift;
+        int need = v.slab_index - slab_owner_of(v, s_lo); // slabs to my first one at/after s_lo
+        if (need < 0) need += v.slab_count;
+        any = need <= s_hi - s_lo;
+        all = (s_hi == s_lo) && need == 0;
+      }
+      if (!any) { // the band misses every slab of this rank
+        live = false;
+        tl.culled += 1;
+      }
+      inside = inside && all;
+    }
     check_bounds = !__all_sync(0xFFFFFFFFu, inside || !live);
   }
+  if (!live) cp = cq = 0u;
+  if (!cp) conf = 0.0f;
+  if (!cq) conf_q = 0.0f;
   if (BOUNDED && inside) {
     lim = mc.lim_bounded;
   } else {
@@ -133,25 +191,39 @@ __device__ __forceinline__ void march_warp(const VolumeDev &v, WarpCache &wc, co
     lim = (qmax < 4.0e6f) ? 0.5f - qmax * 2.3841858e-7f : -1.0f; // 2^-22
     far = !(qmax < 8.0e6f);
   }
-  // first in-band sample: i_lo is conservative (ray.cuh), advance it exactly
-  int i = r.i_lo;
-  if (live && !far) {
-#pragma unroll 1
-    while (i < r.n - 1 && fabsf(__fsub_rn(r.len, __fmul_rn((float)i, r.lstep))) > mc.trunc) ++i;
-  }
-  const int cnt = (live && !far) ? (r.n - i) : 0;
-  const int J = __reduce_max_sync(0xFFFFFFFFu, cnt);
-  if (live && far) tl.dropped += 1;
-  const float MAGIC = 12582912.0f; // 1.5 * 2^23
+  if (live && far) tl.culled += 1;
+  // exact in-band range [i0, i1]: sdf_i = fl(len - dist_i) is non-increasing in
+  // i, so {i : !(abs(sdf_i) > trunc)} (global_volume.py:66-67) is contiguous.
   const float last_dist = (r.n == 1) ? 0.0f : r.maxd; // np.linspace endpoint / n == 1
+  int i0 = r.i_lo, cnt = 0;
+  if (live && !far) {
+    int i1 = r.n - 1;
+#pragma unroll 1
+    while (i0 < i1 && __fsub_rn(r.len, __fmul_rn((float)i0, r.lstep)) > mc.trunc) ++i0;
+    const float s_last = __fsub_rn(r.len, last_dist);
+    if (s_last < -mc.trunc) { // the endpoint itself fell out of the band by rounding
+      --i1;
+#pragma unroll 1
+      while (i1 > i0 && __fsub_rn(r.len, __fmul_rn((float)i1, r.lstep)) < -mc.trunc) --i1;
+    }
+    if (i1 >= i0) {
+      float sa = __fsub_rn(r.len, (i0 == r.n - 1) ? last_dist : __fmul_rn((float)i0, r.lstep));
+      float sb = __fsub_rn(r.len, (i1 == r.n - 1) ? last_dist : __fmul_rn((float)i1, r.lstep));
+      if (!(fabsf(sa) > mc.trunc) && !(fabsf(sb) > mc.trunc)) cnt = i1 - i0 + 1;
+    }
+  }
+  const int J = __reduce_max_sync(0xFFFFFFFFu, cnt);
+  const float MAGIC = 12582912.0f; // 1.5 * 2^23
+  const int i_end = r.n - 1;
   int ax = 0, ay = 0, az = 0;
   float su = 0.f, wu = 0.f;
-  uint32_t n = 0, total = 0;
-  float fi = (float)i;
+  uint32_t n = 0;
+  int i = i0;
+  float fi = (float)i0;
   for (int j = 0; j < J; ++j, ++i, fi += 1.0f) {
-    float dist = (i == r.n - 1) ? last_dist : __fmul_rn(fi, r.lstep);
+    const bool act = j < cnt;
+    float dist = (i == i_end) ? last_dist : __fmul_rn(fi, r.lstep);
     float sdf = __fsub_rn(r.len, dist);
-    const bool inb = (j < cnt) && !(fabsf(sdf) > mc.trunc); // :66-67
     float sx = __fadd_rn(r.ox, __fmul_rn(dist, r.dx));
     float sy = __fadd_rn(r.oy, __fmul_rn(dist, r.dy));
     float sz = __fadd_rn(r.oz, __fmul_rn(dist, r.dz));
@@ -163,7 +235,7 @@ __device__ __forceinline__ void march_warp(const VolumeDev &v, WarpCache &wc, co
     float ux = __fsub_rn(qx, __fsub_rn(yx, MAGIC)), uy = __fsub_rn(qy, __fsub_rn(yy, MAGIC)),
           uz = __fsub_rn(qz, __fsub_rn(yz, MAGIC));
     float m = fmaxf(fabsf(ux), fmaxf(fabsf(uy), fabsf(uz)));
-    const bool slow = inb && !(m < lim);
+    const bool slow = act && !(m < lim);
     if (__any_sync(0xFFFFFFFFu, slow)) {
       if (slow) { // the reference operation itself (:133-134)
         float fx = floorf(__fdiv_rn(sx, mc.vs)), fy = floorf(__fdiv_rn(sy, mc.vs)),
@@ -171,27 +243,27 @@ __device__ __forceinline__ void march_warp(const VolumeDev &v, WarpCache &wc, co
         kx = (int)fx, ky = (int)fy, kz = (int)fz;
       }
     }
-    const bool chg = inb && n != 0 && (kx != ax || ky != ay || kz != az);
+    const bool chg = act && n != 0 && (((kx ^ ax) | (ky ^ ay) | (kz ^ az)) != 0);
     if (__any_sync(0xFFFFFFFFu, chg)) {
-      fold_warp<BOUNDED>(v, wc, chg, ax, ay, az, su, wu, n, conf, conf_q, cp, cq, check_bounds,
-                         tl);
+      fold_warp<BOUNDED, DIR>(v, wc, chg, ax, ay, az, su, wu, n, conf, conf_q, cp, cq,
+                              check_bounds, tl);
       if (chg) {
         su = wu = 0.f;
         n = 0;
       }
     }
-    if (inb) {
+    if (act) {
       ax = kx, ay = ky, az = kz;
       float e = ex2_ftz(fabsf(sdf) * mc.nl2e_inv_trunc); // :69 exp(-|sdf| / trunc)
       su = fmaf(sdf * mc.inv_trunc, e, su);               // :68 (|t| <= 1 inside the band)
       wu += e;
       n += 1;
-      total += 1;
     }
   }
   const bool fin = n != 0;
   if (__any_sync(0xFFFFFFFFu, fin))
-    fold_warp<BOUNDED>(v, wc, fin, ax, ay, az, su, wu, n, conf, conf_q, cp, cq, check_bounds, tl);
-  tl.ev_p += total * cp;
-  tl.ev_q += total * cq;
+    fold_warp<BOUNDED, DIR>(v, wc, fin, ax, ay, az, su, wu, n, conf, conf_q, cp, cq,
+                            check_bounds, tl);
+  tl.ev_p += (uint32_t)cnt * cp;
+  tl.ev_q += (uint32_t)cnt * cq;
 }

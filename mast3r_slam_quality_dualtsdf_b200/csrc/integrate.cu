@@ -29,15 +29,16 @@ struct BlockCache {
 };
 
 __device__ __forceinline__ void flush_voxel(const VolumeDev &v, const Acc &a, BlockCache &bc,
-                                            uint32_t &dropped, uint32_t &overflow) {
+                                            uint32_t &ev_p, uint32_t &ev_q, uint32_t &dropped,
+                                            uint32_t &overflow) {
   if (!a.live) return;
-  if (v.bounded && (a.kx < v.kmin[0] || a.kx >= v.kmax[0] || a.ky < v.kmin[1] ||
-                    a.ky >= v.kmax[1] || a.kz < v.kmin[2] || a.kz >= v.kmax[2])) {
-    dropped += a.np + a.nq;
-    return;
-  }
+  const bool out =
+      (v.bounded && (a.kx < v.kmin[0] || a.kx >= v.kmax[0] || a.ky < v.kmin[1] ||
+                     a.ky >= v.kmax[1] || a.kz < v.kmin[2] || a.kz >= v.kmax[2])) ||
+      !slab_owns_z(v, a.kz);
   int bx = a.kx >> B200_BLOCK_LOG2, by = a.ky >> B200_BLOCK_LOG2, bz = a.kz >> B200_BLOCK_LOG2;
-  if (!block_in_range(bx, by, bz)) {
+  if (out || !block_in_range(bx, by, bz)) { // counters hold APPLIED updates
+    ev_p -= a.np, ev_q -= a.nq;
     dropped += a.np + a.nq;
     return;
   }
@@ -87,7 +88,7 @@ __device__ __forceinline__ void march_ray(const VolumeDev &v, const Ray<T> &r, T
     float e = expf((float)a); // global_volume.py:69 (f64 there; 1e-5 tolerance)
     float tf = (float)t;
     if (!acc.live || kx != acc.kx || ky != acc.ky || kz != acc.kz) {
-      flush_voxel(v, acc, bc, dropped, overflow);
+      flush_voxel(v, acc, bc, ev_p, ev_q, dropped, overflow);
       acc.live = true;
       acc.kx = kx, acc.ky = ky, acc.kz = kz;
       acc.sp = acc.wp = acc.sq = acc.wq = 0.f;
@@ -108,7 +109,7 @@ __device__ __forceinline__ void march_ray(const VolumeDev &v, const Ray<T> &r, T
       ev_q += 1;
     }
   }
-  flush_voxel(v, acc, bc, dropped, overflow);
+  flush_voxel(v, acc, bc, ev_p, ev_q, dropped, overflow);
 }
 
 __device__ __forceinline__ void commit_counters(const VolumeDev &v, uint32_t rays, uint32_t ev_p,
@@ -152,17 +153,17 @@ __global__ void __launch_bounds__(256)
   commit_counters(v, rays, ev_p, ev_q, dropped, overflow);
 }
 
-template <bool BOUNDED>
+template <bool BOUNDED, bool DIR>
 __global__ void __launch_bounds__(256)
     integrate_points_f32_kernel(VolumeDev v, const float *__restrict__ pts,
                                 const double *__restrict__ conf,
                                 const double *__restrict__ conf_q, float ox, float oy, float oz,
                                 long long m, float step, MarchConst mc) {
-  __shared__ WarpCache wcs[8];
-  WarpCache &wc = wcs[threadIdx.x >> 5];
-  warp_cache_init(wc);
+  __shared__ WarpCache wcs[DIR ? 1 : 8];
+  WarpCache &wc = wcs[DIR ? 0 : (threadIdx.x >> 5)];
+  if (!DIR) warp_cache_init(wc);
   long long p = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  Tally tl = {0, 0, 0, 0, 0};
+  Tally tl = {0, 0, 0, 0, 0, 0, 0};
   Ray<float> r = {};
   bool have = false;
   float c = 0.f, cq = 0.f;
@@ -175,7 +176,7 @@ __global__ void __launch_bounds__(256)
       cq = conf_q ? (float)conf_q[p] : 0.f;
     }
   }
-  march_warp<BOUNDED>(v, wc, mc, have, r, c, cq, conf_q != nullptr, tl);
+  march_warp<BOUNDED, DIR>(v, wc, mc, have, r, c, cq, conf_q != nullptr, tl);
   commit_tally(v, tl);
 }
 
@@ -200,7 +201,47 @@ __device__ __forceinline__ void sim3_act(const float *__restrict__ P, float x0, 
   y2 = __fadd_rn(__fmul_rn(a2, s), P[2]);
 }
 
-template <bool BOUNDED>
+// ---- keyframe staging: TMA bulk copies (cp.async.bulk -> UBLKCP) of the CTA's
+// 32 x 8 pixel tile into shared memory, completion on an mbarrier.
+__device__ __forceinline__ uint32_t smem_u32(const void *p) {
+  return (uint32_t)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void *src, uint32_t bytes,
+                                         uint32_t bar) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::
+          "r"(dst),
+      "l"(src), "r"(bytes), "r"(bar)
+      : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t phase) {
+  asm volatile(
+      "{\n"
+      ".reg .pred P1;\n"
+      "WAIT_LOOP:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n"
+      "@P1 bra WAIT_DONE;\n"
+      "bra WAIT_LOOP;\n"
+      "WAIT_DONE:\n"
+      "}\n" ::"r"(bar),
+      "r"(phase)
+      : "memory");
+}
+
+#define TILE_W 32
+#define TILE_H 8
+#define SX_ROW 104 // floats per staged X row: 96 + 8 pad (bank-conflict-free, 16 B multiple)
+#define SC_ROW 40  // floats per staged C row: 32 + 8 pad
+
+template <bool BOUNDED, bool DIR, bool TMA>
 __global__ void __launch_bounds__(256)
     integrate_keyframes_kernel(VolumeDev v, const float *__restrict__ X,
                                const float *__restrict__ C, const float *__restrict__ qg,
@@ -208,47 +249,84 @@ __global__ void __launch_bounds__(256)
                                float min_conf, float step, MarchConst mc) {
   // CTA = 32 x 8 pixel tile, warp = 8 x 4 sub-tile: rays of a warp stay close
   // in the volume, so their reductions share 32-byte sectors.
-  __shared__ WarpCache wcs[8];
+  __shared__ WarpCache wcs[DIR ? 1 : 8];
+  __shared__ __align__(128) float sX[TMA ? TILE_H * SX_ROW : 4];
+  __shared__ __align__(128) float sC[TMA ? TILE_H * SC_ROW : 4];
+  __shared__ __align__(8) unsigned long long s_bar;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  WarpCache &wc = wcs[warp];
-  warp_cache_init(wc);
+  WarpCache &wc = wcs[DIR ? 0 : warp];
   const int kf = blockIdx.z;
-  const int px = blockIdx.x * 32 + (warp & 3) * 8 + (lane & 7);
-  const int py = blockIdx.y * 8 + (warp >> 2) * 4 + (lane >> 3);
   const long long npix = (long long)H * W;
-  Tally tl = {0, 0, 0, 0, 0};
-  Ray<float> r = {};
-  bool have = false;
-  float c = 0.f, cq = 0.f;
-  if (px < W && py < H) {
-    const long long pix = (long long)py * W + px;
-    const float *P = poses + 8 * kf;
-    c = C[kf * npix + pix];
-    if (c > min_conf) { // global_manager.py:92
-      const float *x = X + (kf * npix + pix) * 3;
-      float wx, wy, wz;
-      sim3_act(P, x[0], x[1], x[2], wx, wy, wz);
-      have = ray_setup<float>(r, wx, wy, wz, P[0], P[1], P[2], step, mc.trunc);
-      if (have) {
-        tl.rays = 1;
-        float q = 1.0f;
-        if (qg) {
-          const int ch = H / gh, cw = W / gw; // uniform; power-of-two cells avoid the division
-          int gy = (ch & (ch - 1)) ? py / ch : py >> (31 - __clz(ch));
-          int gx = (cw & (cw - 1)) ? px / cw : px >> (31 - __clz(cw));
-          gy = min(gy, gh - 1), gx = min(gx, gw - 1);
-          q = qg[((long long)kf * gh + gy) * gw + gx];
-        }
-        cq = c * q;
+  const int tx = (warp & 3) * 8 + (lane & 7), ty = (warp >> 2) * 4 + (lane >> 3);
+  const int px = blockIdx.x * TILE_W + tx, py = blockIdx.y * TILE_H + ty;
+  if (TMA) { // host guarantees full tiles and 16-byte aligned rows
+    const uint32_t bar = smem_u32(&s_bar);
+    if (threadIdx.x == 0) {
+      mbar_init(bar, 1);
+      mbar_expect_tx(bar, TILE_H * (TILE_W * 12 + TILE_W * 4));
+      const long long p0 = kf * npix + (long long)(blockIdx.y * TILE_H) * W + blockIdx.x * TILE_W;
+#pragma unroll
+      for (int row = 0; row < TILE_H; ++row) {
+        bulk_g2s(smem_u32(sX + row * SX_ROW), X + (p0 + (long long)row * W) * 3, TILE_W * 12, bar);
+        bulk_g2s(smem_u32(sC + row * SC_ROW), C + p0 + (long long)row * W, TILE_W * 4, bar);
       }
     }
   }
-  march_warp<BOUNDED>(v, wc, mc, have, r, c, cq, true, tl);
+  if (!DIR) warp_cache_init(wc);
+  const float *P = poses + 8 * kf;
+  float q = 1.0f;
+  if (qg) { // nearest-neighbour upsample of the per-patch quality weight
+    int gy = mc.cell_h_shift >= 0 ? py >> mc.cell_h_shift : py / mc.cell_h;
+    int gx = mc.cell_w_shift >= 0 ? px >> mc.cell_w_shift : px / mc.cell_w;
+    gy = min(gy, gh - 1), gx = min(gx, gw - 1);
+    q = __ldg(qg + ((long long)kf * gh + gy) * gw + gx);
+  }
+  Tally tl = {0, 0, 0, 0, 0, 0, 0};
+  Ray<float> r = {};
+  bool have = false;
+  float c = 0.f, cq = 0.f, x0 = 0.f, x1 = 0.f, x2 = 0.f;
+  bool in_img = true;
+  if (TMA) {
+    __syncthreads(); // mbarrier init visible to the waiters
+    mbar_wait(smem_u32(&s_bar), 0);
+    c = sC[ty * SC_ROW + tx];
+    x0 = sX[ty * SX_ROW + tx * 3], x1 = sX[ty * SX_ROW + tx * 3 + 1],
+    x2 = sX[ty * SX_ROW + tx * 3 + 2];
+  } else {
+    in_img = px < W && py < H;
+    if (in_img) {
+      const long long pix = (long long)py * W + px;
+      c = C[kf * npix + pix];
+      if (c > min_conf) {
+        const float *x = X + (kf * npix + pix) * 3;
+        x0 = x[0], x1 = x[1], x2 = x[2];
+      }
+    }
+  }
+  if (in_img && c > min_conf) { // global_manager.py:92
+    float wx, wy, wz;
+    sim3_act(P, x0, x1, x2, wx, wy, wz);
+    have = ray_setup<float>(r, wx, wy, wz, P[0], P[1], P[2], step, mc.trunc);
+    if (have) {
+      tl.rays = 1;
+      cq = c * q;
+    }
+  }
+  march_warp<BOUNDED, DIR>(v, wc, mc, have, r, c, cq, true, tl);
   commit_tally(v, tl);
 }
 
 // ------------------------------------------------------------------ C ABI
-static MarchConst make_consts(const b200tsdf *h) {
+static int pow2_shift(int x) {
+  if (x <= 0 || (x & (x - 1))) return -1;
+  int s = 0;
+  while ((1 << s) < x) ++s;
+  return s;
+}
+
+static bool use_bounded(const b200tsdf *h) { return h->d.bounded || h->d.slab_count > 1; }
+
+static MarchConst make_consts(const b200tsdf *h, int cell_h = 1, int cell_w = 1) {
   MarchConst mc;
   mc.trunc = (float)h->cfg.truncation;
   mc.vs = (float)h->cfg.voxel_size;
@@ -262,8 +340,13 @@ static MarchConst make_consts(const b200tsdf *h) {
     qb = fmaxf(qb, fmaxf(fabsf((float)h->d.kmin[a]), fabsf((float)h->d.kmax[a])) + 2.0f);
   }
   mc.lim_bounded = (qb < 4.0e6f) ? 0.5f - qb * 2.3841858e-7f : -1.0f;
-  const char *e = getenv("B200TSDF_DEBUG");
-  mc.dbg = e ? atoi(e) : 0;
+  if (!h->d.bounded) // slabs on an unbounded volume: no ray is ever "inside"
+    mc.blo[0] = mc.blo[1] = mc.blo[2] = 3.0e38f;
+  mc.cell_h = cell_h > 0 ? cell_h : 1;
+  mc.cell_w = cell_w > 0 ? cell_w : 1;
+  mc.cell_h_shift = pow2_shift(mc.cell_h);
+  mc.cell_w_shift = pow2_shift(mc.cell_w);
+  mc.use_dir = h->d.dir_on;
   return mc;
 }
 
@@ -289,14 +372,18 @@ extern "C" int b200tsdf_integrate_points(b200tsdf_t *h, const void *pts_dev, int
     unsigned grid = (unsigned)((m + 255) / 256);
     if (dtype == B200TSDF_F32) {
       const float *o = (const float *)origin_host;
-      if (h->d.bounded)
-        integrate_points_f32_kernel<true><<<grid, 256, 0, st>>>(
-            h->d, (const float *)pts_dev, conf_dev, conf_q_dev, o[0], o[1], o[2], (long long)m,
-            (float)step_d, make_consts(h));
+      const MarchConst mc = make_consts(h);
+#define LAUNCH_PTS(BD, DR)                                                                     \
+  integrate_points_f32_kernel<BD, DR><<<grid, 256, 0, st>>>(                                    \
+      h->d, (const float *)pts_dev, conf_dev, conf_q_dev, o[0], o[1], o[2], (long long)m,       \
+      (float)step_d, mc)
+      if (!use_bounded(h))
+        LAUNCH_PTS(false, false);
+      else if (h->d.dir_on)
+        LAUNCH_PTS(true, true);
       else
-        integrate_points_f32_kernel<false><<<grid, 256, 0, st>>>(
-            h->d, (const float *)pts_dev, conf_dev, conf_q_dev, o[0], o[1], o[2], (long long)m,
-            (float)step_d, make_consts(h));
+        LAUNCH_PTS(true, false);
+#undef LAUNCH_PTS
     } else {
       const double *o = (const double *)origin_host;
       integrate_points_f64_kernel<<<grid, 256, 0, st>>>(
@@ -333,16 +420,26 @@ extern "C" int b200tsdf_integrate_keyframes(b200tsdf_t *h, const float *X_dev, c
   B200_CUDA(cudaSetDevice(h->cfg.device));
   double step_d = h->cfg.voxel_size * step_scale;
   if (step_d < 1.0e-4) step_d = 1.0e-4;
-  long long npix = (long long)H * W;
-  dim3 grid((unsigned)((W + 31) / 32), (unsigned)((H + 7) / 8), (unsigned)B);
-  if (h->d.bounded)
-    integrate_keyframes_kernel<true><<<grid, 256, 0, st>>>(
-        h->d, X_dev, C_dev, q_grid_dev, pose_dev, H, W, gh, gw, min_conf, (float)step_d,
-        make_consts(h));
-  else
-    integrate_keyframes_kernel<false><<<grid, 256, 0, st>>>(
-        h->d, X_dev, C_dev, q_grid_dev, pose_dev, H, W, gh, gw, min_conf, (float)step_d,
-        make_consts(h));
+  dim3 grid((unsigned)((W + TILE_W - 1) / TILE_W), (unsigned)((H + TILE_H - 1) / TILE_H),
+            (unsigned)B);
+  const MarchConst mc = q_grid_dev ? make_consts(h, H / gh, W / gw) : make_consts(h);
+  // TMA staging needs full tiles and 16-byte aligned row segments
+  const bool tma = (W % TILE_W == 0) && (H % TILE_H == 0) && (((uintptr_t)X_dev & 15) == 0) &&
+                   (((uintptr_t)C_dev & 15) == 0);
+#define LAUNCH_KF(BD, DR, TM)                                                                  \
+  integrate_keyframes_kernel<BD, DR, TM><<<grid, 256, 0, st>>>(                                 \
+      h->d, X_dev, C_dev, q_grid_dev, pose_dev, H, W, gh, gw, min_conf, (float)step_d, mc)
+  const int mode = !use_bounded(h) ? 0 : (h->d.dir_on ? 2 : 1);
+  if (tma) {
+    if (mode == 0) LAUNCH_KF(false, false, true);
+    else if (mode == 1) LAUNCH_KF(true, false, true);
+    else LAUNCH_KF(true, true, true);
+  } else {
+    if (mode == 0) LAUNCH_KF(false, false, false);
+    else if (mode == 1) LAUNCH_KF(true, false, false);
+    else LAUNCH_KF(true, true, false);
+  }
+#undef LAUNCH_KF
   B200_CUDA(cudaGetLastError());
   return B200TSDF_OK;
 }

@@ -69,8 +69,51 @@ extern "C" int b200tsdf_create(const b200tsdf_config *cfg, b200tsdf_t **out) {
     d.kmin[i] = clamp_i32(cfg->key_min[i]);
     d.kmax[i] = clamp_i32(cfg->key_max[i]);
   }
+  if (!cfg->bounded) // slabs on an unbounded volume run the bounded code path
+    for (int i = 0; i < 3; ++i) d.kmin[i] = -2000000000, d.kmax[i] = 2000000000;
   d.max_weight = (float)cfg->max_weight;
   d.min_weight = (float)cfg->min_weight;
+  // z-slab ownership
+  d.slab_count = cfg->slab_count > 1 ? cfg->slab_count : 1;
+  d.slab_index = cfg->slab_count > 1 ? cfg->slab_index : 0;
+  d.slab_z0 = cfg->bounded ? d.kmin[2] : 0;
+  d.slab_shift = 3;
+  if (d.slab_count > 1) {
+    int64_t w = cfg->slab_width;
+    if (w < 8 || (w & (w - 1)) != 0 || w > (1ll << 30) || cfg->slab_index < 0 ||
+        cfg->slab_index >= cfg->slab_count || (d.slab_z0 & 7) != 0) {
+      b200_set_error("b200tsdf_create: bad slab config (count %d index %d width %lld; width must "
+                     "be a power of two >= 8 and key_min[2] a multiple of 8)",
+                     cfg->slab_count, cfg->slab_index, (long long)cfg->slab_width);
+      b200tsdf_destroy(h);
+      return B200TSDF_E_INVALID;
+    }
+    d.slab_shift = 0;
+    while ((1ll << d.slab_shift) < w) d.slab_shift++;
+  }
+  // block directory for bounded volumes (<= 256 MB of u32 entries)
+  d.dir = nullptr;
+  d.dir_on = 0;
+  if (cfg->bounded) {
+    unsigned long long n = 1;
+    bool ok = true;
+    for (int i = 0; i < 3; ++i) {
+      if (d.kmax[i] <= d.kmin[i]) ok = false;
+      d.dir_b0[i] = d.kmin[i] >> 3;
+      d.dir_n[i] = ok ? ((d.kmax[i] - 1) >> 3) - d.dir_b0[i] + 1 : 0;
+      if (ok && (d.dir_n[i] <= 0 || d.dir_n[i] > 4096)) ok = false;
+      if (ok) n *= (unsigned long long)d.dir_n[i];
+    }
+    if (ok && n <= (1ull << 26)) {
+      h->dir_entries = n;
+      if (cudaMalloc(&d.dir, n * sizeof(uint32_t)) == cudaSuccess)
+        d.dir_on = 1;
+      else {
+        (void)cudaGetLastError();
+        d.dir = nullptr;
+      }
+    }
+  }
   int rc = b200tsdf_reset(h, nullptr);
   if (rc != 0) {
     b200tsdf_destroy(h);
@@ -89,6 +132,7 @@ extern "C" int b200tsdf_destroy(b200tsdf_t *h) {
   cudaFree(h->d.cnt);
   cudaFree(h->d.list);
   cudaFree(h->d.ctr);
+  cudaFree(h->d.dir);
   cudaFree(h->scratch);
   cudaFree(h->stage_dev);
   delete h;
@@ -103,16 +147,18 @@ extern "C" int b200tsdf_reset(b200tsdf_t *h, void *stream) {
   B200_CUDA(cudaMemsetAsync(h->d.vox, 0, h->cap * B200_BLOCK_VOX * sizeof(float4), st));
   B200_CUDA(cudaMemsetAsync(h->d.cnt, 0, h->cap * B200_BLOCK_VOX * sizeof(unsigned long long), st));
   B200_CUDA(cudaMemsetAsync(h->d.ctr, 0, CTR_COUNT * sizeof(unsigned long long), st));
+  if (h->d.dir_on)
+    B200_CUDA(cudaMemsetAsync(h->d.dir, 0xFF, h->dir_entries * sizeof(uint32_t), st));
   return B200TSDF_OK;
 }
 
-extern "C" int b200tsdf_counters(b200tsdf_t *h, int64_t out_host[6], void *stream) {
+extern "C" int b200tsdf_counters(b200tsdf_t *h, int64_t out_host[8], void *stream) {
   if (!h || !out_host) return B200TSDF_E_INVALID;
   cudaStream_t st = (cudaStream_t)stream;
   unsigned long long tmp[CTR_COUNT];
   B200_CUDA(cudaMemcpyAsync(tmp, h->d.ctr, sizeof(tmp), cudaMemcpyDeviceToHost, st));
   B200_CUDA(cudaStreamSynchronize(st));
-  for (int i = 0; i < 6; ++i) out_host[i] = (int64_t)tmp[i];
+  for (int i = 0; i < 8; ++i) out_host[i] = (int64_t)tmp[i];
   return B200TSDF_OK;
 }
 

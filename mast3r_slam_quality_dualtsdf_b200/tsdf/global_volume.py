@@ -33,6 +33,7 @@ class TSDFVolume:
         *,
         capacity_log2: int = 17,
         bounds=None,
+        slabs=None,
         device="cuda:0",
     ) -> None:
         self.voxel_size = float(voxel_size)
@@ -53,8 +54,11 @@ class TSDFVolume:
             for i in range(3):
                 cfg.key_min[i] = int(bounds[0][i])
                 cfg.key_max[i] = int(bounds[1][i])
+        if slabs is not None:  # (slab_count, slab_index, slab_width): interleaved z-slabs
+            cfg.slab_count, cfg.slab_index, cfg.slab_width = (int(x) for x in slabs)
         cfg.device = self.device.index or 0
         self.bounds = bounds
+        self.slabs = slabs
         self._h = C.c_void_p()
         _ffi.check(_ffi.lib().b200tsdf_create(C.byref(cfg), C.byref(self._h)), "b200tsdf_create")
 
@@ -186,11 +190,12 @@ class TSDFVolume:
         return {"valid_voxels": a.value, "total_voxels": b.value}
 
     def counters(self) -> Dict[str, int]:
-        out = (C.c_int64 * 6)()
+        out = (C.c_int64 * 8)()
         with self._lock:
             _ffi.check(_ffi.lib().b200tsdf_counters(self._h, out, _stream_ptr(self.device)),
                        "counters")
-        names = ["rays", "updates_primary", "updates_quality", "blocks", "dropped", "overflow"]
+        names = ["rays", "updates_primary", "updates_quality", "blocks", "dropped", "overflow",
+                 "culled_rays"]
         d = dict(zip(names, [int(x) for x in out]))
         if d["overflow"]:
             raise _ffi.B200TSDFError(

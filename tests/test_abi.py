@@ -24,12 +24,12 @@ def test_library_exports_every_declared_symbol(built_lib):
     for name in _declared():
         assert hasattr(L, name), f"{name} missing from libb200tsdf.so"
     L.b200tsdf_abi_version.restype = ctypes.c_int
-    assert L.b200tsdf_abi_version() == 1
+    assert L.b200tsdf_abi_version() == 2
 
 
 def test_config_struct_layout():
-    # must match b200tsdf_config in include/b200tsdf.h: 4 doubles, 2 i32, 6 i64, 2 i32
-    assert ctypes.sizeof(_ffi.Config) == 4 * 8 + 2 * 4 + 6 * 8 + 2 * 4
+    # must match b200tsdf_config in include/b200tsdf.h: 4 doubles, 2 i32, 6 i64, 2 i32, 2 i32, 1 i64
+    assert ctypes.sizeof(_ffi.Config) == 4 * 8 + 2 * 4 + 6 * 8 + 2 * 4 + 2 * 4 + 8
 
 
 def test_create_without_gpu_fails_loudly(built_lib):

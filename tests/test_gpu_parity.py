@@ -156,6 +156,44 @@ def test_bounds_drop_outside(cuda_device):
     assert_volume_matches(got, (keys, t, w, c), "z-slab union")
 
 
+@pytest.mark.parametrize("bounded", [True, False])
+@pytest.mark.parametrize("count,width", [(2, 8), (4, 8), (3, 16), (2, 64)])
+def test_interleaved_z_slabs_union_is_exact(cuda_device, bounded, count, width):
+    """every rank fuses only its own z-slabs; the union of the
+    per-rank voxel sets equals the single-volume result bit-exactly, applied
+    update counters add up, and rays whose band misses a rank are culled."""
+    kf = synth.make_keyframes(synth.SCENES["sphere"], 2, H=48, W=64, seed=4, f=50.0, total=8)
+    vp, vq, rays = oracle_dual(kf, 0.02, 0.08)
+    keys = vp.export()[0]
+    lo = (keys.min(0) // 8) * 8 - 8
+    hi = keys.max(0) + 9
+    bounds = (tuple(int(x) for x in lo), tuple(int(x) for x in hi)) if bounded else None
+    parts, partsq, ev_p, ev_q, culled = [], [], 0, 0, 0
+    for r in range(count):
+        vol = _vol(cuda_device, 0.02, 0.08, bounds=bounds, slabs=(count, r, width))
+        vol.integrate_keyframes(*(torch.from_numpy(kf[k]).to(cuda_device)
+                                  for k in ("X", "C", "pose")),
+                                torch.from_numpy(kf["q"]).to(cuda_device), 0.05, 48, 64)
+        c = vol.counters()
+        assert c["rays"] == rays
+        ev_p += c["updates_primary"]
+        ev_q += c["updates_quality"]
+        culled += c["culled_rays"]
+        parts.append(vol.export(0))
+        partsq.append(vol.export(1))
+        z0 = bounds[0][2] if bounded else 0
+        if len(parts[-1][0]):
+            assert np.all(((parts[-1][0][:, 2] - z0) // width) % count == r)
+    assert ev_p == vp.events and ev_q == vq.events
+    if width >= 64:
+        assert culled > 0
+    for ps, want in ((parts, vp), (partsq, vq)):
+        gk = np.concatenate([p[0] for p in ps])
+        order = np.lexsort((gk[:, 2], gk[:, 1], gk[:, 0]))
+        got = tuple(np.concatenate([p[i] for p in ps])[order] for i in range(4))
+        assert_volume_matches(got, want.export(), "interleaved z-slab union")
+
+
 @pytest.mark.parametrize("case", ["plane_v30_f32", "sphere_v30_f32", "sphere_v30_f64",
                                   "room_v10_f32", "plane_clamp_f32"])
 def test_against_reference_golden(cuda_device, case):
