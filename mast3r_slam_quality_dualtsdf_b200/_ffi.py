@@ -8,7 +8,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libb200tsdf.so")
+# B200TSDF_LIB: alternative build of the same library (kernel A/B experiments)
+LIB_PATH = os.environ.get("B200TSDF_LIB") or os.path.join(_HERE, "libb200tsdf.so")
 
 F32, F64 = 0, 1
 

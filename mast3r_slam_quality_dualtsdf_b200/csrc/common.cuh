@@ -32,13 +32,18 @@ enum {
   CTR_CULLED = 6, // rays skipped because their band misses this rank's slabs
   CTR_COUNT = 8
 };
+// Statistics counters are replicated CTR_COPIES times (one 64-byte line per
+// copy) and summed on read: a warp adds to copy (its global warp id mod
+// CTR_COPIES), so no L2 slice sees a hot address.  CTR_BLOCKS -- the block
+// allocation cursor -- lives in copy 0 only.
+#define CTR_COPIES 512
 
 struct VolumeDev {
   unsigned long long *keys;
   float4 *vox;
   unsigned long long *cnt;
   uint32_t *list;
-  unsigned long long *ctr; // CTR_COUNT counters
+  unsigned long long *ctr; // CTR_COPIES x CTR_COUNT counters (see CTR_COPIES)
   uint32_t cap_mask;
   int bounded;
   int kmin[3], kmax[3]; // voxel-key bounds (clamped to int32 range)
@@ -160,8 +165,19 @@ __device__ __forceinline__ bool voxel_view(const float4 &a, unsigned long long c
 }
 #endif
 
+#ifdef __CUDACC__
+// This warp's replica of the statistics counters.
+__device__ __forceinline__ unsigned long long *ctr_replica(const VolumeDev &v) {
+  unsigned b = (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
+  unsigned w = b * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  return v.ctr + (size_t)(w & (CTR_COPIES - 1)) * CTR_COUNT;
+}
+#endif
+
 // ---------------------------------------------------------------- errors
 void b200_set_error(const char *fmt, ...);
+// Sum of the counter replicas (synchronises the stream).
+int b200_read_counters(struct b200tsdf *h, cudaStream_t st, unsigned long long out[CTR_COUNT]);
 #define B200_CUDA(call)                                                          \
   do {                                                                           \
     cudaError_t e__ = (call);                                                    \

@@ -28,6 +28,15 @@
 #include "ray.cuh"
 
 #define FUSE_CACHE_WAYS 32
+#ifndef FUSE_SLOT_REUSE
+#define FUSE_SLOT_REUSE 1
+#endif
+#ifndef FUSE_EX2_EARLY
+#define FUSE_EX2_EARLY 1
+#endif
+#ifndef FUSE_MINB
+#define FUSE_MINB 4
+#endif
 
 struct WarpCache { // one per warp, in shared memory (unbounded volumes)
   unsigned long long key[FUSE_CACHE_WAYS];
@@ -74,7 +83,8 @@ template <bool BOUNDED, bool DIR>
 __device__ __forceinline__ void fold_warp(const VolumeDev &v, WarpCache &wc, bool pred, int kx,
                                           int ky, int kz, float su, float wu, uint32_t n,
                                           float conf, float conf_q, uint32_t cp, uint32_t cq,
-                                          bool check_bounds, Tally &tl) {
+                                          bool check_bounds, Tally &tl, int &cdi,
+                                          uint32_t &cslot) {
   bool ok = pred;
   if (BOUNDED && check_bounds) {
     bool in = (uint32_t)(kx - v.kmin[0]) < (uint32_t)(v.kmax[0] - v.kmin[0]) &&
@@ -92,7 +102,14 @@ __device__ __forceinline__ void fold_warp(const VolumeDev &v, WarpCache &wc, boo
   if (DIR) {
     const int di = ((bz - v.dir_b0[2]) * v.dir_n[1] + (by - v.dir_b0[1])) * v.dir_n[0] +
                    (bx - v.dir_b0[0]);
+#if FUSE_SLOT_REUSE
+    // consecutive voxels of a ray mostly share a block: re-read the directory
+    // only when the lane's block changed
+    slot = (ok && di != cdi) ? v.dir[di] : cslot;
+    if (ok) cdi = di;
+#else
     slot = ok ? v.dir[di] : 0u;
+#endif
     const bool miss = ok && slot == B200_NO_SLOT;
     const unsigned mm = __ballot_sync(0xFFFFFFFFu, miss);
     if (mm) { // only while the batch reaches fresh blocks
@@ -106,6 +123,10 @@ __device__ __forceinline__ void fold_warp(const VolumeDev &v, WarpCache &wc, boo
         }
       }
     }
+#if FUSE_SLOT_REUSE
+    if (ok) cslot = slot;
+    else if (di == cdi) cdi = -1;
+#endif
   } else {
     const unsigned long long key = pack_block_key(bx, by, bz);
     const int h = (bx + 3 * by + 5 * bz) & (FUSE_CACHE_WAYS - 1);
@@ -130,9 +151,13 @@ __device__ __forceinline__ void fold_warp(const VolumeDev &v, WarpCache &wc, boo
   if (ok) {
     const uint32_t li = ((kz & 7) << 6) | ((ky & 7) << 3) | (kx & 7);
     const size_t off = (size_t)slot * B200_BLOCK_VOX + li;
+#ifndef FUSE_DBG_NO_VOXRED
     red_add_v4(v.vox + off, conf * su, conf * wu, conf_q * su, conf_q * wu);
+#endif
+#ifndef FUSE_DBG_NO_CNTRED
     red_add_u64(v.cnt + off, (unsigned long long)(cp ? n : 0u) |
                                  ((unsigned long long)(cq ? n : 0u) << 32));
+#endif
   }
 }
 
@@ -218,12 +243,16 @@ __device__ __forceinline__ void march_warp(const VolumeDev &v, WarpCache &wc, co
   int ax = 0, ay = 0, az = 0;
   float su = 0.f, wu = 0.f;
   uint32_t n = 0;
-  int i = i0;
+  int i = i0, cdi = -1;
+  uint32_t cslot = 0;
   float fi = (float)i0;
   for (int j = 0; j < J; ++j, ++i, fi += 1.0f) {
     const bool act = j < cnt;
     float dist = (i == i_end) ? last_dist : __fmul_rn(fi, r.lstep);
     float sdf = __fsub_rn(r.len, dist);
+#if FUSE_EX2_EARLY
+    const float e = ex2_ftz(fabsf(sdf) * mc.nl2e_inv_trunc); // :69 exp(-|sdf| / trunc)
+#endif
     float sx = __fadd_rn(r.ox, __fmul_rn(dist, r.dx));
     float sy = __fadd_rn(r.oy, __fmul_rn(dist, r.dy));
     float sz = __fadd_rn(r.oz, __fmul_rn(dist, r.dz));
@@ -246,7 +275,7 @@ __device__ __forceinline__ void march_warp(const VolumeDev &v, WarpCache &wc, co
     const bool chg = act && n != 0 && (((kx ^ ax) | (ky ^ ay) | (kz ^ az)) != 0);
     if (__any_sync(0xFFFFFFFFu, chg)) {
       fold_warp<BOUNDED, DIR>(v, wc, chg, ax, ay, az, su, wu, n, conf, conf_q, cp, cq,
-                              check_bounds, tl);
+                              check_bounds, tl, cdi, cslot);
       if (chg) {
         su = wu = 0.f;
         n = 0;
@@ -254,7 +283,9 @@ __device__ __forceinline__ void march_warp(const VolumeDev &v, WarpCache &wc, co
     }
     if (act) {
       ax = kx, ay = ky, az = kz;
-      float e = ex2_ftz(fabsf(sdf) * mc.nl2e_inv_trunc); // :69 exp(-|sdf| / trunc)
+#if !FUSE_EX2_EARLY
+      const float e = ex2_ftz(fabsf(sdf) * mc.nl2e_inv_trunc); // :69 exp(-|sdf| / trunc)
+#endif
       su = fmaf(sdf * mc.inv_trunc, e, su);               // :68 (|t| <= 1 inside the band)
       wu += e;
       n += 1;
@@ -263,7 +294,7 @@ __device__ __forceinline__ void march_warp(const VolumeDev &v, WarpCache &wc, co
   const bool fin = n != 0;
   if (__any_sync(0xFFFFFFFFu, fin))
     fold_warp<BOUNDED, DIR>(v, wc, fin, ax, ay, az, su, wu, n, conf, conf_q, cp, cq,
-                            check_bounds, tl);
+                            check_bounds, tl, cdi, cslot);
   tl.ev_p += (uint32_t)cnt * cp;
   tl.ev_q += (uint32_t)cnt * cq;
 }

@@ -121,11 +121,12 @@ __device__ __forceinline__ void commit_counters(const VolumeDev &v, uint32_t ray
   dropped = __reduce_add_sync(0xFFFFFFFFu, dropped);
   overflow = __reduce_add_sync(0xFFFFFFFFu, overflow);
   if ((threadIdx.x & 31) == 0) {
-    if (rays) atomicAdd(v.ctr + CTR_RAYS, (unsigned long long)rays);
-    if (ev_p) atomicAdd(v.ctr + CTR_EV_P, (unsigned long long)ev_p);
-    if (ev_q) atomicAdd(v.ctr + CTR_EV_Q, (unsigned long long)ev_q);
-    if (dropped) atomicAdd(v.ctr + CTR_DROPPED, (unsigned long long)dropped);
-    if (overflow) atomicAdd(v.ctr + CTR_OVERFLOW, (unsigned long long)overflow);
+    unsigned long long *ctr = ctr_replica(v);
+    if (rays) atomicAdd(ctr + CTR_RAYS, (unsigned long long)rays);
+    if (ev_p) atomicAdd(ctr + CTR_EV_P, (unsigned long long)ev_p);
+    if (ev_q) atomicAdd(ctr + CTR_EV_Q, (unsigned long long)ev_q);
+    if (dropped) atomicAdd(ctr + CTR_DROPPED, (unsigned long long)dropped);
+    if (overflow) atomicAdd(ctr + CTR_OVERFLOW, (unsigned long long)overflow);
   }
 }
 
@@ -242,7 +243,7 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t phase) {
 #define SC_ROW 40  // floats per staged C row: 32 + 8 pad
 
 template <bool BOUNDED, bool DIR, bool TMA>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, FUSE_MINB)
     integrate_keyframes_kernel(VolumeDev v, const float *__restrict__ X,
                                const float *__restrict__ C, const float *__restrict__ qg,
                                const float *__restrict__ poses, int H, int W, int gh, int gw,
@@ -363,8 +364,10 @@ extern "C" int b200tsdf_integrate_points(b200tsdf_t *h, const void *pts_dev, int
   B200_CUDA(cudaSetDevice(h->cfg.device));
   unsigned long long before = 0;
   if (rays_fused_host) {
-    B200_CUDA(cudaMemcpyAsync(&before, h->d.ctr + CTR_RAYS, 8, cudaMemcpyDeviceToHost, st));
-    B200_CUDA(cudaStreamSynchronize(st));
+    unsigned long long c[CTR_COUNT];
+    int rc = b200_read_counters(h, st, c);
+    if (rc) return rc;
+    before = c[CTR_RAYS];
   }
   if (m > 0) {
     double step_d = h->cfg.voxel_size * step_scale; // global_volume.py:46
@@ -394,8 +397,10 @@ extern "C" int b200tsdf_integrate_points(b200tsdf_t *h, const void *pts_dev, int
   }
   if (rays_fused_host) {
     unsigned long long after = 0;
-    B200_CUDA(cudaMemcpyAsync(&after, h->d.ctr + CTR_RAYS, 8, cudaMemcpyDeviceToHost, st));
-    B200_CUDA(cudaStreamSynchronize(st));
+    unsigned long long c[CTR_COUNT];
+    int rc = b200_read_counters(h, st, c);
+    if (rc) return rc;
+    after = c[CTR_RAYS];
     *rays_fused_host = (int64_t)(after - before);
   }
   return B200TSDF_OK;

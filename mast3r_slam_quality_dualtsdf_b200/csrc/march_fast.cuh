@@ -37,12 +37,18 @@ __device__ __forceinline__ void commit_tally(const VolumeDev &v, Tally tl) {
   uint32_t dropped = __reduce_add_sync(0xFFFFFFFFu, tl.drop_p + tl.drop_q);
   tl.overflow = __reduce_add_sync(0xFFFFFFFFu, tl.overflow);
   tl.culled = __reduce_add_sync(0xFFFFFFFFu, tl.culled);
-  if ((threadIdx.x & 31) == 0) {
-    if (tl.rays) atomicAdd(v.ctr + CTR_RAYS, (unsigned long long)tl.rays);
-    if (tl.ev_p) atomicAdd(v.ctr + CTR_EV_P, (unsigned long long)tl.ev_p);
-    if (tl.ev_q) atomicAdd(v.ctr + CTR_EV_Q, (unsigned long long)tl.ev_q);
-    if (dropped) atomicAdd(v.ctr + CTR_DROPPED, (unsigned long long)dropped);
-    if (tl.overflow) atomicAdd(v.ctr + CTR_OVERFLOW, (unsigned long long)tl.overflow);
-    if (tl.culled) atomicAdd(v.ctr + CTR_CULLED, (unsigned long long)tl.culled);
+#ifdef FUSE_DBG_NO_TALLY
+  if (tl.rays == 0xFFFFFFFFu)
+#else
+  if ((threadIdx.x & 31) == 0)
+#endif
+  {
+    unsigned long long *ctr = ctr_replica(v);
+    if (tl.rays) atomicAdd(ctr + CTR_RAYS, (unsigned long long)tl.rays);
+    if (tl.ev_p) atomicAdd(ctr + CTR_EV_P, (unsigned long long)tl.ev_p);
+    if (tl.ev_q) atomicAdd(ctr + CTR_EV_Q, (unsigned long long)tl.ev_q);
+    if (dropped) atomicAdd(ctr + CTR_DROPPED, (unsigned long long)dropped);
+    if (tl.overflow) atomicAdd(ctr + CTR_OVERFLOW, (unsigned long long)tl.overflow);
+    if (tl.culled) atomicAdd(ctr + CTR_CULLED, (unsigned long long)tl.culled);
   }
 }

@@ -55,7 +55,7 @@ extern "C" int b200tsdf_create(const b200tsdf_config *cfg, b200tsdf_t **out) {
   if (e == cudaSuccess) e = cudaMalloc(&d.vox, h->cap * B200_BLOCK_VOX * sizeof(float4));
   if (e == cudaSuccess) e = cudaMalloc(&d.cnt, h->cap * B200_BLOCK_VOX * sizeof(unsigned long long));
   if (e == cudaSuccess) e = cudaMalloc(&d.list, h->cap * sizeof(uint32_t));
-  if (e == cudaSuccess) e = cudaMalloc(&d.ctr, CTR_COUNT * sizeof(unsigned long long));
+  if (e == cudaSuccess) e = cudaMalloc(&d.ctr, CTR_COPIES * CTR_COUNT * sizeof(unsigned long long));
   if (e == cudaSuccess) e = cudaMalloc(&h->scratch, 64 * sizeof(unsigned long long));
   if (e != cudaSuccess) {
     b200_set_error("b200tsdf_create: cudaMalloc failed for 2^%d blocks (%s)", cfg->capacity_log2,
@@ -146,7 +146,7 @@ extern "C" int b200tsdf_reset(b200tsdf_t *h, void *stream) {
   B200_CUDA(cudaMemsetAsync(h->d.keys, 0xFF, h->cap * sizeof(unsigned long long), st));
   B200_CUDA(cudaMemsetAsync(h->d.vox, 0, h->cap * B200_BLOCK_VOX * sizeof(float4), st));
   B200_CUDA(cudaMemsetAsync(h->d.cnt, 0, h->cap * B200_BLOCK_VOX * sizeof(unsigned long long), st));
-  B200_CUDA(cudaMemsetAsync(h->d.ctr, 0, CTR_COUNT * sizeof(unsigned long long), st));
+  B200_CUDA(cudaMemsetAsync(h->d.ctr, 0, CTR_COPIES * CTR_COUNT * sizeof(unsigned long long), st));
   if (h->d.dir_on)
     B200_CUDA(cudaMemsetAsync(h->d.dir, 0xFF, h->dir_entries * sizeof(uint32_t), st));
   return B200TSDF_OK;
@@ -156,9 +156,39 @@ extern "C" int b200tsdf_counters(b200tsdf_t *h, int64_t out_host[8], void *strea
   if (!h || !out_host) return B200TSDF_E_INVALID;
   cudaStream_t st = (cudaStream_t)stream;
   unsigned long long tmp[CTR_COUNT];
-  B200_CUDA(cudaMemcpyAsync(tmp, h->d.ctr, sizeof(tmp), cudaMemcpyDeviceToHost, st));
-  B200_CUDA(cudaStreamSynchronize(st));
+  int rc = b200_read_counters(h, st, tmp);
+  if (rc) return rc;
   for (int i = 0; i < 8; ++i) out_host[i] = (int64_t)tmp[i];
+  return B200TSDF_OK;
+}
+
+// Sum of the counter replicas: one CTA, thread c holds replica c.
+__global__ void __launch_bounds__(CTR_COPIES)
+    sum_counters_kernel(const unsigned long long *__restrict__ ctr, unsigned long long *out) {
+  __shared__ unsigned long long part[CTR_COPIES / 32][CTR_COUNT];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int i = 0; i < CTR_COUNT; ++i) {
+    unsigned long long x = ctr[(size_t)threadIdx.x * CTR_COUNT + i];
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) x += __shfl_down_sync(0xFFFFFFFFu, x, d);
+    if (lane == 0) part[warp][i] = x;
+  }
+  __syncthreads();
+  if (threadIdx.x < CTR_COUNT) {
+    unsigned long long t = 0;
+    for (int w = 0; w < CTR_COPIES / 32; ++w) t += part[w][threadIdx.x];
+    out[threadIdx.x] = t;
+  }
+}
+
+int b200_read_counters(b200tsdf *h, cudaStream_t st, unsigned long long out[CTR_COUNT]) {
+  B200_CUDA(cudaSetDevice(h->cfg.device));
+  sum_counters_kernel<<<1, CTR_COPIES, 0, st>>>(h->d.ctr, h->scratch + 16);
+  B200_CUDA(cudaGetLastError());
+  B200_CUDA(cudaMemcpyAsync(out, h->scratch + 16, CTR_COUNT * sizeof(unsigned long long),
+                            cudaMemcpyDeviceToHost, st));
+  B200_CUDA(cudaStreamSynchronize(st));
   return B200TSDF_OK;
 }
 
