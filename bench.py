@@ -56,56 +56,66 @@ def scene_for(n_gpus):
     return {"kind": "room", "half": 2.4874}, 1024, 1.2
 
 
-def gen_batch(scene, orbit_r, step_idx, kf_per_step, seed=0):
+SLAB_WIDTH = 32  # voxel layers per interleaved z-slab (N > 1): 16 cm at 5 mm
+
+
+def gen_batch(scene, orbit_r, step_idx, kf_per_step, seed=0, up_axis="y"):
     from mast3r_slam_quality_dualtsdf_b200 import synth
 
     start = (step_idx * kf_per_step) % ORBIT_TOTAL
     return synth.make_keyframes(scene, kf_per_step, H, W, seed=seed, orbit_radius=orbit_r,
-                                gh=GH, gw=GW, start=start, total=ORBIT_TOTAL)
+                                gh=GH, gw=GW, start=start, total=ORBIT_TOTAL, up_axis=up_axis)
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled during the timed region."""
-
-    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,"
-         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
-         "clocks_event_reasons.sw_power_cap")
+    """SM clock / throttle reasons sampled DURING the timed region.  The region
+    lasts milliseconds, so NVML is polled from a thread (~1 kHz); nvidia-smi
+    -lms 100 would return no sample at all."""
 
     def __init__(self, index=0):
-        self.p = None
+        self.sm, self.mx, self.reasons = [], None, set()
+        self.stop_flag = threading.Event()
+        self.err = None
         try:
-            self.p = subprocess.Popen(
-                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                 "-lms", "100", "-i", str(index)], stdout=subprocess.PIPE,
-                stderr=subprocess.DEVNULL, text=True)
-        except Exception:
-            self.p = None
+            import pynvml as nv
+
+            nv.nvmlInit()
+            self.nv = nv
+            self.h = nv.nvmlDeviceGetHandleByIndex(index)
+            self.mx = float(nv.nvmlDeviceGetMaxClockInfo(self.h, nv.NVML_CLOCK_SM))
+            self.t = threading.Thread(target=self._run, daemon=True)
+            self.t.start()
+        except Exception as e:  # noqa: BLE001
+            self.err = f"nvml unavailable: {e}"
+            self.t = None
+
+    def _poll(self):
+        nv = self.nv
+        self.sm.append(float(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)))
+        r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h) \
+            if hasattr(nv, "nvmlDeviceGetCurrentClocksEventReasons") \
+            else nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+        for name, bit in (("hw_slowdown", 0x8), ("sw_power_cap", 0x4),
+                          ("hw_thermal_slowdown", 0x40), ("sw_thermal_slowdown", 0x20)):
+            if r & bit:
+                self.reasons.add(name)
+
+    def _run(self):
+        while not self.stop_flag.is_set():
+            try:
+                self._poll()
+            except Exception as e:  # noqa: BLE001
+                self.err = str(e)
+                return
+            time.sleep(0.0005)
 
     def stop(self):
-        if self.p is None:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        self.p.terminate()
-        try:
-            out = self.p.communicate(timeout=5)[0]
-        except Exception:
-            out = ""
-        sm, mx, reasons = [], [], set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for line in out.strip().splitlines():
-            f = [x.strip() for x in line.split(",")]
-            if len(f) < 6:
-                continue
-            try:
-                sm.append(float(f[0]))
-                mx.append(float(f[1]))
-            except ValueError:
-                continue
-            for n, v in zip(names, f[2:6]):
-                if v.lower().startswith("active"):
-                    reasons.add(n)
-        return {"sm_mhz": float(np.median(sm)) if sm else None,
-                "sm_max_mhz": float(max(mx)) if mx else None, "reasons": sorted(reasons),
-                "samples": len(sm)}
+        if self.t is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [self.err], "samples": 0}
+        self.stop_flag.set()
+        self.t.join(timeout=2)
+        return {"sm_mhz": float(np.median(self.sm)) if self.sm else None, "sm_max_mhz": self.mx,
+                "reasons": sorted(self.reasons), "samples": len(self.sm)}
 
 
 # ---------------------------------------------------------------- CPU legs
@@ -151,7 +161,7 @@ def run_reference(args):
     threads = 2 if (os.cpu_count() or 1) >= 2 else 1
     ev_total, t_total = 0, 0.0
     for s in range(args.warmup + args.steps):
-        kf = gen_batch(scene, orbit_r, s, sample_kf)
+        kf = gen_batch(scene, orbit_r, s, sample_kf, up_axis="z" if args.gpus > 1 else "y")
         ev, dt = cpu_fuse(kf, range(sample_kf), threads)
         if s >= args.warmup:
             ev_total += ev
@@ -182,7 +192,8 @@ def workload_config(n_gpus, dim, kf_per_step):
                      f"(primary + quality-weighted), {dim}^3 @ 5 mm, trunc 20 mm"),
         "keyframes_per_step": kf_per_step, "volume_dim": dim, "voxel_size": VOXEL,
         "truncation": TRUNC, "orbit_keyframes": ORBIT_TOTAL,
-        "partition": "single volume" if n_gpus == 1 else f"{n_gpus} z-slabs, NCCL keyframe broadcast",
+        "partition": "single volume" if n_gpus == 1 else
+        f"interleaved z-slabs of {SLAB_WIDTH} voxel layers over {n_gpus} ranks, NCCL keyframe broadcast",
         "l2": "each step reads a fresh keyframe batch larger than L2 (157 MB > 126 MB)",
     }
 
@@ -209,12 +220,14 @@ def run_b200(args):
     n_gpus = world
     scene, dim, orbit_r = scene_for(n_gpus)
     lo, hi = synth.bounds_for(scene, VOXEL, dim)
-    slab = dim // world
-    z0, z1 = lo[2] + rank * slab, (hi[2] if rank == world - 1 else lo[2] + (rank + 1) * slab)
-    bounds = ((lo[0], lo[1], z0), (hi[0], hi[1], z1))
+    # N > 1: interleaved z-slabs (slab s -> rank s mod N); z is the vertical axis of the
+    # orbit so the slabs cut every view (DESIGN.md "Multi-GPU")
+    bounds = (lo, hi)
+    slabs = (world, rank, SLAB_WIDTH) if world > 1 else None
+    up_axis = "z" if world > 1 else "y"
     cap = 18 if world == 1 else 19
-    vol = TSDFVolume(VOXEL, TRUNC, capacity_log2=cap, bounds=bounds, device=dev)
-    scratch = TSDFVolume(VOXEL, TRUNC, capacity_log2=16, bounds=bounds, device=dev)
+    vol = TSDFVolume(VOXEL, TRUNC, capacity_log2=cap, bounds=bounds, slabs=slabs, device=dev)
+    scratch = TSDFVolume(VOXEL, TRUNC, capacity_log2=16, bounds=bounds, slabs=slabs, device=dev)
     B = args.kf_per_step
     n_steps = args.warmup + args.steps
     names = ("X", "C", "q", "pose")
@@ -224,7 +237,7 @@ def run_b200(args):
     host = []
     if rank == 0:
         for s in range(n_steps):
-            kf = gen_batch(scene, orbit_r, s, B)
+            kf = gen_batch(scene, orbit_r, s, B, up_axis=up_axis)
             host.append({k: torch.from_numpy(kf[k]).pin_memory() for k in names})
 
     def fuse(v, t):

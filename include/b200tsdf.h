@@ -167,6 +167,23 @@ int b200tsdf_export_blocks(b200tsdf_t *h, int64_t *bkeys_dev, int64_t cap,
 int b200tsdf_extract_mesh(b200tsdf_t *h, int which, float *verts_dev,
                           int64_t tri_cap, int64_t *n_tris_host, void *stream);
 
+/* ---- multi-GPU seams (no reference counterpart) ---------------
+ * Marching cubes over the top voxel layer of a z-slab needs the first layer of
+ * the slab above, which another rank owns.  export_seam_blocks dumps the voxel
+ * blocks of the first block layer of every slab this handle owns (two-call
+ * protocol: cap = 0 returns the count): bkeys n x 3 int64 block coordinates,
+ * vox n x 512 x 4 float32 packed voxels {S_p, W_p, S_q, W_q}, cnt n x 512
+ * uint64 hit counters.  The rank that owns the slabs below passes them to
+ * import_halo_blocks: the blocks become read-only neighbours for
+ * b200tsdf_extract_mesh (found through the block hash) but are never fused
+ * into, meshed, counted or exported by this handle.  Re-importing overwrites. */
+int b200tsdf_export_seam_blocks(b200tsdf_t *h, int64_t *bkeys_dev, float *vox_dev,
+                                uint64_t *cnt_dev, int64_t cap, int64_t *n_host,
+                                void *stream);
+int b200tsdf_import_halo_blocks(b200tsdf_t *h, const int64_t *bkeys_dev,
+                                const float *vox_dev, const uint64_t *cnt_dev,
+                                int64_t n, void *stream);
+
 /* ---- local (per-ROI, dense) TSDF of the refiner: stateless calls ---------- */
 
 /* Replaces the config keys read by TSDFRefiner (mast3r_slam/tsdf_refine.py

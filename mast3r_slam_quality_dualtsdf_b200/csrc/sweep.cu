@@ -220,3 +220,108 @@ extern "C" int b200tsdf_query(b200tsdf_t *h, int which, const void *pts_dev, int
   B200_CUDA(cudaGetLastError());
   return B200TSDF_OK;
 }
+
+// ------------------------------------------------------- multi-GPU seams
+// Marching cubes needs, for the top voxel layer of every z-slab, the first
+// voxel layer of the slab above -- owned by another rank.  The
+// owner exports the voxel blocks of the FIRST block layer of each of its slabs
+// (export_seam_blocks); the rank below imports them as read-only halo blocks:
+// present in the hash (so mc_kernel finds them as +z neighbours) but not in
+// the block list (so no sweep meshes, counts or exports them).
+__device__ __forceinline__ bool is_seam_block(const VolumeDev &v, int bz) {
+  return v.slab_count > 1 && (((bz * 8 - v.slab_z0) & ((1 << v.slab_shift) - 1)) == 0);
+}
+
+__global__ void __launch_bounds__(128)
+    export_seam_kernel(VolumeDev v, long long *bkeys, float4 *vox, unsigned long long *cnt,
+                       long long cap, unsigned long long *n_out) {
+  __shared__ long long s_idx;
+  const uint32_t nb = (uint32_t)v.ctr[CTR_BLOCKS];
+  for (uint32_t b = blockIdx.x; b < nb; b += gridDim.x) {
+    const uint32_t slot = v.list[b];
+    int bx, by, bz;
+    unpack_block_key(v.keys[slot], bx, by, bz);
+    if (!is_seam_block(v, bz)) continue; // uniform per CTA
+    __syncthreads();
+    if (threadIdx.x == 0) s_idx = (long long)atomicAdd(n_out, 1ull);
+    __syncthreads();
+    const long long o = s_idx;
+    if (o >= cap) continue;
+    if (threadIdx.x == 0) bkeys[3 * o] = bx, bkeys[3 * o + 1] = by, bkeys[3 * o + 2] = bz;
+    const size_t base = (size_t)slot * B200_BLOCK_VOX;
+    for (int i = threadIdx.x; i < B200_BLOCK_VOX; i += blockDim.x) {
+      vox[o * B200_BLOCK_VOX + i] = v.vox[base + i];
+      cnt[o * B200_BLOCK_VOX + i] = v.cnt[base + i];
+    }
+  }
+}
+
+extern "C" int b200tsdf_export_seam_blocks(b200tsdf_t *h, int64_t *bkeys_dev, float *vox_dev,
+                                           uint64_t *cnt_dev, int64_t cap, int64_t *n_host,
+                                           void *stream) {
+  if (!h || !n_host || cap < 0 || (cap > 0 && (!bkeys_dev || !vox_dev || !cnt_dev))) {
+    b200_set_error("b200tsdf_export_seam_blocks: invalid argument");
+    return B200TSDF_E_INVALID;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  B200_CUDA(cudaSetDevice(h->cfg.device));
+  B200_CUDA(cudaMemsetAsync(h->scratch, 0, 8, st));
+  export_seam_kernel<<<148 * 8, 128, 0, st>>>(h->d, (long long *)bkeys_dev, (float4 *)vox_dev,
+                                              (unsigned long long *)cnt_dev, (long long)cap,
+                                              h->scratch);
+  B200_CUDA(cudaGetLastError());
+  unsigned long long n;
+  B200_CUDA(cudaMemcpyAsync(&n, h->scratch, 8, cudaMemcpyDeviceToHost, st));
+  B200_CUDA(cudaStreamSynchronize(st));
+  *n_host = (int64_t)n;
+  return B200TSDF_OK;
+}
+
+__global__ void __launch_bounds__(128)
+    import_halo_kernel(VolumeDev v, const long long *__restrict__ bkeys,
+                       const float4 *__restrict__ vox, const unsigned long long *__restrict__ cnt,
+                       long long n, unsigned long long *overflow) {
+  __shared__ uint32_t s_slot;
+  for (long long b = blockIdx.x; b < n; b += gridDim.x) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      int bx = (int)bkeys[3 * b], by = (int)bkeys[3 * b + 1], bz = (int)bkeys[3 * b + 2];
+      bool fresh;
+      s_slot = block_in_range(bx, by, bz) ? hash_insert(v, pack_block_key(bx, by, bz), &fresh)
+                                          : B200_NO_SLOT;
+      if (s_slot == B200_NO_SLOT) atomicAdd(overflow, 1ull);
+    }
+    __syncthreads();
+    if (s_slot == B200_NO_SLOT) continue;
+    const size_t base = (size_t)s_slot * B200_BLOCK_VOX;
+    for (int i = threadIdx.x; i < B200_BLOCK_VOX; i += blockDim.x) {
+      v.vox[base + i] = vox[b * B200_BLOCK_VOX + i]; // overwrite: a halo block is a copy
+      v.cnt[base + i] = cnt[b * B200_BLOCK_VOX + i];
+    }
+  }
+}
+
+extern "C" int b200tsdf_import_halo_blocks(b200tsdf_t *h, const int64_t *bkeys_dev,
+                                           const float *vox_dev, const uint64_t *cnt_dev,
+                                           int64_t n, void *stream) {
+  if (!h || n < 0 || (n > 0 && (!bkeys_dev || !vox_dev || !cnt_dev))) {
+    b200_set_error("b200tsdf_import_halo_blocks: invalid argument");
+    return B200TSDF_E_INVALID;
+  }
+  if (n == 0) return B200TSDF_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  B200_CUDA(cudaSetDevice(h->cfg.device));
+  B200_CUDA(cudaMemsetAsync(h->scratch + 1, 0, 8, st));
+  import_halo_kernel<<<(unsigned)(n < 1184 ? n : 1184), 128, 0, st>>>(
+      h->d, (const long long *)bkeys_dev, (const float4 *)vox_dev,
+      (const unsigned long long *)cnt_dev, (long long)n, h->scratch + 1);
+  B200_CUDA(cudaGetLastError());
+  unsigned long long ov;
+  B200_CUDA(cudaMemcpyAsync(&ov, h->scratch + 1, 8, cudaMemcpyDeviceToHost, st));
+  B200_CUDA(cudaStreamSynchronize(st));
+  if (ov) {
+    b200_set_error("b200tsdf_import_halo_blocks: voxel-block hash full (%llu blocks lost)", ov);
+    return B200TSDF_E_CAPACITY;
+  }
+  return B200TSDF_OK;
+}

@@ -1,0 +1,137 @@
+"""One process per GPU: the dual TSDF volume sharded in interleaved z-slabs
+(BASELINE north_star "z-slabs across the GPUs of one box").
+
+No reference counterpart: the reference is single-process Python.  Layout:
+  * world-z is cut into slabs of `slab_width` voxel layers; slab s belongs to
+    rank s mod world_size (slab_width = dim / world gives the classic
+    contiguous z-slabs; a smaller power of two deals slabs round-robin and
+    balances surfaces that are not uniform in z);
+  * every keyframe batch (pointmaps, confidences, quality grid, poses) is
+    broadcast from the rank that holds it (NCCL over NVLink); every rank runs
+    the staging of the full batch, culls the rays whose +-truncation band
+    misses its slabs and fuses the rest into its own voxel-block hash -- there
+    is no other data-path collective;
+  * meshes are stitched at slab seams: before marching cubes every rank sends
+    the first block layer of each of its slabs to the rank below, which
+    installs it as read-only halo blocks; the lower rank emits the seam cubes,
+    so no triangle is duplicated or missing;
+  * counters / stats are sums over ranks (all_reduce).
+`torch.distributed` is plumbing only; the group may be NCCL (GPU) or gloo
+(host-logic tests with an injected volume factory).
+"""
+import torch
+import torch.distributed as dist
+
+
+def slab_of(kz, z0, slab_width):
+    """Slab index of voxel layer kz (floor division, like the kernels)."""
+    return (kz - z0) // slab_width
+
+
+def slab_owner(kz, z0, slab_width, world):
+    return slab_of(kz, z0, slab_width) % world
+
+
+class ShardedTSDFVolume:
+    def __init__(self, voxel_size, truncation, max_weight=100.0, min_weight=1.0e-3, *,
+                 slab_width, bounds=None, capacity_log2=17, device=None, group=None,
+                 volume_factory=None):
+        self.group = group
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.slab_width = int(slab_width)
+        if self.slab_width < 8 or self.slab_width & (self.slab_width - 1):
+            raise ValueError("slab_width must be a power of two >= 8")
+        self.z0 = int(bounds[0][2]) if bounds is not None else 0
+        self.device = device
+        if volume_factory is None:
+            from .tsdf.global_volume import TSDFVolume
+
+            def volume_factory(**kw):
+                return TSDFVolume(voxel_size, truncation, max_weight, min_weight, **kw)
+        self.vol = volume_factory(capacity_log2=capacity_log2, bounds=bounds, device=device,
+                                  slabs=(self.world, self.rank, self.slab_width))
+
+    # -- keyframes ---------------------------------------------------------
+    def broadcast_keyframes(self, X, Cf, poses, q_grid=None, src=0):
+        """In-place broadcast of one batch from rank `src`; every rank passes
+        tensors of the batch's shape (contents matter on `src` only)."""
+        if self.world > 1:
+            for t in (X, Cf, poses) + ((q_grid,) if q_grid is not None else ()):
+                dist.broadcast(t, src, group=self.group)
+        return X, Cf, poses, q_grid
+
+    def integrate_keyframes(self, X, Cf, poses, q_grid=None, min_conf=0.05, H=None, W=None,
+                            step_scale=0.5, src=0, broadcast=True):
+        if broadcast:
+            self.broadcast_keyframes(X, Cf, poses, q_grid, src)
+        self.vol.integrate_keyframes(X, Cf, poses, q_grid, min_conf, H, W, step_scale)
+
+    # -- reductions --------------------------------------------------------
+    def _sum(self, values):
+        t = torch.tensor(values, dtype=torch.int64,
+                         device=self.device if dist.is_initialized() and
+                         dist.get_backend(self.group) == "nccl" else "cpu")
+        if self.world > 1:
+            dist.all_reduce(t, group=self.group)
+        return [int(x) for x in t.cpu()]
+
+    def counters(self):
+        c = self.vol.counters()
+        keys = ["updates_primary", "updates_quality", "blocks", "dropped", "culled_rays"]
+        out = dict(zip(keys, self._sum([c[k] for k in keys])))
+        out["rays"] = c["rays"]  # every rank stages the full batch
+        out["local"] = c
+        return out
+
+    def stats(self, which=0):
+        s = self.vol.stats(which)
+        v = self._sum([s["valid_voxels"], s["total_voxels"]])
+        return {"valid_voxels": v[0], "total_voxels": v[1]}
+
+    # -- seams / mesh --------------------------------------------------------
+    def exchange_seams(self):
+        """Send my seam blocks to the rank below, install the ones of the rank
+        above as halo blocks.  Returns the number of halo blocks installed."""
+        if self.world == 1:
+            return 0
+        bk, vox, cnt = self.vol.export_seam_blocks()
+        down, up = (self.rank - 1) % self.world, (self.rank + 1) % self.world
+        n_mine = torch.tensor([bk.shape[0]], dtype=torch.int64, device=bk.device)
+        counts = [torch.zeros_like(n_mine) for _ in range(self.world)]
+        dist.all_gather(counts, n_mine, group=self.group)
+        n_up = int(counts[up].item())
+        rbk = torch.zeros(n_up, 3, dtype=torch.int64, device=bk.device)
+        rvox = torch.zeros(n_up, 512, 4, dtype=torch.float32, device=bk.device)
+        rcnt = torch.zeros(n_up, 512, dtype=torch.int64, device=bk.device)
+        ops = []
+        for s_t, r_t in ((bk, rbk), (vox, rvox), (cnt, rcnt)):
+            if s_t.shape[0]:
+                ops.append(dist.P2POp(dist.isend, s_t, down, group=self.group))
+            if r_t.shape[0]:
+                ops.append(dist.P2POp(dist.irecv, r_t, up, group=self.group))
+        if ops:
+            for w in dist.batch_isend_irecv(ops):
+                w.wait()
+        self.vol.import_halo_blocks(rbk, rvox, rcnt)
+        return n_up
+
+    def extract_mesh(self, which=0, gather=False):
+        """Marching cubes of this rank's slabs incl. their top seams.  With
+        gather=True rank 0 receives the whole mesh (others get their part)."""
+        self.exchange_seams()
+        verts = self.vol.extract_mesh(which)
+        if not gather or self.world == 1:
+            return verts
+        n = torch.tensor([verts.shape[0]], dtype=torch.int64, device=verts.device)
+        counts = [torch.zeros_like(n) for _ in range(self.world)]
+        dist.all_gather(counts, n, group=self.group)
+        counts = [int(c.item()) for c in counts]
+        pad = max(counts + [1])
+        buf = torch.zeros(pad, 3, dtype=torch.float32, device=verts.device)
+        buf[: verts.shape[0]] = verts
+        parts = [torch.zeros_like(buf) for _ in range(self.world)]
+        dist.all_gather(parts, buf, group=self.group)
+        if self.rank != 0:
+            return verts
+        return torch.cat([p[:c] for p, c in zip(parts, counts)], dim=0)

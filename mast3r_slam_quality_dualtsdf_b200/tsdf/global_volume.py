@@ -250,3 +250,39 @@ class TSDFVolume:
                                                    C.byref(n), _stream_ptr(self.device)),
                            "extract_mesh")
         return verts[: n.value * 3]
+
+    # ------------------------------------------------------------------
+    # Multi-GPU seams (see parallel.ShardedTSDFVolume)
+    # ------------------------------------------------------------------
+    def export_seam_blocks(self):
+        """Voxel blocks of the first block layer of every z-slab this volume
+        owns: (bkeys i64 (n,3), vox f32 (n,512,4), cnt i64 (n,512)) device
+        tensors (cnt holds the raw u64 hit-counter words)."""
+        n = C.c_int64()
+        L = _ffi.lib()
+        with self._lock:
+            _ffi.check(L.b200tsdf_export_seam_blocks(self._h, None, None, None, 0, C.byref(n),
+                                                     _stream_ptr(self.device)), "export_seam")
+            cap = n.value
+            bk = torch.zeros(cap, 3, dtype=torch.int64, device=self.device)
+            vox = torch.zeros(cap, 512, 4, dtype=torch.float32, device=self.device)
+            cnt = torch.zeros(cap, 512, dtype=torch.int64, device=self.device)
+            if cap:
+                _ffi.check(L.b200tsdf_export_seam_blocks(
+                    self._h, bk.data_ptr(), vox.data_ptr(), cnt.data_ptr(), cap, C.byref(n),
+                    _stream_ptr(self.device)), "export_seam")
+        return bk, vox, cnt
+
+    def import_halo_blocks(self, bkeys, vox, cnt):
+        """Install another rank's seam blocks as read-only +z neighbours for
+        extract_mesh."""
+        n = int(bkeys.shape[0])
+        if n == 0:
+            return
+        bkeys = bkeys.to(self.device, torch.int64).contiguous()
+        vox = vox.to(self.device, torch.float32).contiguous()
+        cnt = cnt.to(self.device, torch.int64).contiguous()
+        with self._lock:
+            _ffi.check(_ffi.lib().b200tsdf_import_halo_blocks(
+                self._h, bkeys.data_ptr(), vox.data_ptr(), cnt.data_ptr(), n,
+                _stream_ptr(self.device)), "import_halo")

@@ -47,3 +47,58 @@ def test_mesh_empty_volume(cuda_device):
 
     vol = TSDFVolume(0.03, 0.12, device=cuda_device)
     assert vol.extract_mesh().shape == (0, 3)
+
+
+def _same_soup(got, want, tol=1.0e-5):
+    """Triangle soups equal as sets up to float32 rounding of the voxel sums
+    (reductions land in a different order in every run)."""
+    from scipy.spatial import cKDTree
+
+    if len(got) != len(want):
+        return False
+    d, idx = cKDTree(want.reshape(-1, 9)).query(got.reshape(-1, 9))
+    return bool(d.max(initial=0.0) <= tol and len(np.unique(idx)) == len(want))
+
+
+@pytest.mark.parametrize("world,width", [(2, 8), (4, 8), (2, 16), (3, 8)])
+def test_mesh_stitched_at_slab_seams(cuda_device, world, width):
+    """`world` ranks emulated by `world` handles on one GPU.  Each
+    fuses its interleaved z-slabs, seam blocks go to the rank below as halo
+    blocks, and the union of the per-rank meshes is the single-volume mesh,
+    triangle for triangle (none duplicated, none missing)."""
+    from mast3r_slam_quality_dualtsdf_b200.tsdf import TSDFVolume
+
+    voxel, trunc = 0.03, 0.12
+    kf = synth.make_keyframes(synth.SCENES["sphere"], 3, H=48, W=64, seed=4, f=50.0, total=12)
+    args = [torch.from_numpy(kf[k]).to(cuda_device) for k in ("X", "C", "pose")]
+    q = torch.from_numpy(kf["q"]).to(cuda_device)
+    single = TSDFVolume(voxel, trunc, device=cuda_device)
+    single.integrate_keyframes(*args, q, 0.05, 48, 64)
+    ranks = [TSDFVolume(voxel, trunc, device=cuda_device, slabs=(world, r, width))
+             for r in range(world)]
+    for v in ranks:
+        v.integrate_keyframes(*args, q, 0.05, 48, 64)
+    seams = [v.export_seam_blocks() for v in ranks]
+    assert sum(s[0].shape[0] for s in seams) > 0
+    for r, v in enumerate(ranks):
+        v.import_halo_blocks(*seams[(r + 1) % world])
+    for which in (0, 1):
+        want = single.extract_mesh(which).cpu().numpy().reshape(-1, 3, 3)
+        parts = [v.extract_mesh(which).cpu().numpy().reshape(-1, 3, 3) for v in ranks]
+        got = np.concatenate(parts)
+        assert len(want) > 100 and len(got) == len(want)
+        assert _same_soup(got, want)
+    # halo blocks are invisible to stats / export / block list
+    tot = sum(v.stats(0)["total_voxels"] for v in ranks)
+    assert tot == single.stats(0)["total_voxels"]
+    assert sum(len(v.block_keys()) for v in ranks) == len(single.block_keys())
+    # re-import after more fusion overwrites the halo copy (no double counting)
+    for v in ranks:
+        v.integrate_keyframes(*args, q, 0.05, 48, 64)
+    single.integrate_keyframes(*args, q, 0.05, 48, 64)
+    seams = [v.export_seam_blocks() for v in ranks]
+    for r, v in enumerate(ranks):
+        v.import_halo_blocks(*seams[(r + 1) % world])
+    want = single.extract_mesh(0).cpu().numpy().reshape(-1, 3, 3)
+    got = np.concatenate([v.extract_mesh(0).cpu().numpy().reshape(-1, 3, 3) for v in ranks])
+    assert _same_soup(got, want)

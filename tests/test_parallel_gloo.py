@@ -1,0 +1,122 @@
+"""Host logic of parallel.ShardedTSDFVolume on CPU: world_size-2 gloo group,
+the CUDA volume replaced by a numpy stand-in through `volume_factory` (the
+kernels themselves are covered by the gpu-marked slab / seam tests)."""
+import os
+import socket
+
+import numpy as np
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from mast3r_slam_quality_dualtsdf_b200 import parallel
+
+
+class FakeVolume:
+    """Records what the sharded wrapper asks of a volume; 'fuses' one voxel
+    per pixel at kz = round(100 * X.z) so ownership can be checked."""
+
+    def __init__(self, capacity_log2, bounds, device, slabs):
+        self.world, self.rank, self.width = slabs
+        self.z0 = bounds[0][2] if bounds is not None else 0
+        self.blocks = {}  # (bx,by,bz) -> payload value
+        self.halo = {}
+        self.rays = 0
+        self.applied = 0
+        self.culled = 0
+
+    def integrate_keyframes(self, X, Cf, poses, q_grid, min_conf, H, W, step_scale):
+        kz = torch.round(X[..., 2] * 100).to(torch.int64).reshape(-1)
+        self.rays += kz.numel()
+        own = parallel.slab_owner(kz, self.z0, self.width, self.world) == self.rank
+        self.applied += int(own.sum())
+        self.culled += int((~own).sum())
+        for z in kz[own].tolist():
+            key = (0, 0, z >> 3)
+            self.blocks[key] = self.blocks.get(key, 0.0) + float(poses.sum())
+
+    def counters(self):
+        return {"rays": self.rays, "updates_primary": self.applied, "updates_quality": self.applied,
+                "blocks": len(self.blocks), "dropped": 0, "overflow": 0,
+                "culled_rays": self.culled}
+
+    def stats(self, which=0):
+        return {"valid_voxels": len(self.blocks), "total_voxels": len(self.blocks)}
+
+    def export_seam_blocks(self):
+        keys = [k for k in sorted(self.blocks) if (k[2] * 8 - self.z0) % self.width == 0]
+        bk = torch.tensor(keys, dtype=torch.int64).reshape(-1, 3)
+        vox = torch.zeros(len(keys), 512, 4)
+        for i, k in enumerate(keys):
+            vox[i] += self.blocks[k]
+        return bk, vox, torch.full((len(keys), 512), self.rank, dtype=torch.int64)
+
+    def import_halo_blocks(self, bk, vox, cnt):
+        for i in range(bk.shape[0]):
+            self.halo[tuple(int(x) for x in bk[i])] = (float(vox[i, 0, 0]), int(cnt[i, 0]))
+
+    def extract_mesh(self, which=0):
+        return torch.full((3 * (self.rank + 1), 3), float(self.rank))
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, world, port, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        bounds = ((-64, -64, -64), (64, 64, 64))
+        sv = parallel.ShardedTSDFVolume(0.01, 0.04, slab_width=16, bounds=bounds, device="cpu",
+                                        volume_factory=lambda **kw: FakeVolume(**kw))
+        assert sv.vol.world == world and sv.vol.rank == rank
+        # rank 0 holds the keyframes; the others pass empty buffers of the same shape
+        g = torch.Generator().manual_seed(7)
+        X = torch.rand(2, 48, 3, generator=g) * 1.2 - 0.6
+        Cf, P = torch.ones(2, 48), torch.arange(16.0).reshape(2, 8)
+        if rank != 0:
+            X, Cf, P = torch.zeros_like(X), torch.zeros_like(Cf), torch.zeros_like(P)
+        sv.integrate_keyframes(X, Cf, P, None, 0.05, 6, 8)
+        g = torch.Generator().manual_seed(7)
+        want = torch.rand(2, 48, 3, generator=g) * 1.2 - 0.6
+        assert torch.equal(X, want) and float(P.sum()) == 120.0  # broadcast delivered
+        c = sv.counters()
+        assert c["rays"] == 96 and c["updates_primary"] == 96  # every voxel fused exactly once
+        assert c["culled_rays"] == 96 * (world - 1)
+        st = sv.stats()
+        n_halo = sv.exchange_seams()
+        # what I received is exactly what the rank above exported
+        up = (rank + 1) % world
+        assert all(v[1] == up for v in sv.vol.halo.values()) and len(sv.vol.halo) == n_halo
+        for k in sv.vol.halo:
+            assert parallel.slab_owner(k[2] * 8, -64, 16, world) == up
+            assert (k[2] * 8 + 64) % 16 == 0
+        mesh = sv.extract_mesh(gather=True)
+        out[rank] = (st["total_voxels"], len(sv.vol.blocks), n_halo, tuple(mesh.shape),
+                     sorted(sv.vol.halo))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_sharded_volume_host_logic_world2():
+    world = 2
+    with mp.Manager() as m:
+        out = m.dict()
+        mp.spawn(_worker, args=(world, _free_port(), out), nprocs=world, join=True)
+        res = dict(out)
+    assert res[0][0] == res[1][0] == res[0][1] + res[1][1]  # stats are all-reduced
+    assert res[0][3] == (3 * 1 + 3 * 2, 3) and res[1][3] == (6, 3)  # rank 0 gathers the mesh
+    assert res[0][2] + res[1][2] > 0
+
+
+def test_slab_owner_matches_kernel_convention():
+    kz = np.arange(-70, 70)
+    own = parallel.slab_owner(kz, -64, 16, 4)
+    assert own[kz == -64][0] == 0 and own[kz == -49][0] == 0 and own[kz == -48][0] == 1
+    assert own[kz == -65][0] == 3  # floor division below the origin
+    assert set(np.unique(own)) == {0, 1, 2, 3}
