@@ -1,2 +1,4 @@
 """Mirror of the reference package `mast3r_slam.tsdf` (tsdf/__init__.py:3)."""
+from .global_manager import TSDFGlobalManager  # noqa: F401
 from .global_volume import TSDFVolume  # noqa: F401
+from .tsdf_optimizer import TSDFPoseOptimizer  # noqa: F401

@@ -60,6 +60,40 @@ class CountingVolume:
         return k, t, w, c
 
 
+def _quat_R(q):
+    x, y, z, w = q
+    return np.array([[1 - 2 * (y * y + z * z), 2 * (x * y - z * w), 2 * (x * z + y * w)],
+                     [2 * (x * y + z * w), 1 - 2 * (x * x + z * z), 2 * (y * z - x * w)],
+                     [2 * (x * z - y * w), 2 * (y * z + x * w), 1 - 2 * (x * x + y * y)]])
+
+
+def _R_quat(R):
+    from scipy.spatial.transform import Rotation
+
+    q = Rotation.from_matrix(R).as_quat()  # xyzw
+    return q if q[3] >= 0 else -q
+
+
+def sim3_exp_np(d):
+    """exp of a Sim(3) tangent [tau, phi, sigma] as [t, q_xyzw, s] (float64)."""
+    from scipy.linalg import expm
+
+    phi = d[3:6]
+    O = np.array([[0, -phi[2], phi[1]], [phi[2], 0, -phi[0]], [-phi[1], phi[0], 0]])
+    M = np.zeros((4, 4))
+    M[:3, :3] = O + d[6] * np.eye(3)
+    M[:3, 3] = d[:3]
+    E = expm(M)
+    s = np.cbrt(np.linalg.det(E[:3, :3]))
+    return np.concatenate([E[:3, 3], _R_quat(E[:3, :3] / s), [s]])
+
+
+def sim3_mul_np(a, b):
+    Ra, Rb = _quat_R(a[3:7]), _quat_R(b[3:7])
+    t = a[7] * (Ra @ b[:3]) + a[:3]
+    return np.concatenate([t, _R_quat(Ra @ Rb), [a[7] * b[7]]])
+
+
 def _sim3_stub():
     """~30-line stand-in for the absent lietorch; only what
     tsdf_refine.py touches: Sim3(data).act/.matrix/.clone/.to/.data."""
@@ -104,6 +138,20 @@ def _sim3_stub():
             M[:3, 3] = t[0]
             return M.unsqueeze(0)
 
+        # exp / composition for tsdf_optimizer.py:85-86, through the 4x4 matrix
+        # exponential (scipy) -- deliberately independent of the product's sim3.py
+        @staticmethod
+        def exp(delta):
+            d = delta.detach().cpu().double().numpy().reshape(7)
+            return Sim3(torch.from_numpy(sim3_exp_np(d)).to(delta.dtype).reshape(1, 8).to(
+                delta.device))
+
+        def __mul__(self, other):
+            a = self.data.detach().cpu().double().numpy().reshape(8)
+            b = other.data.detach().cpu().double().numpy().reshape(8)
+            return Sim3(torch.from_numpy(sim3_mul_np(a, b)).to(self.data.dtype).reshape(1, 8).to(
+                self.data.device))
+
     class SE3(Sim3):
         embedded_dim = 7
 
@@ -125,3 +173,47 @@ def load_tsdf_refine():
 
     mod = importlib.import_module("mast3r_slam.tsdf_refine")
     return mod, sys.modules["lietorch"]
+
+
+def load_tsdf_optimizer():
+    """reference mast3r_slam/tsdf/tsdf_optimizer.py by file path (it imports
+    only numpy, torch and lietorch -> the stub)."""
+    sys.modules["lietorch"] = _sim3_stub()
+    path = os.path.join(REF_ROOT, "mast3r_slam", "tsdf", "tsdf_optimizer.py")
+    spec = importlib.util.spec_from_file_location("_ref_tsdf_optimizer", path)
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod, sys.modules["lietorch"]
+
+
+class FakeKeyframes:
+    """Duck-type of SharedKeyframes (frame.py:220-334) for the TSDF path."""
+
+    class _Frame:
+        pass
+
+    def __init__(self, X, C, poses, lietorch_mod=None, img_shape=None):
+        import threading
+
+        import torch
+
+        self.lock = threading.RLock()
+        self.X = [torch.as_tensor(x) for x in X]
+        self.C = [torch.as_tensor(c).reshape(-1, 1) for c in C]
+        self.T_WC = [torch.as_tensor(p).reshape(1, 8).clone() for p in poses]
+        self.lt = lietorch_mod
+        self.img_shape = img_shape
+        self.device = "cpu"
+
+    def __len__(self):
+        return len(self.X)
+
+    def __getitem__(self, idx):
+        import torch
+
+        f = self._Frame()
+        f.X_canon, f.C, f.frame_id = self.X[idx], self.C[idx], idx
+        f.T_WC = self.lt.Sim3(self.T_WC[idx]) if self.lt is not None else self.T_WC[idx]
+        if self.img_shape is not None:
+            f.img_shape = torch.tensor([list(self.img_shape)])
+        return f
