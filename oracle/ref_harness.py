@@ -192,7 +192,7 @@ class FakeKeyframes:
     class _Frame:
         pass
 
-    def __init__(self, X, C, poses, lietorch_mod=None, img_shape=None):
+    def __init__(self, X, C, poses, lietorch_mod=None, img_shape=None, K=None):
         import threading
 
         import torch
@@ -203,6 +203,8 @@ class FakeKeyframes:
         self.T_WC = [torch.as_tensor(p).reshape(1, 8).clone() for p in poses]
         self.lt = lietorch_mod
         self.img_shape = img_shape
+        self.K = K
+        self.version = torch.zeros(len(self.X), dtype=torch.long)
         self.device = "cpu"
 
     def __len__(self):
@@ -214,6 +216,7 @@ class FakeKeyframes:
         f = self._Frame()
         f.X_canon, f.C, f.frame_id = self.X[idx], self.C[idx], idx
         f.T_WC = self.lt.Sim3(self.T_WC[idx]) if self.lt is not None else self.T_WC[idx]
+        f.K = self.K
         if self.img_shape is not None:
             f.img_shape = torch.tensor([list(self.img_shape)])
         return f
