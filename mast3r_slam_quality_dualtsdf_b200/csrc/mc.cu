@@ -133,10 +133,10 @@ extern "C" int b200tsdf_extract_mesh(b200tsdf_t *h, int which, float *verts_dev,
   B200_CUDA(cudaMemsetAsync(h->scratch, 0, 8, st));
   const float vs = (float)h->cfg.voxel_size;
   if (verts_dev && tri_cap > 0)
-    mc_kernel<true><<<148 * 4, MC_THREADS, 0, st>>>(h->d, which, vs, verts_dev,
+    mc_kernel<true><<<148 * 8, MC_THREADS, 0, st>>>(h->d, which, vs, verts_dev,
                                                      (long long)tri_cap, h->scratch);
   else
-    mc_kernel<false><<<148 * 4, MC_THREADS, 0, st>>>(h->d, which, vs, nullptr, 0, h->scratch);
+    mc_kernel<false><<<148 * 8, MC_THREADS, 0, st>>>(h->d, which, vs, nullptr, 0, h->scratch);
   B200_CUDA(cudaGetLastError());
   unsigned long long n;
   B200_CUDA(cudaMemcpyAsync(&n, h->scratch, 8, cudaMemcpyDeviceToHost, st));

@@ -237,19 +237,31 @@ class TSDFVolume:
         k = bk[:n.value].cpu().numpy()
         return k[np.lexsort((k[:, 2], k[:, 1], k[:, 0]))]
 
-    def extract_mesh(self, which: int = 0):
-        """Marching cubes; returns verts f32 (3T,3) device tensor (triangle soup)."""
+    def extract_mesh(self, which: int = 0, out=None):
+        """Marching cubes; returns verts f32 (3T,3) device tensor (triangle soup).
+        One optimistic write pass into a buffer sized from the block count (or
+        into `out`, a float32 (cap*3, 3) tensor to reuse); only if the mesh
+        does not fit is it repeated with the exact size the first pass
+        returned."""
         n = C.c_int64()
         L = _ffi.lib()
         with self._lock:
-            _ffi.check(L.b200tsdf_extract_mesh(self._h, which, None, 0, C.byref(n),
+            if out is None:
+                nblk = C.c_int64()
+                _ffi.check(L.b200tsdf_export_blocks(self._h, None, 0, C.byref(nblk),
+                                                    _stream_ptr(self.device)), "export_blocks")
+                cap = max(1024, nblk.value * 96, int(getattr(self, "_last_tris", 0) * 1.25))
+                out = torch.empty(cap * 3, 3, dtype=torch.float32, device=self.device)
+            cap = out.shape[0] // 3
+            _ffi.check(L.b200tsdf_extract_mesh(self._h, which, out.data_ptr(), cap, C.byref(n),
                                                _stream_ptr(self.device)), "extract_mesh")
-            verts = torch.zeros(max(n.value, 1) * 3, 3, dtype=torch.float32, device=self.device)
-            if n.value:
-                _ffi.check(L.b200tsdf_extract_mesh(self._h, which, verts.data_ptr(), n.value,
+            if n.value > cap:  # did not fit: exact size, second pass
+                out = torch.empty(n.value * 3, 3, dtype=torch.float32, device=self.device)
+                _ffi.check(L.b200tsdf_extract_mesh(self._h, which, out.data_ptr(), n.value,
                                                    C.byref(n), _stream_ptr(self.device)),
                            "extract_mesh")
-        return verts[: n.value * 3]
+            self._last_tris = n.value
+        return out[: n.value * 3]
 
     # ------------------------------------------------------------------
     # Multi-GPU seams (see parallel.ShardedTSDFVolume)
