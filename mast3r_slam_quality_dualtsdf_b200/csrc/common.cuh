@@ -77,6 +77,7 @@ struct b200tsdf {
   void *stage_dev;
   size_t stage_bytes;
   unsigned long long *scratch; // small device scratch (counters for sweeps)
+  uint32_t *nbr;               // marching cubes: 8 neighbour slots per block (lazy)
 };
 
 // ---------------------------------------------------------------- hashing

@@ -2,11 +2,13 @@
 //
 // No reference counterpart (the reference has no mesh path):
 // semantics are stated in oracle/mc_oracle.c and checked against it.
-// One CTA per voxel block: the 9x9x9 corner lattice (block + one-voxel halo
-// from the +x/+y/+z neighbour blocks, found through the block hash) is staged
-// in shared memory with 128-bit loads; every thread classifies two cubes;
-// triangle slots are assigned by a warp-scan (shfl_up) + per-CTA offsets and
-// ONE atomicAdd per CTA on the global triangle counter (warp-scan compaction).
+// A pre-pass resolves every block's 8 neighbour slots through the block hash
+// (one thread per lookup).  Then one CTA per voxel block: the 9x9x9 corner
+// lattice (block + one-voxel halo from the +x/+y/+z neighbour blocks) is
+// staged in shared memory with 128-bit loads; every thread classifies two
+// cubes; triangle slots are assigned by a warp scan (shfl_up) and ONE
+// atomicAdd per warp on the global triangle counter (warp-scan compaction);
+// triangles are then emitted one per lane (balanced within the warp).
 #include <math.h>
 
 #include "common.cuh"
@@ -16,38 +18,48 @@
 
 #define MC_THREADS 256
 
+// Pass 0: the 8 block slots every block's 9^3 corner lattice draws from (itself
+// and its +x/+y/+z neighbours), one thread per (block, neighbour): the
+// dependent hash probes run massively parallel instead of serially per CTA.
+__global__ void mc_neighbors_kernel(VolumeDev v, uint32_t *__restrict__ nbr) {
+  const uint32_t nb = (uint32_t)v.ctr[CTR_BLOCKS];
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < (long long)nb * 8;
+       i += (long long)gridDim.x * blockDim.x) {
+    const uint32_t b = (uint32_t)(i >> 3), k = (uint32_t)(i & 7);
+    const uint32_t slot = v.list[b];
+    uint32_t s = slot;
+    if (k) {
+      int bx, by, bz;
+      unpack_block_key(v.keys[slot], bx, by, bz);
+      int nx = bx + (k & 1), ny = by + ((k >> 1) & 1), nz = bz + (k >> 2);
+      s = block_in_range(nx, ny, nz) ? hash_find(v, pack_block_key(nx, ny, nz)) : B200_NO_SLOT;
+    }
+    nbr[i] = s;
+  }
+}
+
 template <bool WRITE>
 __global__ void __launch_bounds__(MC_THREADS)
-    mc_kernel(VolumeDev v, int which, float vs, float *__restrict__ verts, long long tri_cap,
-              unsigned long long *n_tris) {
+    mc_kernel(VolumeDev v, const uint32_t *__restrict__ nbr, int which, float vs,
+              float *__restrict__ verts, long long tri_cap, unsigned long long *n_tris) {
   __shared__ float tv[9 * 9 * 9];
-  __shared__ uint32_t nslot[8];
   __shared__ signed char s_tri[256 * 16];
   __shared__ unsigned char s_num[256];
-  __shared__ uint32_t warp_tot[MC_THREADS / 32];
-  __shared__ unsigned long long s_base;
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int tid = threadIdx.x, lane = tid & 31;
   for (int i = tid; i < 256 * 16; i += MC_THREADS) s_tri[i] = ((const signed char *)MC_TRI_TABLE)[i];
   if (tid < 256) s_num[tid] = MC_NUM_TRIS[tid];
   const uint32_t nb = (uint32_t)v.ctr[CTR_BLOCKS];
   for (uint32_t b = blockIdx.x; b < nb; b += gridDim.x) {
-    __syncthreads();
-    const uint32_t slot = v.list[b];
+    __syncthreads(); // tv of the previous block is no longer read
+    const uint32_t *nb8 = nbr + (size_t)b * 8;
     int bx, by, bz;
-    unpack_block_key(v.keys[slot], bx, by, bz);
-    if (tid < 8) {
-      int nx = bx + (tid & 1), ny = by + ((tid >> 1) & 1), nz = bz + (tid >> 2);
-      nslot[tid] = tid == 0 ? slot
-                            : (block_in_range(nx, ny, nz) ? hash_find(v, pack_block_key(nx, ny, nz))
-                                                          : 0xFFFFFFFFu);
-    }
-    __syncthreads();
+    unpack_block_key(v.keys[nb8[0]], bx, by, bz);
     for (int i = tid; i < 729; i += MC_THREADS) {
       int x = i % 9, y = (i / 9) % 9, z = i / 81;
       int nbk = (x == 8) | ((y == 8) << 1) | ((z == 8) << 2);
-      uint32_t s = nslot[nbk];
+      uint32_t s = nb8[nbk];
       float val = NAN;
-      if (s != 0xFFFFFFFFu) {
+      if (s != B200_NO_SLOT) {
         size_t off = (size_t)s * B200_BLOCK_VOX + (((z & 7) << 6) | ((y & 7) << 3) | (x & 7));
         float t, w;
         uint32_t hits;
@@ -74,48 +86,60 @@ __global__ void __launch_bounds__(MC_THREADS)
       mask[c2] = m;
       nt[c2] = ok ? s_num[m] : 0;
     }
-    // warp-scan compaction of the per-thread triangle counts
+    // warp-scan compaction of the per-thread triangle counts: an inclusive
+    // shfl_up scan, then ONE atomicAdd per warp reserves the warp's output run
     uint32_t mine = nt[0] + nt[1], incl = mine;
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
       uint32_t o = __shfl_up_sync(0xFFFFFFFFu, incl, d);
       if (lane >= d) incl += o;
     }
-    if (lane == 31) warp_tot[warp] = incl;
-    __syncthreads();
-    uint32_t wbase = 0, total = 0;
+    const uint32_t wtot = __shfl_sync(0xFFFFFFFFu, incl, 31);
+    if (wtot == 0) continue;
+    unsigned long long wbase = 0;
+    if (lane == 31) wbase = atomicAdd(n_tris, (unsigned long long)wtot);
+    wbase = __shfl_sync(0xFFFFFFFFu, wbase, 31);
+    if (WRITE) {
+      // balanced emission: triangle k of the warp's run goes to lane k % 32; its
+      // source cube is found by a binary search over the scan (5 shuffles)
+      const uint32_t excl = incl - mine;
+      for (uint32_t k0 = 0; k0 < wtot; k0 += 32) {
+        const uint32_t k = k0 + lane;
+        const bool act = k < wtot;
+        int src = 0;
 #pragma unroll
-    for (int w = 0; w < MC_THREADS / 32; ++w) {
-      if (w < warp) wbase += warp_tot[w];
-      total += warp_tot[w];
-    }
-    if (tid == 0 && total) s_base = atomicAdd(n_tris, (unsigned long long)total);
-    __syncthreads();
-    if (WRITE && total) {
-      long long o = (long long)s_base + wbase + (incl - mine);
+        for (int step = 16; step > 0; step >>= 1) {
+          uint32_t vv = __shfl_sync(0xFFFFFFFFu, incl, src + step - 1);
+          if (act && vv <= k) src += step;
+        }
+        const uint32_t e_s = __shfl_sync(0xFFFFFFFFu, excl, src);
+        const int n0_s = __shfl_sync(0xFFFFFFFFu, nt[0], src);
+        const int m0_s = __shfl_sync(0xFFFFFFFFu, mask[0], src);
+        const int m1_s = __shfl_sync(0xFFFFFFFFu, mask[1], src);
+        if (!act) continue;
+        int q = (int)(k - e_s);
+        const int c2 = q >= n0_s ? 1 : 0;
+        if (c2) q -= n0_s;
+        const int m = c2 ? m1_s : m0_s;
+        const int c = (tid - lane + src) + c2 * MC_THREADS;
+        const int x = c & 7, y = (c >> 3) & 7, z = c >> 6;
+        const long long o = (long long)wbase + k;
+        if (o >= tri_cap) continue;
 #pragma unroll
-      for (int c2 = 0; c2 < 2; ++c2) {
-        int c = tid + c2 * MC_THREADS;
-        int x = c & 7, y = (c >> 3) & 7, z = c >> 6;
-        for (int q = 0; q < nt[c2]; ++q, ++o) {
-          if (o >= tri_cap) break;
+        for (int vtx = 0; vtx < 3; ++vtx) {
+          int e = s_tri[m * 16 + 3 * q + vtx];
+          int a = MC_EDGE_CORNERS[e][0], bb = MC_EDGE_CORNERS[e][1];
+          int ax = x + (a & 1), ay = y + ((a >> 1) & 1), az = z + (a >> 2);
+          int cx = x + (bb & 1), cy = y + ((bb >> 1) & 1), cz = z + (bb >> 2);
+          float ta = tv[az * 81 + ay * 9 + ax], tb = tv[cz * 81 + cy * 9 + cx];
+          float mu = __fdiv_rn(ta, __fsub_rn(ta, tb));
+          float pa[3] = {__fmul_rn((float)(bx * 8 + ax), vs), __fmul_rn((float)(by * 8 + ay), vs),
+                         __fmul_rn((float)(bz * 8 + az), vs)};
+          float pb[3] = {__fmul_rn((float)(bx * 8 + cx), vs), __fmul_rn((float)(by * 8 + cy), vs),
+                         __fmul_rn((float)(bz * 8 + cz), vs)};
 #pragma unroll
-          for (int vtx = 0; vtx < 3; ++vtx) {
-            int e = s_tri[mask[c2] * 16 + 3 * q + vtx];
-            int a = MC_EDGE_CORNERS[e][0], bb = MC_EDGE_CORNERS[e][1];
-            int ax = x + (a & 1), ay = y + ((a >> 1) & 1), az = z + (a >> 2);
-            int cx = x + (bb & 1), cy = y + ((bb >> 1) & 1), cz = z + (bb >> 2);
-            float ta = tv[az * 81 + ay * 9 + ax], tb = tv[cz * 81 + cy * 9 + cx];
-            float mu = __fdiv_rn(ta, __fsub_rn(ta, tb));
-            float pa[3] = {__fmul_rn((float)(bx * 8 + ax), vs), __fmul_rn((float)(by * 8 + ay), vs),
-                           __fmul_rn((float)(bz * 8 + az), vs)};
-            float pb[3] = {__fmul_rn((float)(bx * 8 + cx), vs), __fmul_rn((float)(by * 8 + cy), vs),
-                           __fmul_rn((float)(bz * 8 + cz), vs)};
-#pragma unroll
-            for (int d = 0; d < 3; ++d)
-              verts[o * 9 + vtx * 3 + d] =
-                  __fadd_rn(pa[d], __fmul_rn(__fsub_rn(pb[d], pa[d]), mu));
-          }
+          for (int d = 0; d < 3; ++d)
+            verts[o * 9 + vtx * 3 + d] = __fadd_rn(pa[d], __fmul_rn(__fsub_rn(pb[d], pa[d]), mu));
         }
       }
     }
@@ -132,11 +156,14 @@ extern "C" int b200tsdf_extract_mesh(b200tsdf_t *h, int which, float *verts_dev,
   B200_CUDA(cudaSetDevice(h->cfg.device));
   B200_CUDA(cudaMemsetAsync(h->scratch, 0, 8, st));
   const float vs = (float)h->cfg.voxel_size;
+  if (!h->nbr) B200_CUDA(cudaMalloc(&h->nbr, h->cap * 8 * sizeof(uint32_t)));
+  mc_neighbors_kernel<<<148 * 8, 256, 0, st>>>(h->d, h->nbr);
   if (verts_dev && tri_cap > 0)
-    mc_kernel<true><<<148 * 8, MC_THREADS, 0, st>>>(h->d, which, vs, verts_dev,
+    mc_kernel<true><<<148 * 4, MC_THREADS, 0, st>>>(h->d, h->nbr, which, vs, verts_dev,
                                                      (long long)tri_cap, h->scratch);
   else
-    mc_kernel<false><<<148 * 8, MC_THREADS, 0, st>>>(h->d, which, vs, nullptr, 0, h->scratch);
+    mc_kernel<false><<<148 * 8, MC_THREADS, 0, st>>>(h->d, h->nbr, which, vs, nullptr, 0,
+                                                      h->scratch);
   B200_CUDA(cudaGetLastError());
   unsigned long long n;
   B200_CUDA(cudaMemcpyAsync(&n, h->scratch, 8, cudaMemcpyDeviceToHost, st));

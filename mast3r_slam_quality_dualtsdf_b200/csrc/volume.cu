@@ -134,6 +134,7 @@ extern "C" int b200tsdf_destroy(b200tsdf_t *h) {
   cudaFree(h->d.ctr);
   cudaFree(h->d.dir);
   cudaFree(h->scratch);
+  cudaFree(h->nbr);
   cudaFree(h->stage_dev);
   delete h;
   return B200TSDF_OK;
