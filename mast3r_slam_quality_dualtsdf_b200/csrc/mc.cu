@@ -13,7 +13,7 @@
 
 #include "common.cuh"
 
-#define MC_TABLE_QUAL __device__ const
+#define MC_TABLE_QUAL __device__ __align__(16) const
 #include "mc_tables.h"
 
 #define MC_THREADS 256
@@ -43,11 +43,14 @@ __global__ void __launch_bounds__(MC_THREADS)
     mc_kernel(VolumeDev v, const uint32_t *__restrict__ nbr, int which, float vs,
               float *__restrict__ verts, long long tri_cap, unsigned long long *n_tris) {
   __shared__ float tv[9 * 9 * 9];
-  __shared__ signed char s_tri[256 * 16];
+  __shared__ __align__(16) signed char s_tri[256 * 16];
   __shared__ unsigned char s_num[256];
   const int tid = threadIdx.x, lane = tid & 31;
-  for (int i = tid; i < 256 * 16; i += MC_THREADS) s_tri[i] = ((const signed char *)MC_TRI_TABLE)[i];
-  if (tid < 256) s_num[tid] = MC_NUM_TRIS[tid];
+  // case tables -> shared memory, 128 bits per thread (one row of the table)
+  if (tid < 256) {
+    reinterpret_cast<int4 *>(s_tri)[tid] = reinterpret_cast<const int4 *>(MC_TRI_TABLE)[tid];
+    s_num[tid] = MC_NUM_TRIS[tid];
+  }
   const uint32_t nb = (uint32_t)v.ctr[CTR_BLOCKS];
   for (uint32_t b = blockIdx.x; b < nb; b += gridDim.x) {
     __syncthreads(); // tv of the previous block is no longer read
@@ -159,7 +162,7 @@ extern "C" int b200tsdf_extract_mesh(b200tsdf_t *h, int which, float *verts_dev,
   if (!h->nbr) B200_CUDA(cudaMalloc(&h->nbr, h->cap * 8 * sizeof(uint32_t)));
   mc_neighbors_kernel<<<148 * 8, 256, 0, st>>>(h->d, h->nbr);
   if (verts_dev && tri_cap > 0)
-    mc_kernel<true><<<148 * 4, MC_THREADS, 0, st>>>(h->d, h->nbr, which, vs, verts_dev,
+    mc_kernel<true><<<148 * 6, MC_THREADS, 0, st>>>(h->d, h->nbr, which, vs, verts_dev,
                                                      (long long)tri_cap, h->scratch);
   else
     mc_kernel<false><<<148 * 8, MC_THREADS, 0, st>>>(h->d, h->nbr, which, vs, nullptr, 0,
