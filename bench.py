@@ -183,7 +183,7 @@ def run_reference(args):
                 "d2h_bytes_per_step": 0},
         "gpu_launches": 0, "host_cores": os.cpu_count(),
     }
-    print(json.dumps(line))
+    emit(line)
 
 
 def workload_config(n_gpus, dim, kf_per_step):
@@ -426,12 +426,24 @@ def run_b200(args):
                       "TSDFVolume.integrate (oracle/tsdf_oracle.c), primary and quality volume "
                       "on one thread each; the reference's own Python loop measured 12.9 k "
                       "updates/s on 1 core (BASELINE.md)"}
-    print(json.dumps(line))
+    emit(line)
     if world > 1:
         dist.destroy_process_group()
 
 
+def emit(line):
+    """The ONE JSON line goes to the real stdout; everything else this process
+    or its libraries print (NCCL writes its version banner to fd 1) goes to
+    stderr."""
+    os.write(_REAL_STDOUT, (json.dumps(line) + "\n").encode())
+
+
+_REAL_STDOUT = 1
+
 if __name__ == "__main__":
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     a = parse()
     if a.impl == "reference":
         run_reference(a)

@@ -307,10 +307,27 @@ __global__ void __launch_bounds__(256, FUSE_MINB)
   if (in_img && c > min_conf) { // global_manager.py:92
     float wx, wy, wz;
     sim3_act(P, x0, x1, x2, wx, wy, wz);
-    have = ray_setup<float>(r, wx, wy, wz, P[0], P[1], P[2], step, mc.trunc);
+    float rx, ry, rz;
+    have = ray_length<float>(r, wx, wy, wz, P[0], P[1], P[2], rx, ry, rz);
     if (have) {
       tl.rays = 1;
       cq = c * q;
+      // multi-GPU: cheap conservative pre-cull before the divisions of the ray
+      // set-up -- the band's z extent lies within trunc (+3 voxels) of the point
+      if (BOUNDED && v.slab_count > 1) {
+        const float zc = wz * mc.inv_vs, ext = mc.trunc * mc.inv_vs + 3.0f;
+        if (fabsf(zc) < 1.0e9f) {
+          const int s_lo = ((int)floorf(zc - ext) - v.slab_z0) >> v.slab_shift;
+          const int s_hi = ((int)floorf(zc + ext) - v.slab_z0) >> v.slab_shift;
+          int need = v.slab_index - slab_owner_of(v, s_lo);
+          if (need < 0) need += v.slab_count;
+          if (need > s_hi - s_lo) { // no slab of this rank within reach
+            have = false;
+            tl.culled += 1;
+          }
+        }
+      }
+      if (have) ray_finish<float>(r, rx, ry, rz, P[0], P[1], P[2], step, mc.trunc);
     }
   }
   march_warp<BOUNDED, DIR>(v, wc, mc, have, r, c, cq, true, tl);

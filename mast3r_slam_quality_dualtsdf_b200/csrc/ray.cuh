@@ -60,17 +60,26 @@ struct Ray {
   int i_lo; // first sample index that can lie inside the +-trunc band
 };
 
-// global_volume.py:54-61.  Returns false when the reference `continue`s (:56).
+// global_volume.py:54-56: ray = p - o, len = ||ray||.  Returns false when the
+// reference `continue`s (:56).
 template <typename T>
-__device__ __forceinline__ bool ray_setup(Ray<T> &r, T px, T py, T pz, T ox, T oy, T oz, T step,
-                                          T trunc) {
+__device__ __forceinline__ bool ray_length(Ray<T> &r, T px, T py, T pz, T ox, T oy, T oz, T &rx,
+                                           T &ry, T &rz) {
   using R = Real<T>;
-  T rx = R::sub(px, ox), ry = R::sub(py, oy), rz = R::sub(pz, oz);
+  rx = R::sub(px, ox), ry = R::sub(py, oy), rz = R::sub(pz, oz);
   T len = R::norm3(rx, ry, rz);
-  if (!isfinite(len) || len < R::tiny()) return false;
+  r.len = len;
+  return isfinite(len) && !(len < R::tiny());
+}
+
+// global_volume.py:57-61: direction, sample count, np.linspace step.
+template <typename T>
+__device__ __forceinline__ void ray_finish(Ray<T> &r, T rx, T ry, T rz, T ox, T oy, T oz, T step,
+                                           T trunc) {
+  using R = Real<T>;
+  const T len = r.len;
   r.ox = ox, r.oy = oy, r.oz = oz;
   r.dx = R::div(rx, len), r.dy = R::div(ry, len), r.dz = R::div(rz, len);
-  r.len = len;
   r.maxd = R::add(len, trunc);
   T q = R::div(r.maxd, step);
   int n = (q < (T)1073741824.0) ? (int)q : 1073741824; // int() truncates
@@ -88,6 +97,14 @@ __device__ __forceinline__ bool ray_setup(Ray<T> &r, T px, T py, T pz, T ox, T o
     if (lo > n - 1) lo = n - 1;
   }
   r.i_lo = lo;
+}
+
+template <typename T>
+__device__ __forceinline__ bool ray_setup(Ray<T> &r, T px, T py, T pz, T ox, T oy, T oz, T step,
+                                          T trunc) {
+  T rx, ry, rz;
+  if (!ray_length<T>(r, px, py, pz, ox, oy, oz, rx, ry, rz)) return false;
+  ray_finish<T>(r, rx, ry, rz, ox, oy, oz, step, trunc);
   return true;
 }
 
