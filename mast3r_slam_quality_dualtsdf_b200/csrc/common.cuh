@@ -21,6 +21,7 @@
 #define B200_EMPTY_KEY 0xFFFFFFFFFFFFFFFFull
 #define B200_KEY_BIAS (1 << 20) /* block coords in [-2^20, 2^20) */
 #define B200_MAX_PROBE 4096
+#define B200_H2D_CHUNKS 8
 
 enum {
   CTR_RAYS = 0,
@@ -76,6 +77,8 @@ struct b200tsdf {
   // host staging for the *_host entry points
   void *stage_dev;
   size_t stage_bytes;
+  cudaStream_t copy_stream;                 // H2D of chunk k+1 overlaps the fuse of chunk k
+  cudaEvent_t copy_ev[B200_H2D_CHUNKS + 1];
   unsigned long long *scratch; // small device scratch (counters for sweeps)
   uint32_t *nbr;               // marching cubes: 8 neighbour slots per block (lazy)
 };

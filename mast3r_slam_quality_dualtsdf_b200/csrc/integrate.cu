@@ -494,10 +494,37 @@ extern "C" int b200tsdf_integrate_keyframes_host(b200tsdf_t *h, const float *X_h
   float *dC = (float *)(base + al(bx));
   float *dQ = (float *)(base + al(bx) + al(bc));
   float *dP = (float *)(base + al(bx) + al(bc) + al(bq));
-  B200_CUDA(cudaMemcpyAsync(dX, X_host, bx, cudaMemcpyHostToDevice, st));
-  B200_CUDA(cudaMemcpyAsync(dC, C_host, bc, cudaMemcpyHostToDevice, st));
-  if (bq) B200_CUDA(cudaMemcpyAsync(dQ, q_grid_host, bq, cudaMemcpyHostToDevice, st));
-  B200_CUDA(cudaMemcpyAsync(dP, pose_host, bp, cudaMemcpyHostToDevice, st));
-  return b200tsdf_integrate_keyframes(h, dX, dC, bq ? dQ : nullptr, dP, B, H, W, gh, gw, min_conf,
-                                      step_scale, st);
+  // Chunked pipeline: the H2D copy of chunk k+1 (copy stream) overlaps the fuse
+  // of chunk k (caller's stream); the call stays stream-ordered on `st`.
+  const int nchunk = B < B200_H2D_CHUNKS ? B : B200_H2D_CHUNKS;
+  if (!h->copy_stream) {
+    B200_CUDA(cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
+    for (int i = 0; i <= B200_H2D_CHUNKS; ++i)
+      B200_CUDA(cudaEventCreateWithFlags(&h->copy_ev[i], cudaEventDisableTiming));
+  }
+  // the staging area may still be read by kernels queued on `st` earlier
+  B200_CUDA(cudaEventRecord(h->copy_ev[B200_H2D_CHUNKS], st));
+  B200_CUDA(cudaStreamWaitEvent(h->copy_stream, h->copy_ev[B200_H2D_CHUNKS], 0));
+  const size_t qsz = (size_t)gh * gw;
+  for (int c = 0; c < nchunk; ++c) {
+    const int b0 = (int)((long long)B * c / nchunk), b1 = (int)((long long)B * (c + 1) / nchunk);
+    const size_t nb = (size_t)(b1 - b0);
+    cudaStream_t cs = h->copy_stream;
+    B200_CUDA(cudaMemcpyAsync(dX + (size_t)b0 * npix * 3, X_host + (size_t)b0 * npix * 3,
+                              nb * npix * 3 * sizeof(float), cudaMemcpyHostToDevice, cs));
+    B200_CUDA(cudaMemcpyAsync(dC + (size_t)b0 * npix, C_host + (size_t)b0 * npix,
+                              nb * npix * sizeof(float), cudaMemcpyHostToDevice, cs));
+    if (bq)
+      B200_CUDA(cudaMemcpyAsync(dQ + (size_t)b0 * qsz, q_grid_host + (size_t)b0 * qsz,
+                                nb * qsz * sizeof(float), cudaMemcpyHostToDevice, cs));
+    B200_CUDA(cudaMemcpyAsync(dP + (size_t)b0 * 8, pose_host + (size_t)b0 * 8,
+                              nb * 8 * sizeof(float), cudaMemcpyHostToDevice, cs));
+    B200_CUDA(cudaEventRecord(h->copy_ev[c], cs));
+    B200_CUDA(cudaStreamWaitEvent(st, h->copy_ev[c], 0));
+    rc = b200tsdf_integrate_keyframes(h, dX + (size_t)b0 * npix * 3, dC + (size_t)b0 * npix,
+                                      bq ? dQ + (size_t)b0 * qsz : nullptr, dP + (size_t)b0 * 8,
+                                      (int32_t)nb, H, W, gh, gw, min_conf, step_scale, st);
+    if (rc) return rc;
+  }
+  return B200TSDF_OK;
 }

@@ -136,6 +136,10 @@ extern "C" int b200tsdf_destroy(b200tsdf_t *h) {
   cudaFree(h->scratch);
   cudaFree(h->nbr);
   cudaFree(h->stage_dev);
+  if (h->copy_stream) {
+    for (int i = 0; i <= B200_H2D_CHUNKS; ++i) cudaEventDestroy(h->copy_ev[i]);
+    cudaStreamDestroy(h->copy_stream);
+  }
   delete h;
   return B200TSDF_OK;
 }
