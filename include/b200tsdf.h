@@ -113,6 +113,19 @@ int b200tsdf_integrate_keyframes(b200tsdf_t *h, const float *X_dev,
                                  float min_conf, double step_scale,
                                  void *stream);
 
+/* Exact inverse of b200tsdf_integrate_keyframes for the same inputs (no
+ * reference counterpart: the reference re-fuses a keyframe at its new pose
+ * WITHOUT removing the old contribution, global_manager.py:71-79; SURVEY 8(f)
+ * rank 2).  Sums are subtracted, hit counters decremented exactly; a voxel whose
+ * counter returns to 0 reads as absent again.  The keyframe must have been
+ * integrated with these very tensors and pose. */
+int b200tsdf_deintegrate_keyframes(b200tsdf_t *h, const float *X_dev,
+                                   const float *C_dev, const float *q_grid_dev,
+                                   const float *pose_dev, int32_t B, int32_t H,
+                                   int32_t W, int32_t gh, int32_t gw,
+                                   float min_conf, double step_scale,
+                                   void *stream);
+
 /* Same call with HOST buffers (pinned or pageable): copies H2D on `stream`
  * into an internal staging area, then fuses.  This is the entry the
  * reference-facing plugin uses when keyframes live on the host. */

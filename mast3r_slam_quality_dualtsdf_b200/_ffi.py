@@ -17,7 +17,7 @@ F32, F64 = 0, 1
 SYMBOLS = [
     "b200tsdf_last_error", "b200tsdf_abi_version", "b200tsdf_create", "b200tsdf_destroy",
     "b200tsdf_reset", "b200tsdf_integrate_points", "b200tsdf_integrate_keyframes",
-    "b200tsdf_integrate_keyframes_host", "b200tsdf_counters", "b200tsdf_stats",
+    "b200tsdf_integrate_keyframes_host", "b200tsdf_deintegrate_keyframes", "b200tsdf_counters", "b200tsdf_stats",
     "b200tsdf_query", "b200tsdf_export_voxels", "b200tsdf_export_blocks",
     "b200tsdf_extract_mesh", "b200tsdf_export_seam_blocks", "b200tsdf_import_halo_blocks",
     "b200tsdf_local_dims", "b200tsdf_local_build",
@@ -70,6 +70,7 @@ def lib():
     L.b200tsdf_integrate_keyframes.argtypes = [vp, vp, vp, vp, vp, i32, i32, i32, i32, i32,
                                                C.c_float, dbl, vp]
     L.b200tsdf_integrate_keyframes_host.argtypes = L.b200tsdf_integrate_keyframes.argtypes
+    L.b200tsdf_deintegrate_keyframes.argtypes = L.b200tsdf_integrate_keyframes.argtypes
     L.b200tsdf_counters.argtypes = [vp, vp, vp]
     L.b200tsdf_stats.argtypes = [vp, C.c_int, vp, vp, vp]
     L.b200tsdf_query.argtypes = [vp, C.c_int, vp, C.c_int, i64, vp, vp, vp, vp]

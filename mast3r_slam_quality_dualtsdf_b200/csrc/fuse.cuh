@@ -84,7 +84,7 @@ __device__ __forceinline__ void fold_warp(const VolumeDev &v, WarpCache &wc, boo
                                           int ky, int kz, float su, float wu, uint32_t n,
                                           float conf, float conf_q, uint32_t cp, uint32_t cq,
                                           bool check_bounds, Tally &tl, int &cdi,
-                                          uint32_t &cslot) {
+                                          uint32_t &cslot, bool neg) {
   bool ok = pred;
   if (BOUNDED && check_bounds) {
     bool in = (uint32_t)(kx - v.kmin[0]) < (uint32_t)(v.kmax[0] - v.kmin[0]) &&
@@ -155,8 +155,9 @@ __device__ __forceinline__ void fold_warp(const VolumeDev &v, WarpCache &wc, boo
     red_add_v4(v.vox + off, conf * su, conf * wu, conf_q * su, conf_q * wu);
 #endif
 #ifndef FUSE_DBG_NO_CNTRED
-    red_add_u64(v.cnt + off, (unsigned long long)(cp ? n : 0u) |
-                                 ((unsigned long long)(cq ? n : 0u) << 32));
+    const unsigned long long hits = (unsigned long long)(cp ? n : 0u) |
+                                    ((unsigned long long)(cq ? n : 0u) << 32);
+    red_add_u64(v.cnt + off, neg ? 0ull - hits : hits); // de-integration: exact 64-bit subtract
 #endif
   }
 }
@@ -207,6 +208,8 @@ __device__ __forceinline__ void march_warp(const VolumeDev &v, WarpCache &wc, co
   if (!live) cp = cq = 0u;
   if (!cp) conf = 0.0f;
   if (!cq) conf_q = 0.0f;
+  const bool neg = mc.negate != 0; // de-integration: subtract what the same call added
+  if (neg) conf = -conf, conf_q = -conf_q;
   if (BOUNDED && inside) {
     lim = mc.lim_bounded;
   } else {
@@ -275,7 +278,7 @@ __device__ __forceinline__ void march_warp(const VolumeDev &v, WarpCache &wc, co
     const bool chg = act && n != 0 && (((kx ^ ax) | (ky ^ ay) | (kz ^ az)) != 0);
     if (__any_sync(0xFFFFFFFFu, chg)) {
       fold_warp<BOUNDED, DIR>(v, wc, chg, ax, ay, az, su, wu, n, conf, conf_q, cp, cq,
-                              check_bounds, tl, cdi, cslot);
+                              check_bounds, tl, cdi, cslot, neg);
       if (chg) {
         su = wu = 0.f;
         n = 0;
@@ -294,7 +297,7 @@ __device__ __forceinline__ void march_warp(const VolumeDev &v, WarpCache &wc, co
   const bool fin = n != 0;
   if (__any_sync(0xFFFFFFFFu, fin))
     fold_warp<BOUNDED, DIR>(v, wc, fin, ax, ay, az, su, wu, n, conf, conf_q, cp, cq,
-                            check_bounds, tl, cdi, cslot);
+                            check_bounds, tl, cdi, cslot, neg);
   tl.ev_p += (uint32_t)cnt * cp;
   tl.ev_q += (uint32_t)cnt * cq;
 }

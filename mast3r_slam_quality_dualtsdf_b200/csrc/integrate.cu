@@ -365,6 +365,7 @@ static MarchConst make_consts(const b200tsdf *h, int cell_h = 1, int cell_w = 1)
   mc.cell_h_shift = pow2_shift(mc.cell_h);
   mc.cell_w_shift = pow2_shift(mc.cell_w);
   mc.use_dir = h->d.dir_on;
+  mc.negate = 0;
   return mc;
 }
 
@@ -423,11 +424,10 @@ extern "C" int b200tsdf_integrate_points(b200tsdf_t *h, const void *pts_dev, int
   return B200TSDF_OK;
 }
 
-extern "C" int b200tsdf_integrate_keyframes(b200tsdf_t *h, const float *X_dev, const float *C_dev,
-                                            const float *q_grid_dev, const float *pose_dev,
-                                            int32_t B, int32_t H, int32_t W, int32_t gh,
-                                            int32_t gw, float min_conf, double step_scale,
-                                            void *stream) {
+static int fuse_keyframes(b200tsdf_t *h, const float *X_dev, const float *C_dev,
+                          const float *q_grid_dev, const float *pose_dev, int32_t B, int32_t H,
+                          int32_t W, int32_t gh, int32_t gw, float min_conf, double step_scale,
+                          void *stream, int negate) {
   if (!h || B < 0 || H <= 0 || W <= 0 || (B > 0 && (!X_dev || !C_dev || !pose_dev))) {
     b200_set_error("b200tsdf_integrate_keyframes: invalid argument");
     return B200TSDF_E_INVALID;
@@ -444,7 +444,8 @@ extern "C" int b200tsdf_integrate_keyframes(b200tsdf_t *h, const float *X_dev, c
   if (step_d < 1.0e-4) step_d = 1.0e-4;
   dim3 grid((unsigned)((W + TILE_W - 1) / TILE_W), (unsigned)((H + TILE_H - 1) / TILE_H),
             (unsigned)B);
-  const MarchConst mc = q_grid_dev ? make_consts(h, H / gh, W / gw) : make_consts(h);
+  MarchConst mc = q_grid_dev ? make_consts(h, H / gh, W / gw) : make_consts(h);
+  mc.negate = negate;
   // TMA staging needs full tiles and 16-byte aligned row segments
   const bool tma = (W % TILE_W == 0) && (H % TILE_H == 0) && (((uintptr_t)X_dev & 15) == 0) &&
                    (((uintptr_t)C_dev & 15) == 0);
@@ -464,6 +465,24 @@ extern "C" int b200tsdf_integrate_keyframes(b200tsdf_t *h, const float *X_dev, c
 #undef LAUNCH_KF
   B200_CUDA(cudaGetLastError());
   return B200TSDF_OK;
+}
+
+extern "C" int b200tsdf_integrate_keyframes(b200tsdf_t *h, const float *X_dev, const float *C_dev,
+                                            const float *q_grid_dev, const float *pose_dev,
+                                            int32_t B, int32_t H, int32_t W, int32_t gh,
+                                            int32_t gw, float min_conf, double step_scale,
+                                            void *stream) {
+  return fuse_keyframes(h, X_dev, C_dev, q_grid_dev, pose_dev, B, H, W, gh, gw, min_conf,
+                        step_scale, stream, 0);
+}
+
+extern "C" int b200tsdf_deintegrate_keyframes(b200tsdf_t *h, const float *X_dev,
+                                              const float *C_dev, const float *q_grid_dev,
+                                              const float *pose_dev, int32_t B, int32_t H,
+                                              int32_t W, int32_t gh, int32_t gw, float min_conf,
+                                              double step_scale, void *stream) {
+  return fuse_keyframes(h, X_dev, C_dev, q_grid_dev, pose_dev, B, H, W, gh, gw, min_conf,
+                        step_scale, stream, 1);
 }
 
 int b200_ensure_stage(b200tsdf *h, size_t bytes);

@@ -23,6 +23,7 @@ struct MarchConst {
   // quality grid cell size in pixels (H / gh, W / gw) and shifts when a power of two (-1: divide)
   int cell_h, cell_w, cell_h_shift, cell_w_shift;
   int use_dir; // bounded volume with a block directory
+  int negate;  // 1: de-integration (sums and hit counters are subtracted)
 };
 
 struct Tally {

@@ -59,6 +59,11 @@ class TSDFGlobalIntegrator(threading.Thread):
         self.patch_size = int(cfg.get("patch_size", 16))
         self._last_log = time.time()
         self.integrated = 0
+        # "additive" = the reference (old contribution stays, global_manager.py:71-79);
+        # "replace" = de-integrate the keyframe at the pose it was fused with, then fuse
+        # it at the new pose
+        self.reintegration_mode = str(cfg.get("reintegration_mode", "additive"))
+        self._fused = {}  # idx -> (X, C, pose, q, H, W) exactly as fused
 
     def request_stop(self) -> None:
         self.stop_flag.set()
@@ -127,6 +132,14 @@ class TSDFGlobalIntegrator(threading.Thread):
                 fid = getattr(frame, "frame_id", idx)
                 q = quality_grid_from_result(self.quality_service.get(fid),
                                              H // self.patch_size, W // self.patch_size, dev)
+            if self.reintegration_mode == "replace":
+                old = self._fused.pop(idx, None)
+                if old is not None:
+                    self.volume.deintegrate_keyframes(old[0], old[1], old[2], old[3],
+                                                      self.min_conf, old[4], old[5])
+                # private copies: the removal must see exactly what was fused
+                X, Cf, pose = X.clone(), Cf.clone(), pose.clone()
+                self._fused[idx] = (X, Cf, pose, q, H, W)
             self.volume.integrate_keyframes(X, Cf, pose, q, self.min_conf, H, W)
             torch.cuda.current_stream(dev).synchronize()  # inputs may change after the lock
         self.integrated += 1

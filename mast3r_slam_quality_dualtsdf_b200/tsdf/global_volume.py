@@ -117,8 +117,15 @@ class TSDFVolume:
                 _stream_ptr(self.device)), "integrate_points")
         return int(fused.value)
 
+    def deintegrate_keyframes(self, X, Cf, poses, q_grid=None, min_conf=0.05, H=None, W=None,
+                              step_scale=0.5):
+        """Exact inverse of `integrate_keyframes` for the same device tensors
+        (new: the reference never removes a stale contribution)."""
+        return self.integrate_keyframes(X, Cf, poses, q_grid, min_conf, H, W, step_scale,
+                                        _negate=True)
+
     def integrate_keyframes(self, X, Cf, poses, q_grid=None, min_conf=0.05, H=None, W=None,
-                            step_scale=0.5):
+                            step_scale=0.5, _negate=False):
         """Fused staging + allocation + dual fold for a batch of keyframes
         (replaces global_manager.py:81-106 per keyframe).  Tensors may live on
         the device (zero-copy) or on the host (copied inside the call).
@@ -140,7 +147,10 @@ class TSDFVolume:
             if t.dtype != torch.float32 or not t.is_contiguous() or t.is_cuda != on_dev:
                 raise ValueError("keyframe tensors must be contiguous float32 on one device")
         Xc, Cc, Pc = ts[0], ts[1], ts[2]
-        fn = (_ffi.lib().b200tsdf_integrate_keyframes if on_dev
+        if _negate and not on_dev:
+            raise ValueError("deintegrate_keyframes needs device tensors")
+        fn = (_ffi.lib().b200tsdf_deintegrate_keyframes if _negate else
+              _ffi.lib().b200tsdf_integrate_keyframes if on_dev
               else _ffi.lib().b200tsdf_integrate_keyframes_host)
         with self._lock:
             _ffi.check(fn(self._h, Xc.data_ptr(), Cc.data_ptr(),

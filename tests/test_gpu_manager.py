@@ -148,3 +148,53 @@ def test_manager_threads_start_and_stop(cuda_device):
     assert not mgr.integrator.is_alive() and not mgr.opt_worker.is_alive()
     assert mgr.integrator.integrated == 3  # 2 new + 1 re-integration (keyframe 0 is pinned)
     assert torch.isfinite(kfs.T_WC[1]).all() and kfs.T_WC[1].shape == before.shape
+
+
+def test_deintegrate_is_the_exact_inverse(cuda_device):
+    """integrate A, B, C then remove B == integrate A, C
+    (voxel key set and hit counters exact, tsdf / weight within tolerance)."""
+    from mast3r_slam_quality_dualtsdf_b200 import synth
+    from mast3r_slam_quality_dualtsdf_b200.tsdf import TSDFVolume
+
+    kf = synth.make_keyframes(synth.SCENES["sphere"], 3, H=48, W=64, seed=8, f=50.0, total=9)
+    t = {k: torch.from_numpy(kf[k]).to(cuda_device) for k in ("X", "C", "pose", "q")}
+    vol = TSDFVolume(0.03, 0.12, device=cuda_device)
+    vol.integrate_keyframes(t["X"], t["C"], t["pose"], t["q"], 0.05, 48, 64)
+    sl = slice(1, 2)
+    vol.deintegrate_keyframes(t["X"][sl].contiguous(), t["C"][sl].contiguous(),
+                              t["pose"][sl].contiguous(), t["q"][sl].contiguous(), 0.05, 48, 64)
+    vp, vq, _ = oracle_dual(kf, 0.03, 0.12, idx=[0, 2])
+    for which, want in ((0, vp), (1, vq)):
+        gk, gt, gw, gc = vol.export(which)
+        wk, wt, ww, wc = want.export()
+        assert np.array_equal(gk, wk) and np.array_equal(gc.astype(np.int64), wc.astype(np.int64))
+        assert np.abs(gt - wt).max() <= 5e-5  # float32 cancellation of the removed sums
+        assert (np.abs(gw - ww) / np.maximum(1.0, ww)).max() <= 5e-5
+    assert vol.stats(0) == vp.stats()
+
+
+def test_manager_replace_mode_removes_the_stale_pose(cuda_device):
+    from mast3r_slam_quality_dualtsdf_b200 import synth
+    from mast3r_slam_quality_dualtsdf_b200.tsdf import TSDFGlobalManager
+
+    kf = synth.make_keyframes(synth.SCENES["sphere"], 3, H=48, W=64, seed=3, f=50.0, total=12)
+    kfs = _keyframes(kf, kf["pose"], cuda_device)
+    cfg = {"enabled": True, "voxel_size": 0.03, "trunc_dist": 0.12, "min_confidence": 0.05,
+           "async_optimize": False, "max_iterations": 0, "pin": 1,
+           "reintegration_mode": "replace"}
+    mgr = TSDFGlobalManager(kfs, cfg, False, cuda_device)
+    mgr.integrator.step()
+    # the backend moves keyframe 2; the manager replaces its contribution
+    new_pose = kf["pose"][2].copy()
+    new_pose[:3] += np.array([0.02, -0.01, 0.015], np.float32)
+    kfs.T_WC[2] = torch.from_numpy(new_pose).to(cuda_device).reshape(1, 8)
+    mgr.on_after_backend_solve(types.SimpleNamespace(last_unique_kf_idx=torch.tensor([0, 2])))
+    mgr.integrator.step()
+    moved = dict(kf)
+    moved["pose"] = kf["pose"].copy()
+    moved["pose"][2] = new_pose
+    vp, _, _ = oracle_dual(moved, 0.03, 0.12, use_q=False)
+    gk, gt, gw, gc = mgr.volume.export(0)
+    wk, wt, ww, wc = vp.export()
+    assert np.array_equal(gk, wk) and np.array_equal(gc.astype(np.int64), wc.astype(np.int64))
+    assert np.abs(gt - wt).max() <= 5e-5
