@@ -330,7 +330,9 @@ __global__ void __launch_bounds__(256, FUSE_MINB)
       if (have) ray_finish<float>(r, rx, ry, rz, P[0], P[1], P[2], step, mc.trunc);
     }
   }
-  march_warp<BOUNDED, DIR>(v, wc, mc, have, r, c, cq, true, tl);
+  // a warp whose rays were all filtered / culled skips the march altogether
+  if (__any_sync(0xFFFFFFFFu, have))
+    march_warp<BOUNDED, DIR>(v, wc, mc, have, r, c, cq, true, tl);
   commit_tally(v, tl);
 }
 

@@ -32,12 +32,18 @@ struct Tally {
 
 // ev_* arrive as ENUMERATED in-band samples; applied = enumerated - dropped.
 __device__ __forceinline__ void commit_tally(const VolumeDev &v, Tally tl) {
+  const uint32_t rare = tl.drop_p | tl.drop_q | tl.overflow | tl.culled;
+  const bool any_rare = __any_sync(0xFFFFFFFFu, rare != 0);
   tl.rays = __reduce_add_sync(0xFFFFFFFFu, tl.rays);
+  if (tl.rays == 0 && !any_rare) return; // nothing to report (warp-uniform)
   tl.ev_p = __reduce_add_sync(0xFFFFFFFFu, tl.ev_p - tl.drop_p);
   tl.ev_q = __reduce_add_sync(0xFFFFFFFFu, tl.ev_q - tl.drop_q);
-  uint32_t dropped = __reduce_add_sync(0xFFFFFFFFu, tl.drop_p + tl.drop_q);
-  tl.overflow = __reduce_add_sync(0xFFFFFFFFu, tl.overflow);
-  tl.culled = __reduce_add_sync(0xFFFFFFFFu, tl.culled);
+  uint32_t dropped = 0;
+  if (any_rare) { // out-of-bounds / foreign-slab drops, overflow, culled rays
+    dropped = __reduce_add_sync(0xFFFFFFFFu, tl.drop_p + tl.drop_q);
+    tl.overflow = __reduce_add_sync(0xFFFFFFFFu, tl.overflow);
+    tl.culled = __reduce_add_sync(0xFFFFFFFFu, tl.culled);
+  }
 #ifdef FUSE_DBG_NO_TALLY
   if (tl.rays == 0xFFFFFFFFu)
 #else
@@ -48,8 +54,10 @@ __device__ __forceinline__ void commit_tally(const VolumeDev &v, Tally tl) {
     if (tl.rays) atomicAdd(ctr + CTR_RAYS, (unsigned long long)tl.rays);
     if (tl.ev_p) atomicAdd(ctr + CTR_EV_P, (unsigned long long)tl.ev_p);
     if (tl.ev_q) atomicAdd(ctr + CTR_EV_Q, (unsigned long long)tl.ev_q);
-    if (dropped) atomicAdd(ctr + CTR_DROPPED, (unsigned long long)dropped);
-    if (tl.overflow) atomicAdd(ctr + CTR_OVERFLOW, (unsigned long long)tl.overflow);
-    if (tl.culled) atomicAdd(ctr + CTR_CULLED, (unsigned long long)tl.culled);
+    if (any_rare) {
+      if (dropped) atomicAdd(ctr + CTR_DROPPED, (unsigned long long)dropped);
+      if (tl.overflow) atomicAdd(ctr + CTR_OVERFLOW, (unsigned long long)tl.overflow);
+      if (tl.culled) atomicAdd(ctr + CTR_CULLED, (unsigned long long)tl.culled);
+    }
   }
 }
