@@ -56,11 +56,13 @@ struct VolumeDev {
   // z-slab ownership (multi-GPU): slab s = (kz - slab_z0) >> slab_shift is
   // owned iff s mod slab_count == slab_index
   int slab_count, slab_index, slab_shift, slab_z0;
+  int slab_mask; // slab_count - 1 when slab_count is a power of two, else -1
 };
 
 #define B200_NO_SLOT 0xFFFFFFFFu
 
 __host__ __device__ __forceinline__ int slab_owner_of(const VolumeDev &v, int s) {
+  if (v.slab_mask >= 0) return s & v.slab_mask; // two's complement: also right for s < 0
   int m = s % v.slab_count;
   return m < 0 ? m + v.slab_count : m;
 }
@@ -81,6 +83,11 @@ struct b200tsdf {
   cudaEvent_t copy_ev[B200_H2D_CHUNKS + 1];
   unsigned long long *scratch; // small device scratch (counters for sweeps)
   uint32_t *nbr;               // marching cubes: 8 neighbour slots per block (lazy)
+  // multi-GPU fuse: tile list of the classify pass, [0] list length / [1] ticket cursor
+  int *tile_list;
+  size_t tile_cap;
+  unsigned int *sched;
+  int sm_count;
 };
 
 // ---------------------------------------------------------------- hashing

@@ -237,103 +237,288 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t phase) {
       : "memory");
 }
 
+// multi-GPU: the band's z extent lies within trunc (+3 voxels) of the surface
+// point; true when no slab of this rank is within that reach (conservative).
+__device__ __forceinline__ bool slab_zmiss_vox(const VolumeDev &v, float zc, float ext) {
+  if (!(fabsf(zc) < 1.0e9f)) return false; // the per-voxel test decides
+  const int s_lo = ((int)floorf(zc - ext) - v.slab_z0) >> v.slab_shift;
+  const int s_hi = ((int)floorf(zc + ext) - v.slab_z0) >> v.slab_shift;
+  int need = v.slab_index - slab_owner_of(v, s_lo);
+  if (need < 0) need += v.slab_count;
+  return need > s_hi - s_lo;
+}
+// The in-band samples of a ray lie within trunc * |dz| of the surface point in
+// z (dz = z component of the unit direction); + 2.5 voxels for the floor and
+// rounding.  d2 = squared ray length, az = its z component.
+__device__ __forceinline__ float band_reach_vox(const MarchConst &mc, float az, float d2) {
+  float dz = fabsf(az) * rsqrtf(d2);
+  if (!(dz < 1.0f)) dz = 1.0f; // also d2 = 0 / NaN
+  return fmaf(mc.trunc * mc.inv_vs, dz, 2.5f);
+}
+// A ray the reference would fuse (global_volume.py:56: finite, len >= 1e-4)?
+// Certain when 1e-3 < len < 3e18; otherwise the exact ray_length decides.
+__device__ __forceinline__ bool surely_a_ray(float d2) { return d2 > 1.0e-6f && d2 < 1.0e37f; }
+
+// One pixel per lane: Sim3 act, slab cull, ray set-up, warp-converged march.
+// `take` = the pixel passed the confidence filter (global_manager.py:92).
+// The order keeps a rank's cost for rays of OTHER ranks minimal: world point,
+// conservative z test, and only for survivors the exact length (sqrt, float64
+// sum), the divisions of the ray set-up and the quality-grid lookup.
+template <bool BOUNDED, bool DIR>
+__device__ __forceinline__ void fuse_pixels_warp(const VolumeDev &v, WarpCache &wc,
+                                                 const MarchConst &mc, const float *P, bool take,
+                                                 float c, float x0, float x1, float x2, float step,
+                                                 const float *__restrict__ qg, long long q_base,
+                                                 int gh, int gw, int px, int py, Tally &tl) {
+  Ray<float> r = {};
+  bool have = false;
+  if (take) {
+    float wx, wy, wz;
+    sim3_act(P, x0, x1, x2, wx, wy, wz);
+    const float ax = wx - P[0], ay = wy - P[1], az = wz - P[2];
+    const float d2 = fmaf(ax, ax, fmaf(ay, ay, az * az));
+    const bool zmiss = BOUNDED && v.slab_count > 1 &&
+                       slab_zmiss_vox(v, wz * mc.inv_vs, band_reach_vox(mc, az, d2));
+    const bool counted = zmiss && surely_a_ray(d2);
+    if (counted) {
+      tl.rays += 1;
+      tl.culled += 1;
+    } else {
+      float rx, ry, rz;
+      have = ray_length<float>(r, wx, wy, wz, P[0], P[1], P[2], rx, ry, rz);
+      if (have) {
+        tl.rays += 1;
+        if (zmiss) {
+          have = false;
+          tl.culled += 1;
+        } else {
+          ray_finish<float>(r, rx, ry, rz, P[0], P[1], P[2], step, mc.trunc);
+        }
+      }
+    }
+  }
+  // a warp whose rays were all filtered / culled skips the march altogether
+  if (__any_sync(0xFFFFFFFFu, have)) {
+    float cq = c;
+    if (qg) { // nearest-neighbour upsample of the per-patch quality weight
+      int gy = mc.cell_h_shift >= 0 ? py >> mc.cell_h_shift : py / mc.cell_h;
+      int gx = mc.cell_w_shift >= 0 ? px >> mc.cell_w_shift : px / mc.cell_w;
+      gy = min(gy, gh - 1), gx = min(gx, gw - 1);
+      cq = c * __ldg(qg + q_base + (long long)gy * gw + gx);
+    }
+    march_warp<BOUNDED, DIR>(v, wc, mc, have, r, c, cq, true, tl);
+  }
+}
+
 #define TILE_W 32
 #define TILE_H 8
 #define SX_ROW 104 // floats per staged X row: 96 + 8 pad (bank-conflict-free, 16 B multiple)
 #define SC_ROW 40  // floats per staged C row: 32 + 8 pad
 
-template <bool BOUNDED, bool DIR, bool TMA>
-__global__ void __launch_bounds__(256, FUSE_MINB)
-    integrate_keyframes_kernel(VolumeDev v, const float *__restrict__ X,
-                               const float *__restrict__ C, const float *__restrict__ qg,
-                               const float *__restrict__ poses, int H, int W, int gh, int gw,
-                               float min_conf, float step, MarchConst mc) {
-  // CTA = 32 x 8 pixel tile, warp = 8 x 4 sub-tile: rays of a warp stay close
-  // in the volume, so their reductions share 32-byte sectors.
-  __shared__ WarpCache wcs[DIR ? 1 : 8];
-  __shared__ __align__(128) float sX[TMA ? TILE_H * SX_ROW : 4];
-  __shared__ __align__(128) float sC[TMA ? TILE_H * SC_ROW : 4];
-  __shared__ __align__(8) unsigned long long s_bar;
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  WarpCache &wc = wcs[DIR ? 0 : warp];
-  const int kf = blockIdx.z;
-  const long long npix = (long long)H * W;
-  const int tx = (warp & 3) * 8 + (lane & 7), ty = (warp >> 2) * 4 + (lane >> 3);
-  const int px = blockIdx.x * TILE_W + tx, py = blockIdx.y * TILE_H + ty;
-  if (TMA) { // host guarantees full tiles and 16-byte aligned rows
-    const uint32_t bar = smem_u32(&s_bar);
-    if (threadIdx.x == 0) {
-      mbar_init(bar, 1);
-      mbar_expect_tx(bar, TILE_H * (TILE_W * 12 + TILE_W * 4));
-      const long long p0 = kf * npix + (long long)(blockIdx.y * TILE_H) * W + blockIdx.x * TILE_W;
+struct KfArgs { // one keyframe batch (device pointers)
+  const float *X, *C, *qg, *poses;
+  int H, W, gh, gw;
+  float min_conf, step;
+};
+
+// thread 0: TMA bulk copies of tile (bx, by) of keyframe kf into shared memory
+__device__ __forceinline__ void tile_issue(const KfArgs &a, float *sX, float *sC, uint32_t bar,
+                                           int bx, int by, int kf) {
+  mbar_expect_tx(bar, TILE_H * (TILE_W * 12 + TILE_W * 4));
+  const long long p0 = (long long)kf * a.H * a.W + (long long)(by * TILE_H) * a.W + bx * TILE_W;
 #pragma unroll
-      for (int row = 0; row < TILE_H; ++row) {
-        bulk_g2s(smem_u32(sX + row * SX_ROW), X + (p0 + (long long)row * W) * 3, TILE_W * 12, bar);
-        bulk_g2s(smem_u32(sC + row * SC_ROW), C + p0 + (long long)row * W, TILE_W * 4, bar);
-      }
-    }
+  for (int row = 0; row < TILE_H; ++row) {
+    bulk_g2s(smem_u32(sX + row * SX_ROW), a.X + (p0 + (long long)row * a.W) * 3, TILE_W * 12, bar);
+    bulk_g2s(smem_u32(sC + row * SC_ROW), a.C + p0 + (long long)row * a.W, TILE_W * 4, bar);
   }
-  if (!DIR) warp_cache_init(wc);
-  const float *P = poses + 8 * kf;
-  float q = 1.0f;
-  if (qg) { // nearest-neighbour upsample of the per-patch quality weight
-    int gy = mc.cell_h_shift >= 0 ? py >> mc.cell_h_shift : py / mc.cell_h;
-    int gx = mc.cell_w_shift >= 0 ? px >> mc.cell_w_shift : px / mc.cell_w;
-    gy = min(gy, gh - 1), gx = min(gx, gw - 1);
-    q = __ldg(qg + ((long long)kf * gh + gy) * gw + gx);
-  }
-  Tally tl = {0, 0, 0, 0, 0, 0, 0};
-  Ray<float> r = {};
-  bool have = false;
-  float c = 0.f, cq = 0.f, x0 = 0.f, x1 = 0.f, x2 = 0.f;
+}
+
+// CTA = 32 x 8 pixel tile, warp = 8 x 4 sub-tile: rays of a warp stay close in
+// the volume, so their reductions share 32-byte sectors.
+template <bool BOUNDED, bool DIR, bool TMA>
+__device__ __forceinline__ void tile_consume(const VolumeDev &v, WarpCache &wc, const KfArgs &a,
+                                             const MarchConst &mc, const float *sX,
+                                             const float *sC, uint32_t bar, uint32_t phase,
+                                             int bx, int by, int kf, Tally &tl) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int tx = (warp & 3) * 8 + (lane & 7), ty = (warp >> 2) * 4 + (lane >> 3);
+  const int px = bx * TILE_W + tx, py = by * TILE_H + ty;
+  float c = 0.f, x0 = 0.f, x1 = 0.f, x2 = 0.f;
   bool in_img = true;
-  if (TMA) {
-    __syncthreads(); // mbarrier init visible to the waiters
-    mbar_wait(smem_u32(&s_bar), 0);
+  if (TMA) { // host guarantees full tiles and 16-byte aligned rows
+    mbar_wait(bar, phase);
     c = sC[ty * SC_ROW + tx];
     x0 = sX[ty * SX_ROW + tx * 3], x1 = sX[ty * SX_ROW + tx * 3 + 1],
     x2 = sX[ty * SX_ROW + tx * 3 + 2];
   } else {
-    in_img = px < W && py < H;
+    in_img = px < a.W && py < a.H;
     if (in_img) {
-      const long long pix = (long long)py * W + px;
-      c = C[kf * npix + pix];
-      if (c > min_conf) {
-        const float *x = X + (kf * npix + pix) * 3;
+      const long long pix = (long long)kf * a.H * a.W + (long long)py * a.W + px;
+      c = a.C[pix];
+      if (c > a.min_conf) {
+        const float *x = a.X + pix * 3;
         x0 = x[0], x1 = x[1], x2 = x[2];
       }
     }
   }
-  if (in_img && c > min_conf) { // global_manager.py:92
-    float wx, wy, wz;
-    sim3_act(P, x0, x1, x2, wx, wy, wz);
-    float rx, ry, rz;
-    have = ray_length<float>(r, wx, wy, wz, P[0], P[1], P[2], rx, ry, rz);
-    if (have) {
-      tl.rays = 1;
-      cq = c * q;
-      // multi-GPU: cheap conservative pre-cull before the divisions of the ray
-      // set-up -- the band's z extent lies within trunc (+3 voxels) of the point
-      if (BOUNDED && v.slab_count > 1) {
-        const float zc = wz * mc.inv_vs, ext = mc.trunc * mc.inv_vs + 3.0f;
-        if (fabsf(zc) < 1.0e9f) {
-          const int s_lo = ((int)floorf(zc - ext) - v.slab_z0) >> v.slab_shift;
-          const int s_hi = ((int)floorf(zc + ext) - v.slab_z0) >> v.slab_shift;
-          int need = v.slab_index - slab_owner_of(v, s_lo);
-          if (need < 0) need += v.slab_count;
-          if (need > s_hi - s_lo) { // no slab of this rank within reach
-            have = false;
-            tl.culled += 1;
-          }
-        }
-      }
-      if (have) ray_finish<float>(r, rx, ry, rz, P[0], P[1], P[2], step, mc.trunc);
+  fuse_pixels_warp<BOUNDED, DIR>(v, wc, mc, a.poses + 8 * (long long)kf,
+                                 in_img && c > a.min_conf, c, x0, x1, x2, a.step, a.qg,
+                                 (long long)kf * a.gh * a.gw, a.gh, a.gw, px, py, tl);
+}
+
+// One CTA per tile (grid = tiles_x, tiles_y, keyframes): the single-GPU path.
+template <bool BOUNDED, bool DIR, bool TMA>
+__global__ void __launch_bounds__(256, FUSE_MINB)
+    integrate_keyframes_kernel(VolumeDev v, KfArgs a, MarchConst mc) {
+  __shared__ WarpCache wcs[DIR ? 1 : 8];
+  __shared__ __align__(128) float sX[TMA ? TILE_H * SX_ROW : 4];
+  __shared__ __align__(128) float sC[TMA ? TILE_H * SC_ROW : 4];
+  __shared__ __align__(8) unsigned long long s_bar;
+  WarpCache &wc = wcs[DIR ? 0 : (threadIdx.x >> 5)];
+  const uint32_t bar = smem_u32(&s_bar);
+  if (TMA && threadIdx.x == 0) {
+    mbar_init(bar, 1);
+    tile_issue(a, sX, sC, bar, blockIdx.x, blockIdx.y, blockIdx.z);
+  }
+  if (!DIR) warp_cache_init(wc);
+  if (TMA) __syncthreads(); // mbarrier init visible to the waiters
+  Tally tl = {0, 0, 0, 0, 0, 0, 0};
+  tile_consume<BOUNDED, DIR, TMA>(v, wc, a, mc, sX, sC, bar, 0, blockIdx.x, blockIdx.y,
+                                  blockIdx.z, tl);
+  commit_tally(v, tl);
+}
+
+// ---- multi-GPU (z-slab ownership): two launches per batch.
+// (1) slab_classify_kernel streams the whole batch once at full occupancy
+//     (plain coalesced loads, ~30 registers): a tile with at least one ray that
+//     can reach a slab of this rank goes on the tile list; the rays of every
+//     other tile are counted (rays, culled) here and never touched again.
+// (2) integrate_keyframes_listed_kernel: persistent CTAs take listed tiles
+//     through a ticket counter and run the same tile path as above.
+// A rank's cost is then one streaming pass plus the march of its own tiles,
+// instead of a full-weight CTA per foreign tile.  sched[0] = list length,
+// sched[1] = ticket cursor (zeroed on the stream before (1)).
+#define CLS_TILES 4 // tiles per classify CTA: 4 x 4 independent loads per thread in flight
+
+__global__ void __launch_bounds__(256)
+    slab_classify_kernel(VolumeDev v, KfArgs a, MarchConst mc, int *__restrict__ list,
+                         unsigned int *sched, int tiles_x, int tiles_y) {
+  // CTA = CLS_TILES consecutive tiles of one tile row; thread = one pixel of each
+  const int lx = threadIdx.x & 31, py = blockIdx.y * TILE_H + (threadIdx.x >> 5);
+  const int kf = blockIdx.z;
+  const float *P = a.poses + 8 * (long long)kf;
+  const long long row = (long long)kf * a.H * a.W + (long long)py * a.W;
+  float c[CLS_TILES], x0[CLS_TILES], x1[CLS_TILES], x2[CLS_TILES];
+#pragma unroll
+  for (int t = 0; t < CLS_TILES; ++t) { // all loads first (the pass is latency-bound otherwise)
+    const int px = (blockIdx.x * CLS_TILES + t) * TILE_W + lx;
+    c[t] = 0.f, x0[t] = x1[t] = x2[t] = 0.f;
+    if (px < a.W && py < a.H) {
+      c[t] = a.C[row + px];
+      const float *x = a.X + (row + px) * 3;
+      x0[t] = x[0], x1[t] = x[1], x2[t] = x[2];
     }
   }
-  // a warp whose rays were all filtered / culled skips the march altogether
-  if (__any_sync(0xFFFFFFFFu, have))
-    march_warp<BOUNDED, DIR>(v, wc, mc, have, r, c, cq, true, tl);
+  // world z in voxels, z = s * (row 2 of the rotation sim3_act applies) . x + t_z.
+  // Not the exact operation order, so the reach is widened by a bound on the
+  // rounding difference (+1 voxel): "miss" here implies the exact test misses.
+  const float q0 = P[3], q1 = P[4], q2 = P[5], q3 = P[6], sv = P[7] * mc.inv_vs;
+  const float k0 = 2.0f * (q0 * q2 - q1 * q3) * sv, k1 = 2.0f * (q1 * q2 + q0 * q3) * sv,
+              k2 = (1.0f - 2.0f * (q0 * q0 + q1 * q1)) * sv, tzv = P[2] * mc.inv_vs;
+  const float s2 = P[7] * P[7], tv = mc.trunc * mc.inv_vs;
+  Tally tl = {0, 0, 0, 0, 0, 0, 0};
+#pragma unroll
+  for (int t = 0; t < CLS_TILES; ++t) {
+    const int bx = blockIdx.x * CLS_TILES + t;
+    if (bx >= tiles_x) break; // uniform
+    const int px = bx * TILE_W + lx;
+    const bool take = px < a.W && py < a.H && c[t] > a.min_conf;
+    bool zmiss = false;
+    if (take) {
+      const float zc = fmaf(x0[t], k0, fmaf(x1[t], k1, fmaf(x2[t], k2, tzv)));
+      const float mag = fmaf(fabsf(x0[t]), fabsf(k0),
+                             fmaf(fabsf(x1[t]), fabsf(k1), fmaf(fabsf(x2[t]), fabsf(k2), fabsf(tzv))));
+      // reach as in band_reach_vox, from len = s * |x|, widened by 1% + 1 voxel
+      const float d2 = s2 * fmaf(x0[t], x0[t], fmaf(x1[t], x1[t], x2[t] * x2[t]));
+      float dz = fmaf(fabsf(zc - tzv) * mc.vs * rsqrtf(d2), 1.01f, 1.0e-3f);
+      if (!(dz < 1.0f)) dz = 1.0f;
+      zmiss = slab_zmiss_vox(v, zc, fmaf(tv, dz, fmaf(mag, 4.0e-6f, 3.5f)));
+    }
+    if (__syncthreads_or(take && !zmiss)) { // the fuse pass counts this tile's rays itself
+      if (threadIdx.x == 0)
+        list[atomicAdd(sched, 1u)] = (kf * tiles_y + blockIdx.y) * tiles_x + bx;
+    } else if (take) { // exactly the accounting of fuse_pixels_warp for a culled ray
+      // len = s * |x| up to rounding: certainly a ray when 2e-3 < len < 1e18
+      const float d2 = s2 * fmaf(x0[t], x0[t], fmaf(x1[t], x1[t], x2[t] * x2[t]));
+      bool ray = d2 > 4.0e-6f && d2 < 1.0e36f;
+      if (!ray) {
+        float wx, wy, wz, rx, ry, rz;
+        sim3_act(P, x0[t], x1[t], x2[t], wx, wy, wz);
+        Ray<float> r;
+        ray = ray_length<float>(r, wx, wy, wz, P[0], P[1], P[2], rx, ry, rz);
+      }
+      if (ray) tl.rays += 1, tl.culled += 1;
+    }
+  }
   commit_tally(v, tl);
+}
+
+// Persistent CTAs over the tile list, double-buffered: while tile k is marched,
+// the TMA copies of tile k+1 are in flight, the list entry of tile k+2 is being
+// read and the ticket after that is being fetched (thread 0 keeps them in
+// registers and never waits on a value it requested in the same iteration).
+template <bool BOUNDED, bool DIR, bool TMA>
+__global__ void __launch_bounds__(256, FUSE_MINB)
+    integrate_keyframes_listed_kernel(VolumeDev v, KfArgs a, MarchConst mc,
+                                      const int *__restrict__ list, unsigned int *sched,
+                                      int tiles_x, int tiles_y) {
+  __shared__ WarpCache wcs[DIR ? 1 : 8];
+  __shared__ __align__(128) float sX[2][TMA ? TILE_H * SX_ROW : 4];
+  __shared__ __align__(128) float sC[2][TMA ? TILE_H * SC_ROW : 4];
+  __shared__ __align__(8) unsigned long long s_bar[2];
+  __shared__ int s_tile[2];
+  WarpCache &wc = wcs[DIR ? 0 : (threadIdx.x >> 5)];
+  const int tiles_kf = tiles_x * tiles_y;
+  const unsigned int n_list = *(volatile unsigned int *)sched;
+  auto lookup = [&](unsigned int t) { return t < n_list ? list[t] : -1; };
+  auto issue = [&](int tile, int b) {
+    if (TMA && tile >= 0) {
+      const int kf = tile / tiles_kf, rem = tile - kf * tiles_kf;
+      const int by = rem / tiles_x;
+      tile_issue(a, sX[b], sC[b], smem_u32(&s_bar[b]), rem - by * tiles_x, by, kf);
+    }
+  };
+  int nxt = -1;          // thread 0: tile of the next iteration
+  unsigned int pend = 0; // thread 0: ticket of the iteration after that
+  if (threadIdx.x == 0) {
+    if (TMA) mbar_init(smem_u32(&s_bar[0]), 1), mbar_init(smem_u32(&s_bar[1]), 1);
+    const int cur = lookup(atomicAdd(sched + 1, 1u));
+    issue(cur, 0);
+    s_tile[0] = cur;
+    nxt = cur >= 0 ? lookup(atomicAdd(sched + 1, 1u)) : -1;
+    pend = nxt >= 0 ? atomicAdd(sched + 1, 1u) : 0xFFFFFFFFu;
+  }
+  if (!DIR) warp_cache_init(wc);
+  for (unsigned int k = 0;; ++k) {
+    __syncthreads(); // tile k-1 is consumed: its buffers and s_tile slot are free
+    const int b = k & 1;
+    const int tile = s_tile[b];
+    if (tile < 0) break;
+    if (threadIdx.x == 0) {
+      issue(nxt, b ^ 1);
+      s_tile[b ^ 1] = nxt;
+      if (nxt >= 0) {
+        nxt = lookup(pend);
+        pend = atomicAdd(sched + 1, 1u);
+      }
+    }
+    const int kf = tile / tiles_kf, rem = tile - kf * tiles_kf;
+    const int by = rem / tiles_x;
+    Tally tl = {0, 0, 0, 0, 0, 0, 0};
+    tile_consume<BOUNDED, DIR, TMA>(v, wc, a, mc, sX[b], sC[b], smem_u32(&s_bar[b]), (k >> 1) & 1u,
+                                    rem - by * tiles_x, by, kf, tl);
+    commit_tally(v, tl);
+  }
 }
 
 // ------------------------------------------------------------------ C ABI
@@ -448,23 +633,48 @@ static int fuse_keyframes(b200tsdf_t *h, const float *X_dev, const float *C_dev,
             (unsigned)B);
   MarchConst mc = q_grid_dev ? make_consts(h, H / gh, W / gw) : make_consts(h);
   mc.negate = negate;
-  // TMA staging needs full tiles and 16-byte aligned row segments
-  const bool tma = (W % TILE_W == 0) && (H % TILE_H == 0) && (((uintptr_t)X_dev & 15) == 0) &&
-                   (((uintptr_t)C_dev & 15) == 0);
-#define LAUNCH_KF(BD, DR, TM)                                                                  \
-  integrate_keyframes_kernel<BD, DR, TM><<<grid, 256, 0, st>>>(                                 \
-      h->d, X_dev, C_dev, q_grid_dev, pose_dev, H, W, gh, gw, min_conf, (float)step_d, mc)
+  const bool aligned = (((uintptr_t)X_dev & 15) == 0) && (((uintptr_t)C_dev & 15) == 0);
   const int mode = !use_bounded(h) ? 0 : (h->d.dir_on ? 2 : 1);
-  if (tma) {
-    if (mode == 0) LAUNCH_KF(false, false, true);
-    else if (mode == 1) LAUNCH_KF(true, false, true);
-    else LAUNCH_KF(true, true, true);
-  } else {
-    if (mode == 0) LAUNCH_KF(false, false, false);
-    else if (mode == 1) LAUNCH_KF(true, false, false);
-    else LAUNCH_KF(true, true, false);
+  // TMA staging needs full tiles and 16-byte aligned row segments
+  const bool tma = (W % TILE_W == 0) && (H % TILE_H == 0) && aligned;
+  const KfArgs ka = {X_dev, C_dev, q_grid_dev, pose_dev, H, W, gh, gw, min_conf, (float)step_d};
+#define DISPATCH_KF(LAUNCH)                                                                    \
+  if (tma) {                                                                                   \
+    if (mode == 0) LAUNCH(false, false, true);                                                 \
+    else if (mode == 1) LAUNCH(true, false, true);                                             \
+    else LAUNCH(true, true, true);                                                             \
+  } else {                                                                                     \
+    if (mode == 0) LAUNCH(false, false, false);                                                \
+    else if (mode == 1) LAUNCH(true, false, false);                                            \
+    else LAUNCH(true, true, false);                                                            \
   }
+  const long long n_tiles = (long long)grid.x * grid.y * grid.z;
+  if (h->d.slab_count > 2 && n_tiles < (1ll << 31)) {
+    // multi-GPU: classify pass + persistent fuse over the listed tiles (with two
+    // ranks nearly every tile reaches both, so the direct launch is cheaper)
+    if ((size_t)n_tiles > h->tile_cap) {
+      cudaFree(h->tile_list);
+      h->tile_list = nullptr, h->tile_cap = 0;
+      B200_CUDA(cudaMalloc(&h->tile_list, (size_t)n_tiles * sizeof(int)));
+      h->tile_cap = (size_t)n_tiles;
+    }
+    B200_CUDA(cudaMemsetAsync(h->sched, 0, 2 * sizeof(unsigned int), st));
+    const dim3 cgrid((grid.x + CLS_TILES - 1) / CLS_TILES, grid.y, grid.z);
+    slab_classify_kernel<<<cgrid, 256, 0, st>>>(h->d, ka, mc, h->tile_list, h->sched, (int)grid.x,
+                                                (int)grid.y);
+    const long long cap = (long long)h->sm_count * FUSE_MINB;
+    const unsigned ctas = (unsigned)(n_tiles < cap ? n_tiles : cap);
+#define LAUNCH_LISTED(BD, DR, TM)                                                              \
+  integrate_keyframes_listed_kernel<BD, DR, TM><<<ctas, 256, 0, st>>>(                          \
+      h->d, ka, mc, h->tile_list, h->sched, (int)grid.x, (int)grid.y)
+    DISPATCH_KF(LAUNCH_LISTED)
+#undef LAUNCH_LISTED
+  } else {
+#define LAUNCH_KF(BD, DR, TM) integrate_keyframes_kernel<BD, DR, TM><<<grid, 256, 0, st>>>(h->d, ka, mc)
+    DISPATCH_KF(LAUNCH_KF)
 #undef LAUNCH_KF
+  }
+#undef DISPATCH_KF
   B200_CUDA(cudaGetLastError());
   return B200TSDF_OK;
 }

@@ -31,19 +31,25 @@ struct Tally {
 };
 
 // ev_* arrive as ENUMERATED in-band samples; applied = enumerated - dropped.
+// Every vote / reduction is skipped when no lane has the quantity, so a warp
+// whose rays were all culled pays for two reductions and two atomics only.
 __device__ __forceinline__ void commit_tally(const VolumeDev &v, Tally tl) {
-  const uint32_t rare = tl.drop_p | tl.drop_q | tl.overflow | tl.culled;
-  const bool any_rare = __any_sync(0xFFFFFFFFu, rare != 0);
+  const uint32_t lost = tl.drop_p | tl.drop_q | tl.overflow;
+  const bool any_lost = __any_sync(0xFFFFFFFFu, lost != 0);
+  const bool any_culled = __any_sync(0xFFFFFFFFu, tl.culled != 0);
+  const bool any_ev = __any_sync(0xFFFFFFFFu, (tl.ev_p | tl.ev_q) != 0);
   tl.rays = __reduce_add_sync(0xFFFFFFFFu, tl.rays);
-  if (tl.rays == 0 && !any_rare) return; // nothing to report (warp-uniform)
-  tl.ev_p = __reduce_add_sync(0xFFFFFFFFu, tl.ev_p - tl.drop_p);
-  tl.ev_q = __reduce_add_sync(0xFFFFFFFFu, tl.ev_q - tl.drop_q);
+  if (tl.rays == 0 && !any_lost && !any_culled) return; // nothing to report (warp-uniform)
+  tl.ev_p = any_ev ? __reduce_add_sync(0xFFFFFFFFu, tl.ev_p - tl.drop_p) : 0u;
+  tl.ev_q = any_ev ? __reduce_add_sync(0xFFFFFFFFu, tl.ev_q - tl.drop_q) : 0u;
   uint32_t dropped = 0;
-  if (any_rare) { // out-of-bounds / foreign-slab drops, overflow, culled rays
+  tl.overflow = 0;
+  if (any_lost) { // out-of-bounds / foreign-slab drops, hash overflow
     dropped = __reduce_add_sync(0xFFFFFFFFu, tl.drop_p + tl.drop_q);
     tl.overflow = __reduce_add_sync(0xFFFFFFFFu, tl.overflow);
-    tl.culled = __reduce_add_sync(0xFFFFFFFFu, tl.culled);
   }
+  tl.culled = any_culled ? __reduce_add_sync(0xFFFFFFFFu, tl.culled) : 0u;
+  const bool any_rare = any_lost || any_culled;
 #ifdef FUSE_DBG_NO_TALLY
   if (tl.rays == 0xFFFFFFFFu)
 #else

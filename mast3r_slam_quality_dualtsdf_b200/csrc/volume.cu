@@ -57,6 +57,9 @@ extern "C" int b200tsdf_create(const b200tsdf_config *cfg, b200tsdf_t **out) {
   if (e == cudaSuccess) e = cudaMalloc(&d.list, h->cap * sizeof(uint32_t));
   if (e == cudaSuccess) e = cudaMalloc(&d.ctr, CTR_COPIES * CTR_COUNT * sizeof(unsigned long long));
   if (e == cudaSuccess) e = cudaMalloc(&h->scratch, 64 * sizeof(unsigned long long));
+  if (e == cudaSuccess) e = cudaMalloc(&h->sched, 64);
+  if (e == cudaSuccess)
+    e = cudaDeviceGetAttribute(&h->sm_count, cudaDevAttrMultiProcessorCount, cfg->device);
   if (e != cudaSuccess) {
     b200_set_error("b200tsdf_create: cudaMalloc failed for 2^%d blocks (%s)", cfg->capacity_log2,
                    cudaGetErrorString(e));
@@ -76,6 +79,7 @@ extern "C" int b200tsdf_create(const b200tsdf_config *cfg, b200tsdf_t **out) {
   // z-slab ownership
   d.slab_count = cfg->slab_count > 1 ? cfg->slab_count : 1;
   d.slab_index = cfg->slab_count > 1 ? cfg->slab_index : 0;
+  d.slab_mask = (d.slab_count & (d.slab_count - 1)) == 0 ? d.slab_count - 1 : -1;
   d.slab_z0 = cfg->bounded ? d.kmin[2] : 0;
   d.slab_shift = 3;
   if (d.slab_count > 1) {
@@ -134,6 +138,8 @@ extern "C" int b200tsdf_destroy(b200tsdf_t *h) {
   cudaFree(h->d.ctr);
   cudaFree(h->d.dir);
   cudaFree(h->scratch);
+  cudaFree(h->sched);
+  cudaFree(h->tile_list);
   cudaFree(h->nbr);
   cudaFree(h->stage_dev);
   if (h->copy_stream) {

@@ -1,0 +1,64 @@
+"""Per-rank kernel time of the sharded fuse, emulated on ONE GPU.
+
+For R in {1,2,4,8} and every rank r, a volume that owns the interleaved
+z-slabs of rank r fuses the same keyframe batches (the N>1 bench scene); the
+step time a real R-GPU run would see is the max over r (plus the broadcast).
+A tuning aid: python scripts/slab_rank_time.py [--kf 40] [--steps 4]
+"""
+import argparse
+import json
+import os
+import sys
+
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import bench  # noqa: E402
+from mast3r_slam_quality_dualtsdf_b200 import synth  # noqa: E402
+from mast3r_slam_quality_dualtsdf_b200.tsdf import TSDFVolume  # noqa: E402
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--kf", type=int, default=40)
+    ap.add_argument("--steps", type=int, default=4)
+    ap.add_argument("--warmup", type=int, default=2)
+    ap.add_argument("--ranks", default="1,2,4,8")
+    ap.add_argument("--width", type=int, default=bench.SLAB_WIDTH)
+    ap.add_argument("--only-rank", type=int, default=-1)
+    a = ap.parse_args()
+    dev = torch.device("cuda:0")
+    scene, dim, orbit_r = bench.scene_for(8)
+    lo, hi = synth.bounds_for(scene, bench.VOXEL, dim)
+    batches = []
+    for s in range(a.warmup + a.steps):
+        kf = bench.gen_batch(scene, orbit_r, s, a.kf, up_axis="z")
+        batches.append(tuple(torch.from_numpy(kf[k]).to(dev) for k in ("X", "C", "pose", "q")))
+    out = {}
+    for R in (int(x) for x in a.ranks.split(",")):
+        per_rank = []
+        for r in (range(R) if a.only_rank < 0 else [a.only_rank % R]):
+            slabs = (R, r, a.width) if R > 1 else None
+            vol = TSDFVolume(bench.VOXEL, bench.TRUNC, capacity_log2=18, bounds=(lo, hi),
+                             slabs=slabs, device=dev)
+            evs = []
+            for i, (X, C, P, q) in enumerate(batches):
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                vol.integrate_keyframes(X, C, P, q, 0.05, bench.H, bench.W)
+                e1.record()
+                torch.cuda.synchronize()
+                if i >= a.warmup:
+                    evs.append(e0.elapsed_time(e1))
+            c = vol.counters()
+            per_rank.append((sum(evs) / len(evs), int(c["updates_primary"] + c["updates_quality"])))
+            del vol
+        ms = [p[0] for p in per_rank]
+        upd = sum(p[1] for p in per_rank)
+        out[R] = {"max_ms": max(ms), "mean_ms": sum(ms) / len(ms), "ms": [round(m, 4) for m in ms],
+                  "updates": upd}
+        print(R, json.dumps(out[R]), flush=True)
+
+
+if __name__ == "__main__":
+    main()

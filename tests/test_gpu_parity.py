@@ -194,6 +194,41 @@ def test_interleaved_z_slabs_union_is_exact(cuda_device, bounded, count, width):
         assert_volume_matches(got, want.export(), "interleaved z-slab union")
 
 
+@pytest.mark.parametrize("count", [3, 4])
+def test_slab_classify_path_ragged_and_degenerate(cuda_device, count):
+    """3+ ranks run the classify pass + listed-tile fuse: ragged image (no TMA,
+    partial tiles), zero-length and non-finite rays, a far-away keyframe whose
+    tiles are all foreign for some ranks.  Rays are counted on every rank
+    exactly as on one GPU and the union stays bit-exact."""
+    H, W = 45, 60
+    kf = synth.make_keyframes(synth.SCENES["sphere"], 3, H=H, W=W, seed=11, f=50.0, total=8,
+                              gh=9, gw=12)
+    X = kf["X"].reshape(3, H * W, 3)
+    Cf = kf["C"].reshape(3, H * W)
+    X[0, np.nonzero(Cf[0] > 0.05)[0][:30]] = 0.0   # point = camera centre: len 0, skipped (:56)
+    X[1, np.nonzero(Cf[1] > 0.05)[0][10:40], 1] = np.nan  # non-finite length: skipped
+    X[2] *= 0.25                # a keyframe that only reaches a few slabs
+    kf["X"] = X.reshape(kf["X"].shape)
+    vp, vq, rays = oracle_dual(kf, 0.02, 0.08)
+    assert rays < int((kf["C"] > 0.05).sum())
+    parts, ev_p, culled = [], 0, 0
+    for r in range(count):
+        vol = _vol(cuda_device, 0.02, 0.08, slabs=(count, r, 8))
+        vol.integrate_keyframes(*(torch.from_numpy(kf[k]).to(cuda_device)
+                                  for k in ("X", "C", "pose")),
+                                torch.from_numpy(kf["q"]).to(cuda_device), 0.05, H, W)
+        c = vol.counters()
+        assert c["rays"] == rays and c["culled_rays"] <= rays
+        ev_p += c["updates_primary"]
+        culled += c["culled_rays"]
+        parts.append(vol.export(0))
+    assert ev_p == vp.events and culled > 0
+    gk = np.concatenate([p[0] for p in parts])
+    order = np.lexsort((gk[:, 2], gk[:, 1], gk[:, 0]))
+    got = tuple(np.concatenate([p[i] for p in parts])[order] for i in range(4))
+    assert_volume_matches(got, vp.export(), "classify-path union")
+
+
 @pytest.mark.parametrize("case", ["plane_v30_f32", "sphere_v30_f32", "sphere_v30_f64",
                                   "room_v10_f32", "plane_clamp_f32"])
 def test_against_reference_golden(cuda_device, case):
