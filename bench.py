@@ -56,15 +56,23 @@ def scene_for(n_gpus):
     return {"kind": "room", "half": 2.4874}, 1024, 1.2
 
 
-SLAB_WIDTH = 32  # voxel layers per interleaved z-slab (N > 1): 16 cm at 5 mm
+SLAB_WIDTH = 32  # voxel layers per interleaved z-slab at N = 8: 16 cm at 5 mm
 
 
-def gen_batch(scene, orbit_r, step_idx, kf_per_step, seed=0, up_axis="y"):
+def slab_width_for(n_gpus, dim=1024):
+    """Four slabs per rank: wide enough that few rays straddle a seam, interleaved
+    enough that every view loads all ranks (measured: scripts/slab_rank_time.py)."""
+    return max(8, dim // (4 * max(1, n_gpus)))
+
+
+def gen_batch(scene, orbit_r, step_idx, kf_per_step, seed=0, up_axis="y", offset=0, count=None):
+    """Keyframes [offset, offset + count) of step `step_idx`'s batch (default: all)."""
     from mast3r_slam_quality_dualtsdf_b200 import synth
 
-    start = (step_idx * kf_per_step) % ORBIT_TOTAL
-    return synth.make_keyframes(scene, kf_per_step, H, W, seed=seed, orbit_radius=orbit_r,
-                                gh=GH, gw=GW, start=start, total=ORBIT_TOTAL, up_axis=up_axis)
+    start = (step_idx * kf_per_step) % ORBIT_TOTAL + offset
+    return synth.make_keyframes(scene, count or kf_per_step, H, W, seed=seed,
+                                orbit_radius=orbit_r, gh=GH, gw=GW, start=start,
+                                total=ORBIT_TOTAL, up_axis=up_axis)
 
 
 class ClockSampler:
@@ -193,7 +201,8 @@ def workload_config(n_gpus, dim, kf_per_step):
         "keyframes_per_step": kf_per_step, "volume_dim": dim, "voxel_size": VOXEL,
         "truncation": TRUNC, "orbit_keyframes": ORBIT_TOTAL,
         "partition": "single volume" if n_gpus == 1 else
-        f"interleaved z-slabs of {SLAB_WIDTH} voxel layers over {n_gpus} ranks, NCCL keyframe broadcast",
+        f"interleaved z-slabs of {slab_width_for(n_gpus, dim)} voxel layers over {n_gpus} ranks; every rank ingests "
+        f"{kf_per_step // max(1, n_gpus)} keyframes per step, NCCL all-gather (= {n_gpus} broadcasts) over NVLink",
         "l2": "each step reads a fresh keyframe batch larger than L2 (157 MB > 126 MB)",
     }
 
@@ -223,7 +232,7 @@ def run_b200(args):
     # N > 1: interleaved z-slabs (slab s -> rank s mod N); z is the vertical axis of the
     # orbit so the slabs cut every view (DESIGN.md "Multi-GPU")
     bounds = (lo, hi)
-    slabs = (world, rank, SLAB_WIDTH) if world > 1 else None
+    slabs = (world, rank, slab_width_for(world, dim)) if world > 1 else None
     up_axis = "z" if world > 1 else "y"
     cap = 18 if world == 1 else 19
     vol = TSDFVolume(VOXEL, TRUNC, capacity_log2=cap, bounds=bounds, slabs=slabs, device=dev)
@@ -233,29 +242,35 @@ def run_b200(args):
     names = ("X", "C", "q", "pose")
     shapes = {"X": (B, H * W, 3), "C": (B, H * W), "q": (B, GH, GW), "pose": (B, 8)}
 
-    # rank 0 renders the synthetic keyframes into pinned host memory
+    # N = 1: the whole batch in pinned host memory.  N > 1: sharded ingest -- every rank
+    # holds B / N keyframes of each batch (pinned host memory, its own PCIe link); the N
+    # simultaneous NCCL broadcasts run as one all-gather over NVLink
+    if B % world:
+        raise SystemExit(f"bench.py: --kf-per-step {B} must be a multiple of the {world} ranks")
+    share = B // world
     host = []
-    if rank == 0:
-        for s in range(n_steps):
-            kf = gen_batch(scene, orbit_r, s, B, up_axis=up_axis)
-            host.append({k: torch.from_numpy(kf[k]).pin_memory() for k in names})
+    for s in range(n_steps):
+        kf = gen_batch(scene, orbit_r, s, B, up_axis=up_axis, offset=rank * share, count=share)
+        host.append({k: torch.from_numpy(kf[k]).pin_memory() for k in names})
+    local_shapes = {k: (share,) + shapes[k][1:] for k in names}
 
     def fuse(v, t):
         v.integrate_keyframes(t["X"], t["C"], t["pose"], t["q"], MIN_CONF, H, W)
 
-    def bcast(t):
-        if world > 1:
-            for k in names:
-                dist.broadcast(t[k], 0)
+    def gather(full, part):
+        for k in names:
+            dist.all_gather_into_tensor(full[k], part[k])
 
     # resident copies on every rank (the `value` loop starts from HBM)
     resident = []
     for s in range(n_steps):
         t = {k: torch.empty(shapes[k], dtype=torch.float32, device=dev) for k in names}
-        if rank == 0:
+        if world == 1:
             for k in names:
                 t[k].copy_(host[s][k], non_blocking=True)
-        bcast(t)
+        else:
+            part = {k: host[s][k].to(dev, non_blocking=True) for k in names}
+            gather(t, part)
         resident.append(t)
     torch.cuda.synchronize()
 
@@ -294,18 +309,18 @@ def run_b200(args):
     total_ms, updates, step_ms, clocks, ctr = timed(lambda s: fuse(vol, resident[s]), vol.reset)
     value = updates / (total_ms * 1e-3)
 
-    # ---- e2e: host buffers -> (H2D, broadcast) -> fuse -> counters back
+    # ---- e2e: host buffers -> (H2D, all-gather) -> fuse -> counters back
     stage = {k: torch.empty(shapes[k], dtype=torch.float32, device=dev) for k in names}
+    stage_local = {k: torch.empty(local_shapes[k], dtype=torch.float32, device=dev) for k in names}
     d2h = [0]
 
     def e2e_body(s):
         if world == 1:
             fuse(vol, host[s])  # *_host entry: H2D inside the C ABI call
         else:
-            if rank == 0:
-                for k in names:
-                    stage[k].copy_(host[s][k], non_blocking=True)
-            bcast(stage)
+            for k in names:
+                stage_local[k].copy_(host[s][k], non_blocking=True)
+            gather(stage, stage_local)
             fuse(vol, stage)
         vol.counters()  # the step's result (8 x int64) read back, synchronises
         d2h[0] = 64
@@ -397,10 +412,13 @@ def run_b200(args):
                 "h2d_bytes_per_step": B * KF_BYTES, "d2h_bytes_per_step": d2h[0],
                 "keyframes_per_s": B * args.steps / (e2e_ms * 1e-3),
                 "ms_per_step": e2e_ms / args.steps},
-        "gpu_launches": args.steps,
+        # kernels of this library inside the timed `value` region, all ranks: one fused launch
+        # per step and rank; from 3 ranks up the classify pass + the listed-tile fuse
+        "gpu_launches": args.steps * world * (2 if world > 2 else 1),
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": traffic,
-                     "kernel": "integrate_keyframes_kernel",
+                     "kernel": "integrate_keyframes_kernel" if world <= 2 else
+                     "slab_classify_kernel + integrate_keyframes_listed_kernel",
                      "peak_source": "measured (MEASURED_PEAKS.json hbm_gbs)" if peaks else "fallback",
                      "algorithmic_bytes_per_launch": alg_bytes_launch,
                      "launch_ms": launch_ms},

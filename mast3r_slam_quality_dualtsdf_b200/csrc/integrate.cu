@@ -649,7 +649,11 @@ static int fuse_keyframes(b200tsdf_t *h, const float *X_dev, const float *C_dev,
     else LAUNCH(true, true, false);                                                            \
   }
   const long long n_tiles = (long long)grid.x * grid.y * grid.z;
-  if (h->d.slab_count > 2 && n_tiles < (1ll << 31)) {
+  static const int classify_min_ranks = [] {
+    const char *e = getenv("B200TSDF_CLASSIFY_MIN_RANKS"); // tuning knob (default 3)
+    return e ? atoi(e) : 3;
+  }();
+  if (h->d.slab_count >= classify_min_ranks && h->d.slab_count > 1 && n_tiles < (1ll << 31)) {
     // multi-GPU: classify pass + persistent fuse over the listed tiles (with two
     // ranks nearly every tile reaches both, so the direct launch is cheaper)
     if ((size_t)n_tiles > h->tile_cap) {

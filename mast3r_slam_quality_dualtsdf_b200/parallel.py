@@ -7,7 +7,8 @@ No reference counterpart: the reference is single-process Python.  Layout:
     contiguous z-slabs; a smaller power of two deals slabs round-robin and
     balances surfaces that are not uniform in z);
   * every keyframe batch (pointmaps, confidences, quality grid, poses) is
-    broadcast from the rank that holds it (NCCL over NVLink); every rank runs
+    broadcast from the rank that holds it (NCCL over NVLink), or all-gathered
+    when every rank ingests a share of the batch; every rank runs
     the staging of the full batch, culls the rays whose +-truncation band
     misses its slabs and fuses the rest into its own voxel-block hash -- there
     is no other data-path collective;
@@ -60,6 +61,32 @@ class ShardedTSDFVolume:
             for t in (X, Cf, poses) + ((q_grid,) if q_grid is not None else ()):
                 dist.broadcast(t, src, group=self.group)
         return X, Cf, poses, q_grid
+
+    def gather_keyframes(self, X, Cf, poses, q_grid=None, out=None):
+        """Sharded ingest: every rank contributes the SAME number of keyframes
+        (its share of the batch, e.g. the cameras it serves); all ranks end up
+        with the whole batch in rank order.  This is the world_size
+        simultaneous broadcasts of `broadcast_keyframes` issued as one
+        all-gather, so the host->device copies run on every rank's own PCIe
+        link.  `out` = optional preallocated (X, Cf, poses, q_grid) of the full
+        batch shape."""
+        parts = (X, Cf, poses) + ((q_grid,) if q_grid is not None else ())
+        if self.world == 1:
+            return X, Cf, poses, q_grid
+        res = []
+        for i, t in enumerate(parts):
+            t = t.contiguous()
+            full = out[i] if out is not None else \
+                torch.empty((t.shape[0] * self.world,) + tuple(t.shape[1:]), dtype=t.dtype,
+                            device=t.device)
+            if dist.get_backend(self.group) == "nccl":
+                dist.all_gather_into_tensor(full, t, group=self.group)
+            else:
+                dist.all_gather(list(full.chunk(self.world)), t, group=self.group)
+            res.append(full)
+        if q_grid is None:
+            res.append(None)
+        return tuple(res)
 
     def integrate_keyframes(self, X, Cf, poses, q_grid=None, min_conf=0.05, H=None, W=None,
                             step_scale=0.5, src=0, broadcast=True):

@@ -24,7 +24,7 @@ def main():
     ap.add_argument("--steps", type=int, default=4)
     ap.add_argument("--warmup", type=int, default=2)
     ap.add_argument("--ranks", default="1,2,4,8")
-    ap.add_argument("--width", type=int, default=bench.SLAB_WIDTH)
+    ap.add_argument("--width", type=int, default=0, help="0: bench.slab_width_for(R)")
     ap.add_argument("--only-rank", type=int, default=-1)
     a = ap.parse_args()
     dev = torch.device("cuda:0")
@@ -38,7 +38,7 @@ def main():
     for R in (int(x) for x in a.ranks.split(",")):
         per_rank = []
         for r in (range(R) if a.only_rank < 0 else [a.only_rank % R]):
-            slabs = (R, r, a.width) if R > 1 else None
+            slabs = (R, r, a.width or bench.slab_width_for(R, dim)) if R > 1 else None
             vol = TSDFVolume(bench.VOXEL, bench.TRUNC, capacity_log2=18, bounds=(lo, hi),
                              slabs=slabs, device=dev)
             evs = []

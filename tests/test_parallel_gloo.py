@@ -88,6 +88,11 @@ def _worker(rank, world, port, out):
         c = sv.counters()
         assert c["rays"] == 96 and c["updates_primary"] == 96  # every voxel fused exactly once
         assert c["culled_rays"] == 96 * (world - 1)
+        # sharded ingest: every rank contributes one keyframe, all get both in rank order
+        gx, gc, gp, gq = sv.gather_keyframes(want[rank:rank + 1].clone(), Cf[:1] * (rank + 1),
+                                             P[rank:rank + 1].clone())
+        assert torch.equal(gx, want) and gq is None and torch.equal(gp, P)
+        assert gc[:, 0].tolist() == [1.0, 2.0]
         st = sv.stats()
         n_halo = sv.exchange_seams()
         # what I received is exactly what the rank above exported
