@@ -82,9 +82,10 @@ __device__ __forceinline__ uint32_t alloc_blocks_warp(const VolumeDev &v, unsign
 template <bool BOUNDED, bool DIR>
 __device__ __forceinline__ void fold_warp(const VolumeDev &v, WarpCache &wc, bool pred, int kx,
                                           int ky, int kz, float su, float wu, uint32_t n,
-                                          float conf, float conf_q, uint32_t cp, uint32_t cq,
+                                          float conf, float conf_q, float inv_trunc, uint32_t cp,
+                                          uint32_t cq, uint32_t mlo, uint32_t mhi,
                                           bool check_bounds, Tally &tl, int &cdi,
-                                          uint32_t &cslot, bool neg) {
+                                          uint32_t &cslot) {
   bool ok = pred;
   if (BOUNDED && check_bounds) {
     bool in = (uint32_t)(kx - v.kmin[0]) < (uint32_t)(v.kmax[0] - v.kmin[0]) &&
@@ -152,12 +153,15 @@ __device__ __forceinline__ void fold_warp(const VolumeDev &v, WarpCache &wc, boo
     const uint32_t li = ((kz & 7) << 6) | ((ky & 7) << 3) | (kx & 7);
     const size_t off = (size_t)slot * B200_BLOCK_VOX + li;
 #ifndef FUSE_DBG_NO_VOXRED
-    red_add_v4(v.vox + off, conf * su, conf * wu, conf_q * su, conf_q * wu);
+    const float st = su * inv_trunc; // su = sum of sdf * e; t = sdf / trunc (:68)
+    red_add_v4(v.vox + off, conf * st, conf * wu, conf_q * st, conf_q * wu);
 #endif
 #ifndef FUSE_DBG_NO_CNTRED
-    const unsigned long long hits = (unsigned long long)(cp ? n : 0u) |
-                                    ((unsigned long long)(cq ? n : 0u) << 32);
-    red_add_u64(v.cnt + off, neg ? 0ull - hits : hits); // de-integration: exact 64-bit subtract
+    // n hits for each volume that takes the ray: n * (cp + 2^32 cq) mod 2^64, with
+    // the multiplier negated for de-integration (an exact 64-bit subtract)
+    const unsigned long long hits =
+        (unsigned long long)n * mlo + ((unsigned long long)(n * mhi) << 32);
+    red_add_u64(v.cnt + off, hits);
 #endif
   }
 }
@@ -208,8 +212,12 @@ __device__ __forceinline__ void march_warp(const VolumeDev &v, WarpCache &wc, co
   if (!live) cp = cq = 0u;
   if (!cp) conf = 0.0f;
   if (!cq) conf_q = 0.0f;
-  const bool neg = mc.negate != 0; // de-integration: subtract what the same call added
-  if (neg) conf = -conf, conf_q = -conf_q;
+  uint32_t mlo = cp, mhi = cq; // hit-counter multiplier (see fold_warp)
+  if (mc.negate != 0) { // de-integration: subtract what the same call added
+    conf = -conf, conf_q = -conf_q;
+    const unsigned long long m = 0ull - ((unsigned long long)cp | ((unsigned long long)cq << 32));
+    mlo = (uint32_t)m, mhi = (uint32_t)(m >> 32);
+  }
   if (BOUNDED && inside) {
     lim = mc.lim_bounded;
   } else {
@@ -277,8 +285,8 @@ __device__ __forceinline__ void march_warp(const VolumeDev &v, WarpCache &wc, co
     }
     const bool chg = act && n != 0 && (((kx ^ ax) | (ky ^ ay) | (kz ^ az)) != 0);
     if (__any_sync(0xFFFFFFFFu, chg)) {
-      fold_warp<BOUNDED, DIR>(v, wc, chg, ax, ay, az, su, wu, n, conf, conf_q, cp, cq,
-                              check_bounds, tl, cdi, cslot, neg);
+      fold_warp<BOUNDED, DIR>(v, wc, chg, ax, ay, az, su, wu, n, conf, conf_q, mc.inv_trunc, cp, cq,
+                              mlo, mhi, check_bounds, tl, cdi, cslot);
       if (chg) {
         su = wu = 0.f;
         n = 0;
@@ -289,15 +297,15 @@ __device__ __forceinline__ void march_warp(const VolumeDev &v, WarpCache &wc, co
 #if !FUSE_EX2_EARLY
       const float e = ex2_ftz(fabsf(sdf) * mc.nl2e_inv_trunc); // :69 exp(-|sdf| / trunc)
 #endif
-      su = fmaf(sdf * mc.inv_trunc, e, su);               // :68 (|t| <= 1 inside the band)
+      su = fmaf(sdf, e, su); // :68 t * w with t = sdf / trunc (|t| <= 1 inside the band)
       wu += e;
       n += 1;
     }
   }
   const bool fin = n != 0;
   if (__any_sync(0xFFFFFFFFu, fin))
-    fold_warp<BOUNDED, DIR>(v, wc, fin, ax, ay, az, su, wu, n, conf, conf_q, cp, cq,
-                            check_bounds, tl, cdi, cslot, neg);
+    fold_warp<BOUNDED, DIR>(v, wc, fin, ax, ay, az, su, wu, n, conf, conf_q, mc.inv_trunc, cp, cq, mlo,
+                            mhi, check_bounds, tl, cdi, cslot);
   tl.ev_p += (uint32_t)cnt * cp;
   tl.ev_q += (uint32_t)cnt * cq;
 }
