@@ -38,11 +38,44 @@ __global__ void mc_neighbors_kernel(VolumeDev v, uint32_t *__restrict__ nbr) {
   }
 }
 
+// cp.async (LDGSTS) helpers: the raw voxel words of the NEXT block travel to
+// shared memory while the current block is classified and emitted.
+__device__ __forceinline__ void cp_async8(void *smem, const void *gmem) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(
+                   (uint32_t)__cvta_generic_to_shared(smem)),
+               "l"(gmem)
+               : "memory");
+}
+__device__ __forceinline__ void cp_async4(void *smem, const void *gmem) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(
+                   (uint32_t)__cvta_generic_to_shared(smem)),
+               "l"(gmem)
+               : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+  asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+
+#define MC_CTAS_PER_SM 5
+#define MC_PTS 3 // lattice points per thread: ceil(729 / 256)
+
+// Persistent CTAs, one voxel block per iteration, double-buffered: while block
+// b is converted / classified / emitted, the (S, W) pair and the hit counter of
+// every corner of block b+1's 9^3 lattice (block + halo from the +x/+y/+z
+// neighbours) are in flight to the other raw buffer (8-byte + 4-byte cp.async
+// per corner: only the words of the selected volume), the neighbour slots of
+// block b+2 and the key of block b+1 are in flight to registers.
 template <bool WRITE>
-__global__ void __launch_bounds__(MC_THREADS)
+__global__ void __launch_bounds__(MC_THREADS, MC_CTAS_PER_SM)
     mc_kernel(VolumeDev v, const uint32_t *__restrict__ nbr, int which, float vs,
               float *__restrict__ verts, long long tri_cap, unsigned long long *n_tris) {
   __shared__ float tv[9 * 9 * 9];
+  __shared__ __align__(16) float2 r_sw[2][9 * 9 * 9 + 7];
+  __shared__ uint32_t r_h[2][9 * 9 * 9 + 7];
+  __shared__ uint32_t s_nb[8];
+  __shared__ unsigned long long s_key;
   __shared__ __align__(16) signed char s_tri[256 * 16];
   __shared__ unsigned char s_num[256];
   const int tid = threadIdx.x, lane = tid & 31;
@@ -51,28 +84,75 @@ __global__ void __launch_bounds__(MC_THREADS)
     reinterpret_cast<int4 *>(s_tri)[tid] = reinterpret_cast<const int4 *>(MC_TRI_TABLE)[tid];
     s_num[tid] = MC_NUM_TRIS[tid];
   }
-  const uint32_t nb = (uint32_t)v.ctr[CTR_BLOCKS];
-  for (uint32_t b = blockIdx.x; b < nb; b += gridDim.x) {
-    __syncthreads(); // tv of the previous block is no longer read
-    const uint32_t *nb8 = nbr + (size_t)b * 8;
-    int bx, by, bz;
-    unpack_block_key(v.keys[nb8[0]], bx, by, bz);
-    for (int i = tid; i < 729; i += MC_THREADS) {
-      int x = i % 9, y = (i / 9) % 9, z = i / 81;
-      int nbk = (x == 8) | ((y == 8) << 1) | ((z == 8) << 2);
-      uint32_t s = nb8[nbk];
-      float val = NAN;
+  // this thread's lattice points: local voxel index | neighbour id << 9 (block-invariant)
+  int pk[MC_PTS];
+#pragma unroll
+  for (int j = 0; j < MC_PTS; ++j) {
+    const int i = tid + j * MC_THREADS;
+    const int x = i % 9, y = (i / 9) % 9, z = i / 81;
+    const int nbk = (x == 8) | ((y == 8) << 1) | ((z == 8) << 2);
+    pk[j] = i < 729 ? ((((z & 7) << 6) | ((y & 7) << 3) | (x & 7)) | (nbk << 9)) : -1;
+  }
+  const char *vox_b = reinterpret_cast<const char *>(v.vox) + which * 8;
+  const char *cnt_b = reinterpret_cast<const char *>(v.cnt) + which * 4;
+  auto prefetch = [&](int buf) { // raw words of the block whose neighbour slots are in s_nb
+#pragma unroll
+    for (int j = 0; j < MC_PTS; ++j) {
+      if (pk[j] < 0) continue;
+      const int i = tid + j * MC_THREADS;
+      const uint32_t s = s_nb[pk[j] >> 9];
       if (s != B200_NO_SLOT) {
-        size_t off = (size_t)s * B200_BLOCK_VOX + (((z & 7) << 6) | ((y & 7) << 3) | (x & 7));
-        float t, w;
-        uint32_t hits;
-        if (voxel_view(v.vox[off], v.cnt[off], which, v.max_weight, t, w, hits) &&
-            w >= v.min_weight)
-          val = t;
+        const size_t off = (size_t)s * B200_BLOCK_VOX + (pk[j] & 511);
+        cp_async8(&r_sw[buf][i], vox_b + off * sizeof(float4));
+        cp_async4(&r_h[buf][i], cnt_b + off * sizeof(unsigned long long));
+      } else {
+        r_h[buf][i] = 0u; // no block there: never observed
+      }
+    }
+    cp_async_commit();
+  };
+  const uint32_t nb = (uint32_t)v.ctr[CTR_BLOCKS];
+  const uint32_t g = gridDim.x;
+  uint32_t b = blockIdx.x;
+  if (b >= nb) return;
+  uint32_t nbA = B200_NO_SLOT;      // threads 0..7: neighbour slot of the block after the current one
+  unsigned long long keyA = 0;      // thread 0: key of the current block
+  if (tid < 8) s_nb[tid] = nbr[(size_t)b * 8 + tid];
+  __syncthreads();
+  prefetch(0);
+  if (tid == 0) keyA = v.keys[s_nb[0]];
+  if (tid < 8 && b + g < nb) nbA = nbr[(size_t)(b + g) * 8 + tid];
+  __syncthreads(); // s_nb is rewritten next
+  for (uint32_t it = 0; b < nb; b += g, ++it) {
+    const int buf = it & 1;
+    if (tid < 8) s_nb[tid] = nbA;
+    if (tid == 0) s_key = keyA;
+    __syncthreads(); // previous block fully emitted; s_nb / s_key of this iteration visible
+    if (b + g < nb) {
+      prefetch(buf ^ 1);
+      if (tid == 0) keyA = v.keys[s_nb[0]];
+      if (tid < 8) nbA = b + 2 * g < nb ? nbr[(size_t)(b + 2 * g) * 8 + tid] : B200_NO_SLOT;
+      cp_async_wait<1>();
+    } else {
+      cp_async_wait<0>();
+    }
+    __syncthreads(); // raw words of block b have landed for every thread
+#pragma unroll
+    for (int j = 0; j < MC_PTS; ++j) {
+      if (pk[j] < 0) continue;
+      const int i = tid + j * MC_THREADS;
+      const uint32_t hits = r_h[buf][i];
+      float val = NAN;
+      if (hits != 0) { // voxel_view (common.cuh) on the staged words
+        const float2 sw = r_sw[buf][i];
+        const float w = (hits == 1) ? sw.y : fminf(sw.y, v.max_weight);
+        if (w >= v.min_weight) val = sw.x / fmaxf(1.0e-9f, w);
       }
       tv[i] = val;
     }
     __syncthreads();
+    int bx, by, bz;
+    unpack_block_key(s_key, bx, by, bz);
     int mask[2], nt[2];
 #pragma unroll
     for (int c2 = 0; c2 < 2; ++c2) {
@@ -162,10 +242,10 @@ extern "C" int b200tsdf_extract_mesh(b200tsdf_t *h, int which, float *verts_dev,
   if (!h->nbr) B200_CUDA(cudaMalloc(&h->nbr, h->cap * 8 * sizeof(uint32_t)));
   mc_neighbors_kernel<<<148 * 8, 256, 0, st>>>(h->d, h->nbr);
   if (verts_dev && tri_cap > 0)
-    mc_kernel<true><<<148 * 6, MC_THREADS, 0, st>>>(h->d, h->nbr, which, vs, verts_dev,
+    mc_kernel<true><<<148 * MC_CTAS_PER_SM, MC_THREADS, 0, st>>>(h->d, h->nbr, which, vs, verts_dev,
                                                      (long long)tri_cap, h->scratch);
   else
-    mc_kernel<false><<<148 * 8, MC_THREADS, 0, st>>>(h->d, h->nbr, which, vs, nullptr, 0,
+    mc_kernel<false><<<148 * MC_CTAS_PER_SM, MC_THREADS, 0, st>>>(h->d, h->nbr, which, vs, nullptr, 0,
                                                       h->scratch);
   B200_CUDA(cudaGetLastError());
   unsigned long long n;
