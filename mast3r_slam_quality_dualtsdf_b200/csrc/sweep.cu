@@ -9,20 +9,32 @@
 // One CTA per allocated block, 128 threads x 4 voxels, 128-bit loads.
 __global__ void __launch_bounds__(128)
     stats_kernel(VolumeDev v, int which, unsigned long long *out /* [valid,total] */) {
-  uint32_t nb = (uint32_t)v.ctr[CTR_BLOCKS];
+  const uint32_t nb = (uint32_t)v.ctr[CTR_BLOCKS];
   uint32_t valid = 0, total = 0;
-  for (uint32_t b = blockIdx.x; b < nb; b += gridDim.x) {
-    size_t base = (size_t)v.list[b] * B200_BLOCK_VOX;
-    for (int i = threadIdx.x; i < B200_BLOCK_VOX; i += blockDim.x) {
-      float4 a = v.vox[base + i];
-      unsigned long long c = v.cnt[base + i];
+  uint32_t b = blockIdx.x;
+  uint32_t slot = b < nb ? v.list[b] : 0u;
+  while (b < nb) {
+    // the next block's slot is fetched while this block streams (no dependent-load bubble)
+    const uint32_t bn = b + gridDim.x;
+    const uint32_t slot_n = bn < nb ? v.list[bn] : 0u;
+    const size_t base = (size_t)slot * B200_BLOCK_VOX + threadIdx.x;
+    float4 a[4];
+    unsigned long long c[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) { // 8 independent 128/64-bit loads in flight per thread
+      a[k] = v.vox[base + k * 128];
+      c[k] = v.cnt[base + k * 128];
+    }
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
       float t, w;
       uint32_t hits;
-      if (voxel_view(a, c, which, v.max_weight, t, w, hits)) {
+      if (voxel_view(a[k], c[k], which, v.max_weight, t, w, hits)) {
         total++;
         if (w >= v.min_weight) valid++;
       }
     }
+    b = bn, slot = slot_n;
   }
   valid = __reduce_add_sync(0xFFFFFFFFu, valid);
   total = __reduce_add_sync(0xFFFFFFFFu, total);
@@ -52,19 +64,30 @@ extern "C" int b200tsdf_stats(b200tsdf_t *h, int which, int64_t *valid_host, int
 __global__ void __launch_bounds__(128)
     export_kernel(VolumeDev v, int which, long long *keys, float *tsdf, float *weight,
                   uint32_t *count, long long cap, unsigned long long *n_out) {
-  uint32_t nb = (uint32_t)v.ctr[CTR_BLOCKS];
+  const uint32_t nb = (uint32_t)v.ctr[CTR_BLOCKS];
   const int lane = threadIdx.x & 31;
-  for (uint32_t b = blockIdx.x; b < nb; b += gridDim.x) {
-    uint32_t slot = v.list[b];
+  uint32_t b = blockIdx.x;
+  uint32_t slot = b < nb ? v.list[b] : 0u;
+  while (b < nb) {
+    const uint32_t bn = b + gridDim.x;
+    const uint32_t slot_n = bn < nb ? v.list[bn] : 0u; // fetched while this block streams
+    const unsigned long long key = v.keys[slot];
+    const size_t base = (size_t)slot * B200_BLOCK_VOX + threadIdx.x;
+    float4 a[4];
+    unsigned long long c[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) { // all loads of the block first
+      a[k] = v.vox[base + k * 128];
+      c[k] = v.cnt[base + k * 128];
+    }
     int bx, by, bz;
-    unpack_block_key(v.keys[slot], bx, by, bz);
-    size_t base = (size_t)slot * B200_BLOCK_VOX;
-    for (int i = threadIdx.x; i < B200_BLOCK_VOX; i += blockDim.x) {
-      float4 a = v.vox[base + i];
-      unsigned long long c = v.cnt[base + i];
+    unpack_block_key(key, bx, by, bz);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const int i = threadIdx.x + k * 128;
       float t, w;
       uint32_t hits;
-      bool on = voxel_view(a, c, which, v.max_weight, t, w, hits);
+      bool on = voxel_view(a[k], c[k], which, v.max_weight, t, w, hits);
       unsigned mask = __ballot_sync(0xFFFFFFFFu, on);
       if (mask == 0) continue;
       unsigned long long start = 0;
@@ -82,6 +105,7 @@ __global__ void __launch_bounds__(128)
         }
       }
     }
+    b = bn, slot = slot_n;
   }
 }
 
