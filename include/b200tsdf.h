@@ -197,6 +197,20 @@ int b200tsdf_import_halo_blocks(b200tsdf_t *h, const int64_t *bkeys_dev,
                                 const float *vox_dev, const uint64_t *cnt_dev,
                                 int64_t n, void *stream);
 
+/* ---- volume state in / out (checkpoint / resume; no
+ * reference counterpart -- the reference keeps its dict in process memory).
+ * export_block_data: every voxel block this handle OWNS, same layout and
+ * two-call protocol as export_seam_blocks.  import_blocks ADDS the blocks into
+ * the volume as owned blocks (allocating them as needed): the stored state
+ * (sums S, W and hit counters) is additive, so importing into an empty volume
+ * restores a checkpoint and importing into a filled one merges two partial
+ * fusions of disjoint keyframe sets into the volume a single fusion of all of
+ * them would give. */
+int b200tsdf_export_block_data(b200tsdf_t *h, int64_t *bkeys_dev, float *vox_dev,
+                               uint64_t *cnt_dev, int64_t cap, int64_t *n_host, void *stream);
+int b200tsdf_import_blocks(b200tsdf_t *h, const int64_t *bkeys_dev, const float *vox_dev,
+                           const uint64_t *cnt_dev, int64_t n, void *stream);
+
 /* ---- local (per-ROI, dense) TSDF of the refiner: stateless calls ---------- */
 
 /* Replaces the config keys read by TSDFRefiner (mast3r_slam/tsdf_refine.py

@@ -20,6 +20,7 @@ SYMBOLS = [
     "b200tsdf_integrate_keyframes_host", "b200tsdf_deintegrate_keyframes", "b200tsdf_counters", "b200tsdf_stats",
     "b200tsdf_query", "b200tsdf_export_voxels", "b200tsdf_export_blocks",
     "b200tsdf_extract_mesh", "b200tsdf_export_seam_blocks", "b200tsdf_import_halo_blocks",
+    "b200tsdf_export_block_data", "b200tsdf_import_blocks",
     "b200tsdf_local_dims", "b200tsdf_local_build",
     "b200tsdf_local_raycast",
 ]
@@ -79,6 +80,8 @@ def lib():
     L.b200tsdf_extract_mesh.argtypes = [vp, C.c_int, vp, i64, vp, vp]
     L.b200tsdf_export_seam_blocks.argtypes = [vp, vp, vp, vp, i64, vp, vp]
     L.b200tsdf_import_halo_blocks.argtypes = [vp, vp, vp, vp, i64, vp]
+    L.b200tsdf_export_block_data.argtypes = [vp, vp, vp, vp, i64, vp, vp]
+    L.b200tsdf_import_blocks.argtypes = [vp, vp, vp, vp, i64, vp]
     L.b200tsdf_local_dims.argtypes = [vp, C.POINTER(LocalCfg), vp]
     L.b200tsdf_local_build.argtypes = [vp, vp, vp, vp, i64, C.POINTER(LocalCfg), vp, vp, vp, vp]
     L.b200tsdf_local_raycast.argtypes = [vp, vp, vp, vp, vp, i64, C.POINTER(LocalCfg), vp, vp, vp]

@@ -258,14 +258,14 @@ __device__ __forceinline__ bool is_seam_block(const VolumeDev &v, int bz) {
 
 __global__ void __launch_bounds__(128)
     export_seam_kernel(VolumeDev v, long long *bkeys, float4 *vox, unsigned long long *cnt,
-                       long long cap, unsigned long long *n_out) {
+                       long long cap, unsigned long long *n_out, int all_blocks) {
   __shared__ long long s_idx;
   const uint32_t nb = (uint32_t)v.ctr[CTR_BLOCKS];
   for (uint32_t b = blockIdx.x; b < nb; b += gridDim.x) {
     const uint32_t slot = v.list[b];
     int bx, by, bz;
     unpack_block_key(v.keys[slot], bx, by, bz);
-    if (!is_seam_block(v, bz)) continue; // uniform per CTA
+    if (!all_blocks && !is_seam_block(v, bz)) continue; // uniform per CTA
     __syncthreads();
     if (threadIdx.x == 0) s_idx = (long long)atomicAdd(n_out, 1ull);
     __syncthreads();
@@ -280,11 +280,11 @@ __global__ void __launch_bounds__(128)
   }
 }
 
-extern "C" int b200tsdf_export_seam_blocks(b200tsdf_t *h, int64_t *bkeys_dev, float *vox_dev,
-                                           uint64_t *cnt_dev, int64_t cap, int64_t *n_host,
-                                           void *stream) {
+static int export_block_payload(b200tsdf_t *h, int64_t *bkeys_dev, float *vox_dev,
+                                uint64_t *cnt_dev, int64_t cap, int64_t *n_host, void *stream,
+                                int all_blocks) {
   if (!h || !n_host || cap < 0 || (cap > 0 && (!bkeys_dev || !vox_dev || !cnt_dev))) {
-    b200_set_error("b200tsdf_export_seam_blocks: invalid argument");
+    b200_set_error("b200tsdf_export_%s: invalid argument", all_blocks ? "block_data" : "seam_blocks");
     return B200TSDF_E_INVALID;
   }
   cudaStream_t st = (cudaStream_t)stream;
@@ -292,7 +292,7 @@ extern "C" int b200tsdf_export_seam_blocks(b200tsdf_t *h, int64_t *bkeys_dev, fl
   B200_CUDA(cudaMemsetAsync(h->scratch, 0, 8, st));
   export_seam_kernel<<<148 * 8, 128, 0, st>>>(h->d, (long long *)bkeys_dev, (float4 *)vox_dev,
                                               (unsigned long long *)cnt_dev, (long long)cap,
-                                              h->scratch);
+                                              h->scratch, all_blocks);
   B200_CUDA(cudaGetLastError());
   unsigned long long n;
   B200_CUDA(cudaMemcpyAsync(&n, h->scratch, 8, cudaMemcpyDeviceToHost, st));
@@ -301,35 +301,63 @@ extern "C" int b200tsdf_export_seam_blocks(b200tsdf_t *h, int64_t *bkeys_dev, fl
   return B200TSDF_OK;
 }
 
+extern "C" int b200tsdf_export_seam_blocks(b200tsdf_t *h, int64_t *bkeys_dev, float *vox_dev,
+                                           uint64_t *cnt_dev, int64_t cap, int64_t *n_host,
+                                           void *stream) {
+  return export_block_payload(h, bkeys_dev, vox_dev, cnt_dev, cap, n_host, stream, 0);
+}
+
+extern "C" int b200tsdf_export_block_data(b200tsdf_t *h, int64_t *bkeys_dev, float *vox_dev,
+                                          uint64_t *cnt_dev, int64_t cap, int64_t *n_host,
+                                          void *stream) {
+  return export_block_payload(h, bkeys_dev, vox_dev, cnt_dev, cap, n_host, stream, 1);
+}
+
 __global__ void __launch_bounds__(128)
     import_halo_kernel(VolumeDev v, const long long *__restrict__ bkeys,
                        const float4 *__restrict__ vox, const unsigned long long *__restrict__ cnt,
-                       long long n, unsigned long long *overflow) {
+                       long long n, unsigned long long *overflow, int owned) {
   __shared__ uint32_t s_slot;
   for (long long b = blockIdx.x; b < n; b += gridDim.x) {
     __syncthreads();
     if (threadIdx.x == 0) {
       int bx = (int)bkeys[3 * b], by = (int)bkeys[3 * b + 1], bz = (int)bkeys[3 * b + 2];
       bool fresh;
+      fresh = false;
       s_slot = block_in_range(bx, by, bz) ? hash_insert(v, pack_block_key(bx, by, bz), &fresh)
                                           : B200_NO_SLOT;
       if (s_slot == B200_NO_SLOT) atomicAdd(overflow, 1ull);
+      if (owned && s_slot != B200_NO_SLOT) {
+        if (fresh) v.list[atomicAdd(v.ctr + CTR_BLOCKS, 1ull)] = s_slot; // an owned block
+        if (v.dir_on) {
+          const int dx = bx - v.dir_b0[0], dy = by - v.dir_b0[1], dz = bz - v.dir_b0[2];
+          if ((unsigned)dx < (unsigned)v.dir_n[0] && (unsigned)dy < (unsigned)v.dir_n[1] &&
+              (unsigned)dz < (unsigned)v.dir_n[2])
+            v.dir[((size_t)dz * v.dir_n[1] + dy) * v.dir_n[0] + dx] = s_slot;
+        }
+      }
     }
     __syncthreads();
     if (s_slot == B200_NO_SLOT) continue;
     const size_t base = (size_t)s_slot * B200_BLOCK_VOX;
     for (int i = threadIdx.x; i < B200_BLOCK_VOX; i += blockDim.x) {
-      v.vox[base + i] = vox[b * B200_BLOCK_VOX + i]; // overwrite: a halo block is a copy
-      v.cnt[base + i] = cnt[b * B200_BLOCK_VOX + i];
+      const float4 a = vox[b * B200_BLOCK_VOX + i];
+      const unsigned long long c = cnt[b * B200_BLOCK_VOX + i];
+      if (owned) { // the fold state (sums, hit counters) is additive: import = merge
+        red_add_v4(v.vox + base + i, a.x, a.y, a.z, a.w);
+        red_add_u64(v.cnt + base + i, c);
+      } else { // overwrite: a halo block is a copy
+        v.vox[base + i] = a;
+        v.cnt[base + i] = c;
+      }
     }
   }
 }
 
-extern "C" int b200tsdf_import_halo_blocks(b200tsdf_t *h, const int64_t *bkeys_dev,
-                                           const float *vox_dev, const uint64_t *cnt_dev,
-                                           int64_t n, void *stream) {
+static int import_block_payload(b200tsdf_t *h, const int64_t *bkeys_dev, const float *vox_dev,
+                                const uint64_t *cnt_dev, int64_t n, void *stream, int owned) {
   if (!h || n < 0 || (n > 0 && (!bkeys_dev || !vox_dev || !cnt_dev))) {
-    b200_set_error("b200tsdf_import_halo_blocks: invalid argument");
+    b200_set_error("b200tsdf_import_blocks: invalid argument");
     return B200TSDF_E_INVALID;
   }
   if (n == 0) return B200TSDF_OK;
@@ -338,14 +366,26 @@ extern "C" int b200tsdf_import_halo_blocks(b200tsdf_t *h, const int64_t *bkeys_d
   B200_CUDA(cudaMemsetAsync(h->scratch + 1, 0, 8, st));
   import_halo_kernel<<<(unsigned)(n < 1184 ? n : 1184), 128, 0, st>>>(
       h->d, (const long long *)bkeys_dev, (const float4 *)vox_dev,
-      (const unsigned long long *)cnt_dev, (long long)n, h->scratch + 1);
+      (const unsigned long long *)cnt_dev, (long long)n, h->scratch + 1, owned);
   B200_CUDA(cudaGetLastError());
   unsigned long long ov;
   B200_CUDA(cudaMemcpyAsync(&ov, h->scratch + 1, 8, cudaMemcpyDeviceToHost, st));
   B200_CUDA(cudaStreamSynchronize(st));
   if (ov) {
-    b200_set_error("b200tsdf_import_halo_blocks: voxel-block hash full (%llu blocks lost)", ov);
+    b200_set_error("b200tsdf_import_blocks: voxel-block hash full (%llu blocks lost)", ov);
     return B200TSDF_E_CAPACITY;
   }
   return B200TSDF_OK;
+}
+
+extern "C" int b200tsdf_import_halo_blocks(b200tsdf_t *h, const int64_t *bkeys_dev,
+                                           const float *vox_dev, const uint64_t *cnt_dev,
+                                           int64_t n, void *stream) {
+  return import_block_payload(h, bkeys_dev, vox_dev, cnt_dev, n, stream, 0);
+}
+
+extern "C" int b200tsdf_import_blocks(b200tsdf_t *h, const int64_t *bkeys_dev,
+                                      const float *vox_dev, const uint64_t *cnt_dev, int64_t n,
+                                      void *stream) {
+  return import_block_payload(h, bkeys_dev, vox_dev, cnt_dev, n, stream, 1);
 }

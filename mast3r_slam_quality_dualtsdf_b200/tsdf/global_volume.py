@@ -276,24 +276,70 @@ class TSDFVolume:
     # ------------------------------------------------------------------
     # Multi-GPU seams (see parallel.ShardedTSDFVolume)
     # ------------------------------------------------------------------
-    def export_seam_blocks(self):
-        """Voxel blocks of the first block layer of every z-slab this volume
-        owns: (bkeys i64 (n,3), vox f32 (n,512,4), cnt i64 (n,512)) device
-        tensors (cnt holds the raw u64 hit-counter words)."""
+    def _export_payload(self, fn, what):
         n = C.c_int64()
-        L = _ffi.lib()
         with self._lock:
-            _ffi.check(L.b200tsdf_export_seam_blocks(self._h, None, None, None, 0, C.byref(n),
-                                                     _stream_ptr(self.device)), "export_seam")
+            _ffi.check(fn(self._h, None, None, None, 0, C.byref(n), _stream_ptr(self.device)), what)
             cap = n.value
             bk = torch.zeros(cap, 3, dtype=torch.int64, device=self.device)
             vox = torch.zeros(cap, 512, 4, dtype=torch.float32, device=self.device)
             cnt = torch.zeros(cap, 512, dtype=torch.int64, device=self.device)
             if cap:
-                _ffi.check(L.b200tsdf_export_seam_blocks(
-                    self._h, bk.data_ptr(), vox.data_ptr(), cnt.data_ptr(), cap, C.byref(n),
-                    _stream_ptr(self.device)), "export_seam")
+                _ffi.check(fn(self._h, bk.data_ptr(), vox.data_ptr(), cnt.data_ptr(), cap,
+                              C.byref(n), _stream_ptr(self.device)), what)
         return bk, vox, cnt
+
+    def export_seam_blocks(self):
+        """Voxel blocks of the first block layer of every z-slab this volume
+        owns: (bkeys i64 (n,3), vox f32 (n,512,4), cnt i64 (n,512)) device
+        tensors (cnt holds the raw u64 hit-counter words)."""
+        return self._export_payload(_ffi.lib().b200tsdf_export_seam_blocks, "export_seam")
+
+    def export_block_data(self):
+        """Every voxel block this volume owns, same layout as export_seam_blocks:
+        the complete state of the volume."""
+        return self._export_payload(_ffi.lib().b200tsdf_export_block_data, "export_block_data")
+
+    def import_blocks(self, bkeys, vox, cnt):
+        """ADD blocks exported by `export_block_data` as owned blocks.  Sums and
+        hit counters are additive: into an empty volume this restores a
+        checkpoint, into a filled one it merges two partial fusions."""
+        n = int(bkeys.shape[0])
+        if n == 0:
+            return
+        bkeys = bkeys.to(self.device, torch.int64).contiguous()
+        vox = vox.to(self.device, torch.float32).contiguous()
+        cnt = cnt.to(self.device, torch.int64).contiguous()
+        with self._lock:
+            _ffi.check(_ffi.lib().b200tsdf_import_blocks(
+                self._h, bkeys.data_ptr(), vox.data_ptr(), cnt.data_ptr(), n,
+                _stream_ptr(self.device)), "import_blocks")
+
+    def save_checkpoint(self, path):
+        """Flat .npz of (block keys, packed voxels, hit counters) + the volume
+        parameters; `load_checkpoint` restores it bit-exactly."""
+        import numpy as np
+
+        bk, vox, cnt = self.export_block_data()
+        order = np.lexsort(bk.cpu().numpy().T[::-1])  # deterministic file contents
+        np.savez(path, block_keys=bk.cpu().numpy()[order], vox=vox.cpu().numpy()[order],
+                 cnt=cnt.cpu().numpy()[order],
+                 params=np.array([self.voxel_size, self.truncation, self.max_weight,
+                                  self.min_weight], np.float64))
+        return int(bk.shape[0])
+
+    def load_checkpoint(self, path, check_params=True):
+        import numpy as np
+
+        with np.load(path) as z:
+            if check_params:
+                mine = np.array([self.voxel_size, self.truncation, self.max_weight,
+                                 self.min_weight], np.float64)
+                if not np.allclose(z["params"], mine, rtol=1e-12, atol=0.0):
+                    raise ValueError(f"checkpoint parameters {z['params']} != volume {mine}")
+            self.import_blocks(torch.from_numpy(z["block_keys"]), torch.from_numpy(z["vox"]),
+                               torch.from_numpy(z["cnt"]))
+            return int(z["block_keys"].shape[0])
 
     def import_halo_blocks(self, bkeys, vox, cnt):
         """Install another rank's seam blocks as read-only +z neighbours for

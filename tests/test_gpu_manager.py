@@ -198,3 +198,45 @@ def test_manager_replace_mode_removes_the_stale_pose(cuda_device):
     wk, wt, ww, wc = vp.export()
     assert np.array_equal(gk, wk) and np.array_equal(gc.astype(np.int64), wc.astype(np.int64))
     assert np.abs(gt - wt).max() <= 5e-5
+
+
+def test_checkpoint_round_trip_and_merge(cuda_device, tmp_path):
+    """the volume state is a flat (block keys, voxels,
+    counters) file; restoring is bit-exact, and because the fold state is
+    additive, importing one partial fusion into another equals fusing all
+    keyframes into one volume (counts exact, sums up to float32 order)."""
+    from mast3r_slam_quality_dualtsdf_b200 import synth
+    from mast3r_slam_quality_dualtsdf_b200.tsdf import TSDFVolume
+
+    kf = synth.make_keyframes(synth.SCENES["sphere"], 4, H=48, W=64, seed=3, f=50.0, total=8)
+    t = {k: torch.from_numpy(kf[k]).to(cuda_device) for k in ("X", "C", "pose", "q")}
+
+    def fused(idx, **kw):
+        v = TSDFVolume(0.02, 0.08, device=cuda_device, **kw)
+        v.integrate_keyframes(t["X"][idx], t["C"][idx], t["pose"][idx], t["q"][idx], 0.05, 48, 64)
+        return v
+
+    whole = fused(slice(0, 4))
+    path = str(tmp_path / "vol.npz")
+    nblk = whole.save_checkpoint(path)
+    assert nblk == whole.counters()["blocks"] > 0
+    for kw in ({}, {"bounds": ((-64, -64, 0), (64, 64, 128))}):  # hash-only and directory volumes
+        back = TSDFVolume(0.02, 0.08, device=cuda_device, **kw)
+        assert back.load_checkpoint(path) == nblk
+        for which in (0, 1):
+            a, b = whole.export(which), back.export(which)
+            assert all(np.array_equal(x, y) for x, y in zip(a, b))
+        assert back.stats() == whole.stats()
+        # the restored volume keeps fusing like the original
+        back.integrate_keyframes(t["X"][:1], t["C"][:1], t["pose"][:1], t["q"][:1], 0.05, 48, 64)
+        assert back.counters()["blocks"] >= nblk
+    # merge: {0,1} + {2,3} == {0,1,2,3}
+    left, right = fused(slice(0, 2)), fused(slice(2, 4))
+    left.import_blocks(*right.export_block_data())
+    for which in (0, 1):
+        gk, gt, gw, gc = left.export(which)
+        wk, wt, ww, wc = whole.export(which)
+        assert np.array_equal(gk, wk) and np.array_equal(gc, wc)
+        assert np.abs(gt - wt).max() <= 1e-5 and np.abs(gw - ww).max() <= 1e-4 * max(1.0, ww.max())
+    with pytest.raises(ValueError):
+        TSDFVolume(0.03, 0.08, device=cuda_device).load_checkpoint(path)
