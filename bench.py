@@ -397,6 +397,25 @@ def run_b200(args):
              "achieved_gbs": vox_bytes / (st_ms * 1e-3) / 1e9,
              "frac": vox_bytes / (st_ms * 1e-3) / 1e9 / peak, "valid_voxels": st["valid_voxels"]}
 
+    # ---- quality producer: per-patch grids + classify on the device
+    quality = None
+    if rank == 0:
+        from mast3r_slam_quality_dualtsdf_b200 import quality_core as qc
+
+        gq = torch.Generator(device="cpu").manual_seed(1)
+        qjob = {"H": H, "W": W, "kf_id": 0, "t_norm": torch.tensor(0.05), "theta": torch.tensor(0.1),
+                "valid_kf": (torch.rand(H * W, generator=gq) > 0.3).to(dev),
+                "r_pix": torch.rand(H * W, generator=gq).to(dev),
+                "Ck": (torch.rand(H * W, generator=gq) * 3).to(dev),
+                "Qk": (torch.rand(H * W, generator=gq) * 2).to(dev)}
+        qargs = dict(ps=16, alpha=0.8, b0=0.15, theta0=0.1745, C_thr=1.5, Q_thr=1.5, thr_zr=1.0,
+                     thr_zu=1.0, thr_dc=0.02, device=dev)
+        q_ms, _ = dev_ms(lambda: [qc.compute_batch([qjob], **qargs) for _ in range(20)])
+        q_bytes = H * W * 13  # C, Q, r_pix float32 + valid u8, read once
+        quality = {"kernels": "quality_patch_kernel + quality_classify_kernel",
+                   "us_per_keyframe": 1e3 * q_ms / 20, "algorithmic_bytes": q_bytes,
+                   "note": "launch/latency-bound: 2.5 MB per keyframe, one CTA classifies"}
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -423,7 +442,7 @@ def run_b200(args):
                      "algorithmic_bytes_per_launch": alg_bytes_launch,
                      "launch_ms": launch_ms},
         "clocks": clocks,
-        "extract": extract, "sweep": sweep,
+        "extract": extract, "sweep": sweep, "quality": quality,
         "volume": {"blocks": ctr["blocks"], "dropped_updates": ctr["dropped"]},
         "host_cores": os.cpu_count(),
     }

@@ -247,6 +247,30 @@ int b200tsdf_local_raycast(const float *tsdf_dev, const int32_t dims3_host[3],
                            int64_t m, const b200tsdf_local_cfg *cfg, float *X_refined_dev,
                            uint8_t *hits_dev, void *stream);
 
+/* ---- quality maps on the device -----------------------
+ * Replaces the per-keyframe torch/numpy round trip of
+ * mast3r_slam/quality_core.py compute_batch (:127-140).
+ * quality_patch_grids: per-patch (patch_size^2 pixels, row-major H x W maps in
+ * device memory) lower medians -- u = median(1 - sqrt(clamp(C/(C_thr+1e-8)) *
+ * clamp(Q/(Q_thr+1e-8)))) (u_from_CQ :43-49; NaN when the patch holds no
+ * finite value), r = median of r_pix over the valid pixels, 0 when there is
+ * none (r_from_scalar :51-52 / reduce_grid :15-27), valid = 1 if any pixel of
+ * the patch is valid (valid_grid :54-56).  Grids are (H/ps) x (W/ps) float32.
+ * quality_classify: classify (:63-109) on flattened grids of n patches
+ * (n <= 3072): class_id int64, priority float32 and, if q_grid_dev is not
+ * NULL, q = 1 - clamp(priority, 0, 1) -- the per-patch weight
+ * b200tsdf_integrate_keyframes takes as q_grid_dev.  Both calls are
+ * stream-ordered and never synchronise. */
+int b200tsdf_quality_patch_grids(const float *C_dev, const float *Q_dev, const float *r_pix_dev,
+                                 const uint8_t *valid_dev, int32_t H, int32_t W,
+                                 int32_t patch_size, double C_thr, double Q_thr,
+                                 float *u_grid_dev, float *r_grid_dev, float *valid_grid_dev,
+                                 int32_t device, void *stream);
+int b200tsdf_quality_classify(const float *delta_cov_dev, const float *r_dev, const float *u_dev,
+                              int32_t n, double thr_zr, double thr_zu, double thr_dc,
+                              int64_t *class_dev, float *priority_dev, float *q_grid_dev,
+                              int32_t device, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -22,7 +22,7 @@ SYMBOLS = [
     "b200tsdf_extract_mesh", "b200tsdf_export_seam_blocks", "b200tsdf_import_halo_blocks",
     "b200tsdf_export_block_data", "b200tsdf_import_blocks",
     "b200tsdf_local_dims", "b200tsdf_local_build",
-    "b200tsdf_local_raycast",
+    "b200tsdf_local_raycast", "b200tsdf_quality_patch_grids", "b200tsdf_quality_classify",
 ]
 
 
@@ -81,6 +81,10 @@ def lib():
     L.b200tsdf_export_seam_blocks.argtypes = [vp, vp, vp, vp, i64, vp, vp]
     L.b200tsdf_import_halo_blocks.argtypes = [vp, vp, vp, vp, i64, vp]
     L.b200tsdf_export_block_data.argtypes = [vp, vp, vp, vp, i64, vp, vp]
+    L.b200tsdf_quality_patch_grids.argtypes = [vp, vp, vp, vp, i32, i32, i32, C.c_double,
+                                               C.c_double, vp, vp, vp, i32, vp]
+    L.b200tsdf_quality_classify.argtypes = [vp, vp, vp, i32, C.c_double, C.c_double, C.c_double,
+                                            vp, vp, vp, i32, vp]
     L.b200tsdf_import_blocks.argtypes = [vp, vp, vp, vp, i64, vp]
     L.b200tsdf_local_dims.argtypes = [vp, C.POINTER(LocalCfg), vp]
     L.b200tsdf_local_build.argtypes = [vp, vp, vp, vp, i64, C.POINTER(LocalCfg), vp, vp, vp, vp]

@@ -1,0 +1,110 @@
+"""B200 mirror of the reference `mast3r_slam/quality_core.py`.
+
+Same function names, arguments and result dict as the reference
+(quality_core.py:15-140), but every grid is produced by CUDA kernels
+(`csrc/quality.cu` through the C ABI) and STAYS on the device: the reference
+moves each keyframe's maps tensor -> numpy -> queue -> tensor -> numpy
+(tracker.py:129-141, quality_async.py:12-46) before the TSDF path reads them.
+`compute_batch` returns device tensors; `pack_result(..., to_host=True)` gives
+the reference's numpy dict for consumers that want it; `quality_grid(result)`
+is the per-patch weight q = 1 - priority that `TSDFVolume.integrate_keyframes`
+takes as `q_grid`.
+"""
+import ctypes as C
+
+import torch
+
+from . import _ffi
+
+
+def _dev_index(device):
+    d = torch.device(device)
+    if d.type != "cuda":
+        raise _ffi.B200TSDFError("quality_core: CUDA device required (there is no CPU fallback)")
+    return d.index if d.index is not None else torch.cuda.current_device()
+
+
+def _stream(device):
+    return C.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+
+
+def _f32(x, device, n):
+    return torch.as_tensor(x).to(device, torch.float32).reshape(-1)[:n].contiguous()
+
+
+def patch_grids(Ck, Qk, r_pix, valid, h, w, ps, C_thr, Q_thr, device):
+    """u (u_from_CQ :43-49), r (r_from_scalar :51-52 with `valid`), valid grid
+    (:54-56) of one keyframe in ONE launch: (gh, gw) float32 device tensors."""
+    n = h * w
+    Ct, Qt, rt = _f32(Ck, device, n), _f32(Qk, device, n), _f32(r_pix, device, n)
+    vt = torch.as_tensor(valid).to(device).reshape(-1)[:n].to(torch.uint8).contiguous()
+    gh, gw = h // ps, w // ps
+    u, r, v = (torch.empty(gh, gw, dtype=torch.float32, device=device) for _ in range(3))
+    _ffi.check(_ffi.lib().b200tsdf_quality_patch_grids(
+        Ct.data_ptr(), Qt.data_ptr(), rt.data_ptr(), vt.data_ptr(), h, w, ps, float(C_thr),
+        float(Q_thr), u.data_ptr(), r.data_ptr(), v.data_ptr(), _dev_index(device),
+        _stream(device)), "quality_patch_grids")
+    return u, r, v
+
+
+def view_weight(t_norm, theta, b0, theta0, device):  # :34-37
+    t = torch.clamp(t_norm / b0, 0, 1) if b0 > 0 else torch.ones((), device=device)
+    r = torch.clamp(theta / theta0, 0, 1) if theta0 > 0 else torch.ones((), device=device)
+    return 0.5 * (t + r)
+
+
+def ema_delta(prev, inc, alpha):  # :39-41
+    new = alpha * prev + (1 - alpha) * inc
+    return new, new - prev
+
+
+def classify(delta_cov, r, u, thr_zr=1.0, thr_zu=1.0, thr_dc=0.02, return_q=False):
+    """:63-109 on the device: (class_id int64, priority float32[, q = 1 - priority])."""
+    shape = delta_cov.shape
+    dev = delta_cov.device
+    dc = delta_cov.to(torch.float32).reshape(-1).contiguous()
+    rr = r.to(dev, torch.float32).reshape(-1).contiguous()
+    uu = u.to(dev, torch.float32).reshape(-1).contiguous()
+    cls = torch.empty(dc.numel(), dtype=torch.int64, device=dev)
+    pri = torch.empty(dc.numel(), dtype=torch.float32, device=dev)
+    q = torch.empty(dc.numel(), dtype=torch.float32, device=dev)
+    _ffi.check(_ffi.lib().b200tsdf_quality_classify(
+        dc.data_ptr(), rr.data_ptr(), uu.data_ptr(), dc.numel(), float(thr_zr), float(thr_zu),
+        float(thr_dc), cls.data_ptr(), pri.data_ptr(), q.data_ptr(), _dev_index(dev),
+        _stream(dev)), "quality_classify")
+    out = (cls.reshape(shape), pri.reshape(shape))
+    return out + (q.reshape(shape),) if return_q else out
+
+
+def pack_result(kfid, dc, r, u, cls, pri, ewma, q=None, to_host=False):  # :111-125
+    conv = (lambda x: x.cpu().numpy()) if to_host else (lambda x: x)
+    out = {"kf_id": int(kfid), "delta_cov": conv(dc), "r": conv(r), "u": conv(u),
+           "class_id": conv(cls), "priority": conv(pri), "cov_ewma": conv(ewma)}
+    if q is not None:
+        out["q_grid"] = conv(q)
+    return out
+
+
+def compute_batch(batch, ps, alpha, b0, theta0, C_thr, Q_thr, thr_zr, thr_zu, thr_dc, device,
+                  to_host=False):  # :127-140
+    outs = []
+    for jb in batch:
+        h, w = jb["H"], jb["W"]
+        u, r, vg = patch_grids(jb["Ck"], jb["Qk"], jb["r_pix"], jb["valid_kf"], h, w, ps, C_thr,
+                               Q_thr, device)
+        inc = vg * view_weight(torch.as_tensor(jb["t_norm"]).to(device),
+                               torch.as_tensor(jb["theta"]).to(device), b0, theta0, device)
+        prev = jb.get("cov_ewma", None)
+        prev = torch.zeros_like(inc) if prev is None else torch.as_tensor(prev).to(device)
+        ew, dc = ema_delta(prev, inc, alpha)
+        cls, pri, q = classify(dc, r, u, thr_zr, thr_zu, thr_dc, return_q=True)
+        outs.append(pack_result(jb["kf_id"], dc, r, u, cls, pri, ew, q, to_host))
+    return outs
+
+
+def quality_grid(result):
+    """(1, gh, gw) device tensor q = 1 - priority for `integrate_keyframes`."""
+    q = result.get("q_grid")
+    if q is None:
+        q = 1.0 - torch.as_tensor(result["priority"], dtype=torch.float32).clamp(0.0, 1.0)
+    return q.reshape(1, *q.shape[-2:]).contiguous()

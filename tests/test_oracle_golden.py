@@ -45,7 +45,7 @@ def test_oracle_matches_reference_golden(case):
 
 def test_all_fixtures_have_cases():
     names = sorted(os.path.basename(p)[:-4] for p in glob.glob(os.path.join(mg.HERE, "*.npz"))
-                   if not os.path.basename(p).startswith(("local_", "mc_", "opt_", "refine_")))
+                   if not os.path.basename(p).startswith(("local_", "mc_", "opt_", "refine_", "quality_")))
     assert names == CASES
 
 
