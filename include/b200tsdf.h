@@ -247,6 +247,19 @@ int b200tsdf_local_raycast(const float *tsdf_dev, const int32_t dims3_host[3],
                            int64_t m, const b200tsdf_local_cfg *cfg, float *X_refined_dev,
                            uint8_t *hits_dev, void *stream);
 
+/* ---- pose optimiser normal equations ---------
+ * One Gauss-Newton linearisation of TSDFPoseOptimizer._optimize_single
+ * (mast3r_slam/tsdf/tsdf_optimizer.py:72-116) in one launch: world points =
+ * Sim3(pose) . pts_cam (float32, :76), r = tsdf(p), J = [g, -p x g, p . g]
+ * (:107-110), w = max(lambda * conf, 1e-6) (:113), H = sum w J J^T (7 x 7
+ * row-major), b = sum w r J, used = points with value and gradient.  pts_cam:
+ * n x 3 float32, conf: n float64 (device); pose: 8 float32 [t, q(xyzw), s],
+ * H, b, used: host.  Synchronises the stream (the caller solves on the host). */
+int b200tsdf_pose_normal_equations(b200tsdf_t *h, int which, const float *pts_cam_dev,
+                                   const double *conf_dev, int64_t n, const float *pose_host,
+                                   double lambda, double *H_host, double *b_host,
+                                   int64_t *used_host, void *stream);
+
 /* ---- quality maps on the device -----------------------
  * Replaces the per-keyframe torch/numpy round trip of
  * mast3r_slam/quality_core.py compute_batch (:127-140).

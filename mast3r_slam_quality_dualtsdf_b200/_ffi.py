@@ -23,6 +23,7 @@ SYMBOLS = [
     "b200tsdf_export_block_data", "b200tsdf_import_blocks",
     "b200tsdf_local_dims", "b200tsdf_local_build",
     "b200tsdf_local_raycast", "b200tsdf_quality_patch_grids", "b200tsdf_quality_classify",
+    "b200tsdf_pose_normal_equations",
 ]
 
 
@@ -83,6 +84,8 @@ def lib():
     L.b200tsdf_export_block_data.argtypes = [vp, vp, vp, vp, i64, vp, vp]
     L.b200tsdf_quality_patch_grids.argtypes = [vp, vp, vp, vp, i32, i32, i32, C.c_double,
                                                C.c_double, vp, vp, vp, i32, vp]
+    L.b200tsdf_pose_normal_equations.argtypes = [vp, i32, vp, vp, i64, vp, C.c_double, vp, vp, vp,
+                                                 vp]
     L.b200tsdf_quality_classify.argtypes = [vp, vp, vp, i32, C.c_double, C.c_double, C.c_double,
                                             vp, vp, vp, i32, vp]
     L.b200tsdf_import_blocks.argtypes = [vp, vp, vp, vp, i64, vp]

@@ -11,7 +11,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libb200tsdf.so")
 SOURCES = ["volume.cu", "integrate.cu", "sweep.cu", "mc.cu", "local.cu", "quality.cu"]
-HEADERS = ["common.cuh", "ray.cuh", "march_fast.cuh", "fuse.cuh", "mc_tables.h", os.path.join("..", "..", "include", "b200tsdf.h")]
+HEADERS = ["common.cuh", "ray.cuh", "march_fast.cuh", "fuse.cuh", "sim3.cuh", "mc_tables.h", os.path.join("..", "..", "include", "b200tsdf.h")]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
     "-O3", "-lineinfo", "-std=c++17",

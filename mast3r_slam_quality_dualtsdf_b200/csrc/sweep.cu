@@ -4,6 +4,7 @@
 // TSDFVolume.query + _estimate_gradient (:93-128); export has no reference
 // counterpart (it dumps what TSDFVolume._voxels holds, for parity tests).
 #include "common.cuh"
+#include "sim3.cuh"
 #include "ray.cuh"
 
 // One CTA per allocated block, 128 threads x 4 voxels, 128-bit loads.
@@ -167,23 +168,22 @@ __device__ __forceinline__ bool fetch(const VolumeDev &v, int which, int kx, int
   return voxel_view(v.vox[off], v.cnt[off], which, v.max_weight, t, w, hits);
 }
 
+// Nearest-voxel tsdf and central-difference gradient of one point
+// (TSDFVolume.query, global_volume.py:93-130).  Returns flags: 1 value, 3 value + gradient.
 template <typename T>
-__global__ void query_kernel(VolumeDev v, int which, const T *__restrict__ pts, long long m,
-                             T vs, double voxel_size, double *tsdf, double *grad,
-                             uint8_t *flags) {
+__device__ __forceinline__ uint8_t query_point(const VolumeDev &v, int which, const T pt[3], T vs,
+                                               double voxel_size, double &tv, double g[3]) {
   using R = Real<T>;
-  long long p = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (p >= m) return;
   int k[3];
   for (int d = 0; d < 3; ++d) { // global_volume.py:133-134
-    T f = R::flr(R::div(pts[3 * p + d], vs));
+    T f = R::flr(R::div(pt[d], vs));
     f = f < (T)-2.0e9 ? (T)-2.0e9 : (f > (T)2.0e9 ? (T)2.0e9 : f);
     k[d] = (int)f;
   }
   uint8_t fl = 0;
-  double tv = 0.0, g[3] = {0.0, 0.0, 0.0};
+  tv = 0.0, g[0] = g[1] = g[2] = 0.0;
   float t, w;
-  if (isfinite((double)pts[3 * p]) && fetch(v, which, k[0], k[1], k[2], t, w) &&
+  if (isfinite((double)pt[0]) && fetch(v, which, k[0], k[1], k[2], t, w) &&
       w >= v.min_weight) { // :98-100
     fl = 1;
     tv = (double)t;
@@ -213,6 +213,18 @@ __global__ void query_kernel(VolumeDev v, int which, const T *__restrict__ pts, 
       }
     }
   }
+  return fl;
+}
+
+template <typename T>
+__global__ void query_kernel(VolumeDev v, int which, const T *__restrict__ pts, long long m,
+                             T vs, double voxel_size, double *tsdf, double *grad,
+                             uint8_t *flags) {
+  long long p = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= m) return;
+  const T pt[3] = {pts[3 * p], pts[3 * p + 1], pts[3 * p + 2]};
+  double tv, g[3];
+  const uint8_t fl = query_point<T>(v, which, pt, vs, voxel_size, tv, g);
   tsdf[p] = tv;
   grad[3 * p] = (fl & 2) ? g[0] : 0.0;
   grad[3 * p + 1] = (fl & 2) ? g[1] : 0.0;
@@ -242,6 +254,88 @@ extern "C" int b200tsdf_query(b200tsdf_t *h, int which, const void *pts_dev, int
                                                h->cfg.voxel_size, h->cfg.voxel_size, tsdf_dev,
                                                grad_dev, flags_dev);
   B200_CUDA(cudaGetLastError());
+  return B200TSDF_OK;
+}
+
+// ---------------------------------------------- pose optimiser (A9, 8(f) rank 4)
+// One launch per Gauss-Newton iteration of TSDFPoseOptimizer._optimize_single
+// (tsdf_optimizer.py:72-116): Sim3 act of the sampled keyframe points (float32,
+// :76), query (:94-105), Jacobian J = [g, -p x g, p . g] and the weighted 7 x 7
+// normal equations H = sum w J J^T, b = sum w r J with w = max(lambda C, 1e-6)
+// (:107-116), reduced in float64: warp shuffles, then one atomicAdd per warp
+// and entry.  out = [H upper triangle (28) | b (7) | used (1)].
+__global__ void __launch_bounds__(128)
+    pose_normal_eq_kernel(VolumeDev v, int which, const float *__restrict__ pts_cam,
+                          const double *__restrict__ conf, long long n, const float *pose,
+                          float vs, double voxel_size, double lambda, double *out) {
+  const long long p = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  double acc[36];
+#pragma unroll
+  for (int i = 0; i < 36; ++i) acc[i] = 0.0;
+  if (p < n) {
+    float w0, w1, w2;
+    sim3_act(pose, pts_cam[3 * p], pts_cam[3 * p + 1], pts_cam[3 * p + 2], w0, w1, w2);
+    const float pt[3] = {w0, w1, w2};
+    double t, g[3];
+    const uint8_t fl = query_point<float>(v, which, pt, vs, voxel_size, t, g);
+    const double x = (double)w0, y = (double)w1, z = (double)w2;
+    double J[7] = {g[0], g[1], g[2], -(y * g[2] - z * g[1]), -(z * g[0] - x * g[2]),
+                   -(x * g[1] - y * g[0]), x * g[0] + y * g[1] + z * g[2]};
+    bool ok = fl == 3 && isfinite(t);
+#pragma unroll
+    for (int i = 0; i < 7; ++i) ok = ok && isfinite(J[i]); // :111-112
+    if (ok) {
+      const double w = fmax(lambda * conf[p], 1.0e-6);
+      int k = 0;
+#pragma unroll
+      for (int i = 0; i < 7; ++i)
+#pragma unroll
+        for (int j = i; j < 7; ++j) acc[k++] = w * J[i] * J[j];
+#pragma unroll
+      for (int i = 0; i < 7; ++i) acc[28 + i] = w * t * J[i];
+      acc[35] = 1.0;
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < 36; ++i) {
+    double a = acc[i];
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) a += __shfl_xor_sync(0xFFFFFFFFu, a, d);
+    if ((threadIdx.x & 31) == 0 && a != 0.0) atomicAdd(out + i, a);
+  }
+}
+
+extern "C" int b200tsdf_pose_normal_equations(b200tsdf_t *h, int which, const float *pts_cam_dev,
+                                              const double *conf_dev, int64_t n,
+                                              const float *pose_host, double lambda,
+                                              double *H_host, double *b_host, int64_t *used_host,
+                                              void *stream) {
+  if (!h || n < 0 || (which != 0 && which != 1) || !pose_host || !H_host || !b_host ||
+      !used_host || (n > 0 && (!pts_cam_dev || !conf_dev))) {
+    b200_set_error("b200tsdf_pose_normal_equations: invalid argument");
+    return B200TSDF_E_INVALID;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  B200_CUDA(cudaSetDevice(h->cfg.device));
+  // scratch (64 x 8 bytes): [24..60) accumulators, [60..64) the pose (8 floats)
+  double *acc = reinterpret_cast<double *>(h->scratch + 24);
+  float *pose_dev = reinterpret_cast<float *>(h->scratch + 60);
+  B200_CUDA(cudaMemsetAsync(acc, 0, 36 * sizeof(double), st));
+  B200_CUDA(cudaMemcpyAsync(pose_dev, pose_host, 8 * sizeof(float), cudaMemcpyHostToDevice, st));
+  if (n > 0) {
+    pose_normal_eq_kernel<<<(unsigned)((n + 127) / 128), 128, 0, st>>>(
+        h->d, which, pts_cam_dev, conf_dev, (long long)n, pose_dev, (float)h->cfg.voxel_size,
+        h->cfg.voxel_size, lambda, acc);
+    B200_CUDA(cudaGetLastError());
+  }
+  double r[36];
+  B200_CUDA(cudaMemcpyAsync(r, acc, sizeof(r), cudaMemcpyDeviceToHost, st));
+  B200_CUDA(cudaStreamSynchronize(st));
+  int k = 0;
+  for (int i = 0; i < 7; ++i)
+    for (int j = i; j < 7; ++j) H_host[i * 7 + j] = H_host[j * 7 + i] = r[k++];
+  for (int i = 0; i < 7; ++i) b_host[i] = r[28 + i];
+  *used_host = (int64_t)(r[35] + 0.5);
   return B200TSDF_OK;
 }
 

@@ -191,6 +191,27 @@ class TSDFVolume:
     # ------------------------------------------------------------------
     # Utility
     # ------------------------------------------------------------------
+    def pose_normal_equations(self, pts_cam, conf, pose, lam, which: int = 0):
+        """One Gauss-Newton linearisation of the TSDF pose optimiser in ONE
+        launch (Sim3 act + query + Jacobian + 7x7 reduction, float64):
+        returns (H (7,7) ndarray, b (7,) ndarray, used int).  pts_cam (n,3)
+        float32 and conf (n,) float64 device tensors, pose 8 floats."""
+        import numpy as np
+
+        pts = pts_cam.to(self.device, torch.float32).reshape(-1, 3).contiguous()
+        cf = conf.to(self.device, torch.float64).reshape(-1).contiguous()
+        ps = np.ascontiguousarray(np.asarray(pose, np.float32).reshape(8))
+        H = np.zeros((7, 7), np.float64)
+        b = np.zeros(7, np.float64)
+        used = C.c_int64()
+        with self._lock:
+            _ffi.check(_ffi.lib().b200tsdf_pose_normal_equations(
+                self._h, which, pts.data_ptr(), cf.data_ptr(), pts.shape[0],
+                ps.ctypes.data_as(C.c_void_p), float(lam), H.ctypes.data_as(C.c_void_p),
+                b.ctypes.data_as(C.c_void_p), C.byref(used), _stream_ptr(self.device)),
+                "pose_normal_equations")
+        return H, b, int(used.value)
+
     def stats(self, which: int = 0) -> Dict[str, float]:
         """Reference signature (global_volume.py:136-140)."""
         a, b = C.c_int64(), C.c_int64()

@@ -35,6 +35,21 @@ def act(pose, pts):
     return pose[7] * (pts @ quat_to_R(pose[3:7]).T) + pose[:3]
 
 
+def act_kernel_order(pose, pts):
+    """`act` in the float32 operation order of the CUDA kernels (csrc/sim3.cuh,
+    the reference's actSO3 / actSim3): x + 2 w (q x x) + 2 q x (q x x), then
+    scale, then translate.  Bit-identical to the device path on CPU tensors."""
+    P = pose.reshape(8).to(torch.float32).cpu()
+    x = pts.to(torch.float32).cpu()
+    q, w, s, t = P[3:6], P[6], P[7], P[:3]
+    uv = 2.0 * torch.stack([q[1] * x[:, 2] - q[2] * x[:, 1], q[2] * x[:, 0] - q[0] * x[:, 2],
+                            q[0] * x[:, 1] - q[1] * x[:, 0]], dim=1)
+    cr = torch.stack([q[1] * uv[:, 2] - q[2] * uv[:, 1], q[2] * uv[:, 0] - q[0] * uv[:, 2],
+                      q[0] * uv[:, 1] - q[1] * uv[:, 0]], dim=1)
+    a = (x + w * uv) + cr
+    return (a * s + t).to(pts.device)
+
+
 def exp(delta):
     """Sim3 exponential of a tangent vector (7,) -> pose (8,) (float64)."""
     d = delta.reshape(7).to(torch.float64)

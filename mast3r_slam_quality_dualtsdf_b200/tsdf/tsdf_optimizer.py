@@ -2,10 +2,10 @@
 
 Same class, constructor, `pre_refine` / `optimize_keyframes` and config keys
 (tsdf_optimizer.py:12-43).  What changes: the per-point Python loop over
-`volume.query` (7 dict lookups per point, :94-105) is ONE batched
-`b200tsdf_query` launch, and the 7x7 normal equations (:107-116) are reduced
-on the device in float64; only H (7x7) and b (7) cross to the host for the
-solve (:82).  The Sim3 retraction `exp(delta) * pose` (:85-86) uses tsdf/sim3.py
+`volume.query` (7 dict lookups per point, :94-105) and the 7x7 normal
+equations (:107-116) are ONE `b200tsdf_pose_normal_equations` launch per
+Gauss-Newton iteration (Sim3 act + query + Jacobian + float64 reduction in the
+kernel); only H (7x7) and b (7) cross to the host for the solve (:82).  The Sim3 retraction `exp(delta) * pose` (:85-86) uses tsdf/sim3.py
 instead of the missing lietorch submodule.
 """
 from typing import Sequence
@@ -74,8 +74,9 @@ class TSDFPoseOptimizer:
         pose = pose0.to(torch.float64).cpu()
         used = 0
         for _ in range(iterations):
-            p_world = sim3.act(pose.to(self.device, torch.float32), pts_cam)  # float32 like :76
-            H, b, used = self._normal_equations(p_world, conf_sel)
+            # :76 + :94-116 fused: float32 Sim3 act, query, Jacobian, 7x7 reduction
+            H, b, used = self.volume.pose_normal_equations(
+                pts_cam, conf_sel, pose.to(torch.float32).numpy(), self.lambda_tsdf, self.which)
             if used < 6:  # :78-79
                 break
             try:
@@ -94,7 +95,10 @@ class TSDFPoseOptimizer:
                     tgt_data.shape)
 
     def _normal_equations(self, p_world, conf_sel):
-        """:94-116 batched: residual r = tsdf(p), J = [g, -p x g, p . g],
+        """Device-tensor statement of the same linearisation from world points
+        (`b200tsdf_query` + torch reductions): kept as the cross-check of the
+        fused kernel (tests) and for callers that hold world points.
+        :94-116 batched: residual r = tsdf(p), J = [g, -p x g, p . g],
         weight lambda * C, H = sum (sqrt(w) J)(sqrt(w) J)^T, b = sum sqrt(w) J r sqrt(w)."""
         t, g, fl = self.volume.query_batch(p_world, self.which)
         ok = fl == 3  # value and gradient present (:99-100)

@@ -80,6 +80,24 @@ def test_normal_equations_match_oracle(cuda_device):
     assert used == uo and used > 50
     assert np.allclose(H, Ho, rtol=1e-4, atol=1e-6 * np.abs(Ho).max())
     assert np.allclose(b, bo, rtol=1e-4, atol=1e-6 * np.abs(bo).max())
+    # the fused kernel (Sim3 act + query + Jacobian + 7x7 reduction in one launch,
+    # b200tsdf_pose_normal_equations) states the same linearisation: float64 sums
+    # in a different order, world points by the kernel's own float32 Sim3 act
+    Hf, bf, uf = vol.pose_normal_equations(pts, conf, bad, mg.CFG["lambda"])
+    assert abs(uf - used) <= 2  # a point on a voxel face may round to the other side
+    assert np.allclose(Hf, H, rtol=2e-2, atol=2e-2 * np.abs(H).max())
+    assert np.allclose(Hf, Hf.T) and np.all(np.linalg.eigvalsh(Hf) > -1e-9 * np.abs(Hf).max())
+    pw_k = torch.from_numpy(kf["X"][1][G["choice"]]).to(cuda_device)
+    # exact cross-check: feed the torch statement the SAME world points the kernel forms
+    from mast3r_slam_quality_dualtsdf_b200.tsdf.sim3 import act_kernel_order
+    Hk, bk, uk = opt._normal_equations(act_kernel_order(torch.from_numpy(bad), pw_k), conf)
+    assert uk == uf
+    assert np.allclose(Hf, Hk, rtol=1e-10, atol=1e-12 * np.abs(Hk).max())
+    assert np.allclose(bf, bk, rtol=1e-10, atol=1e-12 * np.abs(bk).max())
+    # no point, empty volume: zeros
+    H0, b0, u0 = TSDFVolume(mg.VOXEL, mg.TRUNC, device=cuda_device).pose_normal_equations(
+        pts, conf, bad, mg.CFG["lambda"])
+    assert u0 == 0 and not H0.any() and not b0.any()
 
 
 def test_manager_integrates_and_reintegrates_like_reference(cuda_device):
