@@ -37,6 +37,9 @@
 #ifndef FUSE_MINB
 #define FUSE_MINB 4
 #endif
+#ifndef FUSE_SEAM_TRIM
+#define FUSE_SEAM_TRIM 1
+#endif
 
 struct WarpCache { // one per warp, in shared memory (unbounded volumes)
   unsigned long long key[FUSE_CACHE_WAYS];
@@ -182,6 +185,11 @@ __device__ __forceinline__ void march_warp(const VolumeDev &v, WarpCache &wc, co
   // skips the per-voxel bound test.
   float lim;
   bool far = false, check_bounds = false, inside = false;
+  // multi-GPU seam trim: z range [zt_lo, zt_hi) (voxel layers) that holds every
+  // slab of this rank the band can reach; samples clearly outside it are not
+  // marched (the per-voxel ownership test at the fold stays the exact one)
+  bool trim = false;
+  float zt_lo = 0.f, zt_hi = 0.f;
   if (BOUNDED) {
     float d0 = fmaxf(r.len - mc.trunc, 0.0f);
     float ax0 = fmaf(d0, r.dx, r.ox) * mc.inv_vs, ax1 = fmaf(r.maxd, r.dx, r.ox) * mc.inv_vs;
@@ -200,6 +208,17 @@ __device__ __forceinline__ void march_warp(const VolumeDev &v, WarpCache &wc, co
         if (need < 0) need += v.slab_count;
         any = need <= s_hi - s_lo;
         all = (s_hi == s_lo) && need == 0;
+#if FUSE_SEAM_TRIM
+        if (any && !all && fabsf(zl) < 4.0e6f && fabsf(zh) < 4.0e6f) {
+          const int s_own = s_lo + need, span = s_hi - s_own; // first / last owned slab in reach
+          const int s_last = s_own + (v.slab_mask >= 0 ? (span & ~v.slab_mask)
+                                                       : span - span % v.slab_count);
+          const float wz = (float)(1 << v.slab_shift);
+          zt_lo = fmaf((float)s_own, wz, (float)v.slab_z0);
+          zt_hi = fmaf((float)(s_last + 1), wz, (float)v.slab_z0);
+          trim = true;
+        }
+#endif
       }
       if (!any) { // the band misses every slab of this rank
         live = false;
@@ -247,6 +266,24 @@ __device__ __forceinline__ void march_warp(const VolumeDev &v, WarpCache &wc, co
       float sb = __fsub_rn(r.len, (i1 == r.n - 1) ? last_dist : __fmul_rn((float)i1, r.lstep));
       if (!(fabsf(sa) > mc.trunc) && !(fabsf(sb) > mc.trunc)) cnt = i1 - i0 + 1;
     }
+#if FUSE_SEAM_TRIM
+    if (BOUNDED && trim && cnt > 0) {
+      // sample i sits at z ~ zq0 + i * g voxel layers (the exact recipe differs by
+      // rounding only: < 1e-3 layers).  With |g| >= 4e-3 that is < 0.3 samples, and
+      // the range keeps one more guard sample on either side; flatter rays are not
+      // trimmed.  Everything cut here lies in a foreign slab (or off the grid), so
+      // applied = ev - drop is unchanged.
+      const float g = r.dz * r.lstep * mc.inv_vs, zq0 = r.oz * mc.inv_vs;
+      if (fabsf(g) >= 4.0e-3f) {
+        const float ig = 1.0f / g;
+        const float ia = (zt_lo - zq0) * ig, ib = (zt_hi - zq0) * ig;
+        const float flo = fmaxf(fminf(ia, ib), -1.0e9f), fhi = fminf(fmaxf(ia, ib), 1.0e9f);
+        const int j0 = max(i0, (int)floorf(flo) - 1), j1 = min(i1, (int)ceilf(fhi) + 1);
+        i0 = j0;
+        cnt = j1 >= j0 ? j1 - j0 + 1 : 0;
+      }
+    }
+#endif
   }
   const int J = __reduce_max_sync(0xFFFFFFFFu, cnt);
   const float MAGIC = 12582912.0f; // 1.5 * 2^23

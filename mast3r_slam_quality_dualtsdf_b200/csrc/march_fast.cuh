@@ -39,7 +39,9 @@ __device__ __forceinline__ void commit_tally(const VolumeDev &v, Tally tl) {
   const bool any_culled = __any_sync(0xFFFFFFFFu, tl.culled != 0);
   const bool any_ev = __any_sync(0xFFFFFFFFu, (tl.ev_p | tl.ev_q) != 0);
   tl.rays = __reduce_add_sync(0xFFFFFFFFu, tl.rays);
-  if (tl.rays == 0 && !any_lost && !any_culled) return; // nothing to report (warp-uniform)
+  // nothing to report (warp-uniform); a warp can hold updates of rays it did not
+  // count itself once rays are re-dealt between warps
+  if (tl.rays == 0 && !any_lost && !any_culled && !any_ev) return;
   tl.ev_p = any_ev ? __reduce_add_sync(0xFFFFFFFFu, tl.ev_p - tl.drop_p) : 0u;
   tl.ev_q = any_ev ? __reduce_add_sync(0xFFFFFFFFu, tl.ev_q - tl.drop_q) : 0u;
   uint32_t dropped = 0;

@@ -51,12 +51,16 @@ def main():
                 if i >= a.warmup:
                     evs.append(e0.elapsed_time(e1))
             c = vol.counters()
-            per_rank.append((sum(evs) / len(evs), int(c["updates_primary"] + c["updates_quality"])))
+            per_rank.append((sum(evs) / len(evs), int(c["updates_primary"] + c["updates_quality"]),
+                             1.0 - c.get("culled_rays", 0) / max(1, c["rays"])))
             del vol
         ms = [p[0] for p in per_rank]
         upd = sum(p[1] for p in per_rank)
         out[R] = {"max_ms": max(ms), "mean_ms": sum(ms) / len(ms), "ms": [round(m, 4) for m in ms],
-                  "updates": upd}
+                  "updates": upd,
+                  # share of the rays a rank marches / share of the updates it applies
+                  "marched": [round(p[2], 4) for p in per_rank],
+                  "applied": [round(p[1] / max(1, upd), 4) for p in per_rank]}
         print(R, json.dumps(out[R]), flush=True)
 
 
