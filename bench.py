@@ -410,11 +410,28 @@ def run_b200(args):
                 "Qk": (torch.rand(H * W, generator=gq) * 2).to(dev)}
         qargs = dict(ps=16, alpha=0.8, b0=0.15, theta0=0.1745, C_thr=1.5, Q_thr=1.5, thr_zr=1.0,
                      thr_zu=1.0, thr_dc=0.02, device=dev)
-        q_ms, _ = dev_ms(lambda: [qc.compute_batch([qjob], **qargs) for _ in range(20)])
+        q_ms1, _ = dev_ms(lambda: [qc.compute_batch([qjob], **qargs) for _ in range(20)])
+        qjobs = [dict(qjob, kf_id=i) for i in range(B)]
+        qc.compute_batch(qjobs, **qargs)
+        q_ms, _ = dev_ms(lambda: [qc.compute_batch(qjobs, **qargs) for _ in range(5)])
+        st = {k: torch.stack([j[k] for j in qjobs]) for k in ("Ck", "Qk", "r_pix")}
+        st["valid"] = torch.stack([j["valid_kf"] for j in qjobs]).to(torch.uint8)
+        tn, th = (torch.stack([j[k] for j in qjobs]).to(dev) for k in ("t_norm", "theta"))
+        sargs = {k: v for k, v in qargs.items() if k != "device"}
+        run_st = lambda: qc.compute_stacked(st["Ck"], st["Qk"], st["r_pix"], st["valid"], tn, th,  # noqa: E731
+                                            None, H, W, device=dev, **sargs)
+        run_st()
+        q_ms_st, _ = dev_ms(lambda: [run_st() for _ in range(5)])
         q_bytes = H * W * 13  # C, Q, r_pix float32 + valid u8, read once
-        quality = {"kernels": "quality_patch_kernel + quality_classify_kernel",
-                   "us_per_keyframe": 1e3 * q_ms / 20, "algorithmic_bytes": q_bytes,
-                   "note": "launch/latency-bound: 2.5 MB per keyframe, one CTA classifies"}
+        quality = {"kernels": "quality_patch_kernel + quality_finish_batch_kernel (2 launches per batch)",
+                   "keyframes_per_batch": B,
+                   "us_per_keyframe": 1e3 * q_ms / 5 / B,
+                   "us_per_keyframe_batch_of_1": 1e3 * q_ms1 / 20,
+                   "us_per_keyframe_stacked_inputs": 1e3 * q_ms_st / 5 / B,
+                   "stacked_gbs": q_bytes * B * 5 / (q_ms_st * 1e-3) / 1e9,
+                   "algorithmic_bytes": q_bytes,
+                   "note": "through quality_core.compute_batch incl. the stacking of the job "
+                           "tensors; a batch of 1 is launch/latency-bound"}
 
     if rank != 0:
         if world > 1:

@@ -284,6 +284,22 @@ int b200tsdf_quality_classify(const float *delta_cov_dev, const float *r_dev, co
                               int64_t *class_dev, float *priority_dev, float *q_grid_dev,
                               int32_t device, void *stream);
 
+/* compute_batch (quality_core.py:127-140) for B keyframes of one size in two
+ * launches: the per-patch medians of every keyframe (maps B x H*W), then one
+ * CTA per keyframe for inc = valid_grid * view_w[b] (:131; view_w = the
+ * view_weight scalar of :34-37), cov_ewma = alpha * prev + (1 - alpha) * inc
+ * and delta_cov = cov_ewma - prev (ema_delta :39-41, float32 like torch;
+ * prev_ewma_dev NULL = zeros) and classify.  All grids are B x n float32
+ * (class_id int64), n = (H/ps) * (W/ps) <= 3072.  Stream-ordered. */
+int b200tsdf_quality_batch(const float *C_dev, const float *Q_dev, const float *r_pix_dev,
+                           const uint8_t *valid_dev, const float *view_w_dev,
+                           const float *prev_ewma_dev, int32_t B, int32_t H, int32_t W,
+                           int32_t patch_size, double C_thr, double Q_thr, double alpha,
+                           double thr_zr, double thr_zu, double thr_dc, float *u_grid_dev,
+                           float *r_grid_dev, float *valid_grid_dev, float *ewma_dev,
+                           float *delta_cov_dev, int64_t *class_dev, float *priority_dev,
+                           float *q_grid_dev, int32_t device, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

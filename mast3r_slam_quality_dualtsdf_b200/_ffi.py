@@ -23,7 +23,7 @@ SYMBOLS = [
     "b200tsdf_export_block_data", "b200tsdf_import_blocks",
     "b200tsdf_local_dims", "b200tsdf_local_build",
     "b200tsdf_local_raycast", "b200tsdf_quality_patch_grids", "b200tsdf_quality_classify",
-    "b200tsdf_pose_normal_equations",
+    "b200tsdf_pose_normal_equations", "b200tsdf_quality_batch",
 ]
 
 
@@ -88,6 +88,8 @@ def lib():
                                                  vp]
     L.b200tsdf_quality_classify.argtypes = [vp, vp, vp, i32, C.c_double, C.c_double, C.c_double,
                                             vp, vp, vp, i32, vp]
+    L.b200tsdf_quality_batch.argtypes = [vp, vp, vp, vp, vp, vp, i32, i32, i32, i32] + \
+        [C.c_double] * 6 + [vp] * 8 + [i32, vp]
     L.b200tsdf_import_blocks.argtypes = [vp, vp, vp, vp, i64, vp]
     L.b200tsdf_local_dims.argtypes = [vp, C.POINTER(LocalCfg), vp]
     L.b200tsdf_local_build.argtypes = [vp, vp, vp, vp, i64, C.POINTER(LocalCfg), vp, vp, vp, vp]

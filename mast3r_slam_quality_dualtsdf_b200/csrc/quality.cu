@@ -9,10 +9,11 @@
 //
 // Medians are torch's: nanmedian(dim) = LOWER median of the non-NaN entries
 // (NaN if none), median() = lower median, NaN if any entry is NaN.  A warp owns
-// a patch; the median is found by rank counting over the patch in shared
-// memory (ties broken by index, so exactly one element has the target rank):
-// O(ps^4 / 32) compares per warp, ~10 us for a 384 x 512 keyframe -- the pass
-// is bound by its one read of C, Q, r and the mask.
+// a patch; the element of rank k is found by a bitwise select on the
+// order-preserving integer image of the floats (largest key K with
+// #{keys < K} <= k, built from the top bit down: 32 counting passes over the
+// patch in shared memory, one warp reduction each) -- O(32 ps^2 / 32) compares
+// per warp instead of the O(ps^4 / 32) of rank counting.
 #include <math.h>
 #include <stdint.h>
 
@@ -21,22 +22,27 @@
 #define Q_WARPS 4
 #define Q_MAX_PATCH 1024 // ps <= 32
 
-// rank-select the element of rank `target` among the non-NaN entries of s[0..n)
-__device__ __forceinline__ float warp_select(const float *s, int n, int target, int lane) {
-  float out = 0.f;
-  bool found = false;
-  for (int i = lane; i < n; i += 32) {
-    const float x = s[i];
-    if (x != x) continue;
-    int rank = 0;
-    for (int j = 0; j < n; ++j) {
-      const float y = s[j]; // broadcast read
-      rank += (y < x) || (y == x && j < i);
-    }
-    if (rank == target) out = x, found = true;
+// order-preserving map float -> uint32 (-x < +x, -0 < +0); NaN -> 0xFFFFFFFF (above everything)
+__device__ __forceinline__ uint32_t ord_key(float x) {
+  if (x != x) return 0xFFFFFFFFu;
+  const uint32_t b = __float_as_uint(x);
+  return b ^ ((b >> 31) ? 0xFFFFFFFFu : 0x80000000u);
+}
+__device__ __forceinline__ float ord_unkey(uint32_t k) {
+  return __uint_as_float(k ^ ((k >> 31) ? 0x80000000u : 0xFFFFFFFFu));
+}
+
+// element of rank `target` (0-based, target < number of non-NaN keys) of the keys k[0..n)
+__device__ __forceinline__ float warp_select(const uint32_t *k, int n, int target, int lane) {
+  uint32_t prefix = 0;
+#pragma unroll 1
+  for (int bit = 31; bit >= 0; --bit) {
+    const uint32_t cand = prefix | (1u << bit);
+    int c = 0;
+    for (int i = lane; i < n; i += 32) c += k[i] < cand;
+    if (__reduce_add_sync(0xFFFFFFFFu, c) <= target) prefix = cand;
   }
-  const unsigned m = __ballot_sync(0xFFFFFFFFu, found);
-  return m ? __shfl_sync(0xFFFFFFFFu, out, __ffs(m) - 1) : __int_as_float(0x7FC00000);
+  return ord_unkey(prefix);
 }
 
 __global__ void __launch_bounds__(32 * Q_WARPS)
@@ -44,11 +50,16 @@ __global__ void __launch_bounds__(32 * Q_WARPS)
                          const float *__restrict__ r_pix, const uint8_t *__restrict__ valid, int H,
                          int W, int ps, float c_den, float q_den, float *__restrict__ u_grid,
                          float *__restrict__ r_grid, float *__restrict__ v_grid) {
-  __shared__ float s_u[Q_WARPS][Q_MAX_PATCH], s_r[Q_WARPS][Q_MAX_PATCH];
+  __shared__ uint32_t s_u[Q_WARPS][Q_MAX_PATCH], s_r[Q_WARPS][Q_MAX_PATCH];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int gh = H / ps, gw = W / ps, n = ps * ps;
   const int patch = blockIdx.x * Q_WARPS + warp;
   if (patch >= gh * gw) return;
+  { // blockIdx.y = keyframe of the batch: maps are B x H*W, grids B x gh*gw
+    const long long o_pix = (long long)blockIdx.y * H * W, o_grid = (long long)blockIdx.y * gh * gw;
+    C += o_pix, Q += o_pix, r_pix += o_pix, valid += o_pix;
+    u_grid += o_grid, r_grid += o_grid, v_grid += o_grid;
+  }
   const int gy = patch / gw, gx = patch - gy * gw;
   int k_u = 0, k_r = 0, n_valid = 0;
   for (int i = lane; i < n; i += 32) {
@@ -61,8 +72,8 @@ __global__ void __launch_bounds__(32 * Q_WARPS)
     if (C[pix] != C[pix] || Q[pix] != Q[pix]) u = __int_as_float(0x7FC00000); // clamp keeps NaN in torch
     const bool ok = valid[pix] != 0;
     const float r = ok ? r_pix[pix] : __int_as_float(0x7FC00000); // :24 masked_fill(M < 0.5, nan)
-    s_u[warp][i] = u;
-    s_r[warp][i] = r;
+    s_u[warp][i] = ord_key(u);
+    s_r[warp][i] = ord_key(r);
     k_u += u == u;
     k_r += r == r;
     n_valid += ok;
@@ -84,22 +95,28 @@ __global__ void __launch_bounds__(32 * Q_WARPS)
 #define Q_MAX_N 3072 // 1024 x 768 at patch_size 16; 36 KB of shared memory
 #define Q_CLS_THREADS 512
 
-// lower median of s[0..n) (no NaN inside); every thread returns it
+// lower median of s[0..n) (no NaN inside); every thread returns it.  Same
+// bitwise select, the count of every pass reduced over the CTA.
 __device__ float cta_median(const float *s, int n, float *s_res) {
-  const int target = (n - 1) >> 1;
-  for (int i = threadIdx.x; i < n; i += blockDim.x) {
-    const float x = s[i];
-    int rank = 0;
-    for (int j = 0; j < n; ++j) {
-      const float y = s[j];
-      rank += (y < x) || (y == x && j < i);
-    }
-    if (rank == target) *s_res = x;
+  __shared__ int s_cnt[2][Q_CLS_THREADS / 32];
+  const int target = (n - 1) >> 1, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  (void)s_res;
+  uint32_t prefix = 0;
+#pragma unroll 1
+  for (int bit = 31; bit >= 0; --bit) {
+    const uint32_t cand = prefix | (1u << bit);
+    int c = 0;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) c += ord_key(s[i]) < cand;
+    c = __reduce_add_sync(0xFFFFFFFFu, c);
+    if (lane == 0) s_cnt[bit & 1][warp] = c; // double-buffered: one barrier per pass
+    __syncthreads();
+    int total = 0;
+#pragma unroll
+    for (int w = 0; w < Q_CLS_THREADS / 32; ++w) total += s_cnt[bit & 1][w];
+    if (total <= target) prefix = cand;
   }
   __syncthreads();
-  const float m = *s_res;
-  __syncthreads();
-  return m;
+  return ord_unkey(prefix);
 }
 
 // :58-61 robust_z into z[] (shared); NaN input anywhere -> all NaN (torch.median propagates)
@@ -123,11 +140,13 @@ __device__ void cta_robust_z(const float *x, int n, float *z, float *tmp, float 
   __syncthreads();
 }
 
-__global__ void __launch_bounds__(Q_CLS_THREADS)
-    quality_classify_kernel(const float *__restrict__ dc, const float *__restrict__ r,
-                            const float *__restrict__ u, int n, float thr_zr, float thr_zu,
-                            float thr_dc, long long *__restrict__ cls_out,
-                            float *__restrict__ pri_out, float *__restrict__ q_out) {
+// classify (:63-109) of one keyframe's n patches by one CTA
+__device__ __forceinline__ void classify_cta(const float *dc, const float *__restrict__ r,
+                                             const float *__restrict__ u, int n, float thr_zr,
+                                             float thr_zu, float thr_dc,
+                                             long long *__restrict__ cls_out,
+                                             float *__restrict__ pri_out,
+                                             float *__restrict__ q_out) {
   __shared__ float s_zr[Q_MAX_N], s_zu[Q_MAX_N], s_tmp[Q_MAX_N];
   __shared__ float s_res, s_max[Q_CLS_THREADS / 32];
   __shared__ int s_flag;
@@ -165,6 +184,39 @@ __global__ void __launch_bounds__(Q_CLS_THREADS)
   }
 }
 
+__global__ void __launch_bounds__(Q_CLS_THREADS)
+    quality_classify_kernel(const float *__restrict__ dc, const float *__restrict__ r,
+                            const float *__restrict__ u, int n, float thr_zr, float thr_zu,
+                            float thr_dc, long long *__restrict__ cls_out,
+                            float *__restrict__ pri_out, float *__restrict__ q_out) {
+  classify_cta(dc, r, u, n, thr_zr, thr_zu, thr_dc, cls_out, pri_out, q_out);
+}
+
+// compute_batch (:127-140) after the per-patch medians, one CTA per keyframe:
+// inc = valid_grid * view_weight (:131), cov_ewma / delta_cov = ema_delta
+// (:39-41, torch's separately rounded float32 mul / add / sub), then classify.
+__global__ void __launch_bounds__(Q_CLS_THREADS)
+    quality_finish_batch_kernel(const float *__restrict__ v_grid, const float *__restrict__ view_w,
+                                const float *__restrict__ prev, const float *__restrict__ r,
+                                const float *__restrict__ u, int n, float alpha, float one_m_alpha,
+                                float thr_zr, float thr_zu, float thr_dc,
+                                float *__restrict__ ewma_out, float *dc_out,
+                                long long *__restrict__ cls_out, float *__restrict__ pri_out,
+                                float *__restrict__ q_out) {
+  const long long o = (long long)blockIdx.x * n;
+  const float vw = view_w[blockIdx.x];
+  for (int i = threadIdx.x; i < n; i += blockDim.x) { // classify_cta reads dc[i] on the same thread
+    const float pv = prev ? prev[o + i] : 0.0f;
+    const float inc = __fmul_rn(v_grid[o + i], vw);
+    const float nw = __fadd_rn(__fmul_rn(alpha, pv), __fmul_rn(one_m_alpha, inc));
+    ewma_out[o + i] = nw;
+    dc_out[o + i] = __fsub_rn(nw, pv);
+  }
+  __syncthreads();
+  classify_cta(dc_out + o, r + o, u + o, n, thr_zr, thr_zu, thr_dc, cls_out + o, pri_out + o,
+               q_out ? q_out + o : nullptr);
+}
+
 extern "C" int b200tsdf_quality_patch_grids(const float *C_dev, const float *Q_dev,
                                             const float *r_pix_dev, const uint8_t *valid_dev,
                                             int32_t H, int32_t W, int32_t patch_size, double C_thr,
@@ -199,6 +251,41 @@ extern "C" int b200tsdf_quality_classify(const float *delta_cov_dev, const float
   B200_CUDA(cudaSetDevice(device));
   quality_classify_kernel<<<1, Q_CLS_THREADS, 0, (cudaStream_t)stream>>>(
       delta_cov_dev, r_dev, u_dev, n, (float)thr_zr, (float)thr_zu, (float)thr_dc,
+      (long long *)class_dev, priority_dev, q_grid_dev);
+  B200_CUDA(cudaGetLastError());
+  return B200TSDF_OK;
+}
+
+extern "C" int b200tsdf_quality_batch(const float *C_dev, const float *Q_dev,
+                                      const float *r_pix_dev, const uint8_t *valid_dev,
+                                      const float *view_w_dev, const float *prev_ewma_dev,
+                                      int32_t B, int32_t H, int32_t W, int32_t patch_size,
+                                      double C_thr, double Q_thr, double alpha, double thr_zr,
+                                      double thr_zu, double thr_dc, float *u_grid_dev,
+                                      float *r_grid_dev, float *valid_grid_dev, float *ewma_dev,
+                                      float *delta_cov_dev, int64_t *class_dev,
+                                      float *priority_dev, float *q_grid_dev, int32_t device,
+                                      void *stream) {
+  if (!C_dev || !Q_dev || !r_pix_dev || !valid_dev || !view_w_dev || !u_grid_dev || !r_grid_dev ||
+      !valid_grid_dev || !ewma_dev || !delta_cov_dev || !class_dev || !priority_dev || B < 0 ||
+      B > 65535 || H <= 0 || W <= 0 || patch_size <= 0 || patch_size * patch_size > Q_MAX_PATCH) {
+    b200_set_error("b200tsdf_quality_batch: invalid argument (patch_size <= 32, B <= 65535)");
+    return B200TSDF_E_INVALID;
+  }
+  const int n = (H / patch_size) * (W / patch_size);
+  if (n > Q_MAX_N) {
+    b200_set_error("b200tsdf_quality_batch: %d patches per keyframe (max %d)", n, Q_MAX_N);
+    return B200TSDF_E_INVALID;
+  }
+  if (n == 0 || B == 0) return B200TSDF_OK;
+  B200_CUDA(cudaSetDevice(device));
+  cudaStream_t st = (cudaStream_t)stream;
+  quality_patch_kernel<<<dim3((n + Q_WARPS - 1) / Q_WARPS, B), 32 * Q_WARPS, 0, st>>>(
+      C_dev, Q_dev, r_pix_dev, valid_dev, H, W, patch_size, (float)(C_thr + 1e-8),
+      (float)(Q_thr + 1e-8), u_grid_dev, r_grid_dev, valid_grid_dev);
+  quality_finish_batch_kernel<<<B, Q_CLS_THREADS, 0, st>>>(
+      valid_grid_dev, view_w_dev, prev_ewma_dev, r_grid_dev, u_grid_dev, n, (float)alpha,
+      (float)(1.0 - alpha), (float)thr_zr, (float)thr_zu, (float)thr_dc, ewma_dev, delta_cov_dev,
       (long long *)class_dev, priority_dev, q_grid_dev);
   B200_CUDA(cudaGetLastError());
   return B200TSDF_OK;

@@ -85,8 +85,10 @@ def pack_result(kfid, dc, r, u, cls, pri, ewma, q=None, to_host=False):  # :111-
     return out
 
 
-def compute_batch(batch, ps, alpha, b0, theta0, C_thr, Q_thr, thr_zr, thr_zu, thr_dc, device,
-                  to_host=False):  # :127-140
+def _compute_batch_per_job(batch, ps, alpha, b0, theta0, C_thr, Q_thr, thr_zr, thr_zu, thr_dc,
+                           device, to_host=False):
+    """compute_batch one keyframe at a time (two launches + ~15 tensor ops per
+    keyframe): the statement the batched path is checked against."""
     outs = []
     for jb in batch:
         h, w = jb["H"], jb["W"]
@@ -99,6 +101,68 @@ def compute_batch(batch, ps, alpha, b0, theta0, C_thr, Q_thr, thr_zr, thr_zu, th
         ew, dc = ema_delta(prev, inc, alpha)
         cls, pri, q = classify(dc, r, u, thr_zr, thr_zu, thr_dc, return_q=True)
         outs.append(pack_result(jb["kf_id"], dc, r, u, cls, pri, ew, q, to_host))
+    return outs
+
+
+def _stack(batch, key, device, dtype, n):
+    """(B, n) device tensor from the jobs' `key`: one stack (on the device the
+    tensors live on), then ONE device / dtype conversion for the whole batch."""
+    ts = [torch.as_tensor(jb[key]).reshape(-1)[:n] for jb in batch]
+    if len({t.device for t in ts}) > 1:
+        ts = [t.to(device) for t in ts]
+    return torch.stack(ts).to(device=device, dtype=dtype).contiguous()
+
+
+def compute_stacked(Ck, Qk, r_pix, valid, t_norm, theta, prev_ewma, h, w, ps, alpha, b0, theta0,
+                    C_thr, Q_thr, thr_zr, thr_zu, thr_dc, device):
+    """compute_batch (:127-140) on already stacked device tensors -- maps
+    (B, h*w) float32 (valid uint8), t_norm / theta (B,), prev_ewma (B, gh*gw) or
+    None -- in TWO launches (`b200tsdf_quality_batch`).  Returns the dict of
+    (B, gh, gw) device grids: delta_cov, r, u, class_id, priority, cov_ewma, q_grid."""
+    B, gh, gw = Ck.shape[0], h // ps, w // ps
+    vw = view_weight(t_norm, theta, b0, theta0, device).to(torch.float32).expand(B).contiguous()
+    f32 = dict(dtype=torch.float32, device=device)
+    u, r, vg, ew, dc, pri, q = (torch.empty(B, gh, gw, **f32) for _ in range(7))
+    cls = torch.empty(B, gh, gw, dtype=torch.int64, device=device)
+    _ffi.check(_ffi.lib().b200tsdf_quality_batch(
+        Ck.data_ptr(), Qk.data_ptr(), r_pix.data_ptr(), valid.data_ptr(), vw.data_ptr(),
+        prev_ewma.data_ptr() if prev_ewma is not None else None, B, h, w, ps, float(C_thr),
+        float(Q_thr), float(alpha), float(thr_zr), float(thr_zu), float(thr_dc), u.data_ptr(),
+        r.data_ptr(), vg.data_ptr(), ew.data_ptr(), dc.data_ptr(), cls.data_ptr(), pri.data_ptr(),
+        q.data_ptr(), _dev_index(device), _stream(device)), "quality_batch")
+    return {"delta_cov": dc, "r": r, "u": u, "class_id": cls, "priority": pri, "cov_ewma": ew,
+            "q_grid": q}
+
+
+def compute_batch(batch, ps, alpha, b0, theta0, C_thr, Q_thr, thr_zr, thr_zu, thr_dc, device,
+                  to_host=False):  # :127-140
+    """All keyframes of one size go through TWO launches (`compute_stacked`:
+    per-patch medians of every keyframe, then one CTA per keyframe for the
+    coverage EMA and classify); the reference loops over the jobs.  Results are
+    per job, in order, views into the (B, gh, gw) device grids."""
+    outs = [None] * len(batch)
+    groups = {}
+    for i, jb in enumerate(batch):
+        groups.setdefault((int(jb["H"]), int(jb["W"])), []).append(i)
+    for (h, w), idx in groups.items():
+        jobs = [batch[i] for i in idx]
+        B, n, npx = len(jobs), (h // ps) * (w // ps), h * w
+        prev = None
+        if any(jb.get("cov_ewma", None) is not None for jb in jobs):
+            zero = torch.zeros(n, dtype=torch.float32)
+            prev = _stack([{"p": zero if jb.get("cov_ewma", None) is None else jb["cov_ewma"]}
+                           for jb in jobs], "p", device, torch.float32, n)
+        g = compute_stacked(_stack(jobs, "Ck", device, torch.float32, npx),
+                            _stack(jobs, "Qk", device, torch.float32, npx),
+                            _stack(jobs, "r_pix", device, torch.float32, npx),
+                            _stack(jobs, "valid_kf", device, torch.uint8, npx),
+                            _stack(jobs, "t_norm", device, torch.float32, 1).reshape(B),
+                            _stack(jobs, "theta", device, torch.float32, 1).reshape(B), prev, h, w,
+                            ps, alpha, b0, theta0, C_thr, Q_thr, thr_zr, thr_zu, thr_dc, device)
+        for k, i in enumerate(idx):
+            outs[i] = pack_result(batch[i]["kf_id"], g["delta_cov"][k], g["r"][k], g["u"][k],
+                                  g["class_id"][k], g["priority"][k], g["cov_ewma"][k],
+                                  g["q_grid"][k], to_host)
     return outs
 
 

@@ -57,6 +57,30 @@ def test_quality_grid_feeds_the_fuse(cuda_device):
     assert all(np.array_equal(a, b) for a, b in zip(*vols))
 
 
+def test_quality_batch_equals_per_keyframe(cuda_device):
+    """compute_batch runs every keyframe of one size through two launches
+    (b200tsdf_quality_batch); each job's grids are bit-identical to the
+    one-keyframe-at-a-time statement, for mixed sizes, holes and with / without
+    a previous coverage EMA in the same batch."""
+    from mast3r_slam_quality_dualtsdf_b200 import quality_core as qc
+
+    specs = [(3, 96, 128, True, False), (4, 96, 128, False, True), (5, 64, 64, True, True),
+             (6, 96, 128, False, False), (7, 64, 64, False, False), (8, 96, 128, True, True)]
+    jobs = []
+    for k, (seed, H, W, with_prev, holes) in enumerate(specs):
+        jb = dict(mg.make_job(seed, H, W, with_prev, holes))
+        jb["kf_id"] = k
+        jobs.append(jb)
+    got = qc.compute_batch([dict(j) for j in jobs], device=cuda_device, **mg.PARAMS)
+    want = qc._compute_batch_per_job([dict(j) for j in jobs], device=cuda_device, **mg.PARAMS)
+    assert [g["kf_id"] for g in got] == list(range(len(specs)))
+    for g, w in zip(got, want):
+        for key in ("delta_cov", "cov_ewma", "r", "u", "class_id", "priority", "q_grid"):
+            a, b = g[key].cpu().numpy(), w[key].cpu().numpy()
+            assert a.shape == b.shape and np.array_equal(a, b, equal_nan=True), key
+    assert qc.compute_batch([], device=cuda_device, **mg.PARAMS) == []
+
+
 def test_quality_argument_errors(cuda_device):
     from mast3r_slam_quality_dualtsdf_b200 import _ffi
     from mast3r_slam_quality_dualtsdf_b200 import quality_core as qc
