@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define B200TSDF_ABI_VERSION 2
+#define B200TSDF_ABI_VERSION 3
 
 enum {
   B200TSDF_OK = 0,
@@ -259,6 +259,31 @@ int b200tsdf_pose_normal_equations(b200tsdf_t *h, int which, const float *pts_ca
                                    const double *conf_dev, int64_t n, const float *pose_host,
                                    double lambda, double *H_host, double *b_host,
                                    int64_t *used_host, void *stream);
+
+/* ---- sharded query (multi-GPU) ---------------------------------
+ * TSDFVolume.query / _estimate_gradient (global_volume.py:93-128) read the
+ * voxel of the point and its six axis neighbours; with z-slab ownership those
+ * 7 voxels can live on different ranks.  query_taps writes, per point, a
+ * 64-byte record of the taps THIS handle owns (16 float32: tsdf and weight of
+ * the centre, +x, -x, +y, -y, +z, -z voxel, then the presence mask as a float
+ * and a zero; absent taps are zero; halo blocks are not reported).  Summing
+ * the records over the ranks (one float all-reduce) merges them bit-exactly,
+ * because every voxel has exactly one owner.  pose_host != NULL: the points
+ * are camera-frame float32 and are first moved by Sim3(pose)
+ * (tsdf_optimizer.py:76).  taps_dev must be 16-byte aligned.
+ * query_finish evaluates the reference arithmetic on merged records -- the
+ * same code b200tsdf_query runs, so a sharded query equals the single-volume
+ * query bit for bit.  pose_normal_equations_taps is
+ * b200tsdf_pose_normal_equations with the query replaced by merged records. */
+int b200tsdf_query_taps(b200tsdf_t *h, int which, const void *pts_dev, int dtype, int64_t m,
+                        const float *pose_host, float *taps_dev, void *stream);
+int b200tsdf_query_finish(b200tsdf_t *h, const float *taps_dev, int64_t m, double *tsdf_dev,
+                          double *grad_dev, uint8_t *flags_dev, void *stream);
+int b200tsdf_pose_normal_equations_taps(b200tsdf_t *h, const float *taps_dev,
+                                        const float *pts_cam_dev, const double *conf_dev,
+                                        int64_t n, const float *pose_host, double lambda,
+                                        double *H_host, double *b_host, int64_t *used_host,
+                                        void *stream);
 
 /* ---- quality maps on the device -----------------------
  * Replaces the per-keyframe torch/numpy round trip of

@@ -168,52 +168,109 @@ __device__ __forceinline__ bool fetch(const VolumeDev &v, int which, int kx, int
   return voxel_view(v.vox[off], v.cnt[off], which, v.max_weight, t, w, hits);
 }
 
-// Nearest-voxel tsdf and central-difference gradient of one point
-// (TSDFVolume.query, global_volume.py:93-130).  Returns flags: 1 value, 3 value + gradient.
+// The 7 voxels TSDFVolume.query reads (global_volume.py:93-128): tap 0 the
+// voxel of the point, taps 1..6 its +x, -x, +y, -y, +z, -z neighbours.
+// OWNED_ONLY: report only voxels of this handle's z-slabs (multi-GPU: a halo
+// copy of a foreign block is not reported, so every voxel has exactly one
+// reporting rank).  Neighbour taps are fetched only when some rank may need
+// them: always under OWNED_ONLY (the centre may live on another rank),
+// otherwise only when the centre holds a value (the reference's early return).
+struct QueryTaps {
+  float t[7], w[7];
+  uint32_t mask; // bit i: tap i present
+};
+
 template <typename T>
-__device__ __forceinline__ uint8_t query_point(const VolumeDev &v, int which, const T pt[3], T vs,
-                                               double voxel_size, double &tv, double g[3]) {
+__device__ __forceinline__ void query_key(const T pt[3], T vs, int k[3]) {
   using R = Real<T>;
-  int k[3];
   for (int d = 0; d < 3; ++d) { // global_volume.py:133-134
     T f = R::flr(R::div(pt[d], vs));
     f = f < (T)-2.0e9 ? (T)-2.0e9 : (f > (T)2.0e9 ? (T)2.0e9 : f);
     k[d] = (int)f;
   }
+}
+
+template <bool OWNED_ONLY>
+__device__ __forceinline__ void fetch_taps(const VolumeDev &v, int which, const int k[3],
+                                           bool finite, QueryTaps &q) {
+  q.mask = 0;
+#pragma unroll
+  for (int i = 0; i < 7; ++i) q.t[i] = 0.0f, q.w[i] = 0.0f;
+  if (!finite) return;
+  if ((!OWNED_ONLY || slab_owns_z(v, k[2])) && fetch(v, which, k[0], k[1], k[2], q.t[0], q.w[0]))
+    q.mask = 1;
+  if (!OWNED_ONLY && !(q.mask && q.w[0] >= v.min_weight)) return; // :98-100
+#pragma unroll
+  for (int i = 1; i < 7; ++i) {
+    int kk[3] = {k[0], k[1], k[2]};
+    kk[(i - 1) >> 1] += (i & 1) ? 1 : -1;
+    if (OWNED_ONLY && !slab_owns_z(v, kk[2])) continue;
+    if (fetch(v, which, kk[0], kk[1], kk[2], q.t[i], q.w[i])) q.mask |= 1u << i;
+  }
+}
+
+// Value and unit gradient from the taps (global_volume.py:98-100, :107-128).
+// Returns flags: 1 value, 3 value + gradient.
+__device__ __forceinline__ uint8_t finish_query(const QueryTaps &q, float min_weight,
+                                                double voxel_size, double &tv, double g[3]) {
   uint8_t fl = 0;
   tv = 0.0, g[0] = g[1] = g[2] = 0.0;
-  float t, w;
-  if (isfinite((double)pt[0]) && fetch(v, which, k[0], k[1], k[2], t, w) &&
-      w >= v.min_weight) { // :98-100
-    fl = 1;
-    tv = (double)t;
-    int denom = 0;
-    for (int ax = 0; ax < 3; ++ax) { // :112-123
-      int kp[3] = {k[0], k[1], k[2]}, kn[3] = {k[0], k[1], k[2]};
-      kp[ax] += 1;
-      kn[ax] -= 1;
-      float tp, wp, tn, wn;
-      if (!fetch(v, which, kp[0], kp[1], kp[2], tp, wp)) continue;
-      if (!fetch(v, which, kn[0], kn[1], kn[2], tn, wn)) continue;
-      if (wp < v.min_weight || wn < v.min_weight) continue;
-      // voxels are stored as float32 sums: differences at the rounding-noise
-      // level are the reference's exact zeros (equal tsdf on both sides)
-      double diff = (double)tp - (double)tn;
-      if (fabs(diff) <= 4.0e-7) diff = 0.0;
-      g[ax] = diff / (2.0 * voxel_size);
-      denom++;
-    }
-    if (denom) {
-      double nrm = sqrt(fma(g[2], g[2], fma(g[1], g[1], g[0] * g[0])));
-      if (nrm >= 1.0e-9) { // :126-128
-        g[0] /= nrm, g[1] /= nrm, g[2] /= nrm;
-        fl = 3;
-      } else {
-        g[0] = g[1] = g[2] = 0.0;
-      }
+  if (!((q.mask & 1u) && q.w[0] >= min_weight)) return 0; // :98-100
+  fl = 1;
+  tv = (double)q.t[0];
+  int denom = 0;
+#pragma unroll
+  for (int ax = 0; ax < 3; ++ax) { // :112-123
+    const int ip = 1 + 2 * ax, in = 2 + 2 * ax;
+    if (!((q.mask >> ip) & 1u) || !((q.mask >> in) & 1u)) continue;
+    if (q.w[ip] < min_weight || q.w[in] < min_weight) continue;
+    // voxels are stored as float32 sums: differences at the rounding-noise
+    // level are the reference's exact zeros (equal tsdf on both sides)
+    double diff = (double)q.t[ip] - (double)q.t[in];
+    if (fabs(diff) <= 4.0e-7) diff = 0.0;
+    g[ax] = diff / (2.0 * voxel_size);
+    denom++;
+  }
+  if (denom) {
+    double nrm = sqrt(fma(g[2], g[2], fma(g[1], g[1], g[0] * g[0])));
+    if (nrm >= 1.0e-9) { // :126-128
+      g[0] /= nrm, g[1] /= nrm, g[2] /= nrm;
+      fl = 3;
+    } else {
+      g[0] = g[1] = g[2] = 0.0;
     }
   }
   return fl;
+}
+
+// 64-byte record of the taps: {t0,w0,t1,w1}, {t2,w2,t3,w3}, {t4,w4,t5,w5},
+// {t6,w6,mask,0}; the mask travels as a float (<= 127, exact) so that one
+// float SUM over ranks merges records with disjoint presence bits.
+__device__ __forceinline__ void store_taps(float4 *dst, const QueryTaps &q) {
+  dst[0] = make_float4(q.t[0], q.w[0], q.t[1], q.w[1]);
+  dst[1] = make_float4(q.t[2], q.w[2], q.t[3], q.w[3]);
+  dst[2] = make_float4(q.t[4], q.w[4], q.t[5], q.w[5]);
+  dst[3] = make_float4(q.t[6], q.w[6], (float)q.mask, 0.0f);
+}
+__device__ __forceinline__ void load_taps(const float4 *src, QueryTaps &q) {
+  const float4 a = src[0], b = src[1], c = src[2], d = src[3];
+  q.t[0] = a.x, q.w[0] = a.y, q.t[1] = a.z, q.w[1] = a.w;
+  q.t[2] = b.x, q.w[2] = b.y, q.t[3] = b.z, q.w[3] = b.w;
+  q.t[4] = c.x, q.w[4] = c.y, q.t[5] = c.z, q.w[5] = c.w;
+  q.t[6] = d.x, q.w[6] = d.y;
+  q.mask = (uint32_t)d.z;
+}
+
+// Nearest-voxel tsdf and central-difference gradient of one point
+// (TSDFVolume.query, global_volume.py:93-130).  Returns flags: 1 value, 3 value + gradient.
+template <typename T>
+__device__ __forceinline__ uint8_t query_point(const VolumeDev &v, int which, const T pt[3], T vs,
+                                               double voxel_size, double &tv, double g[3]) {
+  int k[3];
+  query_key<T>(pt, vs, k);
+  QueryTaps q;
+  fetch_taps<false>(v, which, k, isfinite((double)pt[0]), q);
+  return finish_query(q, v.min_weight, voxel_size, tv, g);
 }
 
 template <typename T>
@@ -264,10 +321,12 @@ extern "C" int b200tsdf_query(b200tsdf_t *h, int which, const void *pts_dev, int
 // normal equations H = sum w J J^T, b = sum w r J with w = max(lambda C, 1e-6)
 // (:107-116), reduced in float64: warp shuffles, then one atomicAdd per warp
 // and entry.  out = [H upper triangle (28) | b (7) | used (1)].
+template <bool TAPS>
 __global__ void __launch_bounds__(128)
     pose_normal_eq_kernel(VolumeDev v, int which, const float *__restrict__ pts_cam,
                           const double *__restrict__ conf, long long n, const float *pose,
-                          float vs, double voxel_size, double lambda, double *out) {
+                          float vs, double voxel_size, double lambda, double *out,
+                          const float4 *__restrict__ taps) {
   const long long p = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   double acc[36];
 #pragma unroll
@@ -277,7 +336,14 @@ __global__ void __launch_bounds__(128)
     sim3_act(pose, pts_cam[3 * p], pts_cam[3 * p + 1], pts_cam[3 * p + 2], w0, w1, w2);
     const float pt[3] = {w0, w1, w2};
     double t, g[3];
-    const uint8_t fl = query_point<float>(v, which, pt, vs, voxel_size, t, g);
+    uint8_t fl;
+    if (TAPS) {
+      QueryTaps q;
+      load_taps(taps + 4 * p, q);
+      fl = finish_query(q, v.min_weight, voxel_size, t, g);
+    } else {
+      fl = query_point<float>(v, which, pt, vs, voxel_size, t, g);
+    }
     const double x = (double)w0, y = (double)w1, z = (double)w2;
     double J[7] = {g[0], g[1], g[2], -(y * g[2] - z * g[1]), -(z * g[0] - x * g[2]),
                    -(x * g[1] - y * g[0]), x * g[0] + y * g[1] + z * g[2]};
@@ -305,11 +371,10 @@ __global__ void __launch_bounds__(128)
   }
 }
 
-extern "C" int b200tsdf_pose_normal_equations(b200tsdf_t *h, int which, const float *pts_cam_dev,
-                                              const double *conf_dev, int64_t n,
-                                              const float *pose_host, double lambda,
-                                              double *H_host, double *b_host, int64_t *used_host,
-                                              void *stream) {
+static int pose_normal_equations_impl(b200tsdf_t *h, int which, const float *pts_cam_dev,
+                                      const double *conf_dev, int64_t n, const float *pose_host,
+                                      double lambda, double *H_host, double *b_host,
+                                      int64_t *used_host, void *stream, const float *taps_dev) {
   if (!h || n < 0 || (which != 0 && which != 1) || !pose_host || !H_host || !b_host ||
       !used_host || (n > 0 && (!pts_cam_dev || !conf_dev))) {
     b200_set_error("b200tsdf_pose_normal_equations: invalid argument");
@@ -323,9 +388,14 @@ extern "C" int b200tsdf_pose_normal_equations(b200tsdf_t *h, int which, const fl
   B200_CUDA(cudaMemsetAsync(acc, 0, 36 * sizeof(double), st));
   B200_CUDA(cudaMemcpyAsync(pose_dev, pose_host, 8 * sizeof(float), cudaMemcpyHostToDevice, st));
   if (n > 0) {
-    pose_normal_eq_kernel<<<(unsigned)((n + 127) / 128), 128, 0, st>>>(
-        h->d, which, pts_cam_dev, conf_dev, (long long)n, pose_dev, (float)h->cfg.voxel_size,
-        h->cfg.voxel_size, lambda, acc);
+    if (taps_dev)
+      pose_normal_eq_kernel<true><<<(unsigned)((n + 127) / 128), 128, 0, st>>>(
+          h->d, which, pts_cam_dev, conf_dev, (long long)n, pose_dev, (float)h->cfg.voxel_size,
+          h->cfg.voxel_size, lambda, acc, (const float4 *)taps_dev);
+    else
+      pose_normal_eq_kernel<false><<<(unsigned)((n + 127) / 128), 128, 0, st>>>(
+          h->d, which, pts_cam_dev, conf_dev, (long long)n, pose_dev, (float)h->cfg.voxel_size,
+          h->cfg.voxel_size, lambda, acc, nullptr);
     B200_CUDA(cudaGetLastError());
   }
   double r[36];
@@ -337,6 +407,122 @@ extern "C" int b200tsdf_pose_normal_equations(b200tsdf_t *h, int which, const fl
   for (int i = 0; i < 7; ++i) b_host[i] = r[28 + i];
   *used_host = (int64_t)(r[35] + 0.5);
   return B200TSDF_OK;
+}
+
+extern "C" int b200tsdf_pose_normal_equations(b200tsdf_t *h, int which, const float *pts_cam_dev,
+                                              const double *conf_dev, int64_t n,
+                                              const float *pose_host, double lambda,
+                                              double *H_host, double *b_host, int64_t *used_host,
+                                              void *stream) {
+  return pose_normal_equations_impl(h, which, pts_cam_dev, conf_dev, n, pose_host, lambda, H_host,
+                                    b_host, used_host, stream, nullptr);
+}
+
+// ------------------------------------- sharded query (multi-GPU)
+// A query point's 7 voxels may live on up to two ranks (z neighbours across a
+// slab seam; the centre itself on any rank).  Step 1, every rank:
+// query_taps_kernel writes the taps IT OWNS (64 bytes per point, absent = 0);
+// the caller sums the records over the ranks (ownership is disjoint, so the
+// sum is a bit-exact merge); step 2: query_finish / the TAPS variant of the
+// pose kernel evaluate the reference arithmetic on the merged taps -- the
+// same finish_query the single-volume query runs.
+template <typename T, bool ACT>
+__global__ void query_taps_kernel(VolumeDev v, int which, const T *__restrict__ pts, long long m,
+                                  T vs, const float *pose, float4 *__restrict__ taps) {
+  long long p = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= m) return;
+  T pt[3] = {pts[3 * p], pts[3 * p + 1], pts[3 * p + 2]};
+  if (ACT) { // camera-frame float32 points: Sim3 act first (tsdf_optimizer.py:76)
+    float w0, w1, w2;
+    sim3_act(pose, (float)pt[0], (float)pt[1], (float)pt[2], w0, w1, w2);
+    pt[0] = (T)w0, pt[1] = (T)w1, pt[2] = (T)w2;
+  }
+  int k[3];
+  query_key<T>(pt, vs, k);
+  QueryTaps q;
+  fetch_taps<true>(v, which, k, isfinite((double)pt[0]), q);
+  store_taps(taps + 4 * p, q);
+}
+
+__global__ void query_finish_kernel(float min_weight, double voxel_size,
+                                    const float4 *__restrict__ taps, long long m, double *tsdf,
+                                    double *grad, uint8_t *flags) {
+  long long p = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= m) return;
+  QueryTaps q;
+  load_taps(taps + 4 * p, q);
+  double tv, g[3];
+  const uint8_t fl = finish_query(q, min_weight, voxel_size, tv, g);
+  tsdf[p] = tv;
+  grad[3 * p] = g[0], grad[3 * p + 1] = g[1], grad[3 * p + 2] = g[2];
+  flags[p] = fl;
+}
+
+extern "C" int b200tsdf_query_taps(b200tsdf_t *h, int which, const void *pts_dev, int dtype,
+                                   int64_t m, const float *pose_host, float *taps_dev,
+                                   void *stream) {
+  if (!h || m < 0 || (which != 0 && which != 1) || (m > 0 && (!pts_dev || !taps_dev)) ||
+      (dtype != B200TSDF_F32 && dtype != B200TSDF_F64) || (pose_host && dtype != B200TSDF_F32) ||
+      ((uintptr_t)taps_dev & 15)) {
+    b200_set_error("b200tsdf_query_taps: invalid argument");
+    return B200TSDF_E_INVALID;
+  }
+  if (m == 0) return B200TSDF_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  B200_CUDA(cudaSetDevice(h->cfg.device));
+  const unsigned grid = (unsigned)((m + 127) / 128);
+  float4 *taps = (float4 *)taps_dev;
+  if (pose_host) {
+    float *pose_dev = reinterpret_cast<float *>(h->scratch + 60);
+    B200_CUDA(cudaMemcpyAsync(pose_dev, pose_host, 8 * sizeof(float), cudaMemcpyHostToDevice, st));
+    query_taps_kernel<float, true><<<grid, 128, 0, st>>>(h->d, which, (const float *)pts_dev,
+                                                        (long long)m, (float)h->cfg.voxel_size,
+                                                        pose_dev, taps);
+  } else if (dtype == B200TSDF_F32) {
+    query_taps_kernel<float, false><<<grid, 128, 0, st>>>(h->d, which, (const float *)pts_dev,
+                                                         (long long)m, (float)h->cfg.voxel_size,
+                                                         nullptr, taps);
+  } else {
+    query_taps_kernel<double, false><<<grid, 128, 0, st>>>(h->d, which, (const double *)pts_dev,
+                                                          (long long)m, h->cfg.voxel_size, nullptr,
+                                                          taps);
+  }
+  B200_CUDA(cudaGetLastError());
+  return B200TSDF_OK;
+}
+
+extern "C" int b200tsdf_query_finish(b200tsdf_t *h, const float *taps_dev, int64_t m,
+                                     double *tsdf_dev, double *grad_dev, uint8_t *flags_dev,
+                                     void *stream) {
+  if (!h || m < 0 || (m > 0 && (!taps_dev || !tsdf_dev || !grad_dev || !flags_dev)) ||
+      ((uintptr_t)taps_dev & 15)) {
+    b200_set_error("b200tsdf_query_finish: invalid argument");
+    return B200TSDF_E_INVALID;
+  }
+  if (m == 0) return B200TSDF_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  B200_CUDA(cudaSetDevice(h->cfg.device));
+  query_finish_kernel<<<(unsigned)((m + 127) / 128), 128, 0, st>>>(
+      h->d.min_weight, h->cfg.voxel_size, (const float4 *)taps_dev, (long long)m, tsdf_dev,
+      grad_dev, flags_dev);
+  B200_CUDA(cudaGetLastError());
+  return B200TSDF_OK;
+}
+
+extern "C" int b200tsdf_pose_normal_equations_taps(b200tsdf_t *h, const float *taps_dev,
+                                                   const float *pts_cam_dev,
+                                                   const double *conf_dev, int64_t n,
+                                                   const float *pose_host, double lambda,
+                                                   double *H_host, double *b_host,
+                                                   int64_t *used_host, void *stream) {
+  if ((n > 0 && !taps_dev) || ((uintptr_t)taps_dev & 15)) {
+    b200_set_error("b200tsdf_pose_normal_equations_taps: invalid argument");
+    return B200TSDF_E_INVALID;
+  }
+  static const float4 none = {0, 0, 0, 0}; // n == 0: the kernel is not launched
+  return pose_normal_equations_impl(h, 0, pts_cam_dev, conf_dev, n, pose_host, lambda, H_host,
+                                    b_host, used_host, stream,
+                                    taps_dev ? taps_dev : (const float *)&none);
 }
 
 // ------------------------------------------------------- multi-GPU seams

@@ -16,6 +16,11 @@ No reference counterpart: the reference is single-process Python.  Layout:
     the first block layer of each of its slabs to the rank below, which
     installs it as read-only halo blocks; the lower rank emits the seam cubes,
     so no triangle is duplicated or missing;
+  * queries (TSDFVolume.query, the pose optimiser's normal equations) read a
+    voxel and its six axis neighbours, which a seam can split between ranks:
+    every rank writes the taps it owns (`query_taps`), ONE float all-reduce
+    merges them (ownership is disjoint, so the sum is exact), and the reference
+    arithmetic runs on the merged taps -- bit-identical to the single volume;
   * counters / stats are sums over ranks (all_reduce).
 `torch.distributed` is plumbing only; the group may be NCCL (GPU) or gloo
 (host-logic tests with an injected volume factory).
@@ -115,6 +120,40 @@ class ShardedTSDFVolume:
         s = self.vol.stats(which)
         v = self._sum([s["valid_voxels"], s["total_voxels"]])
         return {"valid_voxels": v[0], "total_voxels": v[1]}
+
+    # -- queries across seams --------------------------------------------------
+    def _merged_taps(self, points, which, pose=None):
+        taps = self.vol.query_taps(points, which, pose)
+        if self.world > 1:
+            if dist.get_backend(self.group) == "nccl":
+                dist.all_reduce(taps, group=self.group)
+            else:  # host-logic tests: gloo reduces host tensors
+                host = taps.cpu()
+                dist.all_reduce(host, group=self.group)
+                taps = host.to(taps.device)
+        return taps
+
+    def query_batch(self, points, which=0):
+        """`TSDFVolume.query_batch` over all ranks: every rank passes the same
+        points and gets the same (tsdf, grad, flags)."""
+        return self.vol.query_finish(self._merged_taps(points, which))
+
+    def query(self, point_world):
+        """Reference signature (global_volume.py:93-105); collective."""
+        import numpy as np
+
+        t, g, fl = self.query_batch(np.asarray(point_world).reshape(1, 3))
+        f = int(fl.cpu()[0])
+        if not f & 1:
+            return None, None
+        return float(t.cpu()[0]), (g.cpu().numpy()[0].copy() if f & 2 else None)
+
+    def pose_normal_equations(self, pts_cam, conf, pose, lam, which=0):
+        """`TSDFVolume.pose_normal_equations` over all ranks (collective; every
+        rank passes the same samples and gets the same H, b, used), so a
+        `TSDFPoseOptimizer` can be handed a sharded volume."""
+        taps = self._merged_taps(pts_cam, which, pose)
+        return self.vol.pose_normal_equations_taps(taps, pts_cam, conf, pose, lam)
 
     # -- seams / mesh --------------------------------------------------------
     def exchange_seams(self):

@@ -212,6 +212,65 @@ class TSDFVolume:
                 "pose_normal_equations")
         return H, b, int(used.value)
 
+    # -- sharded query (multi-GPU): taps of this handle, merged by the caller --
+    def query_taps(self, points, which: int = 0, pose=None):
+        """Step 1 of a sharded query: (M, 16) float32 records of the 7 voxels
+        of every point THIS volume owns (see include/b200tsdf.h).  With `pose`
+        (8 floats) the points are camera-frame float32 and are moved by
+        Sim3(pose) first.  Sum the records over the ranks, then `query_finish`
+        or `pose_normal_equations_taps`."""
+        if isinstance(points, np.ndarray):
+            dt = np.float32 if points.dtype == np.float32 else np.float64
+            points = torch.from_numpy(np.ascontiguousarray(points, dtype=dt))
+        pts = points.reshape(-1, 3).to(self.device).contiguous()
+        if pose is not None:
+            pts = pts.to(torch.float32)
+        elif pts.dtype not in (torch.float32, torch.float64):
+            pts = pts.double()
+        m = pts.shape[0]
+        taps = torch.zeros(m, 16, dtype=torch.float32, device=self.device)
+        ps = None if pose is None else np.ascontiguousarray(np.asarray(pose, np.float32).reshape(8))
+        with self._lock:
+            _ffi.check(_ffi.lib().b200tsdf_query_taps(
+                self._h, which, pts.data_ptr(),
+                _ffi.F32 if pts.dtype == torch.float32 else _ffi.F64, m,
+                None if ps is None else ps.ctypes.data_as(C.c_void_p), taps.data_ptr(),
+                _stream_ptr(self.device)), "query_taps")
+            if ps is not None:  # the pose copy reads host memory asynchronously
+                torch.cuda.current_stream(self.device).synchronize()
+        return taps
+
+    def query_finish(self, taps):
+        """Step 2: (tsdf, grad, flags) like `query_batch` from merged records."""
+        taps = taps.to(self.device, torch.float32).reshape(-1, 16).contiguous()
+        m = taps.shape[0]
+        t = torch.zeros(m, dtype=torch.float64, device=self.device)
+        g = torch.zeros(m, 3, dtype=torch.float64, device=self.device)
+        fl = torch.zeros(m, dtype=torch.uint8, device=self.device)
+        with self._lock:
+            _ffi.check(_ffi.lib().b200tsdf_query_finish(
+                self._h, taps.data_ptr(), m, t.data_ptr(), g.data_ptr(), fl.data_ptr(),
+                _stream_ptr(self.device)), "query_finish")
+        return t, g, fl
+
+    def pose_normal_equations_taps(self, taps, pts_cam, conf, pose, lam):
+        """`pose_normal_equations` with the query replaced by merged records
+        (taps = sum over ranks of `query_taps(pts_cam, which, pose)`)."""
+        taps = taps.to(self.device, torch.float32).reshape(-1, 16).contiguous()
+        pts = pts_cam.to(self.device, torch.float32).reshape(-1, 3).contiguous()
+        cf = conf.to(self.device, torch.float64).reshape(-1).contiguous()
+        ps = np.ascontiguousarray(np.asarray(pose, np.float32).reshape(8))
+        H = np.zeros((7, 7), np.float64)
+        b = np.zeros(7, np.float64)
+        used = C.c_int64()
+        with self._lock:
+            _ffi.check(_ffi.lib().b200tsdf_pose_normal_equations_taps(
+                self._h, taps.data_ptr(), pts.data_ptr(), cf.data_ptr(), pts.shape[0],
+                ps.ctypes.data_as(C.c_void_p), float(lam), H.ctypes.data_as(C.c_void_p),
+                b.ctypes.data_as(C.c_void_p), C.byref(used), _stream_ptr(self.device)),
+                "pose_normal_equations_taps")
+        return H, b, int(used.value)
+
     def stats(self, which: int = 0) -> Dict[str, float]:
         """Reference signature (global_volume.py:136-140)."""
         a, b = C.c_int64(), C.c_int64()

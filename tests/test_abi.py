@@ -24,7 +24,7 @@ def test_library_exports_every_declared_symbol(built_lib):
     for name in _declared():
         assert hasattr(L, name), f"{name} missing from libb200tsdf.so"
     L.b200tsdf_abi_version.restype = ctypes.c_int
-    assert L.b200tsdf_abi_version() == 2
+    assert L.b200tsdf_abi_version() == 3
 
 
 def test_config_struct_layout():

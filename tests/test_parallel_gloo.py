@@ -58,6 +58,22 @@ class FakeVolume:
     def extract_mesh(self, which=0):
         return torch.full((3 * (self.rank + 1), 3), float(self.rank))
 
+    # sharded query stand-ins: point i is "owned" by rank i % world
+    def query_taps(self, points, which=0, pose=None):
+        pts = torch.as_tensor(points, dtype=torch.float32).reshape(-1, 3)
+        taps = torch.zeros(pts.shape[0], 16)
+        mine = torch.arange(pts.shape[0]) % self.world == self.rank
+        taps[mine, 0] = pts[mine, 2] + (0.0 if pose is None else float(pose[0]))
+        taps[mine, 14] = 1.0
+        return taps
+
+    def query_finish(self, taps):
+        return taps[:, 0].double(), torch.zeros(taps.shape[0], 3, dtype=torch.float64), \
+            taps[:, 14].to(torch.uint8)
+
+    def pose_normal_equations_taps(self, taps, pts_cam, conf, pose, lam):
+        return np.eye(7) * float(taps[:, 0].sum()), np.zeros(7), int(taps[:, 14].sum())
+
 
 def _free_port():
     s = socket.socket()
@@ -93,6 +109,13 @@ def _worker(rank, world, port, out):
                                              P[rank:rank + 1].clone())
         assert torch.equal(gx, want) and gq is None and torch.equal(gp, P)
         assert gc[:, 0].tolist() == [1.0, 2.0]
+        # sharded query: every rank ends up with every point's merged record
+        t, _, fl = sv.query_batch(want[0])
+        assert fl.tolist() == [1] * 48 and torch.equal(t.float(), want[0][:, 2])
+        tv, gv = sv.query(want[0][5].numpy())
+        assert tv == float(want[0][5, 2]) and gv is None
+        Hq, _, used = sv.pose_normal_equations(want[0], torch.ones(48), [2.0] + [0.0] * 7, 0.5)
+        assert used == 48 and abs(Hq[0, 0] - float(want[0][:, 2].sum() + 96.0)) < 1e-3
         st = sv.stats()
         n_halo = sv.exchange_seams()
         # what I received is exactly what the rank above exported
