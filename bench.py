@@ -473,7 +473,9 @@ def run_b200(args):
                      "launch_ms": launch_ms},
         "clocks": clocks,
         "extract": extract, "sweep": sweep, "quality": quality,
-        "volume": {"blocks": ctr["blocks"], "dropped_updates": ctr["dropped"]},
+        "volume": {"blocks": ctr["blocks"], "dropped_updates": ctr["dropped"],
+                   "dropped_means": "samples outside the bounds or, at N > 1, marched by a rank "
+                                    "that does not own their voxel (the owner applies them)"},
         "host_cores": os.cpu_count(),
     }
     if world == 1 and not args.no_cpu_baseline:
