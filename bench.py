@@ -45,6 +45,11 @@ def parse():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--kf-per-step", type=int, default=KF_PER_STEP)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--e2e-chunks", type=int, default=-1,
+                    help="N > 1: pieces the per-rank share is cut into for the pipelined "
+                         "PCIe -> all-gather -> fuse ingest (0: serial copy, gather, fuse; "
+                         "-1: 2 pieces when a rank ingests >= 16 keyframes per step, else serial "
+                         "-- small shares are launch-latency-bound, profiles/r01j_e2e_chunks.txt)")
     return ap.parse_args()
 
 
@@ -323,6 +328,14 @@ def run_b200(args):
     value = updates / (total_ms * 1e-3)
 
     # ---- e2e: host buffers -> (H2D, all-gather) -> fuse -> counters back
+    sharded = None
+    if args.e2e_chunks < 0:
+        args.e2e_chunks = 2 if share >= 16 else 0
+    if world > 1:
+        from mast3r_slam_quality_dualtsdf_b200 import parallel
+
+        sharded = parallel.ShardedTSDFVolume(VOXEL, TRUNC, slab_width=slabs[2], bounds=bounds,
+                                             device=dev, volume_factory=lambda **kw: vol)
     stage = {k: torch.empty(shapes[k], dtype=torch.float32, device=dev) for k in names}
     stage_local = {k: torch.empty(local_shapes[k], dtype=torch.float32, device=dev) for k in names}
     d2h = [0]
@@ -331,10 +344,15 @@ def run_b200(args):
         if world == 1:
             fuse(vol, host[s])  # *_host entry: H2D inside the C ABI call
         else:
-            for k in names:
-                stage_local[k].copy_(host[s][k], non_blocking=True)
-            gather(stage, stage_local)
-            fuse(vol, stage)
+            if args.e2e_chunks > 0:  # pipelined PCIe -> NVLink all-gather -> fuse
+                h = host[s]
+                sharded.integrate_keyframes_from_host(h["X"], h["C"], h["pose"], h["q"], MIN_CONF,
+                                                      H, W, chunks=args.e2e_chunks)
+            else:
+                for k in names:
+                    stage_local[k].copy_(host[s][k], non_blocking=True)
+                gather(stage, stage_local)
+                fuse(vol, stage)
         vol.counters()  # the step's result (8 x int64) read back, synchronises
         d2h[0] = 64
 

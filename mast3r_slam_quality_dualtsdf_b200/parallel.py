@@ -99,6 +99,66 @@ class ShardedTSDFVolume:
             self.broadcast_keyframes(X, Cf, poses, q_grid, src)
         self.vol.integrate_keyframes(X, Cf, poses, q_grid, min_conf, H, W, step_scale)
 
+    def integrate_keyframes_from_host(self, X, Cf, poses, q_grid=None, min_conf=0.05, H=None,
+                                      W=None, step_scale=0.5, chunks=None):
+        """Sharded ingest from HOST memory, pipelined: every rank passes ITS
+        share of the batch (the same number of keyframes on every rank, pinned
+        host tensors).  The share is cut into `chunks` pieces; piece c+1 crosses
+        PCIe (copy stream) while piece c is all-gathered over NVLink (NCCL
+        stream) and piece c-1 is fused (current stream).  One fuse launch per
+        piece over the R x piece keyframes of all ranks; the fold is
+        commutative, so the piece order does not matter.  chunks=None: 2 pieces
+        for shares of >= 16 keyframes, else 1 (small shares are launch-latency-
+        bound: at 5 keyframes per rank 2 pieces cost 1.59 vs 1.42 ms per step,
+        at 20 they gain 2.08 -> 2.02 ms; profiles/r01j_e2e_chunks.txt)."""
+        parts = [X, Cf, poses] + ([q_grid] if q_grid is not None else [])
+        n = int(X.shape[0])
+        nccl = self.world > 1 and dist.get_backend(self.group) == "nccl"
+        if not nccl:  # single rank / host-logic tests: no streams to overlap
+            dev_parts = [t.to(self.device) for t in parts]
+            full = self.gather_keyframes(*dev_parts[:3],
+                                         dev_parts[3] if q_grid is not None else None)
+            self.vol.integrate_keyframes(full[0], full[1], full[2], full[3], min_conf, H, W,
+                                         step_scale)
+            return
+        if chunks is None:
+            chunks = 2 if n >= 16 else 1
+        chunks = max(1, min(int(chunks), n))
+        cuts = [(n * c) // chunks for c in range(chunks + 1)]
+        key = (tuple(tuple(t.shape) for t in parts), chunks)
+        if getattr(self, "_ingest_key", None) != key:
+            self._ingest_key = key
+            self._copy_stream = torch.cuda.Stream(self.device)
+            self._ingest_bufs = []
+            for c in range(chunks):
+                m = cuts[c + 1] - cuts[c]
+                loc = [torch.empty((m,) + tuple(t.shape[1:]), dtype=t.dtype, device=self.device)
+                       for t in parts]
+                full = [torch.empty((m * self.world,) + tuple(t.shape[1:]), dtype=t.dtype,
+                                    device=self.device) for t in parts]
+                self._ingest_bufs.append((loc, full, torch.cuda.Event()))
+        main = torch.cuda.current_stream(self.device)
+        self._copy_stream.wait_stream(main)  # the previous batch's fuse still reads the buffers
+        with torch.cuda.stream(self._copy_stream):
+            for c in range(chunks):
+                loc, _, ev = self._ingest_bufs[c]
+                for dst, src in zip(loc, parts):
+                    dst.copy_(src[cuts[c]:cuts[c + 1]], non_blocking=True)
+                ev.record(self._copy_stream)
+        works = []
+        for c in range(chunks):
+            loc, full, ev = self._ingest_bufs[c]
+            main.wait_event(ev)
+            works.append([dist.all_gather_into_tensor(f, l, group=self.group, async_op=True)
+                          for f, l in zip(full, loc)])
+        for c in range(chunks):
+            for w in works[c]:
+                w.wait()  # stream-level wait: the fuse below is ordered after the gather
+            full = self._ingest_bufs[c][1]
+            self.vol.integrate_keyframes(full[0], full[1], full[2],
+                                         full[3] if q_grid is not None else None, min_conf, H, W,
+                                         step_scale)
+
     # -- reductions --------------------------------------------------------
     def _sum(self, values):
         t = torch.tensor(values, dtype=torch.int64,

@@ -109,6 +109,11 @@ def _worker(rank, world, port, out):
                                              P[rank:rank + 1].clone())
         assert torch.equal(gx, want) and gq is None and torch.equal(gp, P)
         assert gc[:, 0].tolist() == [1.0, 2.0]
+        # the same ingest from host shares in one call (pipelined on NCCL, serial here)
+        before = sv.counters()["rays"]
+        sv.integrate_keyframes_from_host(want[rank:rank + 1].clone(), Cf[:1].clone(),
+                                         P[rank:rank + 1].clone(), None, 0.05, 6, 8)
+        assert sv.counters()["rays"] == before + 96
         # sharded query: every rank ends up with every point's merged record
         t, _, fl = sv.query_batch(want[0])
         assert fl.tolist() == [1] * 48 and torch.equal(t.float(), want[0][:, 2])
