@@ -21,6 +21,9 @@ No reference counterpart: the reference is single-process Python.  Layout:
     every rank writes the taps it owns (`query_taps`), ONE float all-reduce
     merges them (ownership is disjoint, so the sum is exact), and the reference
     arithmetic runs on the merged taps -- bit-identical to the single volume;
+  * re-integration after a backend solve (`reintegrate`): the keyframes are
+    replicated in every rank's store at first ingest, so a pose update moves
+    32 bytes per keyframe (one broadcast of the new poses);
   * counters / stats are sums over ranks (all_reduce).
 `torch.distributed` is plumbing only; the group may be NCCL (GPU) or gloo
 (host-logic tests with an injected volume factory).
@@ -57,6 +60,7 @@ class ShardedTSDFVolume:
                 return TSDFVolume(voxel_size, truncation, max_weight, min_weight, **kw)
         self.vol = volume_factory(capacity_log2=capacity_log2, bounds=bounds, device=device,
                                   slabs=(self.world, self.rank, self.slab_width))
+        self._store = {}  # keyframe id -> tensors of the keyframe, replicated on every rank
 
     # -- keyframes ---------------------------------------------------------
     def broadcast_keyframes(self, X, Cf, poses, q_grid=None, src=0):
@@ -94,10 +98,72 @@ class ShardedTSDFVolume:
         return tuple(res)
 
     def integrate_keyframes(self, X, Cf, poses, q_grid=None, min_conf=0.05, H=None, W=None,
-                            step_scale=0.5, src=0, broadcast=True):
+                            step_scale=0.5, src=0, broadcast=True, ids=None):
+        """Fuse one batch on every rank.  With `ids` (one int per keyframe, the
+        same list on every rank) the batch is also kept in this rank's
+        keyframe store, so that `reintegrate` later needs the new poses only."""
         if broadcast:
             self.broadcast_keyframes(X, Cf, poses, q_grid, src)
         self.vol.integrate_keyframes(X, Cf, poses, q_grid, min_conf, H, W, step_scale)
+        if ids is not None:
+            ids = [int(i) for i in ids]
+            if len(ids) != int(X.shape[0]):
+                raise ValueError("ids must name every keyframe of the batch")
+            for b, i in enumerate(ids):
+                self._store[i] = {
+                    "X": X[b].clone(), "C": Cf[b].clone(), "pose": poses[b].reshape(8).clone(),
+                    "q": None if q_grid is None else q_grid[b].clone(),
+                    "args": (float(min_conf), int(H), int(W), float(step_scale))}
+
+    # -- re-integration after a backend solve (SURVEY 8(e), config 5) ------------
+    def stored_ids(self):
+        return sorted(self._store)
+
+    def reintegrate(self, ids, poses, src=0, mode="additive", batch=40):
+        """`TSDFGlobalManager.on_after_backend_solve` -> `_process_dirty_queue`
+        (global_manager.py:214-229, :71-79) over ranks: the keyframes `ids`
+        (same list on every rank) are fused again at their new poses.  Only
+        `poses` (len(ids) x 8 float32, 32 bytes per keyframe) travels -- it is
+        broadcast from `src`; pointmaps, confidences and quality grids come
+        from the store every rank filled at first ingest.
+        mode "additive": the reference's semantics (the keyframe is fused on
+        top of its earlier contribution); "replace": the contribution at the
+        stored pose is de-integrated first (exact inverse), so no ghost stays.
+        Returns the number of keyframes fused."""
+        if mode not in ("additive", "replace"):
+            raise ValueError("mode must be 'additive' or 'replace'")
+        ids = [int(i) for i in ids]
+        missing = [i for i in ids if i not in self._store]
+        if missing:
+            raise KeyError(f"keyframes {missing} are not in the store (pass ids= at ingest)")
+        if not ids:
+            return 0
+        first = self._store[ids[0]]
+        poses = poses.reshape(len(ids), 8).to(first["pose"].device, torch.float32).contiguous()
+        if self.world > 1:
+            dist.broadcast(poses, src, group=self.group)
+        # group by ingest arguments / shapes, keep the caller's order inside a group
+        groups = {}
+        for n, i in enumerate(ids):
+            e = self._store[i]
+            key = (e["args"], tuple(e["X"].shape), None if e["q"] is None else tuple(e["q"].shape))
+            groups.setdefault(key, []).append((n, i))
+        for (args, _, qshape), members in groups.items():
+            min_conf, H, W, step_scale = args
+            for a in range(0, len(members), batch):
+                part = members[a:a + batch]
+                es = [self._store[i] for _, i in part]
+                X = torch.stack([e["X"] for e in es])
+                Cf = torch.stack([e["C"] for e in es])
+                Q = None if qshape is None else torch.stack([e["q"] for e in es])
+                if mode == "replace":
+                    old = torch.stack([e["pose"] for e in es])
+                    self.vol.deintegrate_keyframes(X, Cf, old, Q, min_conf, H, W, step_scale)
+                new = poses[[n for n, _ in part]].contiguous()
+                self.vol.integrate_keyframes(X, Cf, new, Q, min_conf, H, W, step_scale)
+                for (n, _), e in zip(part, es):
+                    e["pose"] = poses[n].clone()
+        return len(ids)
 
     def integrate_keyframes_from_host(self, X, Cf, poses, q_grid=None, min_conf=0.05, H=None,
                                       W=None, step_scale=0.5, chunks=None):

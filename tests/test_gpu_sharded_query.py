@@ -136,3 +136,43 @@ def test_sharded_pose_normal_equations(cuda_device):
     t, gr, fl = full.query_batch(pw)
     ts, gs, fs = ranks[0].query_finish(merged)
     assert torch.equal(fs, fl) and torch.equal(ts, t) and torch.equal(gs, gr)
+
+
+@pytest.mark.parametrize("mode", ["replace", "additive"])
+def test_store_and_pose_only_reintegration(cuda_device, mode):
+    """SURVEY 8(e) config 5 on one rank (the NCCL run is
+    scripts/sharded_reintegrate_check.py): keyframes kept in the store at ingest
+    are fused again from their new poses alone.  replace == fused once at the
+    new poses; additive == the reference's re-fusion on top
+    (global_manager.py:71-79)."""
+    from mast3r_slam_quality_dualtsdf_b200 import parallel
+    from mast3r_slam_quality_dualtsdf_b200.tsdf import TSDFVolume
+
+    kf = synth.make_keyframes(synth.SCENES["sphere"], 3, H=H, W=W, seed=8, f=50.0, total=9)
+    t = {k: torch.from_numpy(kf[k]).to(cuda_device) for k in ("X", "C", "pose", "q")}
+    new_pose = t["pose"].clone()
+    new_pose[:, :3] += torch.tensor([0.03, -0.02, 0.025], device=cuda_device)
+    sv = parallel.ShardedTSDFVolume(VOXEL, TRUNC, slab_width=8, device=cuda_device)
+    sv.integrate_keyframes(t["X"], t["C"], t["pose"], t["q"], 0.05, H, W, ids=[4, 7, 9])
+    assert sv.stored_ids() == [4, 7, 9]
+    assert sv.reintegrate([9, 4], new_pose[[2, 0]].contiguous(), mode=mode) == 2
+    want = TSDFVolume(VOXEL, TRUNC, device=cuda_device)
+    if mode == "replace":
+        pose = t["pose"].clone()
+        pose[[2, 0]] = new_pose[[2, 0]]
+        want.integrate_keyframes(t["X"], t["C"], pose, t["q"], 0.05, H, W)
+    else:
+        want.integrate_keyframes(t["X"], t["C"], t["pose"], t["q"], 0.05, H, W)
+        want.integrate_keyframes(t["X"][[2, 0]].contiguous(), t["C"][[2, 0]].contiguous(),
+                                 new_pose[[2, 0]].contiguous(), t["q"][[2, 0]].contiguous(),
+                                 0.05, H, W)
+    for which in (0, 1):
+        gk, gt, gw, gc = sv.vol.export(which)
+        wk, wt, ww, wc = want.export(which)
+        assert np.array_equal(gk, wk) and np.array_equal(gc.astype(np.int64), wc.astype(np.int64))
+        assert np.abs(gt - wt).max() <= 5e-5  # float32 cancellation of the removed sums
+        assert (np.abs(gw - ww) / np.maximum(1.0, ww)).max() <= 5e-5
+    assert torch.equal(sv._store[9]["pose"], new_pose[2])
+    assert torch.equal(sv._store[7]["pose"], t["pose"][1])
+    with pytest.raises(KeyError):
+        sv.reintegrate([1], new_pose[:1])

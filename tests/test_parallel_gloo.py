@@ -35,6 +35,13 @@ class FakeVolume:
             key = (0, 0, z >> 3)
             self.blocks[key] = self.blocks.get(key, 0.0) + float(poses.sum())
 
+    def deintegrate_keyframes(self, X, Cf, poses, q_grid, min_conf, H, W, step_scale):
+        kz = torch.round(X[..., 2] * 100).to(torch.int64).reshape(-1)
+        own = parallel.slab_owner(kz, self.z0, self.width, self.world) == self.rank
+        self.removed = getattr(self, "removed", 0) + int(own.sum())
+        for z in kz[own].tolist():
+            self.blocks[(0, 0, z >> 3)] -= float(poses.sum())
+
     def counters(self):
         return {"rays": self.rays, "updates_primary": self.applied, "updates_quality": self.applied,
                 "blocks": len(self.blocks), "dropped": 0, "overflow": 0,
@@ -121,6 +128,33 @@ def _worker(rank, world, port, out):
         assert tv == float(want[0][5, 2]) and gv is None
         Hq, _, used = sv.pose_normal_equations(want[0], torch.ones(48), [2.0] + [0.0] * 7, 0.5)
         assert used == 48 and abs(Hq[0, 0] - float(want[0][:, 2].sum() + 96.0)) < 1e-3
+        # keyframe store + pose-only re-integration (config 5): rank 0 alone knows the new poses
+        def fake(**kw):
+            return FakeVolume(**kw)
+        sv2 = parallel.ShardedTSDFVolume(0.01, 0.04, slab_width=16, bounds=bounds, device="cpu",
+                                         volume_factory=fake)
+        X2, C2, P2 = want.clone(), torch.ones(2, 48), torch.arange(16.0).reshape(2, 8)
+        if rank != 0:
+            X2, C2, P2 = torch.zeros_like(X2), torch.zeros_like(C2), torch.zeros_like(P2)
+        sv2.integrate_keyframes(X2, C2, P2, None, 0.05, 6, 8, ids=[10, 11])
+        assert sv2.stored_ids() == [10, 11]
+        new_p = torch.arange(16.0).reshape(2, 8) * 2 + 1 if rank == 0 else torch.zeros(2, 8)
+        assert sv2.reintegrate([11, 10], new_p, src=0, mode="replace") == 2
+        want_p = torch.arange(16.0).reshape(2, 8) * 2 + 1   # rows follow ids [11, 10]
+        assert torch.equal(sv2._store[11]["pose"], want_p[0])
+        assert torch.equal(sv2._store[10]["pose"], want_p[1])
+        fresh = FakeVolume(17, bounds, "cpu", (world, rank, 16))
+        fresh.integrate_keyframes(want, C2, want_p, None, 0.05, 6, 8, 0.5)
+        assert sv2.vol.blocks.keys() == fresh.blocks.keys()
+        assert all(abs(sv2.vol.blocks[k] - fresh.blocks[k]) < 1e-3 for k in fresh.blocks)
+        assert sv2.vol.removed == sv2.vol.applied // 2   # every applied update taken out once
+        assert sv2.reintegrate([10], want_p[1:], mode="additive") == 1   # reference semantics
+        assert sv2.vol.rays == 96 * 2 + 48
+        try:
+            sv2.reintegrate([99], want_p[:1])
+            raise AssertionError("unknown keyframe id must raise")
+        except KeyError:
+            pass
         st = sv.stats()
         n_halo = sv.exchange_seams()
         # what I received is exactly what the rank above exported
