@@ -225,6 +225,30 @@ class ShardedTSDFVolume:
                                          full[3] if q_grid is not None else None, min_conf, H, W,
                                          step_scale)
 
+    def on_after_backend_solve(self, indices, poses, pin=1, src=0, mode="additive",
+                               queue_cap=256):
+        """The reference's hook with its filters (global_manager.py:214-229,
+        :46-54, :71-79), over ranks: of the solve's keyframe `indices` (same
+        list on every rank; `poses` row n belongs to indices[n] and matters on
+        `src` only) keep those >= `pin` (`local_opt.pin`), once each, at most
+        `queue_cap` (the bounded re-integration queue drops the rest), skip the
+        ones never ingested (`idx < len(keyframes)` there), and re-fuse them.
+        Returns the list of re-fused indices."""
+        keep, rows, seen = [], [], set()
+        for n, i in enumerate(int(i) for i in indices):
+            if i < pin or i in seen:
+                continue
+            if len(seen) >= queue_cap:
+                break
+            seen.add(i)
+            if i in self._store:
+                keep.append(i)
+                rows.append(n)
+        if keep:
+            poses = poses.reshape(-1, 8)
+            self.reintegrate(keep, poses[rows].contiguous(), src=src, mode=mode)
+        return keep
+
     # -- reductions --------------------------------------------------------
     def _sum(self, values):
         t = torch.tensor(values, dtype=torch.int64,

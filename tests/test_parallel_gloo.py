@@ -150,6 +150,15 @@ def _worker(rank, world, port, out):
         assert sv2.vol.removed == sv2.vol.applied // 2   # every applied update taken out once
         assert sv2.reintegrate([10], want_p[1:], mode="additive") == 1   # reference semantics
         assert sv2.vol.rays == 96 * 2 + 48
+        # the reference's hook: pin filter, dedup, unknown indices skipped
+        rays0 = sv2.vol.rays
+        hook_p = torch.zeros(5, 8) if rank else torch.arange(40.0).reshape(5, 8)
+        assert sv2.on_after_backend_solve([0, 11, 11, 42, 10], hook_p, pin=1) == [11, 10]
+        assert sv2.vol.rays == rays0 + 96
+        assert torch.equal(sv2._store[11]["pose"], torch.arange(8.0) + 8)
+        assert torch.equal(sv2._store[10]["pose"], torch.arange(8.0) + 32)
+        assert sv2.on_after_backend_solve([0], hook_p[:1], pin=1) == []
+        assert sv2.on_after_backend_solve([10, 11], hook_p[:2], pin=0, queue_cap=1) == [10]
         try:
             sv2.reintegrate([99], want_p[:1])
             raise AssertionError("unknown keyframe id must raise")
