@@ -87,3 +87,53 @@ def test_full_size_subsample_matches_oracle(cuda_device, kf):
     oq.integrate(pts[sel], confq[sel], org)
     assert_volume_matches(vol.export(0), op.export(), "40k sub-sample primary")
     assert_volume_matches(vol.export(1), oq.export(), "40k sub-sample quality")
+
+
+def _oracle_dual_threaded(kf, voxel, trunc):
+    """tests.util.oracle_dual with the two volumes on one thread each (the C
+    oracle releases the GIL): full-resolution keyframes take ~0.2 s each."""
+    import threading
+
+    vp, vq = orc.OracleVolume(voxel, trunc), orc.OracleVolume(voxel, trunc)
+    staged = [orc.stage_keyframe(kf["X"][b], kf["C"][b], kf["pose"][b], kf["q"][b], H, W, 0.05)
+              for b in range(kf["X"].shape[0])]
+    rays = [0]
+
+    def run(vol, which):
+        for pts, conf, confq, org in staged:
+            n = vol.integrate(pts, conf if which == 0 else confq, org)
+            if which == 0:
+                rays[0] += n
+
+    th = [threading.Thread(target=run, args=(vp, 0)), threading.Thread(target=run, args=(vq, 1))]
+    [t.start() for t in th]
+    [t.join() for t in th]
+    return vp, vq, rays[0]
+
+
+@pytest.mark.parametrize("name,n_kf,voxel,dim", [("config2_prefix", 16, 0.005, 512),
+                                                 ("config1", 4, 0.01, 256)])
+def test_full_resolution_keyframes_match_oracle(cuda_device, name, n_kf, voxel, dim):
+    """BASELINE config 2's 16-keyframe prefix (512x384 into 512^3 @
+    5 mm) and config 1's geometry (256^3 @ 10 mm), every pixel of every
+    keyframe, dual volume, against the sequential oracle: voxel key sets and
+    per-voxel update counts bit-exact, tsdf / weight within 1e-5, counters and
+    stats equal."""
+    from mast3r_slam_quality_dualtsdf_b200.tsdf import TSDFVolume
+
+    trunc = 4 * voxel
+    scene = synth.SCENES["room"]
+    kfs = synth.make_keyframes(scene, n_kf, H, W, seed=0, orbit_radius=0.6, gh=24, gw=32,
+                               start=100, total=600)
+    vp, vq, rays = _oracle_dual_threaded(kfs, voxel, trunc)
+    lo, hi = synth.bounds_for(scene, voxel, dim)
+    vol = TSDFVolume(voxel, trunc, capacity_log2=17, bounds=(lo, hi), device=cuda_device)
+    t = {k: torch.from_numpy(kfs[k]).to(cuda_device) for k in ("X", "C", "pose", "q")}
+    vol.integrate_keyframes(t["X"], t["C"], t["pose"], t["q"], 0.05, H, W)
+    c = vol.counters()
+    assert c["rays"] == rays and c["dropped"] == 0 and c["overflow"] == 0
+    assert c["updates_primary"] == vp.events and c["updates_quality"] == vq.events
+    assert vp.events > 2_000_000 * n_kf
+    assert_volume_matches(vol.export(0), vp.export(), f"{name} primary")
+    assert_volume_matches(vol.export(1), vq.export(), f"{name} quality")
+    assert vol.stats(0) == vp.stats() and vol.stats(1) == vq.stats()
