@@ -249,6 +249,64 @@ class ShardedTSDFVolume:
             self.reintegrate(keep, poses[rows].contiguous(), src=src, mode=mode)
         return keep
 
+    # -- checkpoint / resume ---------------------------------------------------
+    def save_checkpoint(self, directory):
+        """Collective: every rank writes its slabs as
+        `<directory>/slabs_rank<r>.npz` (`TSDFVolume.save_checkpoint` format:
+        block keys, packed voxels, hit counters, volume parameters); rank 0 adds
+        `meta.json`.  Returns the number of blocks this rank wrote."""
+        import json
+        import os
+
+        os.makedirs(directory, exist_ok=True)
+        n = self.vol.save_checkpoint(os.path.join(directory, f"slabs_rank{self.rank:03d}.npz"))
+        if self.rank == 0:
+            with open(os.path.join(directory, "meta.json"), "w") as f:
+                json.dump({"world": self.world, "slab_width": self.slab_width, "z0": self.z0,
+                           "format": "b200tsdf-slabs-1"}, f)
+        if self.world > 1:
+            dist.barrier(group=self.group)
+        return n
+
+    def load_checkpoint(self, directory):
+        """Restore a `save_checkpoint` directory -- also onto a DIFFERENT number
+        of ranks or slab width: every rank reads all the slab files and imports
+        the blocks whose slab it owns now.  A voxel block is 8 layers and slabs
+        are multiples of 8 layers measured from an origin that is a multiple of
+        8, so a block never straddles a seam; the stored sums are additive, so
+        loading into a filled volume merges.  Returns the blocks imported."""
+        import json
+        import os
+
+        import numpy as np
+
+        with open(os.path.join(directory, "meta.json")) as f:
+            meta = json.load(f)
+        if meta.get("format") != "b200tsdf-slabs-1":
+            raise ValueError(f"{directory}: not a sharded TSDF checkpoint")
+        if (self.z0 - int(meta["z0"])) % 8:
+            raise ValueError("slab origin of the checkpoint is not block-aligned with this volume")
+        mine = None
+        if all(hasattr(self.vol, a) for a in ("voxel_size", "truncation", "max_weight",
+                                              "min_weight")):
+            mine = np.array([self.vol.voxel_size, self.vol.truncation, self.vol.max_weight,
+                             self.vol.min_weight], np.float64)
+        total = 0
+        for r in range(int(meta["world"])):
+            with np.load(os.path.join(directory, f"slabs_rank{r:03d}.npz")) as z:
+                if mine is not None and not np.allclose(z["params"], mine, rtol=1e-12, atol=0.0):
+                    raise ValueError(f"checkpoint parameters {z['params']} != volume {mine}")
+                bk = z["block_keys"].reshape(-1, 3)
+                own = slab_owner(bk[:, 2] * 8, self.z0, self.slab_width, self.world) == self.rank
+                if own.any():
+                    self.vol.import_blocks(torch.from_numpy(bk[own]),
+                                           torch.from_numpy(z["vox"][own]),
+                                           torch.from_numpy(z["cnt"][own]))
+                    total += int(own.sum())
+        if self.world > 1:
+            dist.barrier(group=self.group)
+        return total
+
     # -- reductions --------------------------------------------------------
     def _sum(self, values):
         t = torch.tensor(values, dtype=torch.int64,

@@ -65,6 +65,18 @@ class FakeVolume:
     def extract_mesh(self, which=0):
         return torch.full((3 * (self.rank + 1), 3), float(self.rank))
 
+    def save_checkpoint(self, path):
+        keys = sorted(self.blocks)
+        np.savez(path, block_keys=np.array(keys, np.int64).reshape(-1, 3),
+                 vox=np.array([self.blocks[k] for k in keys], np.float32).reshape(-1, 1),
+                 cnt=np.ones((len(keys), 1), np.int64), params=np.zeros(4))
+        return len(keys)
+
+    def import_blocks(self, bk, vox, cnt):
+        for i in range(bk.shape[0]):
+            k = tuple(int(x) for x in bk[i])
+            self.blocks[k] = self.blocks.get(k, 0.0) + float(vox[i, 0])
+
     # sharded query stand-ins: point i is "owned" by rank i % world
     def query_taps(self, points, which=0, pose=None):
         pts = torch.as_tensor(points, dtype=torch.float32).reshape(-1, 3)
@@ -90,7 +102,7 @@ def _free_port():
     return p
 
 
-def _worker(rank, world, port, out):
+def _worker(rank, world, port, out, ckpt_dir=None):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     dist.init_process_group("gloo", rank=rank, world_size=world)
     try:
@@ -164,6 +176,19 @@ def _worker(rank, world, port, out):
             raise AssertionError("unknown keyframe id must raise")
         except KeyError:
             pass
+        # checkpoint: every rank writes its slabs; reload onto another slab width
+        if ckpt_dir is not None:
+            wrote = sv.save_checkpoint(ckpt_dir)
+            assert wrote == len(sv.vol.blocks)
+            sv3 = parallel.ShardedTSDFVolume(0.01, 0.04, slab_width=32, bounds=bounds,
+                                             device="cpu", volume_factory=fake)
+            got = sv3.load_checkpoint(ckpt_dir)
+            assert got == len(sv3.vol.blocks)
+            assert all(parallel.slab_owner(k[2] * 8, -64, 32, world) == rank
+                       for k in sv3.vol.blocks)
+            tot = torch.tensor([got, wrote])
+            dist.all_reduce(tot)
+            assert tot[0] == tot[1]  # re-sharded, nothing lost or duplicated
         st = sv.stats()
         n_halo = sv.exchange_seams()
         # what I received is exactly what the rank above exported
@@ -179,12 +204,22 @@ def _worker(rank, world, port, out):
         dist.destroy_process_group()
 
 
-def test_sharded_volume_host_logic_world2():
+def test_sharded_volume_host_logic_world2(tmp_path):
     world = 2
+    ckpt = str(tmp_path / "ckpt")
     with mp.Manager() as m:
         out = m.dict()
-        mp.spawn(_worker, args=(world, _free_port(), out), nprocs=world, join=True)
+        mp.spawn(_worker, args=(world, _free_port(), out, ckpt), nprocs=world, join=True)
         res = dict(out)
+    # resume on ONE rank (no process group): all blocks of both files, values kept
+    one = parallel.ShardedTSDFVolume(0.01, 0.04, slab_width=16,
+                                     bounds=((-64, -64, -64), (64, 64, 64)), device="cpu",
+                                     volume_factory=lambda **kw: FakeVolume(**kw))
+    assert one.load_checkpoint(ckpt) == res[0][1] + res[1][1] == len(one.vol.blocks)
+    assert one.load_checkpoint(ckpt) == len(one.vol.blocks)  # additive: a second load merges
+    with np.load(ckpt + "/slabs_rank000.npz") as z:
+        k0 = tuple(int(x) for x in z["block_keys"][0])
+        assert abs(one.vol.blocks[k0] - 2 * float(z["vox"][0, 0])) < 1e-4
     assert res[0][0] == res[1][0] == res[0][1] + res[1][1]  # stats are all-reduced
     assert res[0][3] == (3 * 1 + 3 * 2, 3) and res[1][3] == (6, 3)  # rank 0 gathers the mesh
     assert res[0][2] + res[1][2] > 0
