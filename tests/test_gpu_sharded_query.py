@@ -176,3 +176,27 @@ def test_store_and_pose_only_reintegration(cuda_device, mode):
     assert torch.equal(sv._store[7]["pose"], t["pose"][1])
     with pytest.raises(KeyError):
         sv.reintegrate([1], new_pose[:1])
+
+
+def test_sharded_checkpoint_round_trip(cuda_device, tmp_path):
+    """save_checkpoint / load_checkpoint of the sharded wrapper on the real
+    volume (one rank; the re-sharding logic is in the world-2 gloo test):
+    restoring is bit-exact, a second load merges (sums and counters double)."""
+    from mast3r_slam_quality_dualtsdf_b200 import parallel
+
+    kf = synth.make_keyframes(synth.SCENES["sphere"], 2, H=H, W=W, seed=8, f=50.0, total=9)
+    a = parallel.ShardedTSDFVolume(VOXEL, TRUNC, slab_width=8, device=cuda_device)
+    _fuse(a.vol, kf, cuda_device)
+    n = a.save_checkpoint(str(tmp_path / "ck"))
+    b = parallel.ShardedTSDFVolume(VOXEL, TRUNC, slab_width=16, device=cuda_device)
+    assert b.load_checkpoint(str(tmp_path / "ck")) == n > 0
+    for which in (0, 1):
+        for x, y in zip(a.vol.export(which), b.vol.export(which)):
+            assert np.array_equal(x, y)
+    assert b.load_checkpoint(str(tmp_path / "ck")) == n
+    ka, ta, wa, ca = a.vol.export(0)
+    kb, tb, wb, cb = b.vol.export(0)
+    assert np.array_equal(ka, kb) and np.array_equal(2 * ca.astype(np.int64), cb.astype(np.int64))
+    c = parallel.ShardedTSDFVolume(VOXEL * 2, TRUNC, slab_width=8, device=cuda_device)
+    with pytest.raises(ValueError):
+        c.load_checkpoint(str(tmp_path / "ck"))
