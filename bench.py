@@ -478,7 +478,11 @@ def run_b200(args):
         "e2e": {"value": e2e_value, "unit": "voxel updates/s",
                 "h2d_bytes_per_step": B * KF_BYTES, "d2h_bytes_per_step": d2h[0],
                 "keyframes_per_s": B * args.steps / (e2e_ms * 1e-3),
-                "ms_per_step": e2e_ms / args.steps},
+                "ms_per_step": e2e_ms / args.steps,
+                "ingest": ("b200tsdf_integrate_keyframes_host (chunked H2D overlapped with the "
+                           "fuse)" if world == 1 else
+                           f"pipelined, {args.e2e_chunks} pieces (H2D || all-gather || fuse)"
+                           if args.e2e_chunks > 0 else "serial H2D, all-gather, fuse")},
         # kernels of this library inside the timed `value` region, all ranks: one fused launch
         # per step and rank; from 3 ranks up the classify pass + the listed-tile fuse
         "gpu_launches": args.steps * world * (2 if world > 2 else 1),
