@@ -119,6 +119,19 @@ class ShardedTSDFVolume:
     def stored_ids(self):
         return sorted(self._store)
 
+    def forget(self, ids=None):
+        """Drop keyframes from the store (all of them with ids=None): their
+        contribution stays in the volume, they can no longer be re-fused.
+        Returns the bytes released on this rank."""
+        ids = list(self._store) if ids is None else [int(i) for i in ids]
+        freed = 0
+        for i in ids:
+            e = self._store.pop(i, None)
+            if e is not None:
+                freed += sum(t.numel() * t.element_size() for t in (e["X"], e["C"], e["pose"])
+                             + ((e["q"],) if e["q"] is not None else ()))
+        return freed
+
     def reintegrate(self, ids, poses, src=0, mode="additive", batch=40):
         """`TSDFGlobalManager.on_after_backend_solve` -> `_process_dirty_queue`
         (global_manager.py:214-229, :71-79) over ranks: the keyframes `ids`

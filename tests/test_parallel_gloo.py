@@ -171,6 +171,8 @@ def _worker(rank, world, port, out, ckpt_dir=None):
         assert torch.equal(sv2._store[10]["pose"], torch.arange(8.0) + 32)
         assert sv2.on_after_backend_solve([0], hook_p[:1], pin=1) == []
         assert sv2.on_after_backend_solve([10, 11], hook_p[:2], pin=0, queue_cap=1) == [10]
+        assert sv2.forget([10]) == 4 * (48 * 3 + 48 + 8) and sv2.stored_ids() == [11]
+        assert sv2.on_after_backend_solve([10, 11], hook_p[:2], pin=0) == [11]
         try:
             sv2.reintegrate([99], want_p[:1])
             raise AssertionError("unknown keyframe id must raise")
