@@ -1,24 +1,33 @@
 #!/usr/bin/env python
 """bench.py -- dual-TSDF fusion throughput on B200 (BASELINE.json metric).
 
-A step = one launch of the hot path over one batch of KF_PER_STEP synthetic
-512x384 keyframes (TUM fr1_room-shaped orbit inside a room box) fused into a
-512^3 @ 5 mm dual volume (N=1, BASELINE.json configs[1]) or into the z-slabs
-of a 1024^3 @ 5 mm volume (N>1, configs[3]; rank 0 NCCL-broadcasts each batch).
+Workload (the same at every N, so the 1 -> 8 curve divides like by like): the
+north_star Target -- a TUM fr1_room-shaped synthetic orbit of 600 512x384
+keyframes fused into a 1024^3 @ 5 mm dual volume (primary + quality-weighted),
+truncation 20 mm.  A STEP = one pass over the 600-keyframe sequence, issued as
+15 launches of 40 keyframes (every launch reads a fresh 126 MB batch, the whole
+pass 1.9 GB, so nothing is served from L2 twice).
+
+  N = 1 : one volume on one GPU.
+  N > 1 : the volume is cut into interleaved z-slabs; every rank holds 1/N of
+          each launch's keyframes in its own HBM and the launch's keyframes are
+          NCCL all-gathered (= N simultaneous broadcasts over NVLink) INSIDE
+          the timed region -- the collective is part of the step.
 
   value : voxel updates/s (primary + quality volume), inputs resident in HBM
-  e2e   : same metric through the reference-facing TSDFVolume API with HOST
-          (pinned) keyframe buffers: H2D inside the timed region + D2H of the
-          step's counters
+          when the timed region starts
+  e2e   : same metric through the reference-facing TSDFVolume API from HOST
+          (pinned) keyframe buffers: H2D (+ all-gather) inside the timed
+          region, one D2H read of the counters per step
   roofline / cpu_baseline : see DESIGN.md "Measurement"
 
 `--impl reference` times the CPU oracle port of the reference path (the
-reference itself is Python and does not travel to the GPU box).
+reference itself is Python and does not travel to the GPU box) on the same
+workload, each step a bounded sample of the step's keyframes.
 """
 import argparse
 import json
 import os
-import subprocess
 import sys
 import threading
 import time
@@ -31,37 +40,32 @@ sys.path.insert(0, ROOT)
 H, W, GH, GW = 384, 512, 24, 32
 VOXEL, TRUNC = 0.005, 0.02
 MIN_CONF = 0.05
-KF_PER_STEP = 40
+KF_PER_LAUNCH = 40
 ORBIT_TOTAL = 600
 # algorithmic bytes per keyframe input: X + C + pose + quality grid
 KF_BYTES = H * W * 12 + H * W * 4 + 32 + GH * GW * 4
+
+# the Target workload (north_star): every N runs this scene
+TARGET = {"scene": {"kind": "room", "half": 2.4874}, "dim": 1024, "orbit_r": 1.2, "up": "z",
+          "cap_log2": 19}
+# BASELINE.json configs[1] (512^3 @ 5 mm): reported as a second section at N = 1
+CONFIG2 = {"scene": {"kind": "room", "half": 1.2437}, "dim": 512, "orbit_r": 0.6, "up": "y",
+           "cap_log2": 18}
 
 
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=15)
+    ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--kf-per-step", type=int, default=KF_PER_STEP)
+    ap.add_argument("--kf-per-launch", type=int, default=KF_PER_LAUNCH)
+    ap.add_argument("--launches-per-step", type=int, default=ORBIT_TOTAL // KF_PER_LAUNCH)
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--e2e-chunks", type=int, default=-1,
-                    help="N > 1: pieces the per-rank share is cut into for the pipelined "
-                         "PCIe -> all-gather -> fuse ingest (0: serial copy, gather, fuse; "
-                         "-1: 2 pieces when a rank ingests >= 16 keyframes per step, else serial "
-                         "-- small shares are launch-latency-bound, profiles/r01j_e2e_chunks.txt)")
+    ap.add_argument("--no-sections", action="store_true",
+                    help="skip the secondary sections (config2, extract, sweep, quality, manager, "
+                         "reintegrate): headline value / e2e / roofline only")
     return ap.parse_args()
-
-
-def scene_for(n_gpus):
-    from mast3r_slam_quality_dualtsdf_b200 import synth
-
-    if n_gpus == 1:
-        return dict(synth.SCENES["room"]), 512, 0.6
-    return {"kind": "room", "half": 2.4874}, 1024, 1.2
-
-
-SLAB_WIDTH = 32  # voxel layers per interleaved z-slab at N = 8: 16 cm at 5 mm
 
 
 def slab_width_for(n_gpus, dim=1024):
@@ -70,20 +74,19 @@ def slab_width_for(n_gpus, dim=1024):
     return max(8, dim // (4 * max(1, n_gpus)))
 
 
-def gen_batch(scene, orbit_r, step_idx, kf_per_step, seed=0, up_axis="y", offset=0, count=None):
-    """Keyframes [offset, offset + count) of step `step_idx`'s batch (default: all)."""
+def gen_batch(wl, launch_idx, kf_per_launch, seed=0, offset=0, count=None):
+    """Keyframes [offset, offset + count) of launch `launch_idx`'s batch (default: all)."""
     from mast3r_slam_quality_dualtsdf_b200 import synth
 
-    start = (step_idx * kf_per_step) % ORBIT_TOTAL + offset
-    return synth.make_keyframes(scene, count or kf_per_step, H, W, seed=seed,
-                                orbit_radius=orbit_r, gh=GH, gw=GW, start=start,
-                                total=ORBIT_TOTAL, up_axis=up_axis)
+    start = (launch_idx * kf_per_launch) % ORBIT_TOTAL + offset
+    return synth.make_keyframes(wl["scene"], count or kf_per_launch, H, W, seed=seed,
+                                orbit_radius=wl["orbit_r"], gh=GH, gw=GW, start=start,
+                                total=ORBIT_TOTAL, up_axis=wl["up"])
 
 
 class ClockSampler:
-    """SM clock / throttle reasons sampled DURING the timed region.  The region
-    lasts milliseconds, so NVML is polled from a thread (~1 kHz); nvidia-smi
-    -lms 100 would return no sample at all."""
+    """SM clock / throttle reasons sampled DURING the timed region through NVML
+    from a thread (~1 kHz)."""
 
     def __init__(self, index=0):
         self.sm, self.mx, self.reasons = [], None, set()
@@ -137,7 +140,7 @@ def host_threads():
     return max(1, min(os.cpu_count() or 1, 64))
 
 
-def cpu_fuse(kf, idx, threads=2):
+def cpu_fuse(kf, idx, threads=2, voxel=VOXEL, trunc=TRUNC):
     """Reference semantics on the host: the C oracle port of
     TSDFVolume.integrate.  The reference is one Python thread under an RLock;
     to use every host core the port runs threads // 2 independent volume
@@ -150,7 +153,7 @@ def cpu_fuse(kf, idx, threads=2):
     n_rep = max(1, min(threads // 2, len(idx)))
     staged = [orc.stage_keyframe(kf["X"][b], kf["C"][b], kf["pose"][b], kf["q"][b], H, W,
                                  MIN_CONF) for b in idx]
-    vols = [(orc.OracleVolume(VOXEL, TRUNC), orc.OracleVolume(VOXEL, TRUNC))
+    vols = [(orc.OracleVolume(voxel, trunc), orc.OracleVolume(voxel, trunc))
             for _ in range(n_rep)]
 
     def run(r, which):
@@ -169,22 +172,30 @@ def cpu_fuse(kf, idx, threads=2):
     return sum(vp.events + vq.events for vp, vq in vols), dt
 
 
+def cpu_sample_text(n_kf, threads, per_step):
+    return (f"{n_kf} of the step's {per_step} keyframes per step; C port of "
+            "TSDFVolume.integrate (oracle/tsdf_oracle.c); the reference is single-threaded, so "
+            f"the host cores run {max(1, threads // 2)} independent volume replicas, one keyframe "
+            "each, primary and quality volume on one thread each")
+
+
 def run_reference(args):
     """--impl reference: the reference's CPU path (oracle port; the Python
-    reference cannot travel to the GPU box) on the same workload, each step a
-    bounded sample of the step's keyframes."""
+    reference cannot travel to the GPU box) on the same workload and config,
+    each step a bounded sample of the step's keyframes."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     from oracle import oracle as orc
 
     orc.build()
-    scene, dim, orbit_r = scene_for(args.gpus)
     threads = host_threads()
     sample_kf = max(2, threads // 2)
+    per_step = args.kf_per_launch * args.launches_per_step
     ev_total, t_total = 0, 0.0
     for s in range(args.warmup + args.steps):
-        kf = gen_batch(scene, orbit_r, s, sample_kf, up_axis="z" if args.gpus > 1 else "y")
+        # a different launch of the pass every step, so the sample walks the orbit
+        kf = gen_batch(TARGET, s % args.launches_per_step, sample_kf)
         ev, dt = cpu_fuse(kf, range(sample_kf), threads)
         if s >= args.warmup:
             ev_total += ev
@@ -196,15 +207,9 @@ def run_reference(args):
         "warmup": args.warmup, "ms_per_step": 1e3 * t_total / max(1, args.steps),
         "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
         "data": "synthetic", "keyframes_per_s": sample_kf * args.steps / t_total,
-        "config": workload_config(args.gpus, dim, sample_kf),
+        "config": workload_config(args),
         "cpu_baseline": {"value": value, "unit": "voxel updates/s", "cores": threads,
-                         "kind": "port",
-                         "sample": f"{sample_kf} keyframes per step (of {args.kf_per_step}), "
-                                   "C port of TSDFVolume.integrate; the reference is "
-                                   "single-threaded, so the host cores run "
-                                   f"{max(1, threads // 2)} independent volume replicas, one "
-                                   "keyframe each, primary and quality volume on one thread "
-                                   "each"},
+                         "kind": "port", "sample": cpu_sample_text(sample_kf, threads, per_step)},
         "e2e": {"value": value, "unit": "voxel updates/s", "h2d_bytes_per_step": 0,
                 "d2h_bytes_per_step": 0},
         "gpu_launches": 0, "host_cores": os.cpu_count(),
@@ -212,16 +217,19 @@ def run_reference(args):
     emit(line)
 
 
-def workload_config(n_gpus, dim, kf_per_step):
+def workload_config(args):
+    """The SAME dict on both arms and at every N (the partition of the volume over the
+    ranks is reported under `partition`, outside `config`)."""
     return {
-        "workload": ("TUM fr1_room-shaped synthetic orbit, 512x384 keyframes, dual TSDF "
-                     f"(primary + quality-weighted), {dim}^3 @ 5 mm, trunc 20 mm"),
-        "keyframes_per_step": kf_per_step, "volume_dim": dim, "voxel_size": VOXEL,
-        "truncation": TRUNC, "orbit_keyframes": ORBIT_TOTAL,
-        "partition": "single volume" if n_gpus == 1 else
-        f"interleaved z-slabs of {slab_width_for(n_gpus, dim)} voxel layers over {n_gpus} ranks; every rank ingests "
-        f"{kf_per_step // max(1, n_gpus)} keyframes per step, NCCL all-gather (= {n_gpus} broadcasts) over NVLink",
-        "l2": "each step reads a fresh keyframe batch larger than L2 (157 MB > 126 MB)",
+        "workload": ("north_star Target: TUM fr1_room-shaped synthetic orbit, "
+                     f"{args.kf_per_launch * args.launches_per_step} keyframes 512x384 per step, "
+                     "dual TSDF (primary + quality-weighted), 1024^3 @ 5 mm, trunc 20 mm"),
+        "keyframes_per_step": args.kf_per_launch * args.launches_per_step,
+        "keyframes_per_launch": args.kf_per_launch, "launches_per_step": args.launches_per_step,
+        "volume_dim": TARGET["dim"], "voxel_size": VOXEL, "truncation": TRUNC,
+        "orbit_keyframes": ORBIT_TOTAL,
+        "l2": "every launch reads a fresh 126 MB keyframe batch and a step 1.9 GB "
+              "(L2 = 126 MB): inputs larger than L2, no flush needed",
     }
 
 
@@ -232,6 +240,7 @@ def run_b200(args):
 
     from mast3r_slam_quality_dualtsdf_b200 import build, synth
     from mast3r_slam_quality_dualtsdf_b200.tsdf import TSDFVolume
+    from mast3r_slam_quality_dualtsdf_b200.tsdf.global_volume import pack_keyframes, packed_layout
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -244,75 +253,121 @@ def run_b200(args):
     dev = torch.device("cuda", local)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
-    n_gpus = world
-    scene, dim, orbit_r = scene_for(n_gpus)
-    lo, hi = synth.bounds_for(scene, VOXEL, dim)
+    wl = TARGET
+    lo, hi = synth.bounds_for(wl["scene"], VOXEL, wl["dim"])
+    bounds = (lo, hi)
     # N > 1: interleaved z-slabs (slab s -> rank s mod N); z is the vertical axis of the
     # orbit so the slabs cut every view (DESIGN.md "Multi-GPU")
-    bounds = (lo, hi)
-    slabs = (world, rank, slab_width_for(world, dim)) if world > 1 else None
-    up_axis = "z" if world > 1 else "y"
-    cap = 18 if world == 1 else 19
-    vol = TSDFVolume(VOXEL, TRUNC, capacity_log2=cap, bounds=bounds, slabs=slabs, device=dev)
+    slabs = (world, rank, slab_width_for(world, wl["dim"])) if world > 1 else None
+    vol = TSDFVolume(VOXEL, TRUNC, capacity_log2=wl["cap_log2"], bounds=bounds, slabs=slabs,
+                     device=dev)
     scratch = TSDFVolume(VOXEL, TRUNC, capacity_log2=16, bounds=bounds, slabs=slabs, device=dev)
-    B = args.kf_per_step
-    n_steps = args.warmup + args.steps
-    names = ("X", "C", "q", "pose")
-    shapes = {"X": (B, H * W, 3), "C": (B, H * W), "q": (B, GH, GW), "pose": (B, 8)}
-
-    # N = 1: the whole batch in pinned host memory.  N > 1: sharded ingest -- every rank
-    # holds B / N keyframes of each batch (pinned host memory, its own PCIe link); the N
-    # simultaneous NCCL broadcasts run as one all-gather over NVLink
+    B, L = args.kf_per_launch, args.launches_per_step
     if B % world:
-        raise SystemExit(f"bench.py: --kf-per-step {B} must be a multiple of the {world} ranks")
+        raise SystemExit(f"bench.py: --kf-per-launch {B} must be a multiple of the {world} ranks")
     share = B // world
-    host = []
-    for s in range(n_steps):
-        kf = gen_batch(scene, orbit_r, s, B, up_axis=up_axis, offset=rank * share, count=share)
-        host.append({k: torch.from_numpy(kf[k]).pin_memory() for k in names})
-    local_shapes = {k: (share,) + shapes[k][1:] for k in names}
+    lay = packed_layout(share, H, W, GH, GW)
+    seg_len = lay["seg_len"]
 
-    def fuse(v, t):
-        v.integrate_keyframes(t["X"], t["C"], t["pose"], t["q"], MIN_CONF, H, W)
-
-    def gather(full, part):
-        for k in names:
-            dist.all_gather_into_tensor(full[k], part[k])
-
-    # resident copies on every rank (the `value` loop starts from HBM)
-    resident = []
-    for s in range(n_steps):
-        t = {k: torch.empty(shapes[k], dtype=torch.float32, device=dev) for k in names}
+    # every rank holds ITS share of every launch: a packed segment in pinned host memory
+    # (e2e source) and the same segment resident in its HBM (value source).  N = 1 also
+    # keeps the four separate pinned arrays the reference-facing host entry takes.
+    host_seg, host_sep, res_seg = [], [], []
+    for l in range(L):
+        kf = gen_batch(wl, l, B, offset=rank * share, count=share)
+        seg = torch.zeros(seg_len, dtype=torch.float32).pin_memory()
+        pack_keyframes(kf["X"], kf["C"], kf["pose"], kf["q"], out=seg)
+        host_seg.append(seg)
+        res_seg.append(seg.to(dev, non_blocking=True))
         if world == 1:
-            for k in names:
-                t[k].copy_(host[s][k], non_blocking=True)
-        else:
-            part = {k: host[s][k].to(dev, non_blocking=True) for k in names}
-            gather(t, part)
-        resident.append(t)
+            host_sep.append({k: torch.from_numpy(kf[k]).pin_memory()
+                             for k in ("X", "C", "pose", "q")})
     torch.cuda.synchronize()
 
+    main = torch.cuda.current_stream(dev)
+
+    def fuse_packed(v, buf, n_seg):
+        v.integrate_keyframes_packed(buf, n_seg, share, H, W, GH, GW, MIN_CONF)
+
+    # N > 1: two all-gather targets, gather of launch l+1 overlaps the fuse of launch l
+    full = [torch.empty(world * seg_len, dtype=torch.float32, device=dev) for _ in range(2)] \
+        if world > 1 else None
+    stage_seg = [torch.empty(seg_len, dtype=torch.float32, device=dev) for _ in range(2)] \
+        if world > 1 else None
+    gs = torch.cuda.Stream(dev) if world > 1 else None
+    cs = torch.cuda.Stream(dev) if world > 1 else None
+    fuse_done = [torch.cuda.Event() for _ in range(2)]
+    copy_done = [torch.cuda.Event() for _ in range(2)]
+    gath_done = [torch.cuda.Event() for _ in range(2)]
+
+    def step_value(v):
+        """One pass over the orbit from HBM-resident shares."""
+        if world == 1:
+            for l in range(L):
+                fuse_packed(v, res_seg[l], 1)
+            return
+        for l in range(L + 1):
+            b = l & 1
+            if l < L:
+                with torch.cuda.stream(gs):
+                    gs.wait_event(fuse_done[b])  # launch l-2 has consumed full[b]
+                    dist.all_gather_into_tensor(full[b], res_seg[l])
+                    gath_done[b].record(gs)
+            if l > 0:
+                main.wait_event(gath_done[b ^ 1])
+                fuse_packed(v, full[b ^ 1], world)
+                fuse_done[b ^ 1].record(main)
+
+    def step_e2e(v):
+        """The same pass from pinned HOST buffers."""
+        if world == 1:
+            for l in range(L):  # *_host entry: chunked H2D inside the C ABI call
+                t = host_sep[l]
+                v.integrate_keyframes(t["X"], t["C"], t["pose"], t["q"], MIN_CONF, H, W)
+        else:  # one H2D + one all-gather + one fuse per launch, three-stage pipeline
+            for l in range(L + 2):
+                if l < L:
+                    b = l & 1
+                    with torch.cuda.stream(cs):
+                        cs.wait_event(gath_done[b])  # gather l-2 has read stage_seg[b]
+                        stage_seg[b].copy_(host_seg[l], non_blocking=True)
+                        copy_done[b].record(cs)
+                if 1 <= l <= L:
+                    b = (l - 1) & 1
+                    with torch.cuda.stream(gs):
+                        gs.wait_event(copy_done[b])
+                        gs.wait_event(fuse_done[b])
+                        dist.all_gather_into_tensor(full[b], stage_seg[b])
+                        gath_done[b].record(gs)
+                if l >= 2:
+                    b = l & 1
+                    main.wait_event(gath_done[b])
+                    fuse_packed(v, full[b], world)
+                    fuse_done[b].record(main)
+        v.counters()  # the step's result (8 x int64) read back; synchronises
+
     def barrier():
+        torch.cuda.synchronize()
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    def timed(loop_body, reset):
-        reset()
-        for s in range(args.warmup):
-            loop_body(s)
+    def timed(step_fn, v, steps, warmup, sample_clocks=True):
+        v.reset()
+        for _ in range(warmup):
+            step_fn(v)
         barrier()
-        c0 = vol.counters()
-        sampler = ClockSampler(local) if rank == 0 else None
-        ev = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
+        c0 = v.counters()
+        sampler = ClockSampler(local) if (rank == 0 and sample_clocks) else None
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(steps + 1)]
         ev[0].record()
-        for i in range(args.steps):
-            loop_body(args.warmup + i)
+        for i in range(steps):
+            step_fn(v)
             ev[i + 1].record()
         barrier()
         clocks = sampler.stop() if sampler else None
-        c1 = vol.counters()
-        ms = [ev[i].elapsed_time(ev[i + 1]) for i in range(args.steps)]
+        c1 = v.counters()
+        ms = [ev[i].elapsed_time(ev[i + 1]) for i in range(steps)]
         total_ms = ev[0].elapsed_time(ev[-1])
         upd = (c1["updates_primary"] - c0["updates_primary"]) + \
               (c1["updates_quality"] - c0["updates_quality"])
@@ -323,59 +378,31 @@ def run_b200(args):
             dist.all_reduce(uu, op=dist.ReduceOp.SUM)
         return float(tt.item()), float(uu.item()), ms, clocks, c1
 
-    # ---- value: device-resident inputs, one launch per step
-    total_ms, updates, step_ms, clocks, ctr = timed(lambda s: fuse(vol, resident[s]), vol.reset)
+    # ---- value: device-resident inputs (N > 1: incl. the NCCL keyframe all-gather)
+    total_ms, updates, step_ms, clocks, ctr = timed(step_value, vol, args.steps, args.warmup)
     value = updates / (total_ms * 1e-3)
-
     # ---- e2e: host buffers -> (H2D, all-gather) -> fuse -> counters back
-    sharded = None
-    if args.e2e_chunks < 0:
-        args.e2e_chunks = 2 if share >= 16 else 0
-    if world > 1:
-        from mast3r_slam_quality_dualtsdf_b200 import parallel
-
-        sharded = parallel.ShardedTSDFVolume(VOXEL, TRUNC, slab_width=slabs[2], bounds=bounds,
-                                             device=dev, volume_factory=lambda **kw: vol)
-    stage = {k: torch.empty(shapes[k], dtype=torch.float32, device=dev) for k in names}
-    stage_local = {k: torch.empty(local_shapes[k], dtype=torch.float32, device=dev) for k in names}
-    d2h = [0]
-
-    def e2e_body(s):
-        if world == 1:
-            fuse(vol, host[s])  # *_host entry: H2D inside the C ABI call
-        else:
-            if args.e2e_chunks > 0:  # pipelined PCIe -> NVLink all-gather -> fuse
-                h = host[s]
-                sharded.integrate_keyframes_from_host(h["X"], h["C"], h["pose"], h["q"], MIN_CONF,
-                                                      H, W, chunks=args.e2e_chunks)
-            else:
-                for k in names:
-                    stage_local[k].copy_(host[s][k], non_blocking=True)
-                gather(stage, stage_local)
-                fuse(vol, stage)
-        vol.counters()  # the step's result (8 x int64) read back, synchronises
-        d2h[0] = 64
-
-    e2e_ms, e2e_updates, _, _, _ = timed(e2e_body, vol.reset)
+    e2e_ms, e2e_updates, _, _, _ = timed(step_e2e, vol, args.steps, args.warmup,
+                                         sample_clocks=False)
     e2e_value = e2e_updates / (e2e_ms * 1e-3)
+    n_kf_step = B * L
 
-    # ---- algorithmic bytes per launch: voxels / blocks a step's batch touches
-    touched_v, touched_b = [], []
-    for i in range(args.steps):
+    # ---- algorithmic bytes per launch: voxels / blocks a launch's batch touches on this
+    # rank (fused into an empty scratch volume)
+    touched_v = touched_b = 0
+    for l in range(L):
         scratch.reset()
-        fuse(scratch, resident[args.warmup + i])
-        st = scratch.stats(0)
-        cc = scratch.counters()
-        touched_v.append(st["total_voxels"])
-        touched_b.append(cc["blocks"])
-    tv = torch.tensor([float(sum(touched_v)), float(sum(touched_b))], dtype=torch.float64,
-                      device=dev)
-    if world > 1:
-        dist.all_reduce(tv, op=dist.ReduceOp.SUM)
-    alg_bytes_step = (B * KF_BYTES * world + (tv[0].item() * 32 + tv[1].item() * 8) / args.steps)
-    # per-rank kernel: the launch on this rank reads the whole batch, writes its slab
-    alg_bytes_launch = B * KF_BYTES + (sum(touched_v) * 32 + sum(touched_b) * 8) / args.steps
-    launch_ms = float(np.mean(step_ms))
+        if world == 1:
+            fuse_packed(scratch, res_seg[l], 1)
+        else:
+            dist.all_gather_into_tensor(full[0], res_seg[l])
+            fuse_packed(scratch, full[0], world)
+        touched_v += scratch.stats(0)["total_voxels"]
+        touched_b += scratch.counters()["blocks"]
+    del scratch
+    # the launch on this rank reads the whole batch and writes its slabs
+    alg_bytes_launch = B * KF_BYTES + (touched_v * 32 + touched_b * 8) / L
+    launch_ms = float(np.mean(step_ms)) / L
     peaks = {}
     try:
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
@@ -383,86 +410,26 @@ def run_b200(args):
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0))
     achieved = alg_bytes_launch / (launch_ms * 1e-3) / 1e9
-    # DRAM traffic of the same kernel from the committed ncu --set full capture
-    traffic = None
+    # DRAM traffic and issue statistics of the same kernel from the committed ncu --set full
+    # capture (profiles/ncu_traffic.json, written by scripts/ncu_summary.py)
+    traffic, issue = None, None
     try:
         tr = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
-        if B == KF_PER_STEP and world == 1:
-            traffic = float(tr["integrate_keyframes_kernel"]["dram_bytes_per_launch"])
+        k = tr["integrate_keyframes_kernel"]
+        if B == KF_PER_LAUNCH and world == 1 and k.get("workload", "target") == "target":
+            traffic = float(k["dram_bytes_per_launch"])
+            if "warp_inst_per_launch" in k:
+                issue = {"warp_inst_per_launch": k["warp_inst_per_launch"],
+                         "issue_active_pct": k.get("issue_active_pct"),
+                         "inst_per_update": k["warp_inst_per_launch"] * 32.0 /
+                         (updates / (args.steps * L)),
+                         "source": k.get("source")}
     except Exception:
         pass
 
-    # ---- secondary kernels on the volume the e2e loop left behind (this rank's slabs):
-    # marching cubes (north_star kernel 4) and the stats sweep, both streaming / HBM-bound
-    def dev_ms(fn, reps=3):
-        best = None
-        for _ in range(reps):
-            torch.cuda.synchronize()
-            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            a.record()
-            out = fn()
-            b.record()
-            torch.cuda.synchronize()
-            t = a.elapsed_time(b)
-            best = t if best is None else min(best, t)
-        return best, out
-
-    nblk = vol.counters()["blocks"]
-    verts = vol.extract_mesh(0)
-    n_tris = int(verts.shape[0] // 3)
-    buf = torch.empty(max(n_tris, 1) * 3, 3, dtype=torch.float32, device=dev)
-    del verts
-    mc_ms, _ = dev_ms(lambda: vol.extract_mesh(0, out=buf))  # one write pass, buffer reused
-    st_ms, st = dev_ms(lambda: vol.stats(0))
-    vox_bytes = nblk * 512 * 24  # packed voxel (16 B) + hit counters (8 B)
-    extract = {
-        "kernel": "mc_kernel<write> (single pass, incl. counter memset + D2H of the count)", "blocks": nblk, "triangles": n_tris,
-        "ms": mc_ms, "voxels_per_s": nblk * 512 / (mc_ms * 1e-3),
-        "triangles_per_s": n_tris / (mc_ms * 1e-3),
-        "algorithmic_bytes": vox_bytes + n_tris * 36,
-        "achieved_gbs": (vox_bytes + n_tris * 36) / (mc_ms * 1e-3) / 1e9,
-        "frac": (vox_bytes + n_tris * 36) / (mc_ms * 1e-3) / 1e9 / peak,
-        "l2": "volume %.0f MB vs 126 MB L2" % (vox_bytes / 1e6),
-    }
-    sweep = {"kernel": "stats_kernel", "ms": st_ms, "algorithmic_bytes": vox_bytes,
-             "achieved_gbs": vox_bytes / (st_ms * 1e-3) / 1e9,
-             "frac": vox_bytes / (st_ms * 1e-3) / 1e9 / peak, "valid_voxels": st["valid_voxels"]}
-
-    # ---- quality producer: per-patch grids + classify on the device
-    quality = None
-    if rank == 0:
-        from mast3r_slam_quality_dualtsdf_b200 import quality_core as qc
-
-        gq = torch.Generator(device="cpu").manual_seed(1)
-        qjob = {"H": H, "W": W, "kf_id": 0, "t_norm": torch.tensor(0.05), "theta": torch.tensor(0.1),
-                "valid_kf": (torch.rand(H * W, generator=gq) > 0.3).to(dev),
-                "r_pix": torch.rand(H * W, generator=gq).to(dev),
-                "Ck": (torch.rand(H * W, generator=gq) * 3).to(dev),
-                "Qk": (torch.rand(H * W, generator=gq) * 2).to(dev)}
-        qargs = dict(ps=16, alpha=0.8, b0=0.15, theta0=0.1745, C_thr=1.5, Q_thr=1.5, thr_zr=1.0,
-                     thr_zu=1.0, thr_dc=0.02, device=dev)
-        q_ms1, _ = dev_ms(lambda: [qc.compute_batch([qjob], **qargs) for _ in range(20)])
-        qjobs = [dict(qjob, kf_id=i) for i in range(B)]
-        qc.compute_batch(qjobs, **qargs)
-        q_ms, _ = dev_ms(lambda: [qc.compute_batch(qjobs, **qargs) for _ in range(5)])
-        st = {k: torch.stack([j[k] for j in qjobs]) for k in ("Ck", "Qk", "r_pix")}
-        st["valid"] = torch.stack([j["valid_kf"] for j in qjobs]).to(torch.uint8)
-        tn, th = (torch.stack([j[k] for j in qjobs]).to(dev) for k in ("t_norm", "theta"))
-        sargs = {k: v for k, v in qargs.items() if k != "device"}
-        run_st = lambda: qc.compute_stacked(st["Ck"], st["Qk"], st["r_pix"], st["valid"], tn, th,  # noqa: E731
-                                            None, H, W, device=dev, **sargs)
-        run_st()
-        q_ms_st, _ = dev_ms(lambda: [run_st() for _ in range(5)])
-        q_bytes = H * W * 13  # C, Q, r_pix float32 + valid u8, read once
-        quality = {"kernels": "quality_patch_kernel + quality_finish_batch_kernel (2 launches per batch)",
-                   "keyframes_per_batch": B,
-                   "us_per_keyframe": 1e3 * q_ms / 5 / B,
-                   "us_per_keyframe_batch_of_1": 1e3 * q_ms1 / 20,
-                   "us_per_keyframe_stacked_inputs": 1e3 * q_ms_st / 5 / B,
-                   "stacked_gbs": q_bytes * B * 5 / (q_ms_st * 1e-3) / 1e9,
-                   "algorithmic_bytes": q_bytes,
-                   "note": "through quality_core.compute_batch incl. the stacking of the job "
-                           "tensors; a batch of 1 is launch/latency-bound"}
+    sections = {}
+    if not args.no_sections:
+        sections = secondary_sections(args, vol, dev, rank, world, peak, bounds, slabs)
 
     if rank != 0:
         if world > 1:
@@ -470,43 +437,53 @@ def run_b200(args):
         return
     line = {
         "metric": "tsdf_voxel_updates_per_s", "value": value, "unit": "voxel updates/s",
-        "n_gpus": n_gpus, "steps": args.steps, "warmup": args.warmup,
+        "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "keyframes_per_s": B * args.steps / (total_ms * 1e-3),
-        "config": workload_config(n_gpus, dim, B),
+        "keyframes_per_s": n_kf_step * args.steps / (total_ms * 1e-3),
+        "timed_region_s": total_ms * 1e-3,
+        "config": workload_config(args),
+        "partition": "single volume" if world == 1 else
+        f"interleaved z-slabs of {slab_width_for(world, wl['dim'])} voxel layers over {world} "
+        f"ranks; every rank holds {share} keyframes of each launch; ONE packed NCCL all-gather "
+        f"(= {world} broadcasts over NVLink) per launch inside the timed region, double-buffered "
+        "against the fuse",
         "e2e": {"value": e2e_value, "unit": "voxel updates/s",
-                "h2d_bytes_per_step": B * KF_BYTES, "d2h_bytes_per_step": d2h[0],
-                "keyframes_per_s": B * args.steps / (e2e_ms * 1e-3),
+                "h2d_bytes_per_step": n_kf_step * KF_BYTES, "d2h_bytes_per_step": 64,
+                "keyframes_per_s": n_kf_step * args.steps / (e2e_ms * 1e-3),
                 "ms_per_step": e2e_ms / args.steps,
-                "ingest": ("b200tsdf_integrate_keyframes_host (chunked H2D overlapped with the "
-                           "fuse)" if world == 1 else
-                           f"pipelined, {args.e2e_chunks} pieces (H2D || all-gather || fuse)"
-                           if args.e2e_chunks > 0 else "serial H2D, all-gather, fuse")},
+                "ingest": ("b200tsdf_integrate_keyframes_host per launch (chunked H2D overlapped "
+                           "with the fuse), one counters read per step" if world == 1 else
+                           "per launch ONE packed H2D of the rank's share, ONE all-gather, one "
+                           "fuse (classify + listed-tile march); copy / gather / fuse of "
+                           "consecutive launches overlap on three streams; one counters read "
+                           "per step")},
         # kernels of this library inside the timed `value` region, all ranks: one fused launch
-        # per step and rank; from 3 ranks up the classify pass + the listed-tile fuse
-        "gpu_launches": args.steps * world * (2 if world > 2 else 1),
+        # per 40 keyframes and rank; from 3 ranks up the classify pass + the listed-tile fuse
+        "gpu_launches": args.steps * L * world * (2 if world > 2 else 1),
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": traffic,
                      "kernel": "integrate_keyframes_kernel" if world <= 2 else
                      "slab_classify_kernel + integrate_keyframes_listed_kernel",
                      "peak_source": "measured (MEASURED_PEAKS.json hbm_gbs)" if peaks else "fallback",
                      "algorithmic_bytes_per_launch": alg_bytes_launch,
-                     "launch_ms": launch_ms},
+                     "launch_ms": launch_ms,
+                     "binding": "instruction issue, not HBM (DESIGN.md 5): see `issue`",
+                     "issue": issue},
         "clocks": clocks,
-        "extract": extract, "sweep": sweep, "quality": quality,
         "volume": {"blocks": ctr["blocks"], "dropped_updates": ctr["dropped"],
                    "dropped_means": "samples outside the bounds or, at N > 1, marched by a rank "
                                     "that does not own their voxel (the owner applies them)"},
         "host_cores": os.cpu_count(),
     }
+    line.update(sections)
     if world == 1 and not args.no_cpu_baseline:
         from oracle import oracle as orc
 
         orc.build()
         threads = host_threads()
         n_cpu_kf = max(2, threads // 2)
-        kf = gen_batch(scene, orbit_r, args.warmup, n_cpu_kf)
+        kf = gen_batch(wl, 0, n_cpu_kf)
         ev_c, dt_c = 0, 0.0
         while dt_c < 10.0:
             e, d = cpu_fuse(kf, range(n_cpu_kf), threads)
@@ -514,14 +491,253 @@ def run_b200(args):
             dt_c += d
         line["cpu_baseline"] = {
             "value": ev_c / dt_c, "unit": "voxel updates/s", "cores": threads, "kind": "port",
-            "sample": f"{n_cpu_kf} keyframes of the first timed step, repeated for >= 10 s; C "
-                      "port of TSDFVolume.integrate (oracle/tsdf_oracle.c) as "
-                      f"{max(1, threads // 2)} independent volume replicas (one keyframe each), "
-                      "primary and quality volume on one thread each; the reference's own "
-                      "single-threaded Python loop measured 12.9 k updates/s (BASELINE.md)"}
+            "sample": cpu_sample_text(n_cpu_kf, threads, n_kf_step) + ", repeated for >= 10 s; "
+            "the reference's own single-threaded Python loop measured 12.9 k updates/s "
+            "(BASELINE.md)"}
+        # BASELINE.json configs[0]: the reference's own CPU-runnable case
+        from mast3r_slam_quality_dualtsdf_b200 import synth as sy
+
+        k1 = sy.make_keyframes(sy.SCENES["room"], 16, H, W, seed=0, orbit_radius=0.6, gh=GH, gw=GW,
+                               start=100, total=ORBIT_TOTAL)
+        e1, d1 = cpu_fuse(k1, range(16), threads, voxel=0.01, trunc=0.04)
+        line["cpu_baseline"]["config1"] = {
+            "workload": "BASELINE configs[0]: 16 keyframes 512x384 into 256^3 @ 1 cm, dual volume",
+            "value": e1 / d1, "unit": "voxel updates/s", "seconds": d1, "cores": threads}
     emit(line)
     if world > 1:
         dist.destroy_process_group()
+
+
+def secondary_sections(args, vol, dev, rank, world, peak, bounds, slabs):
+    """Kernels beside the headline, on the volume the e2e loop left behind (this rank's
+    slabs): marching cubes of both volumes (north_star kernel 4; N > 1: incl. the seam
+    exchange over NCCL), the stats sweep, the quality producer, BASELINE config 2 at N = 1,
+    re-integration after a pose update (config 5) and the drop-in manager."""
+    import torch
+    import torch.distributed as dist
+
+    from mast3r_slam_quality_dualtsdf_b200 import synth
+    from mast3r_slam_quality_dualtsdf_b200.tsdf import TSDFVolume
+
+    out = {}
+
+    def dev_ms(fn, reps=3):
+        best = None
+        res = None
+        for _ in range(reps):
+            torch.cuda.synchronize()
+            if world > 1:
+                dist.barrier()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            res = fn()
+            b.record()
+            torch.cuda.synchronize()
+            t = a.elapsed_time(b)
+            best = t if best is None else min(best, t)
+        if world > 1:
+            tt = torch.tensor([best], dtype=torch.float64, device=dev)
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            best = float(tt.item())
+        return best, res
+
+    def allsum(x):
+        if world == 1:
+            return x
+        t = torch.tensor([float(x)], dtype=torch.float64, device=dev)
+        dist.all_reduce(t)
+        return float(t.item())
+
+    # ---- extract: BASELINE configs[2] -- marching cubes of BOTH volumes
+    sharded = None
+    if world > 1:
+        from mast3r_slam_quality_dualtsdf_b200 import parallel
+
+        sharded = parallel.ShardedTSDFVolume(VOXEL, TRUNC, slab_width=slabs[2], bounds=bounds,
+                                             device=dev, volume_factory=lambda **kw: vol)
+    nblk = vol.counters()["blocks"]
+    seam_ms = 0.0
+    if sharded is not None:
+        seam_ms, halo = dev_ms(sharded.exchange_seams, reps=2)
+    extract = {"kernel": "mc_kernel<write>, one optimistic write pass per volume (incl. counter "
+                         "memset + D2H of the triangle count)", "volumes": {}}
+    tot_ms = 0.0
+    for which, name in ((0, "primary"), (1, "quality")):
+        verts = vol.extract_mesh(which)
+        n_tris = int(verts.shape[0] // 3)
+        buf = torch.empty(max(n_tris, 1) * 3, 3, dtype=torch.float32, device=dev)
+        del verts
+        mc_ms, _ = dev_ms(lambda w=which, b=buf: vol.extract_mesh(w, out=b))
+        tot_ms += mc_ms
+        vox_bytes = nblk * 512 * 24  # packed voxel (16 B) + hit counters (8 B)
+        alg = vox_bytes + n_tris * 36
+        extract["volumes"][name] = {
+            "ms": mc_ms, "triangles": allsum(n_tris), "blocks": allsum(nblk),
+            "triangles_per_s": allsum(n_tris) / (mc_ms * 1e-3),
+            "algorithmic_bytes_this_rank": alg,
+            "achieved_gbs": alg / (mc_ms * 1e-3) / 1e9, "frac": alg / (mc_ms * 1e-3) / 1e9 / peak}
+        del buf
+    extract["ms_both_volumes"] = tot_ms
+    extract["l2"] = "volume of this rank %.0f MB vs 126 MB L2" % (nblk * 512 * 24 / 1e6)
+    if sharded is not None:
+        extract["seam_exchange_ms"] = seam_ms
+        extract["seam_exchange"] = ("export_seam_blocks -> NCCL isend/irecv to the rank below -> "
+                                    "import_halo_blocks; max over ranks")
+    out["extract"] = extract
+    st_ms, st = dev_ms(lambda: vol.stats(0))
+    vox_bytes = nblk * 512 * 24
+    out["sweep"] = {"kernel": "stats_kernel", "ms": st_ms, "algorithmic_bytes_this_rank": vox_bytes,
+                    "achieved_gbs": vox_bytes / (st_ms * 1e-3) / 1e9,
+                    "frac": vox_bytes / (st_ms * 1e-3) / 1e9 / peak,
+                    "valid_voxels": allsum(st["valid_voxels"])}
+
+    # ---- reintegrate: BASELINE configs[4] -- after a backend solve every stored keyframe of
+    # the solve window is fused again at its new pose (global_manager.py:214-229 -> :71-79)
+    try:
+        out["reintegrate"] = reintegrate_section(args, dev, rank, world, bounds, slabs, dev_ms)
+    except Exception as e:  # noqa: BLE001
+        out["reintegrate"] = {"error": repr(e)}
+
+    if rank != 0:
+        return out
+    # ---- quality producer (SURVEY 8(f) rank 1): per-patch grids + classify on the device
+    try:
+        out["quality"] = quality_section(args, dev, dev_ms)
+    except Exception as e:  # noqa: BLE001
+        out["quality"] = {"error": repr(e)}
+    if world == 1:
+        try:
+            out["config2"] = config2_section(args, dev)
+        except Exception as e:  # noqa: BLE001
+            out["config2"] = {"error": repr(e)}
+        try:
+            out["manager"] = manager_section(args, dev)
+        except Exception as e:  # noqa: BLE001
+            out["manager"] = {"error": repr(e)}
+    return out
+
+
+def reintegrate_section(args, dev, rank, world, bounds, slabs, dev_ms):
+    """Config 5: 120 keyframes are ingested with ids (every rank keeps them in its store),
+    then a backend solve moves all of them: only the 32-byte poses travel (one broadcast),
+    every rank re-fuses its slabs from its own copy -- additive (the reference's semantics)
+    and replace (de-integrate at the old pose first)."""
+    import torch
+
+    from mast3r_slam_quality_dualtsdf_b200 import parallel
+
+    n_kf = 120
+    sh = parallel.ShardedTSDFVolume(VOXEL, TRUNC, slab_width=(slabs[2] if slabs else 256),
+                                    bounds=bounds, capacity_log2=TARGET["cap_log2"], device=dev)
+    for a in range(0, n_kf, 40):
+        kf = gen_batch(TARGET, a // 40, 40)
+        t = {k: torch.from_numpy(kf[k]).to(dev) for k in ("X", "C", "pose", "q")}
+        sh.integrate_keyframes(t["X"], t["C"], t["pose"], t["q"], MIN_CONF, H, W,
+                               broadcast=False, ids=list(range(a, a + 40)))
+    ids = list(range(n_kf))
+    poses = torch.stack([sh._store[i]["pose"] for i in ids]).clone()
+    poses[:, :3] += 0.004  # the solve shifted every keyframe by 4 mm
+    res = {}
+    for mode in ("additive", "replace"):
+        ms, _ = dev_ms(lambda m=mode: sh.reintegrate(ids, poses, src=0, mode=m), reps=2)
+        res[mode] = {"ms": ms, "keyframes_per_s": n_kf / (ms * 1e-3)}
+    res["keyframes"] = n_kf
+    res["what"] = ("ShardedTSDFVolume.reintegrate of all stored keyframes after a pose update: "
+                   "32 B per keyframe broadcast, pointmaps from every rank's own store")
+    del sh
+    return res
+
+
+def quality_section(args, dev, dev_ms):
+    import torch
+
+    from mast3r_slam_quality_dualtsdf_b200 import quality_core as qc
+
+    B = args.kf_per_launch
+    gq = torch.Generator(device="cpu").manual_seed(1)
+    qjob = {"H": H, "W": W, "kf_id": 0, "t_norm": torch.tensor(0.05), "theta": torch.tensor(0.1),
+            "valid_kf": (torch.rand(H * W, generator=gq) > 0.3).to(dev),
+            "r_pix": torch.rand(H * W, generator=gq).to(dev),
+            "Ck": (torch.rand(H * W, generator=gq) * 3).to(dev),
+            "Qk": (torch.rand(H * W, generator=gq) * 2).to(dev)}
+    qargs = dict(ps=16, alpha=0.8, b0=0.15, theta0=0.1745, C_thr=1.5, Q_thr=1.5, thr_zr=1.0,
+                 thr_zu=1.0, thr_dc=0.02, device=dev)
+    q_ms1, _ = dev_ms(lambda: [qc.compute_batch([qjob], **qargs) for _ in range(20)])
+    qjobs = [dict(qjob, kf_id=i) for i in range(B)]
+    qc.compute_batch(qjobs, **qargs)
+    q_ms, _ = dev_ms(lambda: [qc.compute_batch(qjobs, **qargs) for _ in range(5)])
+    st = {k: torch.stack([j[k] for j in qjobs]) for k in ("Ck", "Qk", "r_pix")}
+    st["valid"] = torch.stack([j["valid_kf"] for j in qjobs]).to(torch.uint8)
+    tn, th = (torch.stack([j[k] for j in qjobs]).to(dev) for k in ("t_norm", "theta"))
+    sargs = {k: v for k, v in qargs.items() if k != "device"}
+    run_st = lambda: qc.compute_stacked(st["Ck"], st["Qk"], st["r_pix"], st["valid"], tn, th,  # noqa: E731
+                                        None, H, W, device=dev, **sargs)
+    run_st()
+    q_ms_st, _ = dev_ms(lambda: [run_st() for _ in range(5)])
+    q_bytes = H * W * 13  # C, Q, r_pix float32 + valid u8, read once
+    return {"kernels": "quality_patch_kernel + quality_finish_batch_kernel (2 launches per batch)",
+            "keyframes_per_batch": B,
+            "us_per_keyframe": 1e3 * q_ms / 5 / B,
+            "us_per_keyframe_batch_of_1": 1e3 * q_ms1 / 20,
+            "us_per_keyframe_stacked_inputs": 1e3 * q_ms_st / 5 / B,
+            "stacked_gbs": q_bytes * B * 5 / (q_ms_st * 1e-3) / 1e9,
+            "algorithmic_bytes": q_bytes,
+            "note": "through quality_core.compute_batch incl. the stacking of the job tensors; a "
+                    "batch of 1 is launch/latency-bound"}
+
+
+def config2_section(args, dev):
+    """BASELINE configs[1]: the same 600-keyframe pass into 512^3 @ 5 mm (the round-1
+    headline workload), device-resident inputs, 3 timed passes."""
+    import torch
+
+    from mast3r_slam_quality_dualtsdf_b200 import synth
+    from mast3r_slam_quality_dualtsdf_b200.tsdf import TSDFVolume
+
+    wl = CONFIG2
+    lo, hi = synth.bounds_for(wl["scene"], VOXEL, wl["dim"])
+    v = TSDFVolume(VOXEL, TRUNC, capacity_log2=wl["cap_log2"], bounds=(lo, hi), device=dev)
+    B, L = args.kf_per_launch, args.launches_per_step
+    res = []
+    for l in range(L):
+        kf = gen_batch(wl, l, B)
+        res.append({k: torch.from_numpy(kf[k]).to(dev) for k in ("X", "C", "pose", "q")})
+
+    def one_pass():
+        for t in res:
+            v.integrate_keyframes(t["X"], t["C"], t["pose"], t["q"], MIN_CONF, H, W)
+
+    one_pass()
+    torch.cuda.synchronize()
+    c0 = v.counters()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(3):
+        one_pass()
+    b.record()
+    torch.cuda.synchronize()
+    c1 = v.counters()
+    ms = a.elapsed_time(b)
+    upd = (c1["updates_primary"] - c0["updates_primary"]) + \
+          (c1["updates_quality"] - c0["updates_quality"])
+    return {"workload": "BASELINE configs[1]: 600 keyframes 512x384 into 512^3 @ 5 mm, 1 B200",
+            "value": upd / (ms * 1e-3), "unit": "voxel updates/s",
+            "keyframes_per_s": 3 * B * L / (ms * 1e-3), "ms_per_launch": ms / (3 * L),
+            "blocks": c1["blocks"]}
+
+
+def manager_section(args, dev):
+    """keyframes/s through the drop-in TSDFGlobalManager (the API main.py:80-90 calls) with
+    device-resident keyframes, against the raw kernel rate of the line."""
+    import torch
+
+    from mast3r_slam_quality_dualtsdf_b200 import synth
+    from mast3r_slam_quality_dualtsdf_b200.tsdf import global_manager as gm
+
+    if not hasattr(gm, "bench_manager"):
+        return {"skipped": "global_manager.bench_manager not built yet"}
+    return gm.bench_manager(TARGET, dev, n_kf=ORBIT_TOTAL, H=H, W=W, gh=GH, gw=GW, voxel=VOXEL,
+                            trunc=TRUNC, min_conf=MIN_CONF, gen_batch=gen_batch)
 
 
 def emit(line):

@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define B200TSDF_ABI_VERSION 3
+#define B200TSDF_ABI_VERSION 4
 
 enum {
   B200TSDF_OK = 0,
@@ -125,6 +125,40 @@ int b200tsdf_deintegrate_keyframes(b200tsdf_t *h, const float *X_dev,
                                    int32_t W, int32_t gh, int32_t gw,
                                    float min_conf, double step_scale,
                                    void *stream);
+
+/* General form of the two calls above (same reference interface,
+ * global_manager.py:81-106) for a batch that is NOT one contiguous array:
+ *  - packed multi-GPU ingest: the batch is n = ceil(B / seg_kf)
+ *    segments, one per source rank, laid out exactly as the all-gather of the
+ *    ranks' packed shares delivers them: segment s starts seg_stride floats
+ *    after segment s-1 for ALL FOUR arrays (X_dev, C_dev, q_grid_dev, pose_dev
+ *    point into segment 0; inside a segment each array is contiguous over its
+ *    seg_kf keyframes).  seg_stride = 0: one contiguous batch.
+ *  - negate = 1: b200tsdf_deintegrate_keyframes.
+ *  - max_points > 0: tsdf_global.max_points_per_kf (global_manager.py:94-99,
+ *    config/base.yaml:116): of the pixels with C > min_conf at most max_points
+ *    per keyframe are fused.  The reference draws them with an unseeded
+ *    torch.randperm; here the choice is the max_points pixels with the smallest
+ *    value of a seeded bijective 32-bit hash of the pixel index (salted with
+ *    `seed` and the keyframe's id from kf_ids_dev, or its batch position when
+ *    kf_ids_dev is NULL), so it is reproducible and has exactly the reference's
+ *    sample count min(n_valid, max_points).  max_points <= 0: every valid pixel.
+ */
+typedef struct {
+  const float *X_dev, *C_dev, *q_grid_dev, *pose_dev;
+  int32_t B, H, W, gh, gw;
+  int32_t seg_kf;      /* keyframes per segment (ignored when seg_stride == 0) */
+  int64_t seg_stride;  /* floats between consecutive segments; 0 = contiguous  */
+  float min_conf;
+  int32_t negate;
+  double step_scale;
+  int32_t max_points;
+  int32_t reserved;
+  uint64_t seed;
+  const int64_t *kf_ids_dev; /* nullable, B entries */
+} b200tsdf_kf_batch;
+int b200tsdf_integrate_keyframes_ex(b200tsdf_t *h, const b200tsdf_kf_batch *batch,
+                                    void *stream);
 
 /* Same call with HOST buffers (pinned or pageable): copies H2D on `stream`
  * into an internal staging area, then fuses.  This is the entry the

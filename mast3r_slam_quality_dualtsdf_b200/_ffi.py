@@ -17,7 +17,8 @@ F32, F64 = 0, 1
 SYMBOLS = [
     "b200tsdf_last_error", "b200tsdf_abi_version", "b200tsdf_create", "b200tsdf_destroy",
     "b200tsdf_reset", "b200tsdf_integrate_points", "b200tsdf_integrate_keyframes",
-    "b200tsdf_integrate_keyframes_host", "b200tsdf_deintegrate_keyframes", "b200tsdf_counters", "b200tsdf_stats",
+    "b200tsdf_integrate_keyframes_host", "b200tsdf_deintegrate_keyframes",
+    "b200tsdf_integrate_keyframes_ex", "b200tsdf_counters", "b200tsdf_stats",
     "b200tsdf_query", "b200tsdf_export_voxels", "b200tsdf_export_blocks",
     "b200tsdf_extract_mesh", "b200tsdf_export_seam_blocks", "b200tsdf_import_halo_blocks",
     "b200tsdf_export_block_data", "b200tsdf_import_blocks",
@@ -36,6 +37,19 @@ class Config(C.Structure):
         ("key_min", C.c_int64 * 3), ("key_max", C.c_int64 * 3),
         ("device", C.c_int32), ("reserved", C.c_int32),
         ("slab_count", C.c_int32), ("slab_index", C.c_int32), ("slab_width", C.c_int64),
+    ]
+
+
+class KfBatch(C.Structure):
+    """b200tsdf_kf_batch (include/b200tsdf.h)."""
+    _fields_ = [
+        ("X_dev", C.c_void_p), ("C_dev", C.c_void_p), ("q_grid_dev", C.c_void_p),
+        ("pose_dev", C.c_void_p),
+        ("B", C.c_int32), ("H", C.c_int32), ("W", C.c_int32), ("gh", C.c_int32),
+        ("gw", C.c_int32), ("seg_kf", C.c_int32), ("seg_stride", C.c_int64),
+        ("min_conf", C.c_float), ("negate", C.c_int32), ("step_scale", C.c_double),
+        ("max_points", C.c_int32), ("reserved", C.c_int32), ("seed", C.c_uint64),
+        ("kf_ids_dev", C.c_void_p),
     ]
 
 
@@ -74,6 +88,7 @@ def lib():
                                                C.c_float, dbl, vp]
     L.b200tsdf_integrate_keyframes_host.argtypes = L.b200tsdf_integrate_keyframes.argtypes
     L.b200tsdf_deintegrate_keyframes.argtypes = L.b200tsdf_integrate_keyframes.argtypes
+    L.b200tsdf_integrate_keyframes_ex.argtypes = [vp, C.POINTER(KfBatch), vp]
     L.b200tsdf_counters.argtypes = [vp, vp, vp]
     L.b200tsdf_stats.argtypes = [vp, C.c_int, vp, vp, vp]
     L.b200tsdf_query.argtypes = [vp, C.c_int, vp, C.c_int, i64, vp, vp, vp, vp]

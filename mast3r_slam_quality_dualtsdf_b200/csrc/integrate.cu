@@ -10,6 +10,7 @@
 // 64-bit reduction for the two hit counters.  The fold is commutative
 // (DESIGN.md "the fold"), so no ordering between rays is needed.
 #include <stdlib.h>
+#include <string.h>
 
 #include "common.cuh"
 #include "ray.cuh"
@@ -297,20 +298,46 @@ __device__ __forceinline__ void fuse_pixels_warp(const VolumeDev &v, WarpCache &
 #define SC_ROW 40  // floats per staged C row: 32 + 8 pad
 
 struct KfArgs { // one keyframe batch (device pointers)
-  const float *X, *C, *qg, *poses;
+  const float *X, *C, *qg, *poses; // bases of segment 0
+  // packed multi-GPU ingest: the batch is n segments (one per source rank) of
+  // seg_kf keyframes each, seg_stride floats apart (0: one contiguous batch)
+  long long seg_stride;
+  int seg_kf;
   int H, W, gh, gw;
   float min_conf, step;
 };
+
+struct KfPtrs {
+  const float *X, *C, *qg, *P;
+};
+// Pointers of keyframe kf (pointmap, confidence, quality grid, pose).
+__device__ __forceinline__ KfPtrs kf_ptrs(const KfArgs &a, int kf) {
+  long long so = 0;
+  int loc = kf;
+  if (a.seg_stride != 0) {
+    const int seg = kf / a.seg_kf;
+    loc = kf - seg * a.seg_kf;
+    so = (long long)seg * a.seg_stride;
+  }
+  const long long npix = (long long)a.H * a.W;
+  KfPtrs p;
+  p.X = a.X + so + (long long)loc * npix * 3;
+  p.C = a.C + so + (long long)loc * npix;
+  p.qg = a.qg ? a.qg + so + (long long)loc * a.gh * a.gw : nullptr;
+  p.P = a.poses + so + (long long)loc * 8;
+  return p;
+}
 
 // thread 0: TMA bulk copies of tile (bx, by) of keyframe kf into shared memory
 __device__ __forceinline__ void tile_issue(const KfArgs &a, float *sX, float *sC, uint32_t bar,
                                            int bx, int by, int kf) {
   mbar_expect_tx(bar, TILE_H * (TILE_W * 12 + TILE_W * 4));
-  const long long p0 = (long long)kf * a.H * a.W + (long long)(by * TILE_H) * a.W + bx * TILE_W;
+  const KfPtrs k = kf_ptrs(a, kf);
+  const long long p0 = (long long)(by * TILE_H) * a.W + bx * TILE_W;
 #pragma unroll
   for (int row = 0; row < TILE_H; ++row) {
-    bulk_g2s(smem_u32(sX + row * SX_ROW), a.X + (p0 + (long long)row * a.W) * 3, TILE_W * 12, bar);
-    bulk_g2s(smem_u32(sC + row * SC_ROW), a.C + p0 + (long long)row * a.W, TILE_W * 4, bar);
+    bulk_g2s(smem_u32(sX + row * SX_ROW), k.X + (p0 + (long long)row * a.W) * 3, TILE_W * 12, bar);
+    bulk_g2s(smem_u32(sC + row * SC_ROW), k.C + p0 + (long long)row * a.W, TILE_W * 4, bar);
   }
 }
 
@@ -326,6 +353,7 @@ __device__ __forceinline__ void tile_consume(const VolumeDev &v, WarpCache &wc, 
   const int px = bx * TILE_W + tx, py = by * TILE_H + ty;
   float c = 0.f, x0 = 0.f, x1 = 0.f, x2 = 0.f;
   bool in_img = true;
+  const KfPtrs k = kf_ptrs(a, kf);
   if (TMA) { // host guarantees full tiles and 16-byte aligned rows
     mbar_wait(bar, phase);
     c = sC[ty * SC_ROW + tx];
@@ -334,17 +362,16 @@ __device__ __forceinline__ void tile_consume(const VolumeDev &v, WarpCache &wc, 
   } else {
     in_img = px < a.W && py < a.H;
     if (in_img) {
-      const long long pix = (long long)kf * a.H * a.W + (long long)py * a.W + px;
-      c = a.C[pix];
+      const long long pix = (long long)py * a.W + px;
+      c = k.C[pix];
       if (c > a.min_conf) {
-        const float *x = a.X + pix * 3;
+        const float *x = k.X + pix * 3;
         x0 = x[0], x1 = x[1], x2 = x[2];
       }
     }
   }
-  fuse_pixels_warp<BOUNDED, DIR>(v, wc, mc, a.poses + 8 * (long long)kf,
-                                 in_img && c > a.min_conf, c, x0, x1, x2, a.step, a.qg,
-                                 (long long)kf * a.gh * a.gw, a.gh, a.gw, px, py, tl);
+  fuse_pixels_warp<BOUNDED, DIR>(v, wc, mc, k.P, in_img && c > a.min_conf, c, x0, x1, x2, a.step,
+                                 k.qg, 0, a.gh, a.gw, px, py, tl);
 }
 
 // One CTA per tile (grid = tiles_x, tiles_y, keyframes): the single-GPU path.
@@ -387,16 +414,17 @@ __global__ void __launch_bounds__(256)
   // CTA = CLS_TILES consecutive tiles of one tile row; thread = one pixel of each
   const int lx = threadIdx.x & 31, py = blockIdx.y * TILE_H + (threadIdx.x >> 5);
   const int kf = blockIdx.z;
-  const float *P = a.poses + 8 * (long long)kf;
-  const long long row = (long long)kf * a.H * a.W + (long long)py * a.W;
+  const KfPtrs k = kf_ptrs(a, kf);
+  const float *P = k.P;
+  const long long row = (long long)py * a.W;
   float c[CLS_TILES], x0[CLS_TILES], x1[CLS_TILES], x2[CLS_TILES];
 #pragma unroll
   for (int t = 0; t < CLS_TILES; ++t) { // all loads first (the pass is latency-bound otherwise)
     const int px = (blockIdx.x * CLS_TILES + t) * TILE_W + lx;
     c[t] = 0.f, x0[t] = x1[t] = x2[t] = 0.f;
     if (px < a.W && py < a.H) {
-      c[t] = a.C[row + px];
-      const float *x = a.X + (row + px) * 3;
+      c[t] = k.C[row + px];
+      const float *x = k.X + (row + px) * 3;
       x0[t] = x[0], x1[t] = x[1], x2[t] = x[2];
     }
   }
@@ -592,11 +620,15 @@ extern "C" int b200tsdf_integrate_points(b200tsdf_t *h, const void *pts_dev, int
   return B200TSDF_OK;
 }
 
-static int fuse_keyframes(b200tsdf_t *h, const float *X_dev, const float *C_dev,
-                          const float *q_grid_dev, const float *pose_dev, int32_t B, int32_t H,
-                          int32_t W, int32_t gh, int32_t gw, float min_conf, double step_scale,
-                          void *stream, int negate) {
-  if (!h || B < 0 || H <= 0 || W <= 0 || (B > 0 && (!X_dev || !C_dev || !pose_dev))) {
+static int fuse_keyframes(b200tsdf_t *h, const b200tsdf_kf_batch *kb, void *stream) {
+  if (!h || !kb) {
+    b200_set_error("b200tsdf_integrate_keyframes: null argument");
+    return B200TSDF_E_INVALID;
+  }
+  const float *X_dev = kb->X_dev, *C_dev = kb->C_dev, *q_grid_dev = kb->q_grid_dev,
+              *pose_dev = kb->pose_dev;
+  const int32_t B = kb->B, H = kb->H, W = kb->W, gh = kb->gh, gw = kb->gw;
+  if (B < 0 || H <= 0 || W <= 0 || (B > 0 && (!X_dev || !C_dev || !pose_dev))) {
     b200_set_error("b200tsdf_integrate_keyframes: invalid argument");
     return B200TSDF_E_INVALID;
   }
@@ -605,20 +637,29 @@ static int fuse_keyframes(b200tsdf_t *h, const float *X_dev, const float *C_dev,
                    H, W);
     return B200TSDF_E_INVALID;
   }
+  if (kb->seg_stride != 0 && (kb->seg_kf <= 0 || kb->seg_stride < 0)) {
+    b200_set_error("b200tsdf_integrate_keyframes: bad segment layout (seg_kf %d, stride %lld)",
+                   kb->seg_kf, (long long)kb->seg_stride);
+    return B200TSDF_E_INVALID;
+  }
   if (B == 0) return B200TSDF_OK;
   cudaStream_t st = (cudaStream_t)stream;
   B200_CUDA(cudaSetDevice(h->cfg.device));
-  double step_d = h->cfg.voxel_size * step_scale;
+  double step_d = h->cfg.voxel_size * kb->step_scale;
   if (step_d < 1.0e-4) step_d = 1.0e-4;
   dim3 grid((unsigned)((W + TILE_W - 1) / TILE_W), (unsigned)((H + TILE_H - 1) / TILE_H),
             (unsigned)B);
   MarchConst mc = q_grid_dev ? make_consts(h, H / gh, W / gw) : make_consts(h);
-  mc.negate = negate;
-  const bool aligned = (((uintptr_t)X_dev & 15) == 0) && (((uintptr_t)C_dev & 15) == 0);
+  mc.negate = kb->negate ? 1 : 0;
+  // TMA bulk copies need 16-byte aligned global addresses: bases, per-keyframe and
+  // per-segment strides (W % 32 == 0 makes every row segment aligned within a keyframe)
+  const bool aligned = (((uintptr_t)X_dev & 15) == 0) && (((uintptr_t)C_dev & 15) == 0) &&
+                       ((kb->seg_stride & 3) == 0);
   const int mode = !use_bounded(h) ? 0 : (h->d.dir_on ? 2 : 1);
   // TMA staging needs full tiles and 16-byte aligned row segments
   const bool tma = (W % TILE_W == 0) && (H % TILE_H == 0) && aligned;
-  const KfArgs ka = {X_dev, C_dev, q_grid_dev, pose_dev, H, W, gh, gw, min_conf, (float)step_d};
+  const KfArgs ka = {X_dev, C_dev, q_grid_dev, pose_dev, (long long)kb->seg_stride,
+                     kb->seg_kf > 0 ? kb->seg_kf : 1, H, W, gh, gw, kb->min_conf, (float)step_d};
 #define DISPATCH_KF(LAUNCH)                                                                    \
   if (tma) {                                                                                   \
     if (mode == 0) LAUNCH(false, false, true);                                                 \
@@ -664,13 +705,26 @@ static int fuse_keyframes(b200tsdf_t *h, const float *X_dev, const float *C_dev,
   return B200TSDF_OK;
 }
 
+static b200tsdf_kf_batch plain_batch(const float *X_dev, const float *C_dev,
+                                     const float *q_grid_dev, const float *pose_dev, int32_t B,
+                                     int32_t H, int32_t W, int32_t gh, int32_t gw, float min_conf,
+                                     double step_scale, int negate) {
+  b200tsdf_kf_batch kb;
+  memset(&kb, 0, sizeof(kb));
+  kb.X_dev = X_dev, kb.C_dev = C_dev, kb.q_grid_dev = q_grid_dev, kb.pose_dev = pose_dev;
+  kb.B = B, kb.H = H, kb.W = W, kb.gh = gh, kb.gw = gw;
+  kb.min_conf = min_conf, kb.step_scale = step_scale, kb.negate = negate;
+  return kb;
+}
+
 extern "C" int b200tsdf_integrate_keyframes(b200tsdf_t *h, const float *X_dev, const float *C_dev,
                                             const float *q_grid_dev, const float *pose_dev,
                                             int32_t B, int32_t H, int32_t W, int32_t gh,
                                             int32_t gw, float min_conf, double step_scale,
                                             void *stream) {
-  return fuse_keyframes(h, X_dev, C_dev, q_grid_dev, pose_dev, B, H, W, gh, gw, min_conf,
-                        step_scale, stream, 0);
+  const b200tsdf_kf_batch kb =
+      plain_batch(X_dev, C_dev, q_grid_dev, pose_dev, B, H, W, gh, gw, min_conf, step_scale, 0);
+  return fuse_keyframes(h, &kb, stream);
 }
 
 extern "C" int b200tsdf_deintegrate_keyframes(b200tsdf_t *h, const float *X_dev,
@@ -678,8 +732,14 @@ extern "C" int b200tsdf_deintegrate_keyframes(b200tsdf_t *h, const float *X_dev,
                                               const float *pose_dev, int32_t B, int32_t H,
                                               int32_t W, int32_t gh, int32_t gw, float min_conf,
                                               double step_scale, void *stream) {
-  return fuse_keyframes(h, X_dev, C_dev, q_grid_dev, pose_dev, B, H, W, gh, gw, min_conf,
-                        step_scale, stream, 1);
+  const b200tsdf_kf_batch kb =
+      plain_batch(X_dev, C_dev, q_grid_dev, pose_dev, B, H, W, gh, gw, min_conf, step_scale, 1);
+  return fuse_keyframes(h, &kb, stream);
+}
+
+extern "C" int b200tsdf_integrate_keyframes_ex(b200tsdf_t *h, const b200tsdf_kf_batch *batch,
+                                               void *stream) {
+  return fuse_keyframes(h, batch, stream);
 }
 
 int b200_ensure_stage(b200tsdf *h, size_t bytes);

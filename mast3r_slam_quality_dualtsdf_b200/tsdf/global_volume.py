@@ -21,6 +21,41 @@ def _stream_ptr(device):
     return C.c_void_p(torch.cuda.current_stream(device).cuda_stream)
 
 
+def packed_layout(seg_kf, H, W, gh=0, gw=0):
+    """Float offsets of the four arrays inside one packed keyframe segment
+    [X seg_kf*H*W*3 | C seg_kf*H*W | q seg_kf*gh*gw | pose seg_kf*8], padded to a
+    multiple of 64 floats so every segment (and, with H*W % 4 == 0, every
+    keyframe row) stays 16-byte aligned for the TMA staging."""
+    n = H * W
+    o_c = seg_kf * n * 3
+    o_q = o_c + seg_kf * n
+    o_p = o_q + seg_kf * gh * gw
+    o_p = (o_p + 3) & ~3
+    seg_len = (o_p + seg_kf * 8 + 63) & ~63
+    return {"X": 0, "C": o_c, "q": o_q, "pose": o_p, "seg_len": seg_len}
+
+
+def pack_keyframes(X, Cf, poses, q_grid=None, out=None):
+    """One packed segment (see `packed_layout`) from the four keyframe arrays
+    (numpy or torch, host or device).  `out`: preallocated 1-D float32 tensor
+    (e.g. pinned host memory) of at least seg_len floats."""
+    X = torch.as_tensor(X)
+    k = int(X.shape[0])
+    n = int(X.shape[1])
+    q = None if q_grid is None else torch.as_tensor(q_grid).reshape(k, -1)
+    gcells = 0 if q is None else int(q.shape[1])
+    # H, W only enter through their product here
+    lay = packed_layout(k, n, 1, gcells, 1 if gcells else 0)
+    if out is None:
+        out = torch.zeros(lay["seg_len"], dtype=torch.float32, device=X.device)
+    out[lay["X"]:lay["X"] + k * n * 3].copy_(X.reshape(-1))
+    out[lay["C"]:lay["C"] + k * n].copy_(torch.as_tensor(Cf).reshape(-1))
+    if q is not None:
+        out[lay["q"]:lay["q"] + k * gcells].copy_(q.reshape(-1))
+    out[lay["pose"]:lay["pose"] + k * 8].copy_(torch.as_tensor(poses).reshape(-1))
+    return out
+
+
 class TSDFVolume:
     """Sparse dual TSDF volume (voxel-block hash on the GPU)."""
 
@@ -157,6 +192,32 @@ class TSDFVolume:
                           q_grid.data_ptr() if q_grid is not None else None, Pc.data_ptr(),
                           B, H, W, gh, gw, float(min_conf), float(step_scale),
                           _stream_ptr(self.device)), "integrate_keyframes")
+
+    def integrate_keyframes_packed(self, buf, n_seg, seg_kf, H, W, gh=0, gw=0, min_conf=0.05,
+                                   step_scale=0.5, negate=False):
+        """Fuse a batch that arrives as `n_seg` packed segments of `seg_kf`
+        keyframes each (one segment per source rank -- exactly what ONE
+        all-gather of the ranks' packed shares delivers, see `packed_layout`):
+        `buf` is a contiguous float32 device tensor of n_seg * seg_len floats.
+        gh = gw = 0: no quality grid in the segments (q = 1)."""
+        lay = packed_layout(seg_kf, H, W, gh, gw)
+        if buf.dtype != torch.float32 or not buf.is_cuda or not buf.is_contiguous():
+            raise ValueError("packed keyframes must be a contiguous float32 device tensor")
+        if buf.numel() < n_seg * lay["seg_len"]:
+            raise ValueError(f"packed buffer holds {buf.numel()} floats, {n_seg} segments need "
+                             f"{n_seg * lay['seg_len']}")
+        kb = _ffi.KfBatch()
+        base = buf.data_ptr()
+        kb.X_dev = base + 4 * lay["X"]
+        kb.C_dev = base + 4 * lay["C"]
+        kb.q_grid_dev = (base + 4 * lay["q"]) if gh and gw else None
+        kb.pose_dev = base + 4 * lay["pose"]
+        kb.B, kb.H, kb.W, kb.gh, kb.gw = n_seg * seg_kf, H, W, gh, gw
+        kb.seg_kf, kb.seg_stride = seg_kf, lay["seg_len"] if n_seg > 1 else 0
+        kb.min_conf, kb.negate, kb.step_scale = float(min_conf), int(bool(negate)), float(step_scale)
+        with self._lock:
+            _ffi.check(_ffi.lib().b200tsdf_integrate_keyframes_ex(
+                self._h, C.byref(kb), _stream_ptr(self.device)), "integrate_keyframes_ex")
 
     # ------------------------------------------------------------------
     # Query helpers

@@ -3,9 +3,9 @@
 mkdir -p gpurun_out
 for n in 1 2 4 8; do
   if [ $n -eq 1 ]; then
-    timeout 600 python bench.py --gpus 1 --steps 6 --warmup 3 --no-cpu-baseline > gpurun_out/scale_n$n.json 2> gpurun_out/scale_n$n.err
+    timeout 900 python bench.py --gpus 1 --steps 6 --warmup 2 --no-cpu-baseline > gpurun_out/scale_n$n.json 2> gpurun_out/scale_n$n.err
   else
-    timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port $((29500+n)) bench.py --gpus $n --steps 6 --warmup 3 > gpurun_out/scale_n$n.json 2> gpurun_out/scale_n$n.err
+    timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port $((29500+n)) bench.py --gpus $n --steps 6 --warmup 2 > gpurun_out/scale_n$n.json 2> gpurun_out/scale_n$n.err
   fi
   echo "N=$n rc=$?"; python -c "
 import json,sys

@@ -24,12 +24,19 @@ def test_library_exports_every_declared_symbol(built_lib):
     for name in _declared():
         assert hasattr(L, name), f"{name} missing from libb200tsdf.so"
     L.b200tsdf_abi_version.restype = ctypes.c_int
-    assert L.b200tsdf_abi_version() == 3
+    hdr = open(os.path.join(ROOT, "include", "b200tsdf.h")).read()
+    assert L.b200tsdf_abi_version() == int(re.search(r"B200TSDF_ABI_VERSION (\d+)", hdr).group(1))
 
 
 def test_config_struct_layout():
     # must match b200tsdf_config in include/b200tsdf.h: 4 doubles, 2 i32, 6 i64, 2 i32, 2 i32, 1 i64
     assert ctypes.sizeof(_ffi.Config) == 4 * 8 + 2 * 4 + 6 * 8 + 2 * 4 + 2 * 4 + 8
+
+
+def test_kf_batch_struct_layout():
+    # b200tsdf_kf_batch: 4 pointers, 6 i32, i64, f32, i32, f64, 2 i32, u64, pointer
+    assert ctypes.sizeof(_ffi.KfBatch) == 4 * 8 + 6 * 4 + 8 + 4 + 4 + 8 + 2 * 4 + 8 + 8
+    assert _ffi.KfBatch.seg_stride.offset == 56 and _ffi.KfBatch.step_scale.offset == 72
 
 
 def test_create_without_gpu_fails_loudly(built_lib):

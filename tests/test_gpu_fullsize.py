@@ -112,10 +112,10 @@ def _oracle_dual_threaded(kf, voxel, trunc):
 
 
 @pytest.mark.parametrize("name,n_kf,voxel,dim", [("config2_prefix", 16, 0.005, 512),
-                                                 ("config1", 4, 0.01, 256)])
+                                                 ("config1", 16, 0.01, 256)])
 def test_full_resolution_keyframes_match_oracle(cuda_device, name, n_kf, voxel, dim):
     """BASELINE config 2's 16-keyframe prefix (512x384 into 512^3 @
-    5 mm) and config 1's geometry (256^3 @ 10 mm), every pixel of every
+    5 mm) and config 1 (16 keyframes into 256^3 @ 10 mm), every pixel of every
     keyframe, dual volume, against the sequential oracle: voxel key sets and
     per-voxel update counts bit-exact, tsdf / weight within 1e-5, counters and
     stats equal."""
@@ -137,3 +137,79 @@ def test_full_resolution_keyframes_match_oracle(cuda_device, name, n_kf, voxel, 
     assert_volume_matches(vol.export(0), vp.export(), f"{name} primary")
     assert_volume_matches(vol.export(1), vq.export(), f"{name} quality")
     assert vol.stats(0) == vp.stats() and vol.stats(1) == vq.stats()
+
+
+# ---------------------------------------------------------------------------
+# north_star Target: 1024^3 @ 5 mm (bench.py's workload at every N)
+# ---------------------------------------------------------------------------
+TARGET_SCENE = {"kind": "room", "half": 2.4874}
+TARGET_DIM, TARGET_ORBIT = 1024, 1.2
+
+
+@pytest.fixture(scope="module")
+def target_case():
+    """8 full-resolution keyframes of bench.py's Target scene (z-up orbit of
+    radius 1.2 m in the 5 m room) and the two sequential oracle volumes."""
+    kfs = synth.make_keyframes(TARGET_SCENE, 8, H, W, seed=0, orbit_radius=TARGET_ORBIT, gh=24,
+                               gw=32, start=100, total=600, up_axis="z")
+    vp, vq, rays = _oracle_dual_threaded(kfs, VOXEL, TRUNC)
+    return kfs, vp, vq, rays
+
+
+def test_target_1024_single_gpu_matches_oracle(cuda_device, target_case):
+    """T1: the Target configuration on ONE GPU (capacity_log2 = 19 as in
+    bench.py), every pixel of 8 keyframes, against the sequential oracle."""
+    from mast3r_slam_quality_dualtsdf_b200.tsdf import TSDFVolume
+
+    kfs, vp, vq, rays = target_case
+    lo, hi = synth.bounds_for(TARGET_SCENE, VOXEL, TARGET_DIM)
+    vol = TSDFVolume(VOXEL, TRUNC, capacity_log2=19, bounds=(lo, hi), device=cuda_device)
+    t = {k: torch.from_numpy(kfs[k]).to(cuda_device) for k in ("X", "C", "pose", "q")}
+    vol.integrate_keyframes(t["X"], t["C"], t["pose"], t["q"], 0.05, H, W)
+    c = vol.counters()
+    assert c["rays"] == rays and c["dropped"] == 0 and c["overflow"] == 0
+    assert c["updates_primary"] == vp.events and c["updates_quality"] == vq.events
+    assert_volume_matches(vol.export(0), vp.export(), "target primary")
+    assert_volume_matches(vol.export(1), vq.export(), "target quality")
+    assert vol.stats(0) == vp.stats() and vol.stats(1) == vq.stats()
+
+
+@pytest.mark.parametrize("R", [2, 4, 8])
+def test_target_1024_slab_union_matches_oracle(cuda_device, target_case, R):
+    """The N > 1 bench configuration with one GPU emulating the R ranks in turn:
+    interleaved z-slabs of 1024 / (4 R) layers, the batch arriving as R packed
+    segments (what the all-gather delivers).  The union of the ranks' volumes
+    is the sequential oracle's volume: keys and counts exact, values 1e-5."""
+    from mast3r_slam_quality_dualtsdf_b200.tsdf import TSDFVolume
+    from mast3r_slam_quality_dualtsdf_b200.tsdf.global_volume import pack_keyframes, packed_layout
+
+    kfs, vp, vq, rays = target_case
+    lo, hi = synth.bounds_for(TARGET_SCENE, VOXEL, TARGET_DIM)
+    share = 8 // R
+    lay = packed_layout(share, H, W, 24, 32)
+    buf = torch.zeros(R * lay["seg_len"], dtype=torch.float32, device=cuda_device)
+    for r in range(R):
+        sl = slice(r * share, (r + 1) * share)
+        pack_keyframes(kfs["X"][sl], kfs["C"][sl], kfs["pose"][sl], kfs["q"][sl],
+                       out=buf[r * lay["seg_len"]:(r + 1) * lay["seg_len"]])
+    width = TARGET_DIM // (4 * R)
+    parts = {0: [], 1: []}
+    upd_p = upd_q = 0
+    for r in range(R):
+        vol = TSDFVolume(VOXEL, TRUNC, capacity_log2=18, bounds=(lo, hi), slabs=(R, r, width),
+                         device=cuda_device)
+        vol.integrate_keyframes_packed(buf, R, share, H, W, 24, 32, 0.05)
+        c = vol.counters()
+        assert c["rays"] == rays and c["overflow"] == 0
+        upd_p += c["updates_primary"]
+        upd_q += c["updates_quality"]
+        for which in (0, 1):
+            parts[which].append(vol.export(which))
+        vol.close()
+    assert upd_p == vp.events and upd_q == vq.events
+    for which, orc_vol, name in ((0, vp, "primary"), (1, vq, "quality")):
+        k = np.concatenate([p[0] for p in parts[which]])
+        order = np.lexsort((k[:, 2], k[:, 1], k[:, 0]))
+        got = tuple(np.concatenate([p[i] for p in parts[which]])[order] for i in range(4))
+        assert len(np.unique(got[0], axis=0)) == len(got[0]), "a voxel has two owners"
+        assert_volume_matches(got, orc_vol.export(), f"R={R} slab union {name}")
