@@ -359,6 +359,14 @@ int b200tsdf_quality_batch(const float *C_dev, const float *Q_dev, const float *
                            float *delta_cov_dev, int64_t *class_dev, float *priority_dev,
                            float *q_grid_dev, int32_t device, void *stream);
 
+/* ---- self-test -------------------------------------------------------------
+ * The fast keyframe path divides with one shared reciprocal per ray instead of
+ * three IEEE divisions (csrc/fuse_fast.cuh).  This entry runs that sequence
+ * against the IEEE division on n pseudo-random operand pairs shaped like its
+ * three uses and returns the number of quotients that differ (must be 0). */
+int b200tsdf_selftest_div(int32_t device, int64_t n, uint64_t seed, int64_t *mismatches_host,
+                          void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -18,7 +18,7 @@ SYMBOLS = [
     "b200tsdf_last_error", "b200tsdf_abi_version", "b200tsdf_create", "b200tsdf_destroy",
     "b200tsdf_reset", "b200tsdf_integrate_points", "b200tsdf_integrate_keyframes",
     "b200tsdf_integrate_keyframes_host", "b200tsdf_deintegrate_keyframes",
-    "b200tsdf_integrate_keyframes_ex", "b200tsdf_counters", "b200tsdf_stats",
+    "b200tsdf_integrate_keyframes_ex", "b200tsdf_selftest_div", "b200tsdf_counters", "b200tsdf_stats",
     "b200tsdf_query", "b200tsdf_export_voxels", "b200tsdf_export_blocks",
     "b200tsdf_extract_mesh", "b200tsdf_export_seam_blocks", "b200tsdf_import_halo_blocks",
     "b200tsdf_export_block_data", "b200tsdf_import_blocks",
@@ -89,6 +89,7 @@ def lib():
     L.b200tsdf_integrate_keyframes_host.argtypes = L.b200tsdf_integrate_keyframes.argtypes
     L.b200tsdf_deintegrate_keyframes.argtypes = L.b200tsdf_integrate_keyframes.argtypes
     L.b200tsdf_integrate_keyframes_ex.argtypes = [vp, C.POINTER(KfBatch), vp]
+    L.b200tsdf_selftest_div.argtypes = [i32, i64, C.c_uint64, vp, vp]
     L.b200tsdf_counters.argtypes = [vp, vp, vp]
     L.b200tsdf_stats.argtypes = [vp, C.c_int, vp, vp, vp]
     L.b200tsdf_query.argtypes = [vp, C.c_int, vp, C.c_int, i64, vp, vp, vp, vp]

@@ -16,6 +16,7 @@
 #include "ray.cuh"
 #include "march_fast.cuh"
 #include "fuse.cuh"
+#include "fuse_fast.cuh"
 #include "sim3.cuh"
 
 struct Acc {
@@ -241,6 +242,55 @@ __device__ __forceinline__ float band_reach_vox(const MarchConst &mc, float az, 
 // Certain when 1e-3 < len < 3e18; otherwise the exact ray_length decides.
 __device__ __forceinline__ bool surely_a_ray(float d2) { return d2 > 1.0e-6f && d2 < 1.0e37f; }
 
+// multi-GPU, per ray: does the band's z range [zl, zh] (voxel layers, already
+// widened by 2) reach a slab of this rank (`any`), lie in ONE owned slab (`all`),
+// and which z range holds every owned slab in reach (seam trim)?
+__device__ __forceinline__ void slab_band(const VolumeDev &v, float zl, float zh, bool &any,
+                                          bool &all, bool &trim, float &zt_lo, float &zt_hi) {
+  any = true, all = false, trim = false;
+  if (fabsf(zl) < 1.0e9f && fabsf(zh) < 1.0e9f) { // else: keep, per-voxel test decides
+    const int s_lo = ((int)floorf(zl) - v.slab_z0) >> v.slab_shift;
+    const int s_hi = ((int)floorf(zh) - v.slab_z0) >> v.slab_shift;
+    int need = v.slab_index - slab_owner_of(v, s_lo); // slabs to my first one at/after s_lo
+    if (need < 0) need += v.slab_count;
+    any = need <= s_hi - s_lo;
+    all = (s_hi == s_lo) && need == 0;
+#if FUSE_SEAM_TRIM
+    if (any && !all && fabsf(zl) < 4.0e6f && fabsf(zh) < 4.0e6f) {
+      const int s_own = s_lo + need, span = s_hi - s_own; // first / last owned slab in reach
+      const int s_last = s_own + (v.slab_mask >= 0 ? (span & ~v.slab_mask)
+                                                   : span - span % v.slab_count);
+      const float wz = (float)(1 << v.slab_shift);
+      zt_lo = fmaf((float)s_own, wz, (float)v.slab_z0);
+      zt_hi = fmaf((float)(s_last + 1), wz, (float)v.slab_z0);
+      trim = true;
+    }
+#endif
+  }
+}
+
+// Cold leg of the fast kernels: a warp in which some ray does not qualify for
+// the fast path (band near the bounds, operands out of range) re-does the
+// generic set-up of ray.cuh and runs march_warp.  Out of line, so that the fast
+// march is compiled without its registers; commits its own tally.
+template <bool BOUNDED, bool DIR>
+__device__ __noinline__ void march_generic_cold(const VolumeDev *vp, const MarchConst *mcp,
+                                                const float *P, bool have, float wx, float wy,
+                                                float wz, float c, float cq, float step,
+                                                uint32_t rays, uint32_t culled) {
+  __shared__ WarpCache wc_cold[DIR ? 1 : 8];
+  Ray<float> r = {};
+  if (have) {
+    float rx, ry, rz;
+    have = ray_length<float>(r, wx, wy, wz, P[0], P[1], P[2], rx, ry, rz);
+    if (have) ray_finish<float>(r, rx, ry, rz, P[0], P[1], P[2], step, mcp->trunc);
+  }
+  Tally tl = {rays, 0, 0, 0, 0, 0, culled};
+  march_warp<BOUNDED, DIR>(*vp, wc_cold[DIR ? 0 : (threadIdx.x >> 5)], *mcp, have, r, c, cq, true,
+                           tl);
+  commit_tally(*vp, tl);
+}
+
 // One pixel per lane: Sim3 act, slab cull, ray set-up, warp-converged march.
 // `take` = the pixel passed the confidence filter (global_manager.py:92).
 // The order keeps a rank's cost for rays of OTHER ranks minimal: world point,
@@ -290,6 +340,114 @@ __device__ __forceinline__ void fuse_pixels_warp(const VolumeDev &v, WarpCache &
     }
     march_warp<BOUNDED, DIR>(v, wc, mc, have, r, c, cq, true, tl);
   }
+}
+
+// The same for a bounded volume with a block directory: the warp takes the fast
+// path (fuse_fast.cuh) when every ray of it qualifies, else march_generic_cold.
+// Commits the warp's tally itself.
+__device__ __forceinline__ void fuse_pixels_warp_fast(const VolumeDev &v, const MarchConst &mc,
+                                                      const FastConst &fc, const float *P,
+                                                      bool take, float c, float x0, float x1,
+                                                      float x2, float step,
+                                                      const float *__restrict__ qg, int gh, int gw,
+                                                      int px, int py, float *d_cta) {
+  FastRay fr = {};
+  bool have = false, fast_ok = true;
+  float wx = 0.f, wy = 0.f, wz = 0.f;
+  Tally tl = {0, 0, 0, 0, 0, 0, 0};
+  if (take) {
+    const float ox = P[0], oy = P[1], oz = P[2];
+    sim3_act(P, x0, x1, x2, wx, wy, wz);
+    const float ax = wx - ox, ay = wy - oy, az = wz - oz;
+    const float d2 = fmaf(ax, ax, fmaf(ay, ay, az * az));
+    const bool zmiss = v.slab_count > 1 &&
+                       slab_zmiss_vox(v, wz * mc.inv_vs, band_reach_vox(mc, az, d2));
+    const bool counted = zmiss && surely_a_ray(d2);
+    if (counted) {
+      tl.rays += 1;
+      tl.culled += 1;
+    } else {
+      const int st = fast_ray_setup(fr, wx, wy, wz, ox, oy, oz, step, rcp_newton(step), mc.trunc,
+                                    fc.band_k);
+      if (st != 0) {
+        tl.rays += 1;
+        if (zmiss) {
+          tl.culled += 1;
+        } else {
+          have = true;
+          // qualifies: operands in range and the whole band inside the shrunk bounds
+          const float ux = fmaf(wx, fc.in_sc[0], fc.in_of[0]), uy = fmaf(wy, fc.in_sc[1], fc.in_of[1]),
+                      uz = fmaf(wz, fc.in_sc[2], fc.in_of[2]);
+          fast_ok = st == 1 && fmaxf(fabsf(ux), fmaxf(fabsf(uy), fabsf(uz))) < 1.0f;
+        }
+      }
+    }
+  }
+  // a warp whose rays were all filtered / culled skips the march altogether
+  if (!__any_sync(0xFFFFFFFFu, have)) {
+    commit_tally(v, tl);
+    return;
+  }
+  float cq = c;
+  if (qg) { // nearest-neighbour upsample of the per-patch quality weight
+    int gy = mc.cell_h_shift >= 0 ? py >> mc.cell_h_shift : py / mc.cell_h;
+    int gx = mc.cell_w_shift >= 0 ? px >> mc.cell_w_shift : px / mc.cell_w;
+    gy = min(gy, gh - 1), gx = min(gx, gw - 1);
+    cq = c * __ldg(qg + (long long)gy * gw + gx);
+  }
+  if (__builtin_expect(!__all_sync(0xFFFFFFFFu, !have || fast_ok), 0)) {
+    march_generic_cold<true, true>(&v, &mc, P, have, wx, wy, wz, c, cq, step, tl.rays, tl.culled);
+    return;
+  }
+  uint32_t cp = (have && c > 0.0f) ? 1u : 0u; // :75  weight <= 0 -> return
+  uint32_t cqf = (have && cq > 0.0f) ? 1u : 0u;
+  bool live = (cp | cqf) != 0;
+  int i0 = 0, cnt = 0;
+  bool slab_check = false;
+  if (v.slab_count > 1) {
+    bool any = true, all = true, trim = false;
+    float zt_lo = 0.f, zt_hi = 0.f;
+    const float oz = P[2];
+    if (live) {
+      const float d0 = fmaxf(fr.len - mc.trunc, 0.0f);
+      const float az0 = fmaf(d0, fr.dz, oz) * mc.inv_vs, az1 = fmaf(fr.maxd, fr.dz, oz) * mc.inv_vs;
+      slab_band(v, fminf(az0, az1) - 2.0f, fmaxf(az0, az1) + 2.0f, any, all, trim, zt_lo, zt_hi);
+      if (!any) { // the band misses every slab of this rank
+        live = false;
+        tl.culled += 1;
+      }
+    }
+    slab_check = !__all_sync(0xFFFFFFFFu, all || !live);
+    if (live) {
+      cnt = fast_band(fr, mc.trunc, i0);
+#if FUSE_SEAM_TRIM
+      if (trim && cnt > 0) { // see march_warp: everything cut lies in a foreign slab
+        const float g = fr.dz * fr.lstep * mc.inv_vs, zq0 = oz * mc.inv_vs;
+        if (fabsf(g) >= 4.0e-3f) {
+          const float ig = 1.0f / g;
+          const float ia = (zt_lo - zq0) * ig, ib = (zt_hi - zq0) * ig;
+          const float flo = fmaxf(fminf(ia, ib), -1.0e9f), fhi = fminf(fmaxf(ia, ib), 1.0e9f);
+          const int i1 = i0 + cnt - 1;
+          const int j0 = max(i0, (int)floorf(flo) - 1), j1 = min(i1, (int)ceilf(fhi) + 1);
+          i0 = j0;
+          cnt = j1 >= j0 ? j1 - j0 + 1 : 0;
+        }
+      }
+#endif
+    }
+    if (!live) cp = cqf = 0u, cnt = 0;
+  } else {
+    if (live) cnt = fast_band(fr, mc.trunc, i0);
+  }
+  // rays and enumerated samples are final here: commit them now so that the
+  // march carries no tally registers (its drops / overflows are committed after)
+  tl.ev_p += (uint32_t)cnt * cp;
+  tl.ev_q += (uint32_t)cnt * cqf;
+  commit_tally(v, tl);
+  tl = Tally{0, 0, 0, 0, 0, 0, 0};
+  march_warp_fast(v, mc, fc, fr, P, i0, cnt, cp ? c : 0.0f, cqf ? cq : 0.0f, cp, cqf, slab_check,
+                  d_cta, tl);
+  commit_tally(v, tl);
 }
 
 #define TILE_W 32
@@ -345,7 +503,8 @@ __device__ __forceinline__ void tile_issue(const KfArgs &a, float *sX, float *sC
 // the volume, so their reductions share 32-byte sectors.
 template <bool BOUNDED, bool DIR, bool TMA>
 __device__ __forceinline__ void tile_consume(const VolumeDev &v, WarpCache &wc, const KfArgs &a,
-                                             const MarchConst &mc, const float *sX,
+                                             const MarchConst &mc, const FastConst &fc,
+                                             float *d_sh, const float *sX,
                                              const float *sC, uint32_t bar, uint32_t phase,
                                              int bx, int by, int kf, Tally &tl) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -370,15 +529,24 @@ __device__ __forceinline__ void tile_consume(const VolumeDev &v, WarpCache &wc, 
       }
     }
   }
-  fuse_pixels_warp<BOUNDED, DIR>(v, wc, mc, k.P, in_img && c > a.min_conf, c, x0, x1, x2, a.step,
-                                 k.qg, 0, a.gh, a.gw, px, py, tl);
+  if (BOUNDED && DIR && fc.enabled) { // commits its own tally
+    fuse_pixels_warp_fast(v, mc, fc, k.P, in_img && c > a.min_conf, c, x0, x1, x2, a.step, k.qg,
+                          a.gh, a.gw, px, py, d_sh);
+  } else {
+    fuse_pixels_warp<BOUNDED, DIR>(v, wc, mc, k.P, in_img && c > a.min_conf, c, x0, x1, x2, a.step,
+                                   k.qg, 0, a.gh, a.gw, px, py, tl);
+  }
 }
 
 // One CTA per tile (grid = tiles_x, tiles_y, keyframes): the single-GPU path.
 template <bool BOUNDED, bool DIR, bool TMA>
 __global__ void __launch_bounds__(256, FUSE_MINB)
-    integrate_keyframes_kernel(VolumeDev v, KfArgs a, MarchConst mc) {
+    integrate_keyframes_kernel(const __grid_constant__ VolumeDev v, const __grid_constant__ KfArgs a,
+                               const __grid_constant__ MarchConst mc,
+                               const __grid_constant__ FastConst fc) {
   __shared__ WarpCache wcs[DIR ? 1 : 8];
+  __shared__ float d_shs[(BOUNDED && DIR) ? 8 * 96 : 1];
+  float *const d_sh = d_shs;
   __shared__ __align__(128) float sX[TMA ? TILE_H * SX_ROW : 4];
   __shared__ __align__(128) float sC[TMA ? TILE_H * SC_ROW : 4];
   __shared__ __align__(8) unsigned long long s_bar;
@@ -391,7 +559,7 @@ __global__ void __launch_bounds__(256, FUSE_MINB)
   if (!DIR) warp_cache_init(wc);
   if (TMA) __syncthreads(); // mbarrier init visible to the waiters
   Tally tl = {0, 0, 0, 0, 0, 0, 0};
-  tile_consume<BOUNDED, DIR, TMA>(v, wc, a, mc, sX, sC, bar, 0, blockIdx.x, blockIdx.y,
+  tile_consume<BOUNDED, DIR, TMA>(v, wc, a, mc, fc, d_sh, sX, sC, bar, 0, blockIdx.x, blockIdx.y,
                                   blockIdx.z, tl);
   commit_tally(v, tl);
 }
@@ -478,10 +646,15 @@ __global__ void __launch_bounds__(256)
 // registers and never waits on a value it requested in the same iteration).
 template <bool BOUNDED, bool DIR, bool TMA>
 __global__ void __launch_bounds__(256, FUSE_MINB)
-    integrate_keyframes_listed_kernel(VolumeDev v, KfArgs a, MarchConst mc,
+    integrate_keyframes_listed_kernel(const __grid_constant__ VolumeDev v,
+                                      const __grid_constant__ KfArgs a,
+                                      const __grid_constant__ MarchConst mc,
+                                      const __grid_constant__ FastConst fc,
                                       const int *__restrict__ list, unsigned int *sched,
                                       int tiles_x, int tiles_y) {
   __shared__ WarpCache wcs[DIR ? 1 : 8];
+  __shared__ float d_shs[(BOUNDED && DIR) ? 8 * 96 : 1];
+  float *const d_sh = d_shs;
   __shared__ __align__(128) float sX[2][TMA ? TILE_H * SX_ROW : 4];
   __shared__ __align__(128) float sC[2][TMA ? TILE_H * SC_ROW : 4];
   __shared__ __align__(8) unsigned long long s_bar[2];
@@ -524,8 +697,8 @@ __global__ void __launch_bounds__(256, FUSE_MINB)
     const int kf = tile / tiles_kf, rem = tile - kf * tiles_kf;
     const int by = rem / tiles_x;
     Tally tl = {0, 0, 0, 0, 0, 0, 0};
-    tile_consume<BOUNDED, DIR, TMA>(v, wc, a, mc, sX[b], sC[b], smem_u32(&s_bar[b]), (k >> 1) & 1u,
-                                    rem - by * tiles_x, by, kf, tl);
+    tile_consume<BOUNDED, DIR, TMA>(v, wc, a, mc, fc, d_sh, sX[b], sC[b], smem_u32(&s_bar[b]),
+                                    (k >> 1) & 1u, rem - by * tiles_x, by, kf, tl);
     commit_tally(v, tl);
   }
 }
@@ -563,6 +736,39 @@ static MarchConst make_consts(const b200tsdf *h, int cell_h = 1, int cell_w = 1)
   mc.use_dir = h->d.dir_on;
   mc.negate = 0;
   return mc;
+}
+
+// Launch constants of the fast path (fuse_fast.cuh); enabled for bounded volumes
+// with a block directory whose slot offsets fit 32 bits.
+static FastConst make_fast_consts(const b200tsdf *h, double step_d) {
+  FastConst fc;
+  memset(&fc, 0, sizeof(fc));
+  static const int off = [] {
+    const char *e = getenv("B200TSDF_NO_FAST"); // A/B knob: 1 = always the generic march
+    return e ? atoi(e) : 0;
+  }();
+  const VolumeDev &d = h->d;
+  const double vs = (double)(float)h->cfg.voxel_size, tr = (double)(float)h->cfg.truncation;
+  bool ok = !off && d.bounded && d.dir_on && h->cfg.capacity_log2 <= 23 && step_d > 1.0e-6 &&
+            step_d < 1.0e6 && vs > 1.0e-6 && vs < 1.0e6;
+  for (int a = 0; a < 3 && ok; ++a) {
+    // world coordinates whose band (+- trunc) stays 3 voxels inside the key bounds
+    const double lo = ((double)d.kmin[a] + 3.0) * vs + tr, hi = ((double)d.kmax[a] - 3.0) * vs - tr;
+    if (!(hi > lo)) {
+      ok = false;
+      break;
+    }
+    fc.in_sc[a] = (float)(2.0 / (hi - lo) * (1.0 - 1.0e-6));
+    fc.in_of[a] = (float)(-(hi + lo) / (hi - lo));
+  }
+  fc.band_k = (int)ceil(2.0 * tr / step_d) + 1;
+  if (fc.band_k > (1 << 20)) ok = false;
+  fc.nx = (uint32_t)d.dir_n[0], fc.ny = (uint32_t)d.dir_n[1];
+  const uint32_t m3 = (uint32_t)MARCH_KEY_MAGIC_BITS >> 3;
+  fc.dir_c = ((m3 + (uint32_t)d.dir_b0[2]) * fc.ny + (m3 + (uint32_t)d.dir_b0[1])) * fc.nx +
+             (m3 + (uint32_t)d.dir_b0[0]);
+  fc.enabled = ok ? 1 : 0;
+  return fc;
 }
 
 extern "C" int b200tsdf_integrate_points(b200tsdf_t *h, const void *pts_dev, int dtype,
@@ -651,6 +857,7 @@ static int fuse_keyframes(b200tsdf_t *h, const b200tsdf_kf_batch *kb, void *stre
             (unsigned)B);
   MarchConst mc = q_grid_dev ? make_consts(h, H / gh, W / gw) : make_consts(h);
   mc.negate = kb->negate ? 1 : 0;
+  const FastConst fc = make_fast_consts(h, step_d);
   // TMA bulk copies need 16-byte aligned global addresses: bases, per-keyframe and
   // per-segment strides (W % 32 == 0 makes every row segment aligned within a keyframe)
   const bool aligned = (((uintptr_t)X_dev & 15) == 0) && (((uintptr_t)C_dev & 15) == 0) &&
@@ -692,11 +899,11 @@ static int fuse_keyframes(b200tsdf_t *h, const b200tsdf_kf_batch *kb, void *stre
     const unsigned ctas = (unsigned)(n_tiles < cap ? n_tiles : cap);
 #define LAUNCH_LISTED(BD, DR, TM)                                                              \
   integrate_keyframes_listed_kernel<BD, DR, TM><<<ctas, 256, 0, st>>>(                          \
-      h->d, ka, mc, h->tile_list, h->sched, (int)grid.x, (int)grid.y)
+      h->d, ka, mc, fc, h->tile_list, h->sched, (int)grid.x, (int)grid.y)
     DISPATCH_KF(LAUNCH_LISTED)
 #undef LAUNCH_LISTED
   } else {
-#define LAUNCH_KF(BD, DR, TM) integrate_keyframes_kernel<BD, DR, TM><<<grid, 256, 0, st>>>(h->d, ka, mc)
+#define LAUNCH_KF(BD, DR, TM) integrate_keyframes_kernel<BD, DR, TM><<<grid, 256, 0, st>>>(h->d, ka, mc, fc)
     DISPATCH_KF(LAUNCH_KF)
 #undef LAUNCH_KF
   }
@@ -802,5 +1009,71 @@ extern "C" int b200tsdf_integrate_keyframes_host(b200tsdf_t *h, const float *X_h
                                       (int32_t)nb, H, W, gh, gw, min_conf, step_scale, st);
     if (rc) return rc;
   }
+  return B200TSDF_OK;
+}
+
+// ---------------------------------------------------------------- self-test
+// The shared-reciprocal division of fuse_fast.cuh must give the IEEE quotient
+// for every operand pair in its documented range; this kernel compares it with
+// __fdiv_rn on pseudo-random operands shaped like the three uses in
+// fast_ray_setup (component / length, maxd / step, maxd / (n - 1)).
+__device__ __forceinline__ uint64_t st_mix(uint64_t x) {
+  x ^= x >> 33, x *= 0xff51afd7ed558ccdull, x ^= x >> 33, x *= 0xc4ceb9fe1a85ec53ull, x ^= x >> 33;
+  return x;
+}
+__device__ __forceinline__ float st_logu(uint64_t h, float lo_exp, float hi_exp) {
+  // 2^U(lo, hi) with a random 23-bit mantissa
+  const float e = lo_exp + (hi_exp - lo_exp) * (float)((h >> 40) & 0xFFFF) * (1.0f / 65536.0f);
+  const float m = 1.0f + (float)(h & 0x7FFFFF) * (1.0f / 8388608.0f);
+  return exp2f(floorf(e)) * m;
+}
+__global__ void selftest_div_kernel(uint64_t seed, long long n, unsigned long long *bad) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const uint64_t h0 = st_mix(seed + 3 * (uint64_t)i), h1 = st_mix(h0 + 1), h2 = st_mix(h1 + 2);
+  float a, b;
+  switch (i % 3) {
+    case 0: // direction component / length: |a| <= b
+      b = st_logu(h0, -13.0f, 56.0f);
+      a = b * (float)((h1 >> 11) * (1.0 / 9007199254740992.0));
+      if (h2 & 1) a = -a;
+      if (fabsf(a) < 1.0e-18f) a = 1.0e-18f * 1.5f;
+      break;
+    case 1: // maxd / step
+      b = st_logu(h0, -13.0f, 0.0f);
+      a = st_logu(h1, -13.0f, 56.0f);
+      break;
+    default: // maxd / (n - 1): integer divisor
+      b = (float)(1 + (h0 % 1073741823ull));
+      a = st_logu(h1, -13.0f, 56.0f);
+      break;
+  }
+  const float q = div_rn_r1(a, b, rcp_newton(b));
+  const float ref = __fdiv_rn(a, b);
+  if (__float_as_uint(q) != __float_as_uint(ref) && !(q == 0.0f && ref == 0.0f))
+    atomicAdd(bad, 1ull);
+}
+
+extern "C" int b200tsdf_selftest_div(int32_t device, int64_t n, uint64_t seed,
+                                     int64_t *mismatches_host, void *stream) {
+  if (n < 0 || !mismatches_host) {
+    b200_set_error("b200tsdf_selftest_div: invalid argument");
+    return B200TSDF_E_INVALID;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  B200_CUDA(cudaSetDevice(device));
+  unsigned long long *bad = nullptr;
+  B200_CUDA(cudaMalloc(&bad, sizeof(*bad)));
+  B200_CUDA(cudaMemsetAsync(bad, 0, sizeof(*bad), st));
+  if (n > 0) selftest_div_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(seed, (long long)n, bad);
+  unsigned long long hbad = 0;
+  cudaError_t e = cudaMemcpyAsync(&hbad, bad, sizeof(hbad), cudaMemcpyDeviceToHost, st);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+  cudaFree(bad);
+  if (e != cudaSuccess) {
+    b200_set_error("b200tsdf_selftest_div: %s", cudaGetErrorString(e));
+    return B200TSDF_E_CUDA;
+  }
+  *mismatches_host = (int64_t)hbad;
   return B200TSDF_OK;
 }

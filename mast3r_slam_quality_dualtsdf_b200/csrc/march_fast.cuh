@@ -42,8 +42,11 @@ __device__ __forceinline__ void commit_tally(const VolumeDev &v, Tally tl) {
   // nothing to report (warp-uniform); a warp can hold updates of rays it did not
   // count itself once rays are re-dealt between warps
   if (tl.rays == 0 && !any_lost && !any_culled && !any_ev) return;
-  tl.ev_p = any_ev ? __reduce_add_sync(0xFFFFFFFFu, tl.ev_p - tl.drop_p) : 0u;
-  tl.ev_q = any_ev ? __reduce_add_sync(0xFFFFFFFFu, tl.ev_q - tl.drop_q) : 0u;
+  // applied = enumerated - dropped; signed, because the fast path commits the
+  // enumerated samples before the march and the drops after it
+  const bool any_app = any_ev || any_lost;
+  const int app_p = any_app ? __reduce_add_sync(0xFFFFFFFFu, (int)tl.ev_p - (int)tl.drop_p) : 0;
+  const int app_q = any_app ? __reduce_add_sync(0xFFFFFFFFu, (int)tl.ev_q - (int)tl.drop_q) : 0;
   uint32_t dropped = 0;
   tl.overflow = 0;
   if (any_lost) { // out-of-bounds / foreign-slab drops, hash overflow
@@ -60,8 +63,8 @@ __device__ __forceinline__ void commit_tally(const VolumeDev &v, Tally tl) {
   {
     unsigned long long *ctr = ctr_replica(v);
     if (tl.rays) atomicAdd(ctr + CTR_RAYS, (unsigned long long)tl.rays);
-    if (tl.ev_p) atomicAdd(ctr + CTR_EV_P, (unsigned long long)tl.ev_p);
-    if (tl.ev_q) atomicAdd(ctr + CTR_EV_Q, (unsigned long long)tl.ev_q);
+    if (app_p) atomicAdd(ctr + CTR_EV_P, (unsigned long long)(long long)app_p);
+    if (app_q) atomicAdd(ctr + CTR_EV_Q, (unsigned long long)(long long)app_q);
     if (any_rare) {
       if (dropped) atomicAdd(ctr + CTR_DROPPED, (unsigned long long)dropped);
       if (tl.overflow) atomicAdd(ctr + CTR_OVERFLOW, (unsigned long long)tl.overflow);

@@ -1,6 +1,20 @@
 #!/bin/bash
-# A/B of kernel build variants (build/variants/lib_*.so) on the bench workload.
+# A/B of kernel build variants on the bench workload (one gpurun call).
+#   build/variants/lib_*.so   : python -c "from mast3r_slam_quality_dualtsdf_b200 import build; build.build_variant('minb3', ['FUSE_MINB=3'])"
+#   env knobs                 : B200TSDF_NO_FAST=1 (generic march only)
+mkdir -p gpurun_out
+run() { # name, env...
+  local name=$1; shift
+  env "$@" timeout 600 python bench.py --steps 6 --warmup 2 --launches-per-step 5 --no-cpu-baseline --no-sections 2>gpurun_out/ab_$name.err | python -c "
+import sys,json
+try:
+    d=json.loads(sys.stdin.read()); print('$name', 'launch_ms', round(d['roofline']['launch_ms'],4), 'value %.4e'%d['value'], 'e2e_ms', round(d['e2e']['ms_per_step'],3), d['clocks']['sm_mhz'])
+except Exception as e: print('$name failed', e)"
+}
+run default X=1
+run nofast B200TSDF_NO_FAST=1
 for f in build/variants/lib_*.so; do
+  [ -e "$f" ] || continue
   n=$(basename $f .so)
-  B200TSDF_LIB=$PWD/$f timeout 300 python bench.py --steps 10 --warmup 3 --no-cpu-baseline 2>/dev/null | python -c "import sys,json; d=json.loads(sys.stdin.read()); print('$n', 'ms_per_step', round(d['ms_per_step'],4), 'value', '%.3e'%d['value'], 'e2e_ms', round(d['e2e']['ms_per_step'],3))"
+  run $n B200TSDF_LIB=$PWD/$f
 done
