@@ -160,9 +160,12 @@ typedef struct {
 int b200tsdf_integrate_keyframes_ex(b200tsdf_t *h, const b200tsdf_kf_batch *batch,
                                     void *stream);
 
-/* Same call with HOST buffers (pinned or pageable): copies H2D on `stream`
- * into an internal staging area, then fuses.  This is the entry the
- * reference-facing plugin uses when keyframes live on the host. */
+/* Same call with HOST buffers (pinned or pageable): copies H2D in chunks on an
+ * internal copy stream into a staging area while the chunks already there are
+ * fused on `stream`.  Returns once every copy has completed -- the host buffers
+ * may be reused or freed right away -- while the fuse itself stays queued on
+ * `stream`.  This is the entry the reference-facing plugin uses when keyframes
+ * live on the host. */
 int b200tsdf_integrate_keyframes_host(b200tsdf_t *h, const float *X_host,
                                       const float *C_host,
                                       const float *q_grid_host,
@@ -171,7 +174,9 @@ int b200tsdf_integrate_keyframes_host(b200tsdf_t *h, const float *X_host,
                                       int32_t gw, float min_conf,
                                       double step_scale, void *stream);
 
-/* Counters since create/reset (synchronises the stream).
+/* Counters since create/reset (synchronises the stream).  Returns
+ * B200TSDF_E_CAPACITY (with out_host filled) when the voxel-block hash
+ * overflowed, i.e. updates were lost: out[5] > 0.
  *  out[0] rays fused        out[1] voxel updates, primary volume
  *  out[2] voxel updates, quality volume   out[3] allocated voxel blocks
  *  out[4] updates dropped (outside bounds / foreign slab)

@@ -12,6 +12,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("B200TSDF_LIB") or os.path.join(_HERE, "libb200tsdf.so")
 
 F32, F64 = 0, 1
+E_INVALID, E_CUDA, E_CAPACITY, E_NOMEM = -1, -2, -3, -4
 
 # every symbol include/b200tsdf.h declares (tests check the .so exports all)
 SYMBOLS = [

@@ -88,6 +88,9 @@ struct b200tsdf {
   size_t tile_cap;
   unsigned int *sched;
   int sm_count;
+  // max_points_per_kf: per-keyframe {hash threshold, salt} of the current batch
+  void *sub_thr;
+  size_t sub_cap;
 };
 
 // ---------------------------------------------------------------- hashing

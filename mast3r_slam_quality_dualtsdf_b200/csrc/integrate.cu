@@ -463,7 +463,30 @@ struct KfArgs { // one keyframe batch (device pointers)
   int seg_kf;
   int H, W, gh, gw;
   float min_conf, step;
+  // tsdf_global.max_points_per_kf: per keyframe {hash threshold, salt}; a valid pixel
+  // is fused iff sub_hash(pixel, salt) <= threshold (nullptr: every valid pixel)
+  const uint2 *sub;
 };
+
+// Seeded bijective 32-bit hash of the pixel index (murmur3 finaliser: xor-shifts
+// and odd multiplications are bijections of Z_2^32, so two pixels of a keyframe
+// never tie and "the max_points smallest hashes" is an exact-size choice).
+__host__ __device__ __forceinline__ uint32_t sub_fmix(uint32_t x) {
+  x ^= x >> 16, x *= 0x85ebca6bu, x ^= x >> 13, x *= 0xc2b2ae35u, x ^= x >> 16;
+  return x;
+}
+__host__ __device__ __forceinline__ uint32_t sub_hash(uint32_t pix, uint32_t salt) {
+  return sub_fmix(pix * 0x9E3779B1u + salt);
+}
+__host__ __device__ __forceinline__ uint32_t sub_salt(uint64_t seed, uint64_t kf_id) {
+  return sub_fmix((uint32_t)seed ^ sub_fmix((uint32_t)kf_id + 0x9E3779B9u * (uint32_t)(seed >> 32)) ^
+                  sub_fmix((uint32_t)(kf_id >> 32) + 0x7F4A7C15u));
+}
+__device__ __forceinline__ bool sub_take(const KfArgs &a, int kf, int pix) {
+  if (!a.sub) return true;
+  const uint2 ts = __ldg(a.sub + kf);
+  return sub_hash((uint32_t)pix, ts.y) <= ts.x;
+}
 
 struct KfPtrs {
   const float *X, *C, *qg, *P;
@@ -529,12 +552,13 @@ __device__ __forceinline__ void tile_consume(const VolumeDev &v, WarpCache &wc, 
       }
     }
   }
+  const bool take = in_img && c > a.min_conf && sub_take(a, kf, py * a.W + px);
   if (BOUNDED && DIR && fc.enabled) { // commits its own tally
-    fuse_pixels_warp_fast(v, mc, fc, k.P, in_img && c > a.min_conf, c, x0, x1, x2, a.step, k.qg,
-                          a.gh, a.gw, px, py, d_sh);
+    fuse_pixels_warp_fast(v, mc, fc, k.P, take, c, x0, x1, x2, a.step, k.qg, a.gh, a.gw, px, py,
+                          d_sh);
   } else {
-    fuse_pixels_warp<BOUNDED, DIR>(v, wc, mc, k.P, in_img && c > a.min_conf, c, x0, x1, x2, a.step,
-                                   k.qg, 0, a.gh, a.gw, px, py, tl);
+    fuse_pixels_warp<BOUNDED, DIR>(v, wc, mc, k.P, take, c, x0, x1, x2, a.step, k.qg, 0, a.gh,
+                                   a.gw, px, py, tl);
   }
 }
 
@@ -609,7 +633,7 @@ __global__ void __launch_bounds__(256)
     const int bx = blockIdx.x * CLS_TILES + t;
     if (bx >= tiles_x) break; // uniform
     const int px = bx * TILE_W + lx;
-    const bool take = px < a.W && py < a.H && c[t] > a.min_conf;
+    const bool take = px < a.W && py < a.H && c[t] > a.min_conf && sub_take(a, kf, py * a.W + px);
     bool zmiss = false;
     if (take) {
       const float zc = fmaf(x0[t], k0, fmaf(x1[t], k1, fmaf(x2[t], k2, tzv)));
@@ -701,6 +725,57 @@ __global__ void __launch_bounds__(256, FUSE_MINB)
                                     (k >> 1) & 1u, rem - by * tiles_x, by, kf, tl);
     commit_tally(v, tl);
   }
+}
+
+// ---- tsdf_global.max_points_per_kf (global_manager.py:94-99): one CTA per keyframe
+// finds the hash threshold that keeps exactly min(n_valid, max_points) valid pixels
+// -- the max_points smallest hashes -- by a three-pass radix select (11 + 11 + 10
+// bits) over shared-memory histograms.  C stays L2-resident between the passes.
+__global__ void __launch_bounds__(1024)
+    subsample_threshold_kernel(KfArgs a, int max_points, unsigned long long seed,
+                               const long long *__restrict__ kf_ids, uint2 *__restrict__ out) {
+  __shared__ unsigned int hist[2048];
+  __shared__ unsigned int s_need, s_bin;
+  const int kf = blockIdx.x, npix = a.H * a.W;
+  const KfPtrs k = kf_ptrs(a, kf);
+  const uint32_t salt = sub_salt(seed, kf_ids ? (unsigned long long)kf_ids[kf] : (unsigned long long)kf);
+  unsigned int prefix = 0, need = (unsigned int)max_points; // hashes < prefix region are all kept
+  // pass p fixes the next `bits` bits of the threshold below the already fixed ones
+  const int shifts[3] = {21, 10, 0}, nbins[3] = {2048, 2048, 1024};
+  unsigned int fixed_mask = 0;
+  bool all = false;
+  for (int p = 0; p < 3; ++p) {
+    for (int i = threadIdx.x; i < 2048; i += blockDim.x) hist[i] = 0;
+    __syncthreads();
+    for (int i = threadIdx.x; i < npix; i += blockDim.x) {
+      if (k.C[i] > a.min_conf) {
+        const uint32_t h = sub_hash((uint32_t)i, salt);
+        if ((h & fixed_mask) == prefix) atomicAdd(&hist[(h >> shifts[p]) & (nbins[p] - 1)], 1u);
+      }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) { // 2048 bins: a serial scan costs ~2 us per pass
+      unsigned int acc = 0, b = 0;
+      for (; b < (unsigned int)nbins[p]; ++b) {
+        if (acc + hist[b] >= need) break;
+        acc += hist[b];
+      }
+      s_bin = b; // == nbins[p]: fewer than `need` pixels match -> keep them all
+      s_need = need - acc;
+    }
+    __syncthreads();
+    if (s_bin >= (unsigned int)nbins[p]) {
+      all = true;
+      break;
+    }
+    prefix |= s_bin << shifts[p];
+    fixed_mask |= (unsigned int)(nbins[p] - 1) << shifts[p];
+    need = s_need;
+    __syncthreads();
+  }
+  // after three passes `prefix` is the hash of the need-th smallest kept pixel
+  // (hashes are distinct), so h <= prefix selects exactly max_points pixels
+  if (threadIdx.x == 0) out[kf] = make_uint2(all ? 0xFFFFFFFFu : prefix, salt);
 }
 
 // ------------------------------------------------------------------ C ABI
@@ -865,8 +940,21 @@ static int fuse_keyframes(b200tsdf_t *h, const b200tsdf_kf_batch *kb, void *stre
   const int mode = !use_bounded(h) ? 0 : (h->d.dir_on ? 2 : 1);
   // TMA staging needs full tiles and 16-byte aligned row segments
   const bool tma = (W % TILE_W == 0) && (H % TILE_H == 0) && aligned;
-  const KfArgs ka = {X_dev, C_dev, q_grid_dev, pose_dev, (long long)kb->seg_stride,
-                     kb->seg_kf > 0 ? kb->seg_kf : 1, H, W, gh, gw, kb->min_conf, (float)step_d};
+  KfArgs ka = {X_dev, C_dev, q_grid_dev, pose_dev, (long long)kb->seg_stride,
+               kb->seg_kf > 0 ? kb->seg_kf : 1, H, W, gh, gw, kb->min_conf, (float)step_d, nullptr};
+  if (kb->max_points > 0 && (long long)kb->max_points < (long long)H * W) {
+    // the reference's per-keyframe cap (global_manager.py:94-99), seeded and exact-size
+    if ((size_t)B > h->sub_cap) {
+      cudaFree(h->sub_thr);
+      h->sub_thr = nullptr, h->sub_cap = 0;
+      B200_CUDA(cudaMalloc(&h->sub_thr, (size_t)B * sizeof(uint2)));
+      h->sub_cap = (size_t)B;
+    }
+    subsample_threshold_kernel<<<(unsigned)B, 1024, 0, st>>>(ka, kb->max_points, kb->seed,
+                                                             (const long long *)kb->kf_ids_dev,
+                                                             (uint2 *)h->sub_thr);
+    ka.sub = (const uint2 *)h->sub_thr;
+  }
 #define DISPATCH_KF(LAUNCH)                                                                    \
   if (tma) {                                                                                   \
     if (mode == 0) LAUNCH(false, false, true);                                                 \
@@ -1009,6 +1097,9 @@ extern "C" int b200tsdf_integrate_keyframes_host(b200tsdf_t *h, const float *X_h
                                       (int32_t)nb, H, W, gh, gw, min_conf, step_scale, st);
     if (rc) return rc;
   }
+  // the host buffers are the caller's again when this returns: wait for the copies
+  // (not for the fuse, which stays queued on `stream`)
+  B200_CUDA(cudaStreamSynchronize(h->copy_stream));
   return B200TSDF_OK;
 }
 

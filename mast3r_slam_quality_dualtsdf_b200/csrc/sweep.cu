@@ -269,7 +269,10 @@ __device__ __forceinline__ uint8_t query_point(const VolumeDev &v, int which, co
   int k[3];
   query_key<T>(pt, vs, k);
   QueryTaps q;
-  fetch_taps<false>(v, which, k, isfinite((double)pt[0]), q);
+  // a non-finite coordinate floors to an integer no voxel has (the reference returns
+  // (None, None), global_volume.py:95-98): all three must be finite
+  const bool fin = isfinite((double)pt[0]) && isfinite((double)pt[1]) && isfinite((double)pt[2]);
+  fetch_taps<false>(v, which, k, fin, q);
   return finish_query(q, v.min_weight, voxel_size, tv, g);
 }
 
@@ -440,7 +443,8 @@ __global__ void query_taps_kernel(VolumeDev v, int which, const T *__restrict__ 
   int k[3];
   query_key<T>(pt, vs, k);
   QueryTaps q;
-  fetch_taps<true>(v, which, k, isfinite((double)pt[0]), q);
+  const bool fin = isfinite((double)pt[0]) && isfinite((double)pt[1]) && isfinite((double)pt[2]);
+  fetch_taps<true>(v, which, k, fin, q);
   store_taps(taps + 4 * p, q);
 }
 

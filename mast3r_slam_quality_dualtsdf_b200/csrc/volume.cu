@@ -140,6 +140,7 @@ extern "C" int b200tsdf_destroy(b200tsdf_t *h) {
   cudaFree(h->scratch);
   cudaFree(h->sched);
   cudaFree(h->tile_list);
+  cudaFree(h->sub_thr);
   cudaFree(h->nbr);
   cudaFree(h->stage_dev);
   if (h->copy_stream) {
@@ -170,6 +171,11 @@ extern "C" int b200tsdf_counters(b200tsdf_t *h, int64_t out_host[8], void *strea
   int rc = b200_read_counters(h, st, tmp);
   if (rc) return rc;
   for (int i = 0; i < 8; ++i) out_host[i] = (int64_t)tmp[i];
+  if (tmp[CTR_OVERFLOW] != 0) { // the values above are valid; the volume is not
+    b200_set_error("voxel-block hash full: %llu updates were lost (capacity_log2 = %d); raise "
+                   "tsdf_global.capacity_log2", tmp[CTR_OVERFLOW], h->cfg.capacity_log2);
+    return B200TSDF_E_CAPACITY;
+  }
   return B200TSDF_OK;
 }
 

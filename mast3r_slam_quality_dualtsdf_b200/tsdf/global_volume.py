@@ -7,6 +7,7 @@ include/b200tsdf.h.  New on top of the reference: a second, quality-weighted
 volume fused in the same pass (`confidences_q`, `integrate_keyframes`),
 `query_batch`, `export`, `extract_mesh`.  No CPU fallback.
 """
+import contextlib
 import ctypes as C
 import threading
 from typing import Dict, Optional, Tuple
@@ -96,6 +97,44 @@ class TSDFVolume:
         self.slabs = slabs
         self._h = C.c_void_p()
         _ffi.check(_ffi.lib().b200tsdf_create(C.byref(cfg), C.byref(self._h)), "b200tsdf_create")
+        # device-side ordering of writers (fuse, import, reset) against readers (query,
+        # normal equations, sweeps) that run on OTHER streams: the RLock only orders
+        # the launches on the host.  A writer waits for the last reader and vice versa.
+        self._write_ev = torch.cuda.Event()
+        self._write_stream = None
+        self._read_evs = {}
+
+    @contextlib.contextmanager
+    def _writing(self):
+        """Host lock + device order for a call that MUTATES the volume."""
+        with self._lock:
+            st = torch.cuda.current_stream(self.device)
+            for other, ev in self._read_evs.items():
+                if other != st:
+                    st.wait_event(ev)
+            if self._write_stream is not None and self._write_stream != st:
+                st.wait_event(self._write_ev)
+            try:
+                yield
+            finally:
+                self._read_evs.clear()  # ordered before this write; later writers wait on it
+                self._write_ev.record(st)
+                self._write_stream = st
+
+    @contextlib.contextmanager
+    def _reading(self):
+        """Host lock + device order for a call that only READS the volume."""
+        with self._lock:
+            st = torch.cuda.current_stream(self.device)
+            if self._write_stream is not None and self._write_stream != st:
+                st.wait_event(self._write_ev)
+            try:
+                yield
+            finally:
+                ev = self._read_evs.get(st)
+                if ev is None:
+                    ev = self._read_evs[st] = torch.cuda.Event()
+                ev.record(st)
 
     def close(self):
         if getattr(self, "_h", None) is not None and self._h:
@@ -109,7 +148,7 @@ class TSDFVolume:
             pass
 
     def reset(self):
-        with self._lock:
+        with self._writing():
             _ffi.check(_ffi.lib().b200tsdf_reset(self._h, _stream_ptr(self.device)), "reset")
 
     # ------------------------------------------------------------------
@@ -144,7 +183,7 @@ class TSDFVolume:
             cq_d = torch.from_numpy(
                 np.ascontiguousarray(confidences_q, dtype=np.float64).reshape(-1)).to(self.device)
         fused = C.c_int64(0)
-        with self._lock:
+        with self._writing():
             _ffi.check(_ffi.lib().b200tsdf_integrate_points(
                 self._h, pts_d.data_ptr(), tdt, conf_d.data_ptr(),
                 cq_d.data_ptr() if cq_d is not None else None,
@@ -153,19 +192,28 @@ class TSDFVolume:
         return int(fused.value)
 
     def deintegrate_keyframes(self, X, Cf, poses, q_grid=None, min_conf=0.05, H=None, W=None,
-                              step_scale=0.5):
-        """Exact inverse of `integrate_keyframes` for the same device tensors
-        (new: the reference never removes a stale contribution)."""
+                              step_scale=0.5, max_points=0, seed=0, kf_ids=None):
+        """Exact inverse of `integrate_keyframes` for the same device tensors and
+        subsample arguments (new: the reference never removes a stale
+        contribution)."""
         return self.integrate_keyframes(X, Cf, poses, q_grid, min_conf, H, W, step_scale,
-                                        _negate=True)
+                                        _negate=True, max_points=max_points, seed=seed,
+                                        kf_ids=kf_ids)
 
     def integrate_keyframes(self, X, Cf, poses, q_grid=None, min_conf=0.05, H=None, W=None,
-                            step_scale=0.5, _negate=False):
+                            step_scale=0.5, _negate=False, max_points=0, seed=0, kf_ids=None):
         """Fused staging + allocation + dual fold for a batch of keyframes
         (replaces global_manager.py:81-106 per keyframe).  Tensors may live on
-        the device (zero-copy) or on the host (copied inside the call).
+        the device (zero-copy) or on the host (copied inside the call; the host
+        buffers are free again when it returns).
         X (B,H*W,3) f32 camera-frame pointmap, Cf (B,H*W[,1]) f32, poses (B,8)
-        f32 Sim3 [t,q,s], q_grid (B,gh,gw) f32 or None."""
+        f32 Sim3 [t,q,s], q_grid (B,gh,gw) f32 or None.
+        max_points > 0: the reference's `max_points_per_kf` cap
+        (global_manager.py:94-99) -- of the pixels with C > min_conf exactly
+        min(n_valid, max_points) per keyframe are fused, chosen by a seeded
+        bijective hash of the pixel index (`seed`, and the keyframe's id from
+        `kf_ids`, default its position in the batch); the reference draws an
+        unseeded randperm.  Device tensors only."""
         X = X if X.dim() == 3 else X.unsqueeze(0)
         B, N = X.shape[0], X.shape[1]
         if H is None or W is None:
@@ -182,16 +230,34 @@ class TSDFVolume:
             if t.dtype != torch.float32 or not t.is_contiguous() or t.is_cuda != on_dev:
                 raise ValueError("keyframe tensors must be contiguous float32 on one device")
         Xc, Cc, Pc = ts[0], ts[1], ts[2]
-        if _negate and not on_dev:
-            raise ValueError("deintegrate_keyframes needs device tensors")
-        fn = (_ffi.lib().b200tsdf_deintegrate_keyframes if _negate else
-              _ffi.lib().b200tsdf_integrate_keyframes if on_dev
-              else _ffi.lib().b200tsdf_integrate_keyframes_host)
-        with self._lock:
-            _ffi.check(fn(self._h, Xc.data_ptr(), Cc.data_ptr(),
-                          q_grid.data_ptr() if q_grid is not None else None, Pc.data_ptr(),
-                          B, H, W, gh, gw, float(min_conf), float(step_scale),
-                          _stream_ptr(self.device)), "integrate_keyframes")
+        capped = max_points is not None and 0 < int(max_points) < N
+        if (_negate or capped) and not on_dev:
+            raise ValueError("deintegrate_keyframes / max_points need device tensors")
+        if not on_dev:
+            with self._writing():
+                _ffi.check(_ffi.lib().b200tsdf_integrate_keyframes_host(
+                    self._h, Xc.data_ptr(), Cc.data_ptr(),
+                    q_grid.data_ptr() if q_grid is not None else None, Pc.data_ptr(),
+                    B, H, W, gh, gw, float(min_conf), float(step_scale),
+                    _stream_ptr(self.device)), "integrate_keyframes_host")
+            return
+        kb = _ffi.KfBatch()
+        kb.X_dev, kb.C_dev, kb.pose_dev = Xc.data_ptr(), Cc.data_ptr(), Pc.data_ptr()
+        kb.q_grid_dev = q_grid.data_ptr() if q_grid is not None else None
+        kb.B, kb.H, kb.W, kb.gh, kb.gw = B, H, W, gh, gw
+        kb.seg_kf, kb.seg_stride = B, 0
+        kb.min_conf, kb.negate, kb.step_scale = float(min_conf), int(bool(_negate)), float(step_scale)
+        ids = None
+        if capped:
+            kb.max_points, kb.seed = int(max_points), int(seed) & 0xFFFFFFFFFFFFFFFF
+            if kf_ids is not None:
+                ids = torch.as_tensor(kf_ids, dtype=torch.int64).reshape(-1).to(self.device)
+                if ids.numel() != B:
+                    raise ValueError("kf_ids must name every keyframe of the batch")
+                kb.kf_ids_dev = ids.data_ptr()
+        with self._writing():
+            _ffi.check(_ffi.lib().b200tsdf_integrate_keyframes_ex(
+                self._h, C.byref(kb), _stream_ptr(self.device)), "integrate_keyframes")
 
     def integrate_keyframes_packed(self, buf, n_seg, seg_kf, H, W, gh=0, gw=0, min_conf=0.05,
                                    step_scale=0.5, negate=False):
@@ -215,7 +281,7 @@ class TSDFVolume:
         kb.B, kb.H, kb.W, kb.gh, kb.gw = n_seg * seg_kf, H, W, gh, gw
         kb.seg_kf, kb.seg_stride = seg_kf, lay["seg_len"] if n_seg > 1 else 0
         kb.min_conf, kb.negate, kb.step_scale = float(min_conf), int(bool(negate)), float(step_scale)
-        with self._lock:
+        with self._writing():
             _ffi.check(_ffi.lib().b200tsdf_integrate_keyframes_ex(
                 self._h, C.byref(kb), _stream_ptr(self.device)), "integrate_keyframes_ex")
 
@@ -235,7 +301,7 @@ class TSDFVolume:
         t = torch.zeros(m, dtype=torch.float64, device=self.device)
         g = torch.zeros(m, 3, dtype=torch.float64, device=self.device)
         fl = torch.zeros(m, dtype=torch.uint8, device=self.device)
-        with self._lock:
+        with self._reading():
             _ffi.check(_ffi.lib().b200tsdf_query(
                 self._h, which, pts.data_ptr(), _ffi.F32 if pts.dtype == torch.float32 else _ffi.F64,
                 m, t.data_ptr(), g.data_ptr(), fl.data_ptr(), _stream_ptr(self.device)), "query")
@@ -265,7 +331,7 @@ class TSDFVolume:
         H = np.zeros((7, 7), np.float64)
         b = np.zeros(7, np.float64)
         used = C.c_int64()
-        with self._lock:
+        with self._reading():
             _ffi.check(_ffi.lib().b200tsdf_pose_normal_equations(
                 self._h, which, pts.data_ptr(), cf.data_ptr(), pts.shape[0],
                 ps.ctypes.data_as(C.c_void_p), float(lam), H.ctypes.data_as(C.c_void_p),
@@ -291,7 +357,7 @@ class TSDFVolume:
         m = pts.shape[0]
         taps = torch.zeros(m, 16, dtype=torch.float32, device=self.device)
         ps = None if pose is None else np.ascontiguousarray(np.asarray(pose, np.float32).reshape(8))
-        with self._lock:
+        with self._reading():
             _ffi.check(_ffi.lib().b200tsdf_query_taps(
                 self._h, which, pts.data_ptr(),
                 _ffi.F32 if pts.dtype == torch.float32 else _ffi.F64, m,
@@ -308,7 +374,7 @@ class TSDFVolume:
         t = torch.zeros(m, dtype=torch.float64, device=self.device)
         g = torch.zeros(m, 3, dtype=torch.float64, device=self.device)
         fl = torch.zeros(m, dtype=torch.uint8, device=self.device)
-        with self._lock:
+        with self._reading():
             _ffi.check(_ffi.lib().b200tsdf_query_finish(
                 self._h, taps.data_ptr(), m, t.data_ptr(), g.data_ptr(), fl.data_ptr(),
                 _stream_ptr(self.device)), "query_finish")
@@ -324,7 +390,7 @@ class TSDFVolume:
         H = np.zeros((7, 7), np.float64)
         b = np.zeros(7, np.float64)
         used = C.c_int64()
-        with self._lock:
+        with self._reading():
             _ffi.check(_ffi.lib().b200tsdf_pose_normal_equations_taps(
                 self._h, taps.data_ptr(), pts.data_ptr(), cf.data_ptr(), pts.shape[0],
                 ps.ctypes.data_as(C.c_void_p), float(lam), H.ctypes.data_as(C.c_void_p),
@@ -335,30 +401,35 @@ class TSDFVolume:
     def stats(self, which: int = 0) -> Dict[str, float]:
         """Reference signature (global_volume.py:136-140)."""
         a, b = C.c_int64(), C.c_int64()
-        with self._lock:
+        with self._reading():
             _ffi.check(_ffi.lib().b200tsdf_stats(self._h, which, C.byref(a), C.byref(b),
                                                  _stream_ptr(self.device)), "stats")
         return {"valid_voxels": a.value, "total_voxels": b.value}
 
-    def counters(self) -> Dict[str, int]:
+    def counters(self, check: bool = True) -> Dict[str, int]:
+        """rays, applied updates per volume, blocks, dropped, overflow, culled rays
+        since create / reset (synchronises).  Raises when the voxel-block hash
+        overflowed (B200TSDF_E_CAPACITY: updates were lost) unless check=False."""
         out = (C.c_int64 * 8)()
-        with self._lock:
-            _ffi.check(_ffi.lib().b200tsdf_counters(self._h, out, _stream_ptr(self.device)),
-                       "counters")
+        with self._reading():
+            rc = _ffi.lib().b200tsdf_counters(self._h, out, _stream_ptr(self.device))
+        if rc not in (0, _ffi.E_CAPACITY) or (rc == _ffi.E_CAPACITY and check):
+            _ffi.check(rc, "counters")
         names = ["rays", "updates_primary", "updates_quality", "blocks", "dropped", "overflow",
                  "culled_rays"]
-        d = dict(zip(names, [int(x) for x in out]))
-        if d["overflow"]:
-            raise _ffi.B200TSDFError(
-                f"voxel-block hash overflow ({d['overflow']} updates lost): raise capacity_log2")
-        return d
+        return dict(zip(names, [int(x) for x in out]))
+
+    def check(self) -> None:
+        """Raise B200TSDFError if any update was lost to a full voxel-block hash
+        (the reference dict grows without limit; here `capacity_log2` bounds it)."""
+        self.counters(check=True)
 
     def export(self, which: int = 0):
         """All voxels of one volume, sorted by key: (keys i64 (n,3), tsdf f32,
         weight f32, count u32) numpy arrays -- what reference _voxels holds."""
         n = C.c_int64()
         L = _ffi.lib()
-        with self._lock:
+        with self._reading():
             _ffi.check(L.b200tsdf_export_voxels(self._h, which, None, None, None, None, 0,
                                                 C.byref(n), _stream_ptr(self.device)), "export")
             cap = n.value
@@ -378,7 +449,7 @@ class TSDFVolume:
     def block_keys(self):
         n = C.c_int64()
         L = _ffi.lib()
-        with self._lock:
+        with self._reading():
             _ffi.check(L.b200tsdf_export_blocks(self._h, None, 0, C.byref(n),
                                                 _stream_ptr(self.device)), "export_blocks")
             bk = torch.zeros(max(n.value, 1), 3, dtype=torch.int64, device=self.device)
@@ -396,7 +467,7 @@ class TSDFVolume:
         returned."""
         n = C.c_int64()
         L = _ffi.lib()
-        with self._lock:
+        with self._reading():
             if out is None:
                 nblk = C.c_int64()
                 _ffi.check(L.b200tsdf_export_blocks(self._h, None, 0, C.byref(nblk),
@@ -419,7 +490,7 @@ class TSDFVolume:
     # ------------------------------------------------------------------
     def _export_payload(self, fn, what):
         n = C.c_int64()
-        with self._lock:
+        with self._reading():
             _ffi.check(fn(self._h, None, None, None, 0, C.byref(n), _stream_ptr(self.device)), what)
             cap = n.value
             bk = torch.zeros(cap, 3, dtype=torch.int64, device=self.device)
@@ -451,7 +522,7 @@ class TSDFVolume:
         bkeys = bkeys.to(self.device, torch.int64).contiguous()
         vox = vox.to(self.device, torch.float32).contiguous()
         cnt = cnt.to(self.device, torch.int64).contiguous()
-        with self._lock:
+        with self._writing():
             _ffi.check(_ffi.lib().b200tsdf_import_blocks(
                 self._h, bkeys.data_ptr(), vox.data_ptr(), cnt.data_ptr(), n,
                 _stream_ptr(self.device)), "import_blocks")
@@ -491,7 +562,7 @@ class TSDFVolume:
         bkeys = bkeys.to(self.device, torch.int64).contiguous()
         vox = vox.to(self.device, torch.float32).contiguous()
         cnt = cnt.to(self.device, torch.int64).contiguous()
-        with self._lock:
+        with self._writing():
             _ffi.check(_ffi.lib().b200tsdf_import_halo_blocks(
                 self._h, bkeys.data_ptr(), vox.data_ptr(), cnt.data_ptr(), n,
                 _stream_ptr(self.device)), "import_halo")

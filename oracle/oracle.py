@@ -147,10 +147,14 @@ def sim3_act(pose, x):
     return y
 
 
-def stage_keyframe(X, Cf, pose, q_grid, H, W, min_conf):
-    """Returns pts_world f32 (n,3), conf f64 (n,), conf_q f64 (n,), cam_origin f32 (3,)."""
+def stage_keyframe(X, Cf, pose, q_grid, H, W, min_conf, max_points=0, seed=0, kf_id=0):
+    """Returns pts_world f32 (n,3), conf f64 (n,), conf_q f64 (n,), cam_origin f32 (3,).
+    max_points > 0: only the pixels of `subsample_mask` are staged."""
     X = np.ascontiguousarray(X, np.float32).reshape(-1, 3)
     Cf = np.ascontiguousarray(Cf, np.float32).reshape(-1)
+    if max_points > 0:
+        Cf = np.where(subsample_mask(Cf, min_conf, max_points, seed, kf_id), Cf,
+                      np.float32(0.0)).astype(np.float32)
     pose = np.ascontiguousarray(pose, np.float32).reshape(8)
     n = H * W
     pts = np.zeros((n, 3), np.float32)
@@ -165,6 +169,40 @@ def stage_keyframe(X, Cf, pose, q_grid, H, W, min_conf):
     k = int(lib().orc_stage_keyframe(_p(X), _p(Cf), _p(pose), _p(qg), gh, gw, H, W,
                                      float(min_conf), _p(pts), _p(conf), _p(confq), _p(org)))
     return pts[:k].copy(), conf[:k].copy(), confq[:k].copy(), org
+
+
+def _fmix32(x):
+    """murmur3 finaliser on uint32 arrays (a bijection of Z_2^32)."""
+    x = np.asarray(x, np.uint64) & 0xFFFFFFFF
+    x ^= x >> 16
+    x = (x * 0x85EBCA6B) & 0xFFFFFFFF
+    x ^= x >> 13
+    x = (x * 0xC2B2AE35) & 0xFFFFFFFF
+    x ^= x >> 16
+    return x
+
+
+def subsample_mask(Cf, min_conf, max_points, seed=0, kf_id=0):
+    """The seeded stand-in for the reference's unseeded random choice of at most
+    `max_points_per_kf` valid pixels (global_manager.py:92-97): boolean mask over
+    the H*W pixels that keeps the max_points valid pixels (C > min_conf) with the
+    smallest hash(pixel) -- the definition the product's
+    subsample_threshold_kernel implements (csrc/integrate.cu: sub_hash, sub_salt)."""
+    Cf = np.ascontiguousarray(Cf, np.float32).reshape(-1)
+    valid = Cf > np.float32(min_conf)
+    if max_points <= 0 or int(valid.sum()) <= max_points:
+        return valid
+    seed, kf_id = int(seed) & 0xFFFFFFFFFFFFFFFF, int(kf_id) & 0xFFFFFFFFFFFFFFFF
+    a = int(_fmix32(((kf_id & 0xFFFFFFFF) + 0x9E3779B9 * (seed >> 32)) & 0xFFFFFFFF))
+    b = int(_fmix32(((kf_id >> 32) + 0x7F4A7C15) & 0xFFFFFFFF))
+    salt = int(_fmix32((seed & 0xFFFFFFFF) ^ a ^ b))
+    pix = np.arange(Cf.shape[0], dtype=np.uint64)
+    h = _fmix32((pix * 0x9E3779B1 + salt) & 0xFFFFFFFF)
+    h_valid = np.where(valid, h, np.uint64(1 << 40))  # invalid pixels sort last
+    keep = np.argsort(h_valid, kind="stable")[:max_points]
+    mask = np.zeros(Cf.shape[0], bool)
+    mask[keep] = True
+    return mask & valid
 
 
 def marching_cubes(keys, tsdf, weight, voxel_size, min_weight=1.0e-3):

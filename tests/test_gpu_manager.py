@@ -258,3 +258,161 @@ def test_checkpoint_round_trip_and_merge(cuda_device, tmp_path):
         assert np.abs(gt - wt).max() <= 1e-5 and np.abs(gw - ww).max() <= 1e-4 * max(1.0, ww.max())
     with pytest.raises(ValueError):
         TSDFVolume(0.03, 0.08, device=cuda_device).load_checkpoint(path)
+
+
+# ---------------------------------------------------------------------------
+# the batching integrator, max_points_per_kf, overflow, config keys
+# ---------------------------------------------------------------------------
+class _StackedKeyframes:
+    """SharedKeyframes-shaped container (frame.py:236-252): stacked device
+    buffers X (n, HW, 3), C (n, HW, 1), T_WC (n, 1, 8) behind an RLock."""
+
+    def __init__(self, kf, dev, n=None):
+        import threading
+
+        self.lock = threading.RLock()
+        self.X = torch.from_numpy(kf["X"]).to(dev)
+        self.C = torch.from_numpy(kf["C"]).to(dev).reshape(kf["C"].shape[0], -1, 1)
+        self.T_WC = torch.from_numpy(kf["pose"]).to(dev).reshape(-1, 1, 8)
+        self.h, self.w = kf["H"], kf["W"]
+        self.n = self.X.shape[0] if n is None else n
+
+    def __len__(self):
+        return self.n
+
+
+def test_integrator_batches_a_wakeup_into_one_launch(cuda_device):
+    """the drop-in class must reach the batched kernel --
+    one wake-up = one snapshot + ONE launch for all pending keyframes, a second
+    wake-up one launch for all dirty ones; results equal the sequential oracle."""
+    from mast3r_slam_quality_dualtsdf_b200 import synth
+    from mast3r_slam_quality_dualtsdf_b200.tsdf import TSDFGlobalManager
+
+    kf = synth.make_keyframes(synth.SCENES["sphere"], 6, H=48, W=64, seed=4, f=50.0, total=12)
+    kfs = _StackedKeyframes(kf, cuda_device)
+    cfg = {"enabled": True, "voxel_size": 0.03, "trunc_dist": 0.12, "min_confidence": 0.05,
+           "async_optimize": False, "max_iterations": 0, "pre_icp_iters": 0, "pin": 1,
+           "volume_dim": 256, "capacity_log2": 14}
+    mgr = TSDFGlobalManager(kfs, cfg, False, cuda_device)
+    assert mgr.volume.bounds == ((-128, -128, -128), (128, 128, 128))
+    mgr.integrator.step()
+    assert mgr.integrator.next_idx == 6 and mgr.integrator.launches == 1
+    vp, _, _ = oracle_dual(kf, 0.03, 0.12, use_q=False)
+    assert_volume_matches(mgr.volume.export(0), vp.export(), "batched wake-up")
+    mgr.on_after_backend_solve(types.SimpleNamespace(last_unique_kf_idx=torch.tensor([1, 3, 5])))
+    mgr.integrator.step()
+    assert mgr.integrator.launches == 2 and mgr.integrator.integrated == 9
+    # with pre-ICP the reference order (fuse i, refine i, fuse i+1) is kept: one launch each
+    kfs2 = _StackedKeyframes(kf, cuda_device)
+    m2 = TSDFGlobalManager(kfs2, dict(cfg, pre_icp_iters=1, samples_per_kf=64, damping=1.0e3),
+                           False, cuda_device)
+    m2.integrator.step()
+    assert m2.integrator.launches == 6
+    m3 = TSDFGlobalManager(_StackedKeyframes(kf, cuda_device),
+                           dict(cfg, pre_icp_iters=1, samples_per_kf=64, damping=1.0e3,
+                                batch_with_pre_icp=True), False, cuda_device)
+    m3.integrator.step()
+    assert m3.integrator.launches == 1
+
+
+@pytest.mark.parametrize("bounded", [False, True])
+def test_max_points_per_kf_is_honoured(cuda_device, bounded):
+    """global_manager.py:94-99 / config/base.yaml:116: at most max_points valid
+    pixels per keyframe are fused.  The choice is the seeded hash subsample of
+    oracle.subsample_mask; volumes equal the oracle fused with the same choice."""
+    from mast3r_slam_quality_dualtsdf_b200 import synth
+    from mast3r_slam_quality_dualtsdf_b200.tsdf import TSDFGlobalManager, TSDFVolume
+
+    kf = synth.make_keyframes(synth.SCENES["sphere"], 3, H=48, W=64, seed=6, f=50.0, total=9)
+    cap, seed = 700, 1234
+    n_valid = (kf["C"] > 0.05).sum(axis=1)
+    assert (n_valid > cap).all()
+    vp, vq, rays = oracle_dual(kf, 0.03, 0.12, max_points=cap, seed=seed)
+    assert rays == 3 * cap
+    kw = {"bounds": ((-128, -128, -64), (128, 128, 192))} if bounded else {}
+    vol = TSDFVolume(0.03, 0.12, device=cuda_device, **kw)
+    t = {k: torch.from_numpy(kf[k]).to(cuda_device) for k in ("X", "C", "pose", "q")}
+    vol.integrate_keyframes(t["X"], t["C"], t["pose"], t["q"], 0.05, 48, 64, max_points=cap,
+                            seed=seed)
+    c = vol.counters()
+    assert c["rays"] == rays and c["updates_primary"] == vp.events
+    assert_volume_matches(vol.export(0), vp.export(), "capped primary")
+    assert_volume_matches(vol.export(1), vq.export(), "capped quality")
+    # the same selection removes what it added
+    vol.deintegrate_keyframes(t["X"], t["C"], t["pose"], t["q"], 0.05, 48, 64, max_points=cap,
+                              seed=seed)
+    assert vol.stats(0)["total_voxels"] == 0
+    # through the manager: keyframe b is salted with its index b
+    kfs = _StackedKeyframes(kf, cuda_device)
+    cfg = {"enabled": True, "voxel_size": 0.03, "trunc_dist": 0.12, "min_confidence": 0.05,
+           "async_optimize": False, "pre_icp_iters": 0, "max_points_per_kf": cap, "seed": seed}
+    mgr = TSDFGlobalManager(kfs, cfg, False, cuda_device)
+    mgr.integrator.step()
+    assert_volume_matches(mgr.volume.export(0), vp.export(), "capped manager")
+    # a different seed is a different choice of the same size
+    other = TSDFVolume(0.03, 0.12, device=cuda_device)
+    other.integrate_keyframes(t["X"], t["C"], t["pose"], t["q"], 0.05, 48, 64, max_points=cap,
+                              seed=seed + 1)
+    assert other.counters()["rays"] == rays
+    ka, kb = other.export(0)[0], vp.export()[0]
+    assert ka.shape != kb.shape or not np.array_equal(ka, kb)
+
+
+def test_hash_overflow_is_an_error(cuda_device):
+    """B200TSDF_E_CAPACITY is returned, and the drop-in
+    integrator raises instead of losing updates silently."""
+    from mast3r_slam_quality_dualtsdf_b200 import _ffi, synth
+    from mast3r_slam_quality_dualtsdf_b200.tsdf import TSDFGlobalManager, TSDFVolume
+
+    kf = synth.make_keyframes(synth.SCENES["sphere"], 2, H=48, W=64, seed=3, f=50.0, total=8)
+    t = {k: torch.from_numpy(kf[k]).to(cuda_device) for k in ("X", "C", "pose", "q")}
+    vol = TSDFVolume(0.01, 0.04, capacity_log2=4, device=cuda_device)  # 16 blocks only
+    vol.integrate_keyframes(t["X"], t["C"], t["pose"], t["q"], 0.05, 48, 64)
+    with pytest.raises(_ffi.B200TSDFError, match="capacity_log2"):
+        vol.counters()
+    assert vol.counters(check=False)["overflow"] > 0
+    with pytest.raises(_ffi.B200TSDFError):
+        vol.check()
+    cfg = {"enabled": True, "voxel_size": 0.01, "trunc_dist": 0.04, "capacity_log2": 4,
+           "async_optimize": False, "pre_icp_iters": 0}
+    mgr = TSDFGlobalManager(_StackedKeyframes(kf, cuda_device), cfg, False, cuda_device)
+    with pytest.raises(_ffi.B200TSDFError):
+        mgr.integrator.step()
+
+
+def test_config_keys_of_the_survey(cuda_device):
+    """volume_dim / volume_origin / quality_volume / seed /
+    parity_mode / num_gpus load from the tsdf_global section."""
+    from mast3r_slam_quality_dualtsdf_b200 import _ffi
+    from mast3r_slam_quality_dualtsdf_b200.tsdf import global_manager as gm
+
+    assert gm.bounds_from_cfg({}) is None
+    assert gm.bounds_from_cfg({"volume_dim": 512, "voxel_size": 0.005}) == \
+        ((-256, -256, -256), (256, 256, 256))
+    b = gm.bounds_from_cfg({"volume_dim": [64, 32, 16], "voxel_size": 0.01,
+                            "volume_origin": [-0.105, 0.0, 0.33]})
+    assert b == ((-16, 0, 32), (48, 32, 48))  # origin floored to a multiple of 8 voxels
+    assert gm.bounds_from_cfg({"bounds": [[0, 0, 0], [8, 8, 8]]}) == ((0, 0, 0), (8, 8, 8))
+    with pytest.raises(ValueError, match="parity_mode"):
+        gm.build_volume({"parity_mode": "projective"}, cuda_device)
+    with pytest.raises(_ffi.B200TSDFError, match="num_gpus"):
+        gm.build_volume({"num_gpus": 2, "volume_dim": 64}, cuda_device)
+
+    class Svc:
+        def get(self, fid):
+            return {"priority": np.full(12, 0.25, np.float32)}
+
+    from mast3r_slam_quality_dualtsdf_b200 import synth
+
+    kf = synth.make_keyframes(synth.SCENES["plane"], 2, H=48, W=64, seed=3, f=50.0)
+    cfg = {"enabled": True, "voxel_size": 0.03, "trunc_dist": 0.12, "async_optimize": False,
+           "pre_icp_iters": 0}
+    on = gm.TSDFGlobalManager(_StackedKeyframes(kf, cuda_device), cfg, False, cuda_device, Svc())
+    on.integrator.step()
+    off = gm.TSDFGlobalManager(_StackedKeyframes(kf, cuda_device), dict(cfg, quality_volume=False),
+                               False, cuda_device, Svc())
+    off.integrator.step()
+    # q = 1 - 0.25 scales the quality volume's weights; quality_volume: false leaves them plain
+    w_on, w_off = on.volume.export(1)[2], off.volume.export(1)[2]
+    assert np.allclose(w_on, 0.75 * w_off, rtol=1e-5)
+    assert np.allclose(off.volume.export(0)[2], w_off, rtol=1e-6)

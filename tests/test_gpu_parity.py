@@ -134,6 +134,19 @@ def test_query_matches_oracle(cuda_device):
     tv, gv = vol.query(probe[0])
     tr, gr = vp.query(probe[0])
     assert abs(tv - tr) <= 1e-5 and (gv is None) == (gr is None)
+    # a non-finite coordinate in ANY axis: the reference returns (None, None)
+    # (floor(nan) is no voxel's key) -- also for points whose other coordinates
+    # would land in a stored voxel
+    bad = np.repeat(probe[:6], 1, axis=0).copy()
+    bad[0, 0] = np.nan
+    bad[1, 1] = np.nan
+    bad[2, 2] = np.nan
+    bad[3, 1] = np.inf
+    bad[4, 2] = -np.inf
+    for dtype in (np.float32, np.float64):
+        _, _, ff = (x.cpu().numpy() for x in vol.query_batch(bad.astype(dtype), 0))
+        assert not ff[:5].any() and ff[5] & 1
+        assert vol.query(bad[1].astype(dtype)) == (None, None)
 
 
 def test_bounds_drop_outside(cuda_device):
