@@ -444,10 +444,12 @@ __device__ __forceinline__ void fuse_pixels_warp_fast(const VolumeDev &v, const 
   tl.ev_p += (uint32_t)cnt * cp;
   tl.ev_q += (uint32_t)cnt * cqf;
   commit_tally(v, tl);
-  tl = Tally{0, 0, 0, 0, 0, 0, 0};
-  march_warp_fast(v, mc, fc, fr, P, i0, cnt, cp ? c : 0.0f, cqf ? cq : 0.0f, cp, cqf, slab_check,
-                  d_cta, tl);
-  commit_tally(v, tl);
+  const uint32_t lost = march_warp_fast(v, mc, fc, fr, P, i0, cnt, cp ? c : 0.0f,
+                                        cqf ? cq : 0.0f, slab_check, d_cta);
+  if (__any_sync(0xFFFFFFFFu, lost != 0)) { // drops at slab seams, hash overflow
+    Tally t2 = {0, 0, 0, lost & 0xFFFu, (lost >> 12) & 0xFFFu, lost >> 24, 0};
+    commit_tally(v, t2);
+  }
 }
 
 #define TILE_W 32
@@ -837,7 +839,7 @@ static FastConst make_fast_consts(const b200tsdf *h, double step_d) {
     fc.in_of[a] = (float)(-(hi + lo) / (hi - lo));
   }
   fc.band_k = (int)ceil(2.0 * tr / step_d) + 1;
-  if (fc.band_k > (1 << 20)) ok = false;
+  if (fc.band_k > 1024) ok = false; // per-lane loss counters of the march are 12 bits wide
   fc.nx = (uint32_t)d.dir_n[0], fc.ny = (uint32_t)d.dir_n[1];
   const uint32_t m3 = (uint32_t)MARCH_KEY_MAGIC_BITS >> 3;
   fc.dir_c = ((m3 + (uint32_t)d.dir_b0[2]) * fc.ny + (m3 + (uint32_t)d.dir_b0[1])) * fc.nx +

@@ -47,11 +47,10 @@ __device__ __forceinline__ void commit_tally(const VolumeDev &v, Tally tl) {
   const bool any_app = any_ev || any_lost;
   const int app_p = any_app ? __reduce_add_sync(0xFFFFFFFFu, (int)tl.ev_p - (int)tl.drop_p) : 0;
   const int app_q = any_app ? __reduce_add_sync(0xFFFFFFFFu, (int)tl.ev_q - (int)tl.drop_q) : 0;
-  uint32_t dropped = 0;
-  tl.overflow = 0;
+  uint32_t dropped = 0, overflow = 0;
   if (any_lost) { // out-of-bounds / foreign-slab drops, hash overflow
     dropped = __reduce_add_sync(0xFFFFFFFFu, tl.drop_p + tl.drop_q);
-    tl.overflow = __reduce_add_sync(0xFFFFFFFFu, tl.overflow);
+    overflow = __reduce_add_sync(0xFFFFFFFFu, tl.overflow);
   }
   tl.culled = any_culled ? __reduce_add_sync(0xFFFFFFFFu, tl.culled) : 0u;
   const bool any_rare = any_lost || any_culled;
@@ -67,7 +66,7 @@ __device__ __forceinline__ void commit_tally(const VolumeDev &v, Tally tl) {
     if (app_q) atomicAdd(ctr + CTR_EV_Q, (unsigned long long)(long long)app_q);
     if (any_rare) {
       if (dropped) atomicAdd(ctr + CTR_DROPPED, (unsigned long long)dropped);
-      if (tl.overflow) atomicAdd(ctr + CTR_OVERFLOW, (unsigned long long)tl.overflow);
+      if (overflow) atomicAdd(ctr + CTR_OVERFLOW, (unsigned long long)overflow);
       if (tl.culled) atomicAdd(ctr + CTR_CULLED, (unsigned long long)tl.culled);
     }
   }

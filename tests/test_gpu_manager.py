@@ -280,6 +280,12 @@ class _StackedKeyframes:
     def __len__(self):
         return self.n
 
+    def __getitem__(self, idx):
+        f = types.SimpleNamespace()
+        f.X_canon, f.C, f.T_WC, f.frame_id = self.X[idx], self.C[idx], self.T_WC[idx], idx
+        f.img_shape = torch.tensor([[self.h, self.w]])
+        return f
+
 
 def test_integrator_batches_a_wakeup_into_one_launch(cuda_device):
     """the drop-in class must reach the batched kernel --
