@@ -299,6 +299,22 @@ int b200tsdf_pose_normal_equations(b200tsdf_t *h, int which, const float *pts_ca
                                    double lambda, double *H_host, double *b_host,
                                    int64_t *used_host, void *stream);
 
+/* The whole of TSDFPoseOptimizer._optimize_single's loop (tsdf_optimizer.py
+ * :72-92) on the device: `iterations` launches, each one Gauss-Newton iteration
+ * -- the linearisation above, then, in the last block to finish, the 7 x 7 solve
+ * (H + damping I) delta = -b in float64 (:82), the float32 cast of delta (:84)
+ * and the retraction pose <- exp(delta) * pose (:85-86) -- with no host round
+ * trip in between; ONE synchronisation at the end returns the pose.  The loop
+ * stops like the reference when fewer than 6 points are usable (:78-79) or the
+ * system is singular (later launches idle).  pose_inout_host: 8 float64
+ * [t, q_xyzw, s]; used_host: points used by the last linearisation;
+ * iterations_done_host: retractions applied.  Single volume only (a sharded
+ * volume merges taps between linearisation and solve, see below). */
+int b200tsdf_pose_optimize(b200tsdf_t *h, int which, const float *pts_cam_dev,
+                           const double *conf_dev, int64_t n, double *pose_inout_host,
+                           double lambda, double damping, int32_t iterations,
+                           int64_t *used_host, int32_t *iterations_done_host, void *stream);
+
 /* ---- sharded query (multi-GPU) ---------------------------------
  * TSDFVolume.query / _estimate_gradient (global_volume.py:93-128) read the
  * voxel of the point and its six axis neighbours; with z-slab ownership those

@@ -25,7 +25,7 @@ SYMBOLS = [
     "b200tsdf_export_block_data", "b200tsdf_import_blocks",
     "b200tsdf_local_dims", "b200tsdf_local_build",
     "b200tsdf_local_raycast", "b200tsdf_quality_patch_grids", "b200tsdf_quality_classify",
-    "b200tsdf_pose_normal_equations", "b200tsdf_quality_batch",
+    "b200tsdf_pose_normal_equations", "b200tsdf_pose_optimize", "b200tsdf_quality_batch",
     "b200tsdf_query_taps", "b200tsdf_query_finish", "b200tsdf_pose_normal_equations_taps",
 ]
 
@@ -104,6 +104,8 @@ def lib():
                                                C.c_double, vp, vp, vp, i32, vp]
     L.b200tsdf_pose_normal_equations.argtypes = [vp, i32, vp, vp, i64, vp, C.c_double, vp, vp, vp,
                                                  vp]
+    L.b200tsdf_pose_optimize.argtypes = [vp, i32, vp, vp, i64, vp, C.c_double, C.c_double, i32, vp,
+                                         vp, vp]
     L.b200tsdf_query_taps.argtypes = [vp, C.c_int, vp, C.c_int, i64, vp, vp, vp]
     L.b200tsdf_query_finish.argtypes = [vp, vp, i64, vp, vp, vp, vp]
     L.b200tsdf_pose_normal_equations_taps.argtypes = [vp, vp, vp, vp, i64, vp, C.c_double, vp, vp,

@@ -91,6 +91,7 @@ struct b200tsdf {
   // max_points_per_kf: per-keyframe {hash threshold, salt} of the current batch
   void *sub_thr;
   size_t sub_cap;
+  void *opt_state; // PoseOptState of b200tsdf_pose_optimize (sweep.cu), lazy
 };
 
 // ---------------------------------------------------------------- hashing

@@ -3,6 +3,8 @@
 // Replaces TSDFVolume.stats (mast3r_slam/tsdf/global_volume.py:136-140),
 // TSDFVolume.query + _estimate_gradient (:93-128); export has no reference
 // counterpart (it dumps what TSDFVolume._voxels holds, for parity tests).
+#include <string.h>
+
 #include "common.cuh"
 #include "sim3.cuh"
 #include "ray.cuh"
@@ -325,11 +327,12 @@ extern "C" int b200tsdf_query(b200tsdf_t *h, int which, const void *pts_dev, int
 // (:107-116), reduced in float64: warp shuffles, then one atomicAdd per warp
 // and entry.  out = [H upper triangle (28) | b (7) | used (1)].
 template <bool TAPS>
-__global__ void __launch_bounds__(128)
-    pose_normal_eq_kernel(VolumeDev v, int which, const float *__restrict__ pts_cam,
-                          const double *__restrict__ conf, long long n, const float *pose,
-                          float vs, double voxel_size, double lambda, double *out,
-                          const float4 *__restrict__ taps) {
+__device__ __forceinline__ void pose_accumulate(const VolumeDev &v, int which,
+                                                const float *__restrict__ pts_cam,
+                                                const double *__restrict__ conf, long long n,
+                                                const float *pose, float vs, double voxel_size,
+                                                double lambda, double *out,
+                                                const float4 *__restrict__ taps) {
   const long long p = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   double acc[36];
 #pragma unroll
@@ -372,6 +375,15 @@ __global__ void __launch_bounds__(128)
     for (int d = 16; d > 0; d >>= 1) a += __shfl_xor_sync(0xFFFFFFFFu, a, d);
     if ((threadIdx.x & 31) == 0 && a != 0.0) atomicAdd(out + i, a);
   }
+}
+
+template <bool TAPS>
+__global__ void __launch_bounds__(128)
+    pose_normal_eq_kernel(VolumeDev v, int which, const float *__restrict__ pts_cam,
+                          const double *__restrict__ conf, long long n, const float *pose,
+                          float vs, double voxel_size, double lambda, double *out,
+                          const float4 *__restrict__ taps) {
+  pose_accumulate<TAPS>(v, which, pts_cam, conf, n, pose, vs, voxel_size, lambda, out, taps);
 }
 
 static int pose_normal_equations_impl(b200tsdf_t *h, int which, const float *pts_cam_dev,
@@ -419,6 +431,201 @@ extern "C" int b200tsdf_pose_normal_equations(b200tsdf_t *h, int which, const fl
                                               void *stream) {
   return pose_normal_equations_impl(h, which, pts_cam_dev, conf_dev, n, pose_host, lambda, H_host,
                                     b_host, used_host, stream, nullptr);
+}
+
+// ---- the whole Gauss-Newton iteration on the device -------
+// TSDFPoseOptimizer._optimize_single (tsdf_optimizer.py:72-92): linearise, solve
+// (H + damping I) delta = -b (:82, np.linalg.solve = LU with partial pivoting),
+// cast delta to the point dtype float32 (:84), pose <- exp(delta) * pose (:85-86).
+// One launch per iteration and no host round trip: the last block to finish the
+// reduction (ticket counter behind a __threadfence) solves the 7 x 7 system in
+// float64, retracts the pose and re-arms the accumulators for the next launch.
+struct PoseOptState {
+  double acc[36];  // upper triangle of H (28), b (7), number of points used
+  double pose[8];  // float64 master copy [t, q_xyzw, s]
+  float pose_f[8]; // what the next linearisation acts with (:76 is float32)
+  unsigned int done_blocks;
+  int stop;       // set when used < 6 (:78-79) or the system is singular (LinAlgError)
+  int iterations; // retractions applied
+  int used;       // points with value and gradient in the last linearisation
+};
+
+// Sim(3) exponential of a tangent [tau, phi, sigma] -> [t, q_xyzw, s]: the closed
+// form of tsdf/sim3.py:exp (the lietorch operation of tsdf_optimizer.py:85).
+__device__ void sim3_exp_d(const double d[7], double out[8]) {
+  const double tau[3] = {d[0], d[1], d[2]}, phi[3] = {d[3], d[4], d[5]}, sigma = d[6];
+  const double theta = sqrt(phi[0] * phi[0] + phi[1] * phi[1] + phi[2] * phi[2]);
+  const double s = exp(sigma), eps = 1.0e-9;
+  double A, B, C;
+  if (fabs(sigma) < eps) {
+    C = 1.0;
+    if (theta < eps) {
+      A = 0.5, B = 1.0 / 6.0;
+    } else {
+      A = (1.0 - cos(theta)) / (theta * theta);
+      B = (theta - sin(theta)) / (theta * theta * theta);
+    }
+  } else {
+    C = (s - 1.0) / sigma;
+    if (theta < eps) {
+      A = ((sigma - 1.0) * s + 1.0) / (sigma * sigma);
+      B = (s * 0.5 * sigma * sigma + s - 1.0 - sigma * s) / (sigma * sigma * sigma);
+    } else {
+      const double a = s * sin(theta), b = s * cos(theta), c = theta * theta + sigma * sigma;
+      A = (a * sigma + (1.0 - b) * theta) / (theta * c);
+      B = (C - ((b - 1.0) * sigma + a * theta) / c) / (theta * theta);
+    }
+  }
+  // W = A [phi]x + B [phi]x^2 + C I ;  t = W tau
+  const double O[3][3] = {{0.0, -phi[2], phi[1]}, {phi[2], 0.0, -phi[0]}, {-phi[1], phi[0], 0.0}};
+  for (int i = 0; i < 3; ++i) {
+    double t = 0.0;
+    for (int j = 0; j < 3; ++j) {
+      double o2 = 0.0;
+      for (int k = 0; k < 3; ++k) o2 += O[i][k] * O[k][j];
+      t += (A * O[i][j] + B * o2 + (i == j ? C : 0.0)) * tau[j];
+    }
+    out[i] = t;
+  }
+  double q[4];
+  if (theta < eps) {
+    q[0] = 0.5 * phi[0], q[1] = 0.5 * phi[1], q[2] = 0.5 * phi[2], q[3] = 1.0;
+  } else {
+    const double k = sin(0.5 * theta) / theta;
+    q[0] = k * phi[0], q[1] = k * phi[1], q[2] = k * phi[2], q[3] = cos(0.5 * theta);
+  }
+  const double qn = sqrt(q[0] * q[0] + q[1] * q[1] + q[2] * q[2] + q[3] * q[3]);
+  for (int i = 0; i < 4; ++i) out[3 + i] = q[i] / qn;
+  out[7] = s;
+}
+
+// Composition a * b (x -> a(b(x))) of [t, q_xyzw, s] poses: tsdf/sim3.py:mul.
+__device__ void sim3_mul_d(const double a[8], const double b[8], double out[8]) {
+  const double x = a[3], y = a[4], z = a[5], w = a[6];
+  const double R[3][3] = {{1 - 2 * (y * y + z * z), 2 * (x * y - z * w), 2 * (x * z + y * w)},
+                          {2 * (x * y + z * w), 1 - 2 * (x * x + z * z), 2 * (y * z - x * w)},
+                          {2 * (x * z - y * w), 2 * (y * z + x * w), 1 - 2 * (x * x + y * y)}};
+  for (int i = 0; i < 3; ++i)
+    out[i] = a[7] * (R[i][0] * b[0] + R[i][1] * b[1] + R[i][2] * b[2]) + a[i];
+  const double bx = b[3], by = b[4], bz = b[5], bw = b[6];
+  double q[4] = {w * bx + x * bw + y * bz - z * by, w * by - x * bz + y * bw + z * bx,
+                 w * bz + x * by - y * bx + z * bw, w * bw - x * bx - y * by - z * bz};
+  const double qn = sqrt(q[0] * q[0] + q[1] * q[1] + q[2] * q[2] + q[3] * q[3]);
+  for (int i = 0; i < 4; ++i) out[3 + i] = q[i] / qn;
+  out[7] = a[7] * b[7];
+}
+
+// (H + damping I) x = -b by Gaussian elimination with partial pivoting (what
+// LAPACK dgesv behind np.linalg.solve does).  false: singular.
+__device__ bool solve7_d(const double *acc, double damping, double x[7]) {
+  double M[7][8];
+  int k = 0;
+  for (int i = 0; i < 7; ++i)
+    for (int j = i; j < 7; ++j) M[i][j] = M[j][i] = acc[k++];
+  for (int i = 0; i < 7; ++i) {
+    M[i][i] += damping;
+    M[i][7] = -acc[28 + i];
+  }
+  for (int c = 0; c < 7; ++c) {
+    int piv = c;
+    for (int r = c + 1; r < 7; ++r)
+      if (fabs(M[r][c]) > fabs(M[piv][c])) piv = r;
+    if (M[piv][c] == 0.0 || !isfinite(M[piv][c])) return false;
+    if (piv != c)
+      for (int j = c; j < 8; ++j) {
+        const double t = M[c][j];
+        M[c][j] = M[piv][j], M[piv][j] = t;
+      }
+    for (int r = c + 1; r < 7; ++r) {
+      const double f = M[r][c] / M[c][c];
+      for (int j = c; j < 8; ++j) M[r][j] -= f * M[c][j];
+    }
+  }
+  for (int i = 6; i >= 0; --i) {
+    double t = M[i][7];
+    for (int j = i + 1; j < 7; ++j) t -= M[i][j] * x[j];
+    x[i] = t / M[i][i];
+  }
+  for (int i = 0; i < 7; ++i)
+    if (!isfinite(x[i])) return false;
+  return true;
+}
+
+__global__ void __launch_bounds__(128)
+    pose_gn_iter_kernel(VolumeDev v, int which, const float *__restrict__ pts_cam,
+                        const double *__restrict__ conf, long long n, PoseOptState *s, float vs,
+                        double voxel_size, double lambda, double damping) {
+  __shared__ int s_last;
+  const int stop = *(volatile int *)&s->stop; // a finished optimisation: later launches idle
+  if (!stop)
+    pose_accumulate<false>(v, which, pts_cam, conf, n, s->pose_f, vs, voxel_size, lambda, s->acc,
+                           nullptr);
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) s_last = atomicAdd(&s->done_blocks, 1u) == gridDim.x - 1;
+  __syncthreads();
+  if (!s_last || threadIdx.x != 0) return;
+  __threadfence();
+  s->done_blocks = 0;
+  if (stop) return;
+  double acc[36];
+  for (int i = 0; i < 36; ++i) {
+    acc[i] = __ldcg(s->acc + i);
+    s->acc[i] = 0.0; // re-armed for the next launch
+  }
+  const int used = (int)(acc[35] + 0.5);
+  s->used = used;
+  double delta[7];
+  if (used < 6 || !solve7_d(acc, damping, delta)) { // :78-79, LinAlgError
+    s->stop = 1;
+    return;
+  }
+  for (int i = 0; i < 7; ++i) delta[i] = (double)(float)delta[i]; // :84 delta in the point dtype
+  double e[8], np[8];
+  sim3_exp_d(delta, e);
+  sim3_mul_d(e, s->pose, np);
+  for (int i = 0; i < 8; ++i) {
+    s->pose[i] = np[i];
+    s->pose_f[i] = (float)np[i];
+  }
+  s->iterations += 1;
+}
+
+extern "C" int b200tsdf_pose_optimize(b200tsdf_t *h, int which, const float *pts_cam_dev,
+                                      const double *conf_dev, int64_t n, double *pose_inout_host,
+                                      double lambda, double damping, int32_t iterations,
+                                      int64_t *used_host, int32_t *iterations_done_host,
+                                      void *stream) {
+  if (!h || n < 0 || (which != 0 && which != 1) || !pose_inout_host || iterations < 0 ||
+      (n > 0 && (!pts_cam_dev || !conf_dev))) {
+    b200_set_error("b200tsdf_pose_optimize: invalid argument");
+    return B200TSDF_E_INVALID;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  B200_CUDA(cudaSetDevice(h->cfg.device));
+  if (!h->opt_state) B200_CUDA(cudaMalloc(&h->opt_state, sizeof(PoseOptState)));
+  PoseOptState init;
+  memset(&init, 0, sizeof(init));
+  for (int i = 0; i < 8; ++i) {
+    init.pose[i] = pose_inout_host[i];
+    init.pose_f[i] = (float)pose_inout_host[i];
+  }
+  // pageable host source: the copy is staged before the call returns to the stream
+  B200_CUDA(cudaMemcpyAsync(h->opt_state, &init, sizeof(init), cudaMemcpyHostToDevice, st));
+  const unsigned grid = (unsigned)((n + 127) / 128);
+  for (int it = 0; it < iterations && grid > 0; ++it)
+    pose_gn_iter_kernel<<<grid, 128, 0, st>>>(h->d, which, pts_cam_dev, conf_dev, (long long)n,
+                                              (PoseOptState *)h->opt_state,
+                                              (float)h->cfg.voxel_size, h->cfg.voxel_size, lambda,
+                                              damping);
+  B200_CUDA(cudaGetLastError());
+  PoseOptState fin;
+  B200_CUDA(cudaMemcpyAsync(&fin, h->opt_state, sizeof(fin), cudaMemcpyDeviceToHost, st));
+  B200_CUDA(cudaStreamSynchronize(st)); // the ONE synchronisation of the optimisation
+  for (int i = 0; i < 8; ++i) pose_inout_host[i] = fin.pose[i];
+  if (used_host) *used_host = fin.used;
+  if (iterations_done_host) *iterations_done_host = fin.iterations;
+  return B200TSDF_OK;
 }
 
 // ------------------------------------- sharded query (multi-GPU)

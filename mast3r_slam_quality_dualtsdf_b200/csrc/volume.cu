@@ -141,6 +141,7 @@ extern "C" int b200tsdf_destroy(b200tsdf_t *h) {
   cudaFree(h->sched);
   cudaFree(h->tile_list);
   cudaFree(h->sub_thr);
+  cudaFree(h->opt_state);
   cudaFree(h->nbr);
   cudaFree(h->stage_dev);
   if (h->copy_stream) {

@@ -339,6 +339,23 @@ class TSDFVolume:
                 "pose_normal_equations")
         return H, b, int(used.value)
 
+    def pose_optimize(self, pts_cam, conf, pose, lam, damping, iterations, which: int = 0):
+        """`iterations` Gauss-Newton iterations of the TSDF pose optimiser entirely
+        on the device (linearise, 7x7 solve, Sim3 retraction; one launch each, one
+        synchronisation at the end): returns (pose (8,) float64 ndarray, used,
+        iterations_done).  pts_cam (n,3) float32 / conf (n,) float64 device
+        tensors, pose 8 values [t, q_xyzw, s]."""
+        pts = pts_cam.to(self.device, torch.float32).reshape(-1, 3).contiguous()
+        cf = conf.to(self.device, torch.float64).reshape(-1).contiguous()
+        ps = np.ascontiguousarray(np.asarray(pose, np.float64).reshape(8)).copy()
+        used, done = C.c_int64(), C.c_int32()
+        with self._reading():
+            _ffi.check(_ffi.lib().b200tsdf_pose_optimize(
+                self._h, which, pts.data_ptr(), cf.data_ptr(), pts.shape[0],
+                ps.ctypes.data_as(C.c_void_p), float(lam), float(damping), int(iterations),
+                C.byref(used), C.byref(done), _stream_ptr(self.device)), "pose_optimize")
+        return ps, int(used.value), int(done.value)
+
     # -- sharded query (multi-GPU): taps of this handle, merged by the caller --
     def query_taps(self, points, which: int = 0, pose=None):
         """Step 1 of a sharded query: (M, 16) float32 records of the 7 voxels

@@ -32,6 +32,8 @@ class TSDFPoseOptimizer:
         self.damping = float(cfg.get("damping", 1.0e-4))
         self.pre_icp_iters = int(cfg.get("pre_icp_iters", 0))
         self.which = int(cfg.get("optimize_against", 0))  # 0 primary, 1 quality-weighted volume
+        # False: linearise on the device, solve with numpy on the host (one sync per iteration)
+        self.device_solve = bool(cfg.get("device_solve", True))
         self.last_info = {}
 
     # ------------------------------------------------------------------
@@ -73,7 +75,15 @@ class TSDFPoseOptimizer:
         conf_sel = conf[choice].to(self.device, torch.float64)
         pose = pose0.to(torch.float64).cpu()
         used = 0
-        for _ in range(iterations):
+        on_device = hasattr(self.volume, "pose_optimize") and self.device_solve
+        if on_device:
+            # :72-92 as `iterations` launches and ONE synchronisation: the 7x7 solve and the
+            # Sim3 retraction run in the last block of every linearisation launch
+            new_pose, used, _ = self.volume.pose_optimize(
+                pts_cam, conf_sel, pose.numpy(), self.lambda_tsdf, self.damping, iterations,
+                self.which)
+            pose = torch.from_numpy(new_pose)
+        for _ in range(0 if on_device else iterations):
             # :76 + :94-116 fused: float32 Sim3 act, query, Jacobian, 7x7 reduction
             H, b, used = self.volume.pose_normal_equations(
                 pts_cam, conf_sel, pose.to(torch.float32).numpy(), self.lambda_tsdf, self.which)

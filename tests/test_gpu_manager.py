@@ -61,6 +61,37 @@ def test_pose_optimizer_matches_reference_golden(cuda_device, case):
     assert np.allclose(got, _canon_q(ref), rtol=tol, atol=tol * 0.1)
 
 
+def test_device_gauss_newton_equals_host_solve(cuda_device):
+    """the whole loop of _optimize_single on the device
+    (b200tsdf_pose_optimize: one launch per iteration -- linearise, 7x7 solve,
+    Sim3 retraction -- and one synchronisation) against the same loop with the
+    solve in numpy on the host after every linearisation."""
+    from mast3r_slam_quality_dualtsdf_b200.tsdf import TSDFPoseOptimizer, TSDFVolume
+
+    kf, bad = mg.scene()
+    vol = TSDFVolume(mg.VOXEL, mg.TRUNC, device=cuda_device)
+    vol.integrate_keyframes(*(torch.from_numpy(kf[k]).to(cuda_device) for k in ("X", "C", "pose")),
+                            None, mg.CFG["min_confidence"], mg.H, mg.W)
+    out = {}
+    for dev_solve in (True, False):
+        kfs = _keyframes(kf, [kf["pose"][0], bad, kf["pose"][2]], cuda_device)
+        opt = TSDFPoseOptimizer(vol, kfs, dict(mg.CFG, device_solve=dev_solve, max_iterations=3),
+                                False, cuda_device)
+        opt._optimize_single(1, iterations=3, choice=G["choice"])
+        out[dev_solve] = (_canon_q(kfs.T_WC[1].cpu().numpy().reshape(8)), opt.last_info["used"])
+    assert out[True][1] == out[False][1] > 50
+    # same float64 normal equations, LU with partial pivoting on both sides
+    assert np.allclose(out[True][0], out[False][0], rtol=1e-6, atol=1e-7), out
+    # direct call: iteration count and the early stop of an empty volume (:78-79)
+    pts = torch.from_numpy(kf["X"][1][G["choice"]]).to(cuda_device)
+    conf = torch.from_numpy(kf["C"][1][G["choice"]]).to(cuda_device, torch.float64)
+    pose, used, done = vol.pose_optimize(pts, conf, bad, mg.CFG["lambda"], 1e-4, 3)
+    assert done == 3 and used > 50 and np.isfinite(pose).all()
+    empty = TSDFVolume(mg.VOXEL, mg.TRUNC, device=cuda_device)
+    pose0, used0, done0 = empty.pose_optimize(pts, conf, bad, mg.CFG["lambda"], 1e-4, 3)
+    assert done0 == 0 and used0 == 0 and np.allclose(pose0, np.asarray(bad, np.float64))
+
+
 def test_normal_equations_match_oracle(cuda_device):
     from mast3r_slam_quality_dualtsdf_b200.tsdf import TSDFPoseOptimizer, TSDFVolume
     from mast3r_slam_quality_dualtsdf_b200.tsdf import sim3
