@@ -219,6 +219,23 @@ int b200tsdf_export_blocks(b200tsdf_t *h, int64_t *bkeys_dev, int64_t cap,
 int b200tsdf_extract_mesh(b200tsdf_t *h, int which, float *verts_dev,
                           int64_t tri_cap, int64_t *n_tris_host, void *stream);
 
+/* The same mesh INDEXED: unique vertices + int32 faces.  Vertices
+ * that marching cubes computes on a shared cube edge are bit-identical, so the
+ * weld is an exact de-duplication, done on the device (csrc/weld.cu: hash table
+ * keyed by the 96-bit position, smallest soup index wins, exclusive scan).
+ * verts_dev: vert_cap x 3 float32, faces_dev: tri_cap x 3 int32 (either may be
+ * NULL / too small: the counts are still returned, so the two-call protocol of
+ * b200tsdf_extract_mesh applies to both).  Vertex order = first occurrence in
+ * the soup.  Synchronises. */
+int b200tsdf_extract_mesh_indexed(b200tsdf_t *h, int which, float *verts_dev, int64_t vert_cap,
+                                  int32_t *faces_dev, int64_t tri_cap, int64_t *n_verts_host,
+                                  int64_t *n_tris_host, void *stream);
+/* The weld alone, for a soup the caller holds (e.g. the gathered per-rank meshes
+ * of a sharded volume, whose seam vertices agree bit for bit): soup_dev
+ * n_tris x 9 float32; faces_dev n_tris x 3 int32 or NULL. */
+int b200tsdf_weld_mesh(int32_t device, const float *soup_dev, int64_t n_tris, float *verts_dev,
+                       int64_t vert_cap, int32_t *faces_dev, int64_t *n_verts_host, void *stream);
+
 /* ---- multi-GPU seams (no reference counterpart) ---------------
  * Marching cubes over the top voxel layer of a z-slab needs the first layer of
  * the slab above, which another rank owns.  export_seam_blocks dumps the voxel

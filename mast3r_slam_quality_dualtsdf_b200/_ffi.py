@@ -21,7 +21,8 @@ SYMBOLS = [
     "b200tsdf_integrate_keyframes_host", "b200tsdf_deintegrate_keyframes",
     "b200tsdf_integrate_keyframes_ex", "b200tsdf_selftest_div", "b200tsdf_counters", "b200tsdf_stats",
     "b200tsdf_query", "b200tsdf_export_voxels", "b200tsdf_export_blocks",
-    "b200tsdf_extract_mesh", "b200tsdf_export_seam_blocks", "b200tsdf_import_halo_blocks",
+    "b200tsdf_extract_mesh", "b200tsdf_extract_mesh_indexed", "b200tsdf_weld_mesh",
+    "b200tsdf_export_seam_blocks", "b200tsdf_import_halo_blocks",
     "b200tsdf_export_block_data", "b200tsdf_import_blocks",
     "b200tsdf_local_dims", "b200tsdf_local_build",
     "b200tsdf_local_raycast", "b200tsdf_quality_patch_grids", "b200tsdf_quality_classify",
@@ -97,6 +98,8 @@ def lib():
     L.b200tsdf_export_voxels.argtypes = [vp, C.c_int, vp, vp, vp, vp, i64, vp, vp]
     L.b200tsdf_export_blocks.argtypes = [vp, vp, i64, vp, vp]
     L.b200tsdf_extract_mesh.argtypes = [vp, C.c_int, vp, i64, vp, vp]
+    L.b200tsdf_extract_mesh_indexed.argtypes = [vp, C.c_int, vp, i64, vp, i64, vp, vp, vp]
+    L.b200tsdf_weld_mesh.argtypes = [i32, vp, i64, vp, i64, vp, vp, vp]
     L.b200tsdf_export_seam_blocks.argtypes = [vp, vp, vp, vp, i64, vp, vp]
     L.b200tsdf_import_halo_blocks.argtypes = [vp, vp, vp, vp, i64, vp]
     L.b200tsdf_export_block_data.argtypes = [vp, vp, vp, vp, i64, vp, vp]

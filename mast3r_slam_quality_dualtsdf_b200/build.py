@@ -10,7 +10,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libb200tsdf.so")
-SOURCES = ["volume.cu", "integrate.cu", "sweep.cu", "mc.cu", "local.cu", "quality.cu"]
+SOURCES = ["volume.cu", "integrate.cu", "sweep.cu", "mc.cu", "weld.cu", "local.cu", "quality.cu"]
 HEADERS = ["common.cuh", "ray.cuh", "march_fast.cuh", "fuse.cuh", "fuse_fast.cuh", "march_key.h",
            "sim3.cuh", "mc_tables.h", os.path.join("..", "..", "include", "b200tsdf.h")]
 NVCC_FLAGS = [

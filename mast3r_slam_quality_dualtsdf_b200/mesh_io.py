@@ -22,11 +22,19 @@ def weld(tri_soup, decimals=7):
     return v[first], inv.reshape(-1, 3).astype(np.int32)
 
 
-def save_mesh_ply(path, tri_soup, weld_vertices=True):
-    """Write the mesh; returns (n_vertices, n_faces)."""
+def save_mesh_ply(path, tri_soup, weld_vertices=True, faces=None):
+    """Write the mesh; returns (n_vertices, n_faces).  `tri_soup` is a triangle
+    soup (welded here on the host) or, with `faces` (T,3) int32, the vertex
+    array of an already indexed mesh (`TSDFVolume.extract_mesh_indexed`: the
+    weld ran on the device)."""
     if hasattr(tri_soup, "detach"):
         tri_soup = tri_soup.detach().cpu().numpy()
-    if weld_vertices:
+    if faces is not None:
+        if hasattr(faces, "detach"):
+            faces = faces.detach().cpu().numpy()
+        verts = np.ascontiguousarray(np.asarray(tri_soup, np.float32).reshape(-1, 3))
+        faces = np.ascontiguousarray(np.asarray(faces, np.int32).reshape(-1, 3))
+    elif weld_vertices:
         verts, faces = weld(tri_soup)
     else:
         verts = np.ascontiguousarray(np.asarray(tri_soup, np.float32).reshape(-1, 3))

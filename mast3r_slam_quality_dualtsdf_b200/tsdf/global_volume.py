@@ -57,6 +57,24 @@ def pack_keyframes(X, Cf, poses, q_grid=None, out=None):
     return out
 
 
+def weld_mesh(tri_soup):
+    """Exact weld of a device triangle soup (3T,3) / (T,3,3) float32 on the
+    device (b200tsdf_weld_mesh): (verts (V,3) f32, faces (T,3) i32).  Used for
+    the gathered per-rank meshes of a sharded volume, whose seam vertices agree
+    bit for bit."""
+    soup = tri_soup.reshape(-1, 3).contiguous()
+    if not soup.is_cuda or soup.dtype != torch.float32:
+        raise ValueError("weld_mesh needs a float32 device tensor")
+    nt = soup.shape[0] // 3
+    nv = C.c_int64()
+    faces = torch.empty(max(nt, 1), 3, dtype=torch.int32, device=soup.device)
+    verts = torch.empty(max(3 * nt, 1), 3, dtype=torch.float32, device=soup.device)
+    _ffi.check(_ffi.lib().b200tsdf_weld_mesh(
+        soup.device.index or 0, soup.data_ptr(), nt, verts.data_ptr(), 3 * nt, faces.data_ptr(),
+        C.byref(nv), C.c_void_p(torch.cuda.current_stream(soup.device).cuda_stream)), "weld_mesh")
+    return verts[: nv.value].clone(), faces[:nt]
+
+
 class TSDFVolume:
     """Sparse dual TSDF volume (voxel-block hash on the GPU)."""
 
@@ -501,6 +519,24 @@ class TSDFVolume:
                            "extract_mesh")
             self._last_tris = n.value
         return out[: n.value * 3]
+
+    def extract_mesh_indexed(self, which: int = 0):
+        """Marching cubes + weld on the device: (verts f32 (V,3), faces i32 (T,3))
+        device tensors.  Shared vertices are stored once; vertex
+        order is the order of first occurrence in the triangle soup."""
+        nv, nt = C.c_int64(), C.c_int64()
+        L = _ffi.lib()
+        with self._reading():
+            _ffi.check(L.b200tsdf_extract_mesh_indexed(self._h, which, None, 0, None, 0,
+                                                       C.byref(nv), C.byref(nt),
+                                                       _stream_ptr(self.device)), "extract_mesh")
+            verts = torch.empty(max(nv.value, 1), 3, dtype=torch.float32, device=self.device)
+            faces = torch.empty(max(nt.value, 1), 3, dtype=torch.int32, device=self.device)
+            if nt.value:
+                _ffi.check(L.b200tsdf_extract_mesh_indexed(
+                    self._h, which, verts.data_ptr(), nv.value, faces.data_ptr(), nt.value,
+                    C.byref(nv), C.byref(nt), _stream_ptr(self.device)), "extract_mesh_indexed")
+        return verts[: nv.value], faces[: nt.value]
 
     # ------------------------------------------------------------------
     # Multi-GPU seams (see parallel.ShardedTSDFVolume)

@@ -75,8 +75,8 @@ def test_device_gauss_newton_equals_host_solve(cuda_device):
     out = {}
     for dev_solve in (True, False):
         kfs = _keyframes(kf, [kf["pose"][0], bad, kf["pose"][2]], cuda_device)
-        opt = TSDFPoseOptimizer(vol, kfs, dict(mg.CFG, device_solve=dev_solve, max_iterations=3),
-                                False, cuda_device)
+        opt = TSDFPoseOptimizer(vol, kfs, dict(mg.CFG, device_solve=dev_solve, max_iterations=3,
+                                               damping=500.0), False, cuda_device)
         opt._optimize_single(1, iterations=3, choice=G["choice"])
         out[dev_solve] = (_canon_q(kfs.T_WC[1].cpu().numpy().reshape(8)), opt.last_info["used"])
     assert out[True][1] == out[False][1] > 50
@@ -85,10 +85,14 @@ def test_device_gauss_newton_equals_host_solve(cuda_device):
     # direct call: iteration count and the early stop of an empty volume (:78-79)
     pts = torch.from_numpy(kf["X"][1][G["choice"]]).to(cuda_device)
     conf = torch.from_numpy(kf["C"][1][G["choice"]]).to(cuda_device, torch.float64)
-    pose, used, done = vol.pose_optimize(pts, conf, bad, mg.CFG["lambda"], 1e-4, 3)
+    pose, used, done = vol.pose_optimize(pts, conf, bad, mg.CFG["lambda"], 500.0, 3)
     assert done == 3 and used > 50 and np.isfinite(pose).all()
+    # the undamped system of this scene runs away after one step: the loop stops like the
+    # reference's `if used < 6: break` (:78-79), on the device as on the host
+    _, used_u, done_u = vol.pose_optimize(pts, conf, bad, mg.CFG["lambda"], 1e-4, 3)
+    assert done_u < 3 and used_u < 6
     empty = TSDFVolume(mg.VOXEL, mg.TRUNC, device=cuda_device)
-    pose0, used0, done0 = empty.pose_optimize(pts, conf, bad, mg.CFG["lambda"], 1e-4, 3)
+    pose0, used0, done0 = empty.pose_optimize(pts, conf, bad, mg.CFG["lambda"], 500.0, 3)
     assert done0 == 0 and used0 == 0 and np.allclose(pose0, np.asarray(bad, np.float64))
 
 

@@ -119,3 +119,46 @@ def test_mesh_stitched_at_slab_seams(cuda_device, world, width):
     want = single.extract_mesh(0).cpu().numpy().reshape(-1, 3, 3)
     got = np.concatenate([v.extract_mesh(0).cpu().numpy().reshape(-1, 3, 3) for v in ranks])
     assert _same_soup(got, want)
+
+
+def test_indexed_mesh_equals_host_weld_of_the_soup(cuda_device, tmp_path):
+    """SURVEY 8(b) / VERDICT r1 #3: verts + int32 faces produced on the device
+    (csrc/weld.cu).  The indexed mesh reconstructs the soup bit for bit, has
+    exactly as many vertices as the host weld (np.unique on the 96-bit
+    positions, mesh_io.weld) and the same vertex set; it is watertight-manifold
+    where the soup is; and the PLY writer stores it unchanged."""
+    from mast3r_slam_quality_dualtsdf_b200 import mesh_io
+    from mast3r_slam_quality_dualtsdf_b200.tsdf import TSDFVolume
+    from mast3r_slam_quality_dualtsdf_b200.tsdf.global_volume import weld_mesh
+
+    kf = synth.make_keyframes(synth.SCENES["sphere"], 4, H=48, W=64, seed=4, f=50.0, total=12)
+    vol = TSDFVolume(0.02, 0.08, device=cuda_device)
+    vol.integrate_keyframes(*(torch.from_numpy(kf[k]).to(cuda_device) for k in ("X", "C", "pose")),
+                            torch.from_numpy(kf["q"]).to(cuda_device), 0.05, 48, 64)
+    for which in (0, 1):
+        soup = vol.extract_mesh(which)
+        verts, faces = vol.extract_mesh_indexed(which)
+        s = soup.cpu().numpy().reshape(-1, 3, 3)
+        v, f = verts.cpu().numpy(), faces.cpu().numpy()
+        assert f.shape == (len(s), 3) and f.dtype == np.int32 and len(s) > 1000
+        assert f.min() >= 0 and f.max() == len(v) - 1
+        hv, hf = mesh_io.weld(s)
+        assert len(v) == len(hv) < 3 * len(s)
+        # same triangle multiset (the two MC passes may order triangles differently)
+        assert np.array_equal(_canon(v[f]), _canon(s))
+        key = lambda a: np.sort(np.ascontiguousarray(a).view(np.dtype((np.void, 12))).reshape(-1))
+        assert np.array_equal(key(v), key(hv))
+        # the weld alone on the soup the caller holds: reconstructs it in order
+        wv, wf = weld_mesh(soup)
+        assert np.array_equal(wv.cpu().numpy()[wf.cpu().numpy()], s)
+        first = wf.cpu().numpy().reshape(-1)
+        # vertex order = first occurrence in the soup
+        _, idx = np.unique(first, return_index=True)
+        assert np.array_equal(first[np.sort(idx)], np.arange(len(wv)))
+    path = str(tmp_path / "m.ply")
+    nv, nf = mesh_io.save_mesh_ply(path, verts, faces=faces)
+    rv, rf = mesh_io.load_mesh_ply(path)
+    assert (nv, nf) == (len(v), len(f)) and np.array_equal(rv, v) and np.array_equal(rf, f)
+    # empty volume: empty indexed mesh
+    ev, ef = TSDFVolume(0.02, 0.08, device=cuda_device).extract_mesh_indexed(0)
+    assert ev.shape == (0, 3) and ef.shape == (0, 3)
