@@ -98,13 +98,15 @@ class ShardedTSDFVolume:
         return tuple(res)
 
     def integrate_keyframes(self, X, Cf, poses, q_grid=None, min_conf=0.05, H=None, W=None,
-                            step_scale=0.5, src=0, broadcast=True, ids=None):
+                            step_scale=0.5, src=0, broadcast=True, ids=None, max_points=0,
+                            seed=0, kf_ids=None):
         """Fuse one batch on every rank.  With `ids` (one int per keyframe, the
         same list on every rank) the batch is also kept in this rank's
         keyframe store, so that `reintegrate` later needs the new poses only."""
         if broadcast:
             self.broadcast_keyframes(X, Cf, poses, q_grid, src)
-        self.vol.integrate_keyframes(X, Cf, poses, q_grid, min_conf, H, W, step_scale)
+        sub = dict(max_points=max_points, seed=seed, kf_ids=kf_ids) if max_points else {}
+        self.vol.integrate_keyframes(X, Cf, poses, q_grid, min_conf, H, W, step_scale, **sub)
         if ids is not None:
             ids = [int(i) for i in ids]
             if len(ids) != int(X.shape[0]):
