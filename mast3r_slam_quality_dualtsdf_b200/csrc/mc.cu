@@ -10,6 +10,7 @@
 // atomicAdd per warp on the global triangle counter (warp-scan compaction);
 // triangles are then emitted one per lane (balanced within the warp).
 #include <math.h>
+#include <stdlib.h>
 
 #include "common.cuh"
 
@@ -229,6 +230,202 @@ __global__ void __launch_bounds__(MC_THREADS, MC_CTAS_PER_SM)
   }
 }
 
+// ---------------------------------------------------------------------------
+// mc_kernel2: the same extraction with the classification done on BIT PLANES.
+// mc_kernel spends 8 shared loads + 16 ALU per cube on the case index and three
+// CTA barriers per block on unevenly loaded warps (ncu: barrier stall 5.6 per
+// issue, 34 % of HBM).  Here the conversion pass also ballots a sign and a
+// validity bit per lattice point into two 729-bit planes; 64 threads then
+// classify the block's 64 cube ROWS with 9-bit extracts (a row of 8 cubes in
+// ~40 instructions: all-valid / all-inside / all-outside by AND of shifted
+// rows), list the few active cubes with their case index, and a two-warp scan
+// gives every active cube its triangle offset -- ONE atomicAdd per block.
+// Emission is one triangle per thread (binary search over the cube scan), so
+// stores are coalesced and no lane idles behind a 5-triangle cube.  Blocks
+// without a sign change (most of a band's blocks) stop after the row pass.
+#define MC2_CUBE_CAP 512
+template <bool WRITE>
+__global__ void __launch_bounds__(MC_THREADS, MC_CTAS_PER_SM)
+    mc_kernel2(VolumeDev v, const uint32_t *__restrict__ nbr, int which, float vs,
+               float *__restrict__ verts, long long tri_cap, unsigned long long *n_tris) {
+  __shared__ float tv[9 * 9 * 9 + 7];
+  __shared__ __align__(16) float2 r_sw[2][9 * 9 * 9 + 7];
+  __shared__ uint32_t r_h[2][9 * 9 * 9 + 7];
+  __shared__ uint32_t s_nb[8];
+  __shared__ unsigned long long s_key[2], s_base; // s_key[it & 1]: emission of block b reads it
+                                                 // while thread 0 already stores the next key
+  __shared__ __align__(16) signed char s_tri[256 * 16];
+  __shared__ unsigned char s_num[256];
+  __shared__ uint32_t p_sgn[24], p_val[24]; // bit planes over the lattice index z*81 + y*9 + x
+  __shared__ uint32_t s_cube[MC2_CUBE_CAP];       // active cubes: id | case << 9
+  __shared__ uint32_t s_scan[MC2_CUBE_CAP + 1];   // exclusive scan of their triangle counts
+  __shared__ uint32_t s_w0, s_tot;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (tid < 256) {
+    reinterpret_cast<int4 *>(s_tri)[tid] = reinterpret_cast<const int4 *>(MC_TRI_TABLE)[tid];
+    s_num[tid] = MC_NUM_TRIS[tid];
+  }
+  int pk[MC_PTS];
+#pragma unroll
+  for (int j = 0; j < MC_PTS; ++j) {
+    const int i = tid + j * MC_THREADS;
+    const int x = i % 9, y = (i / 9) % 9, z = i / 81;
+    const int nbk = (x == 8) | ((y == 8) << 1) | ((z == 8) << 2);
+    pk[j] = i < 729 ? ((((z & 7) << 6) | ((y & 7) << 3) | (x & 7)) | (nbk << 9)) : -1;
+  }
+  const char *vox_b = reinterpret_cast<const char *>(v.vox) + which * 8;
+  const char *cnt_b = reinterpret_cast<const char *>(v.cnt) + which * 4;
+  auto prefetch = [&](int buf) {
+#pragma unroll
+    for (int j = 0; j < MC_PTS; ++j) {
+      if (pk[j] < 0) continue;
+      const int i = tid + j * MC_THREADS;
+      const uint32_t s = s_nb[pk[j] >> 9];
+      if (s != B200_NO_SLOT) {
+        const size_t off = (size_t)s * B200_BLOCK_VOX + (pk[j] & 511);
+        cp_async8(&r_sw[buf][i], vox_b + off * sizeof(float4));
+        cp_async4(&r_h[buf][i], cnt_b + off * sizeof(unsigned long long));
+      } else {
+        r_h[buf][i] = 0u;
+      }
+    }
+    cp_async_commit();
+  };
+  const uint32_t nb = (uint32_t)v.ctr[CTR_BLOCKS];
+  const uint32_t g = gridDim.x;
+  uint32_t b = blockIdx.x;
+  if (b >= nb) return;
+  uint32_t nbA = B200_NO_SLOT;
+  unsigned long long keyA = 0;
+  if (tid < 8) s_nb[tid] = nbr[(size_t)b * 8 + tid];
+  __syncthreads();
+  prefetch(0);
+  if (tid == 0) keyA = v.keys[s_nb[0]];
+  if (tid < 8 && b + g < nb) nbA = nbr[(size_t)(b + g) * 8 + tid];
+  __syncthreads();
+  for (uint32_t it = 0; b < nb; b += g, ++it) {
+    const int buf = it & 1;
+    if (tid < 8) s_nb[tid] = nbA;
+    if (tid == 0) s_key[buf] = keyA;
+    __syncthreads(); // previous block fully emitted; s_nb / s_key of this iteration visible
+    if (b + g < nb) {
+      prefetch(buf ^ 1);
+      if (tid == 0) keyA = v.keys[s_nb[0]];
+      if (tid < 8) nbA = b + 2 * g < nb ? nbr[(size_t)(b + 2 * g) * 8 + tid] : B200_NO_SLOT;
+      cp_async_wait<1>();
+    } else {
+      cp_async_wait<0>();
+    }
+    __syncthreads(); // raw words of block b have landed for every thread
+    // ---- conversion: VoxelData view of every lattice point + the two bit planes
+#pragma unroll
+    for (int j = 0; j < MC_PTS; ++j) {
+      const int i = tid + j * MC_THREADS;
+      float val = NAN;
+      if (pk[j] >= 0) {
+        const uint32_t hits = r_h[buf][i];
+        if (hits != 0) { // voxel_view (common.cuh) on the staged words
+          const float2 sw = r_sw[buf][i];
+          const float w = (hits == 1) ? sw.y : fminf(sw.y, v.max_weight);
+          if (w >= v.min_weight) val = sw.x / fmaxf(1.0e-9f, w);
+        }
+        tv[i] = val;
+      }
+      const unsigned bs = __ballot_sync(0xFFFFFFFFu, val < 0.0f);
+      const unsigned bv = __ballot_sync(0xFFFFFFFFu, !isnan(val));
+      if (lane == 0) p_sgn[warp + 8 * j] = bs, p_val[warp + 8 * j] = bv;
+    }
+    __syncthreads();
+    // ---- rows: thread r < 64 owns the 8 cubes (x = 0..7, y = r & 7, z = r >> 3)
+    if (warp < 2) {
+      const int y = tid & 7, z = tid >> 3, base = 81 * z + 9 * y;
+      auto ext = [&](const uint32_t *a, int pos) {
+        const int w = pos >> 5;
+        return __funnelshift_r(a[w], w + 1 < 24 ? a[w + 1] : 0u, pos & 31) & 0x1FFu;
+      };
+      const uint32_t s0 = ext(p_sgn, base), s1 = ext(p_sgn, base + 9), s2 = ext(p_sgn, base + 81),
+                     s3 = ext(p_sgn, base + 90);
+      const uint32_t v0 = ext(p_val, base), v1 = ext(p_val, base + 9), v2 = ext(p_val, base + 81),
+                     v3 = ext(p_val, base + 90);
+      const uint32_t vc = (v0 & (v0 >> 1)) & (v1 & (v1 >> 1)) & (v2 & (v2 >> 1)) & (v3 & (v3 >> 1));
+      const uint32_t in1 = (s0 & (s0 >> 1)) & (s1 & (s1 >> 1)) & (s2 & (s2 >> 1)) & (s3 & (s3 >> 1));
+      const uint32_t o0 = ~s0, o1 = ~s1, o2 = ~s2, o3 = ~s3;
+      const uint32_t in0 = (o0 & (o0 >> 1)) & (o1 & (o1 >> 1)) & (o2 & (o2 >> 1)) & (o3 & (o3 >> 1));
+      uint32_t act = vc & ~(in1 | in0) & 0xFFu; // all 8 corners observed, signs mixed
+      uint32_t ta = 0;
+      for (uint32_t a = act; a; a &= a - 1) {
+        const int x = __ffs(a) - 1;
+        const uint32_t m = ((s0 >> x) & 3u) | (((s1 >> x) & 3u) << 2) | (((s2 >> x) & 3u) << 4) |
+                           (((s3 >> x) & 3u) << 6);
+        ta += s_num[m];
+      }
+      // two-warp scan of (cubes << 16 | triangles) over the 64 rows
+      const uint32_t mine = ((uint32_t)__popc(act) << 16) | ta;
+      uint32_t incl = mine;
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        const uint32_t o = __shfl_up_sync(0xFFFFFFFFu, incl, d);
+        if (lane >= d) incl += o;
+      }
+      if (tid == 31) s_w0 = incl;
+      asm volatile("bar.sync 1, 64;" ::: "memory"); // the two row warps only
+      if (warp == 1) incl += s_w0;
+      uint32_t co = (incl - mine) >> 16, to = (incl - mine) & 0xFFFFu;
+      for (uint32_t a = act; a; a &= a - 1) {
+        const int x = __ffs(a) - 1;
+        const uint32_t m = ((s0 >> x) & 3u) | (((s1 >> x) & 3u) << 2) | (((s2 >> x) & 3u) << 4) |
+                           (((s3 >> x) & 3u) << 6);
+        s_cube[co] = (uint32_t)(tid * 8 + x) | (m << 9);
+        s_scan[co] = to;
+        ++co;
+        to += s_num[m];
+      }
+      if (tid == 63) { // totals: ONE atomicAdd reserves the block's output run
+        const uint32_t A = incl >> 16, T = incl & 0xFFFFu;
+        s_scan[A] = T;
+        s_tot = incl;
+        if (T) s_base = atomicAdd(n_tris, (unsigned long long)T);
+      }
+    }
+    __syncthreads();
+    if (!WRITE) continue;
+    const uint32_t A = s_tot >> 16, T = s_tot & 0xFFFFu;
+    if (T == 0) continue;
+    int bx, by, bz;
+    unpack_block_key(s_key[buf], bx, by, bz);
+    const unsigned long long base_o = s_base;
+    // ---- emission: one triangle per thread
+    for (uint32_t k = tid; k < T; k += MC_THREADS) {
+      uint32_t lo = 0, hi = A; // largest c with s_scan[c] <= k
+      while (hi - lo > 1) {
+        const uint32_t mid = (lo + hi) >> 1;
+        if (s_scan[mid] <= k) lo = mid; else hi = mid;
+      }
+      const uint32_t ent = s_cube[lo];
+      const int q = (int)(k - s_scan[lo]), c = (int)(ent & 511u), m = (int)(ent >> 9);
+      const int x = c & 7, y = (c >> 3) & 7, z = c >> 6;
+      const long long o = (long long)base_o + k;
+      if (o >= tri_cap) continue;
+#pragma unroll
+      for (int vtx = 0; vtx < 3; ++vtx) {
+        const int e = s_tri[m * 16 + 3 * q + vtx];
+        const int a = MC_EDGE_CORNERS[e][0], bb = MC_EDGE_CORNERS[e][1];
+        const int ax = x + (a & 1), ay = y + ((a >> 1) & 1), az = z + (a >> 2);
+        const int cx = x + (bb & 1), cy = y + ((bb >> 1) & 1), cz = z + (bb >> 2);
+        const float ta = tv[az * 81 + ay * 9 + ax], tb = tv[cz * 81 + cy * 9 + cx];
+        const float mu = __fdiv_rn(ta, __fsub_rn(ta, tb));
+        const float pa[3] = {__fmul_rn((float)(bx * 8 + ax), vs), __fmul_rn((float)(by * 8 + ay), vs),
+                             __fmul_rn((float)(bz * 8 + az), vs)};
+        const float pb[3] = {__fmul_rn((float)(bx * 8 + cx), vs), __fmul_rn((float)(by * 8 + cy), vs),
+                             __fmul_rn((float)(bz * 8 + cz), vs)};
+#pragma unroll
+        for (int d = 0; d < 3; ++d)
+          verts[o * 9 + vtx * 3 + d] = __fadd_rn(pa[d], __fmul_rn(__fsub_rn(pb[d], pa[d]), mu));
+      }
+    }
+  }
+}
+
 extern "C" int b200tsdf_extract_mesh(b200tsdf_t *h, int which, float *verts_dev, int64_t tri_cap,
                                      int64_t *n_tris_host, void *stream) {
   if (!h || !n_tris_host || (which != 0 && which != 1) || tri_cap < 0) {
@@ -240,13 +437,27 @@ extern "C" int b200tsdf_extract_mesh(b200tsdf_t *h, int which, float *verts_dev,
   B200_CUDA(cudaMemsetAsync(h->scratch, 0, 8, st));
   const float vs = (float)h->cfg.voxel_size;
   if (!h->nbr) B200_CUDA(cudaMalloc(&h->nbr, h->cap * 8 * sizeof(uint32_t)));
-  mc_neighbors_kernel<<<148 * 8, 256, 0, st>>>(h->d, h->nbr);
-  if (verts_dev && tri_cap > 0)
-    mc_kernel<true><<<148 * MC_CTAS_PER_SM, MC_THREADS, 0, st>>>(h->d, h->nbr, which, vs, verts_dev,
-                                                     (long long)tri_cap, h->scratch);
-  else
-    mc_kernel<false><<<148 * MC_CTAS_PER_SM, MC_THREADS, 0, st>>>(h->d, h->nbr, which, vs, nullptr, 0,
-                                                      h->scratch);
+  const unsigned sms = (unsigned)(h->sm_count > 0 ? h->sm_count : 148);
+  mc_neighbors_kernel<<<sms * 8, 256, 0, st>>>(h->d, h->nbr);
+  static const int v1 = [] {
+    const char *e = getenv("B200TSDF_MC_V1"); // A/B knob: 1 = the per-cube classification kernel
+    return e ? atoi(e) : 0;
+  }();
+  const bool wr = verts_dev && tri_cap > 0;
+  const unsigned grid = sms * MC_CTAS_PER_SM;
+  if (v1) {
+    if (wr)
+      mc_kernel<true><<<grid, MC_THREADS, 0, st>>>(h->d, h->nbr, which, vs, verts_dev,
+                                                   (long long)tri_cap, h->scratch);
+    else
+      mc_kernel<false><<<grid, MC_THREADS, 0, st>>>(h->d, h->nbr, which, vs, nullptr, 0, h->scratch);
+  } else {
+    if (wr)
+      mc_kernel2<true><<<grid, MC_THREADS, 0, st>>>(h->d, h->nbr, which, vs, verts_dev,
+                                                    (long long)tri_cap, h->scratch);
+    else
+      mc_kernel2<false><<<grid, MC_THREADS, 0, st>>>(h->d, h->nbr, which, vs, nullptr, 0, h->scratch);
+  }
   B200_CUDA(cudaGetLastError());
   unsigned long long n;
   B200_CUDA(cudaMemcpyAsync(&n, h->scratch, 8, cudaMemcpyDeviceToHost, st));

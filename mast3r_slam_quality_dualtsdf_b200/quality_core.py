@@ -1,14 +1,18 @@
 """B200 mirror of the reference `mast3r_slam/quality_core.py`.
 
-Same function names, arguments and result dict as the reference
-(quality_core.py:15-140), but every grid is produced by CUDA kernels
-(`csrc/quality.cu` through the C ABI) and STAYS on the device: the reference
-moves each keyframe's maps tensor -> numpy -> queue -> tensor -> numpy
-(tracker.py:129-141, quality_async.py:12-46) before the TSDF path reads them.
-`compute_batch` returns device tensors; `pack_result(..., to_host=True)` gives
-the reference's numpy dict for consumers that want it; `quality_grid(result)`
-is the per-patch weight q = 1 - priority that `TSDFVolume.integrate_keyframes`
-takes as `q_grid`.
+Every public function of the reference keeps its name and arguments
+(quality_core.py:4-140).  The per-keyframe path -- `compute_batch`, `classify`,
+`u_from_CQ`, `r_from_scalar`, `valid_grid` -- runs on CUDA kernels
+(`csrc/quality.cu` through the C ABI) and its grids STAY on the device: the
+reference moves each keyframe's maps tensor -> numpy -> queue -> tensor ->
+numpy (tracker.py:129-141, quality_async.py:12-46) before the TSDF path reads
+them.  Two deliberate differences, both switchable: `compute_batch` /
+`pack_result` return device tensors unless `to_host=True` (then the
+reference's numpy dict), and `quality_grid(result)` is new (the per-patch
+weight q = 1 - priority that `TSDFVolume.integrate_keyframes` takes as
+`q_grid`).  The small tensor helpers `_hw`, `_grid`, `reduce_grid`,
+`upsample_to_hw`, `robust_z` are plain torch as in the reference (they are
+off the keyframe path and work on any device).
 """
 import ctypes as C
 
@@ -37,7 +41,8 @@ def patch_grids(Ck, Qk, r_pix, valid, h, w, ps, C_thr, Q_thr, device):
     (:54-56) of one keyframe in ONE launch: (gh, gw) float32 device tensors."""
     n = h * w
     Ct, Qt, rt = _f32(Ck, device, n), _f32(Qk, device, n), _f32(r_pix, device, n)
-    vt = torch.as_tensor(valid).to(device).reshape(-1)[:n].to(torch.uint8).contiguous()
+    # any non-zero value is valid, like the reference's .to(torch.bool) (:17)
+    vt = (torch.as_tensor(valid).to(device).reshape(-1)[:n] != 0).to(torch.uint8).contiguous()
     gh, gw = h // ps, w // ps
     u, r, v = (torch.empty(gh, gw, dtype=torch.float32, device=device) for _ in range(3))
     _ffi.check(_ffi.lib().b200tsdf_quality_patch_grids(
@@ -45,6 +50,62 @@ def patch_grids(Ck, Qk, r_pix, valid, h, w, ps, C_thr, Q_thr, device):
         float(Q_thr), u.data_ptr(), r.data_ptr(), v.data_ptr(), _dev_index(device),
         _stream(device)), "quality_patch_grids")
     return u, r, v
+
+
+# ---- tensor helpers of the reference (:4-32, :58-61), off the keyframe path ---
+def _hw(x, h, w):
+    """(h*w,) or (h*w, 1) -> (h, w); anything else unchanged (:4-7)."""
+    if x is not None and (x.ndim == 1 or (x.ndim == 2 and x.shape[-1] == 1)):
+        x = x.view(h, w)
+    return x
+
+
+def _grid(x, ps):
+    """(H, W) -> (gh, gw, ps*ps) patch pixels, with gh, gw (:9-13)."""
+    gh, gw = x.shape[-2] // ps, x.shape[-1] // ps
+    return x[:gh * ps, :gw * ps].unfold(0, ps, ps).unfold(1, ps, ps).reshape(gh, gw, ps * ps), gh, gw
+
+
+def reduce_grid(x, h, w, ps, valid=None, method="median"):
+    """Per-patch lower median / mean, over the valid pixels when a mask is given
+    (patches without a valid pixel give 0) (:15-27)."""
+    X, _, _ = _grid(_hw(x, h, w), ps)
+    if valid is not None:
+        M, _, _ = _grid(_hw(valid, h, w).to(torch.bool).float(), ps)
+        X = X.masked_fill(M < 0.5, float("nan"))
+        v = torch.nanmedian(X, dim=-1).values if method == "median" else torch.nanmean(X, dim=-1)
+        return torch.nan_to_num(v, nan=0.0)
+    return torch.nanmedian(X, dim=-1).values if method == "median" else X.mean(-1)
+
+
+def upsample_to_hw(g, h, w, mode="bilinear"):  # :29-32
+    kw = {} if mode == "nearest" else {"align_corners": False}
+    return torch.nn.functional.interpolate(g[None, None], (h, w), mode=mode, **kw)[0, 0]
+
+
+def robust_z(x, eps=1e-6):  # :58-61
+    m = torch.median(x)
+    return (x - m) / (torch.median(torch.abs(x - m)) + eps)
+
+
+def u_from_CQ(C, Q, C_thr, Q_thr, h, w, ps, quant=0.5):
+    """Reference signature (:43-49); on a CUDA tensor the fused patch kernel."""
+    C = torch.as_tensor(C)
+    if C.is_cuda:
+        ones = torch.ones(h * w, dtype=torch.uint8, device=C.device)
+        return patch_grids(C, Q, torch.zeros(h * w, device=C.device), ones, h, w, ps, C_thr, Q_thr,
+                           C.device)[0]
+    Cn = torch.clamp(_hw(C, h, w) / (C_thr + 1e-8), 0, 1)
+    Qn = torch.clamp(_hw(torch.as_tensor(Q), h, w) / (Q_thr + 1e-8), 0, 1)
+    return reduce_grid(1 - torch.sqrt(torch.clamp(Cn * Qn, 0, 1)), h, w, ps, method="median")
+
+
+def r_from_scalar(r, h, w, ps, valid=None):  # :51-52
+    return reduce_grid(r, h, w, ps, valid=valid, method="median")
+
+
+def valid_grid(valid, h, w, ps):  # :54-56
+    return (reduce_grid(torch.as_tensor(valid).float(), h, w, ps, method="mean") > 0).float()
 
 
 def view_weight(t_norm, theta, b0, theta0, device):  # :34-37
@@ -155,7 +216,8 @@ def compute_batch(batch, ps, alpha, b0, theta0, C_thr, Q_thr, thr_zr, thr_zu, th
         g = compute_stacked(_stack(jobs, "Ck", device, torch.float32, npx),
                             _stack(jobs, "Qk", device, torch.float32, npx),
                             _stack(jobs, "r_pix", device, torch.float32, npx),
-                            _stack(jobs, "valid_kf", device, torch.uint8, npx),
+                            (_stack(jobs, "valid_kf", device, torch.float32, npx) != 0)
+                            .to(torch.uint8),
                             _stack(jobs, "t_norm", device, torch.float32, 1).reshape(B),
                             _stack(jobs, "theta", device, torch.float32, 1).reshape(B), prev, h, w,
                             ps, alpha, b0, theta0, C_thr, Q_thr, thr_zr, thr_zu, thr_dc, device)

@@ -18,3 +18,12 @@ for f in build/variants/lib_*.so; do
   n=$(basename $f .so)
   run $n B200TSDF_LIB=$PWD/$f
 done
+# marching cubes A/B on the 594 MB volume (bit-plane kernel vs per-cube kernel)
+if [ "${AB_MC:-1}" = "1" ]; then
+  timeout 600 python scripts/big_volume_sweeps.py --kf 600 --batch 40 2>gpurun_out/ab_mc2.err | python -c "
+import sys,json
+d=json.loads(sys.stdin.read()); print('mc_kernel2', d['extract_mesh'], d['extract_mesh_indexed'], d['stats'])"
+  B200TSDF_MC_V1=1 timeout 600 python scripts/big_volume_sweeps.py --kf 600 --batch 40 2>gpurun_out/ab_mc1.err | python -c "
+import sys,json
+d=json.loads(sys.stdin.read()); print('mc_kernel ', d['extract_mesh'])"
+fi

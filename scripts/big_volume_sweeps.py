@@ -36,7 +36,8 @@ def main():
     ap.add_argument("--batch", type=int, default=20)
     a = ap.parse_args()
     dev = torch.device("cuda:0")
-    scene, dim, orbit_r = bench.scene_for(8)
+    wl = bench.TARGET
+    scene, dim, orbit_r = wl["scene"], wl["dim"], wl["orbit_r"]
     lo, hi = synth.bounds_for(scene, bench.VOXEL, dim)
     vol = TSDFVolume(bench.VOXEL, bench.TRUNC, capacity_log2=19, bounds=(lo, hi), device=dev)
     fuse_ms = 0.0
@@ -67,7 +68,13 @@ def main():
     ms, _ = ms_of(lambda: vol.extract_mesh(0, out=buf))
     b = vox_bytes + ntri * 36
     out["extract_mesh"] = {"ms": ms, "triangles": ntri, "bytes": b, "gbs": b / ms / 1e6,
-                           "frac": b / ms / 1e6 / peak}
+                           "frac": b / ms / 1e6 / peak,
+                           "kernel": "mc_kernel" if os.environ.get("B200TSDF_MC_V1") == "1"
+                           else "mc_kernel2"}
+    ms, (iv, jf) = ms_of(lambda: vol.extract_mesh_indexed(0), reps=2)
+    out["extract_mesh_indexed"] = {"ms": ms, "vertices": int(iv.shape[0]),
+                                   "faces": int(jf.shape[0]),
+                                   "what": "count pass + write pass + device weld (hash + scan)"}
     ms, st = ms_of(lambda: vol.stats(0))
     out["stats"] = {"ms": ms, "bytes": vox_bytes, "gbs": vox_bytes / ms / 1e6,
                     "frac": vox_bytes / ms / 1e6 / peak, "valid_voxels": st["valid_voxels"]}

@@ -37,3 +37,38 @@ def check_quality(got, name):
     assert np.array_equal(np.asarray(got["class_id"]), G[f"{name}/class_id"])
     np.testing.assert_allclose(np.asarray(got["priority"]), G[f"{name}/priority"], rtol=0,
                                atol=PRI_TOL)
+
+
+def test_reference_helper_functions_are_kept():
+    """every public function of the reference module exists in the
+    mirror with the same results (live check when /root/reference is present;
+    the names are checked always)."""
+    import importlib.util
+    import os
+
+    import torch
+
+    from mast3r_slam_quality_dualtsdf_b200 import quality_core as q
+
+    names = ["_hw", "_grid", "reduce_grid", "upsample_to_hw", "view_weight", "ema_delta",
+             "u_from_CQ", "r_from_scalar", "valid_grid", "robust_z", "classify", "pack_result",
+             "compute_batch"]
+    assert all(callable(getattr(q, n, None)) for n in names)
+    path = "/root/reference/mast3r_slam/quality_core.py"
+    if not os.path.exists(path):
+        return
+    spec = importlib.util.spec_from_file_location("refq", path)
+    r = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(r)
+    g = torch.Generator().manual_seed(0)
+    x = torch.rand(48 * 64, generator=g)
+    v = torch.rand(48 * 64, generator=g) > 0.4
+    for m in ("median", "mean"):
+        assert torch.equal(q.reduce_grid(x, 48, 64, 16, method=m), r.reduce_grid(x, 48, 64, 16, method=m))
+        assert torch.allclose(q.reduce_grid(x, 48, 64, 16, valid=v, method=m),
+                              r.reduce_grid(x, 48, 64, 16, valid=v, method=m))
+    assert torch.equal(q.valid_grid(v, 48, 64, 16), r.valid_grid(v, 48, 64, 16))
+    assert torch.equal(q.u_from_CQ(x * 3, x * 2, 1.5, 1.5, 48, 64, 16),
+                       r.u_from_CQ(x * 3, x * 2, 1.5, 1.5, 48, 64, 16))
+    assert torch.equal(q.robust_z(x), r.robust_z(x))
+    assert torch.equal(q.r_from_scalar(x, 48, 64, 16, valid=v), r.r_from_scalar(x, 48, 64, 16, valid=v))
