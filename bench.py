@@ -252,7 +252,10 @@ def run_b200(args):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
+        import datetime
+
+        # a short collective timeout: a rank that dies must not hold the others for 10 minutes
+        dist.init_process_group("nccl", device_id=dev, timeout=datetime.timedelta(seconds=240))
     wl = TARGET
     lo, hi = synth.bounds_for(wl["scene"], VOXEL, wl["dim"])
     bounds = (lo, hi)
@@ -521,12 +524,14 @@ def secondary_sections(args, vol, dev, rank, world, peak, bounds, slabs):
 
     out = {}
 
-    def dev_ms(fn, reps=3):
+    def dev_ms(fn, reps=3, collective=True):
+        """Best-of-reps device time of fn(); collective: every rank calls it (barrier
+        before each repetition, max over ranks); else a rank-local measurement."""
         best = None
         res = None
         for _ in range(reps):
             torch.cuda.synchronize()
-            if world > 1:
+            if world > 1 and collective:
                 dist.barrier()
             a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             a.record()
@@ -535,7 +540,7 @@ def secondary_sections(args, vol, dev, rank, world, peak, bounds, slabs):
             torch.cuda.synchronize()
             t = a.elapsed_time(b)
             best = t if best is None else min(best, t)
-        if world > 1:
+        if world > 1 and collective:
             tt = torch.tensor([best], dtype=torch.float64, device=dev)
             dist.all_reduce(tt, op=dist.ReduceOp.MAX)
             best = float(tt.item())
@@ -602,7 +607,7 @@ def secondary_sections(args, vol, dev, rank, world, peak, bounds, slabs):
         return out
     # ---- quality producer: per-patch grids + classify on the device
     try:
-        out["quality"] = quality_section(args, dev, dev_ms)
+        out["quality"] = quality_section(args, dev, lambda fn, reps=3: dev_ms(fn, reps, False))
     except Exception as e:  # noqa: BLE001
         out["quality"] = {"error": repr(e)}
     if world == 1:

@@ -189,6 +189,21 @@ __device__ __forceinline__ unsigned long long *ctr_replica(const VolumeDev &v) {
 }
 #endif
 
+// ---------------------------------------------------------------- tracing
+// NVTX range around every C-ABI entry (the reference's analogue is
+// the wall-clock Timer of mast3r_slam/tictoc.py:4-30).  Header-only NVTX3: a no-op
+// unless a profiler (nsys / ncu --nvtx) is attached.
+#ifndef __CUDA_ARCH__
+#include <nvtx3/nvToolsExt.h>
+struct B200NvtxRange {
+  explicit B200NvtxRange(const char *name) { nvtxRangePushA(name); }
+  ~B200NvtxRange() { nvtxRangePop(); }
+};
+#define B200_NVTX(name) B200NvtxRange b200_nvtx_range__(name)
+#else
+#define B200_NVTX(name)
+#endif
+
 // ---------------------------------------------------------------- errors
 void b200_set_error(const char *fmt, ...);
 // Sum of the counter replicas (synchronises the stream).

@@ -852,6 +852,7 @@ extern "C" int b200tsdf_integrate_points(b200tsdf_t *h, const void *pts_dev, int
                                          const double *conf_dev, const double *conf_q_dev,
                                          const void *origin_host, int64_t m, double step_scale,
                                          int64_t *rays_fused_host, void *stream) {
+  B200_NVTX("b200tsdf_integrate_points");
   if (!h || (m > 0 && (!pts_dev || !conf_dev || !origin_host)) || m < 0 ||
       (dtype != B200TSDF_F32 && dtype != B200TSDF_F64)) {
     b200_set_error("b200tsdf_integrate_points: invalid argument");
@@ -1019,6 +1020,7 @@ extern "C" int b200tsdf_integrate_keyframes(b200tsdf_t *h, const float *X_dev, c
                                             int32_t B, int32_t H, int32_t W, int32_t gh,
                                             int32_t gw, float min_conf, double step_scale,
                                             void *stream) {
+  B200_NVTX("b200tsdf_integrate_keyframes");
   const b200tsdf_kf_batch kb =
       plain_batch(X_dev, C_dev, q_grid_dev, pose_dev, B, H, W, gh, gw, min_conf, step_scale, 0);
   return fuse_keyframes(h, &kb, stream);
@@ -1029,6 +1031,7 @@ extern "C" int b200tsdf_deintegrate_keyframes(b200tsdf_t *h, const float *X_dev,
                                               const float *pose_dev, int32_t B, int32_t H,
                                               int32_t W, int32_t gh, int32_t gw, float min_conf,
                                               double step_scale, void *stream) {
+  B200_NVTX("b200tsdf_deintegrate_keyframes");
   const b200tsdf_kf_batch kb =
       plain_batch(X_dev, C_dev, q_grid_dev, pose_dev, B, H, W, gh, gw, min_conf, step_scale, 1);
   return fuse_keyframes(h, &kb, stream);
@@ -1036,6 +1039,7 @@ extern "C" int b200tsdf_deintegrate_keyframes(b200tsdf_t *h, const float *X_dev,
 
 extern "C" int b200tsdf_integrate_keyframes_ex(b200tsdf_t *h, const b200tsdf_kf_batch *batch,
                                                void *stream) {
+  B200_NVTX("b200tsdf_integrate_keyframes_ex");
   return fuse_keyframes(h, batch, stream);
 }
 
@@ -1047,6 +1051,7 @@ extern "C" int b200tsdf_integrate_keyframes_host(b200tsdf_t *h, const float *X_h
                                                  int32_t W, int32_t gh, int32_t gw,
                                                  float min_conf, double step_scale,
                                                  void *stream) {
+  B200_NVTX("b200tsdf_integrate_keyframes_host");
   if (!h || B < 0 || H <= 0 || W <= 0 || (B > 0 && (!X_host || !C_host || !pose_host))) {
     b200_set_error("b200tsdf_integrate_keyframes_host: invalid argument");
     return B200TSDF_E_INVALID;
@@ -1149,6 +1154,7 @@ __global__ void selftest_div_kernel(uint64_t seed, long long n, unsigned long lo
 
 extern "C" int b200tsdf_selftest_div(int32_t device, int64_t n, uint64_t seed,
                                      int64_t *mismatches_host, void *stream) {
+  B200_NVTX("b200tsdf_selftest_div");
   if (n < 0 || !mismatches_host) {
     b200_set_error("b200tsdf_selftest_div: invalid argument");
     return B200TSDF_E_INVALID;

@@ -153,6 +153,7 @@ static void fill_params(LocalParams &lp, const float *box, const b200tsdf_local_
 
 extern "C" int b200tsdf_local_dims(const float *box6_host, const b200tsdf_local_cfg *cfg,
                                    int32_t dims3_host[3]) {
+  B200_NVTX("b200tsdf_local_dims");
   if (!box6_host || !cfg || !dims3_host || !(cfg->voxel_size > 0.0)) {
     b200_set_error("b200tsdf_local_dims: invalid argument");
     return B200TSDF_E_INVALID;
@@ -181,6 +182,7 @@ extern "C" int b200tsdf_local_build(const float *X_dev, const float *C_dev, cons
                                     const float *box6_host, int64_t n_pts,
                                     const b200tsdf_local_cfg *cfg, float *tsdf_dev,
                                     float *weights_dev, int64_t *fused_host, void *stream) {
+  B200_NVTX("b200tsdf_local_build");
   if (!X_dev || !C_dev || !pose_dev || !box6_host || !cfg || !tsdf_dev || !weights_dev ||
       n_pts < 0) {
     b200_set_error("b200tsdf_local_build: invalid argument");
@@ -304,6 +306,7 @@ extern "C" int b200tsdf_local_raycast(const float *tsdf_dev, const int32_t dims3
                                       const int64_t *pix_dev, int64_t m,
                                       const b200tsdf_local_cfg *cfg, float *X_refined_dev,
                                       uint8_t *hits_dev, void *stream) {
+  B200_NVTX("b200tsdf_local_raycast");
   if (!tsdf_dev || !dims3_host || !box6_host || !X_dev || !cfg || m < 0 ||
       (m > 0 && (!pix_dev || !X_refined_dev || !hits_dev))) {
     b200_set_error("b200tsdf_local_raycast: invalid argument");

@@ -428,6 +428,7 @@ __global__ void __launch_bounds__(MC_THREADS, MC_CTAS_PER_SM)
 
 extern "C" int b200tsdf_extract_mesh(b200tsdf_t *h, int which, float *verts_dev, int64_t tri_cap,
                                      int64_t *n_tris_host, void *stream) {
+  B200_NVTX("b200tsdf_extract_mesh");
   if (!h || !n_tris_host || (which != 0 && which != 1) || tri_cap < 0) {
     b200_set_error("b200tsdf_extract_mesh: invalid argument");
     return B200TSDF_E_INVALID;

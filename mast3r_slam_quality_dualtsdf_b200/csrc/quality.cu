@@ -222,6 +222,7 @@ extern "C" int b200tsdf_quality_patch_grids(const float *C_dev, const float *Q_d
                                             int32_t H, int32_t W, int32_t patch_size, double C_thr,
                                             double Q_thr, float *u_grid_dev, float *r_grid_dev,
                                             float *valid_grid_dev, int32_t device, void *stream) {
+  B200_NVTX("b200tsdf_quality_patch_grids");
   if (!C_dev || !Q_dev || !r_pix_dev || !valid_dev || !u_grid_dev || !r_grid_dev ||
       !valid_grid_dev || H <= 0 || W <= 0 || patch_size <= 0 ||
       patch_size * patch_size > Q_MAX_PATCH) {
@@ -243,6 +244,7 @@ extern "C" int b200tsdf_quality_classify(const float *delta_cov_dev, const float
                                          double thr_zu, double thr_dc, int64_t *class_dev,
                                          float *priority_dev, float *q_grid_dev, int32_t device,
                                          void *stream) {
+  B200_NVTX("b200tsdf_quality_classify");
   if (!delta_cov_dev || !r_dev || !u_dev || !class_dev || !priority_dev || n <= 0 ||
       n > Q_MAX_N) {
     b200_set_error("b200tsdf_quality_classify: invalid argument (1 <= n <= %d)", Q_MAX_N);
@@ -266,6 +268,7 @@ extern "C" int b200tsdf_quality_batch(const float *C_dev, const float *Q_dev,
                                       float *delta_cov_dev, int64_t *class_dev,
                                       float *priority_dev, float *q_grid_dev, int32_t device,
                                       void *stream) {
+  B200_NVTX("b200tsdf_quality_batch");
   if (!C_dev || !Q_dev || !r_pix_dev || !valid_dev || !view_w_dev || !u_grid_dev || !r_grid_dev ||
       !valid_grid_dev || !ewma_dev || !delta_cov_dev || !class_dev || !priority_dev || B < 0 ||
       B > 65535 || H <= 0 || W <= 0 || patch_size <= 0 || patch_size * patch_size > Q_MAX_PATCH) {

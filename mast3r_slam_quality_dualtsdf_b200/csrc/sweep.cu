@@ -49,6 +49,7 @@ __global__ void __launch_bounds__(128)
 
 extern "C" int b200tsdf_stats(b200tsdf_t *h, int which, int64_t *valid_host, int64_t *total_host,
                               void *stream) {
+  B200_NVTX("b200tsdf_stats");
   if (!h || !valid_host || !total_host || (which != 0 && which != 1)) return B200TSDF_E_INVALID;
   cudaStream_t st = (cudaStream_t)stream;
   B200_CUDA(cudaSetDevice(h->cfg.device));
@@ -115,6 +116,7 @@ __global__ void __launch_bounds__(128)
 extern "C" int b200tsdf_export_voxels(b200tsdf_t *h, int which, int64_t *keys_dev, float *tsdf_dev,
                                       float *weight_dev, uint32_t *count_dev, int64_t cap,
                                       int64_t *n_host, void *stream) {
+  B200_NVTX("b200tsdf_export_voxels");
   if (!h || !n_host || (which != 0 && which != 1)) return B200TSDF_E_INVALID;
   if (cap > 0 && (!keys_dev || !tsdf_dev || !weight_dev || !count_dev)) return B200TSDF_E_INVALID;
   cudaStream_t st = (cudaStream_t)stream;
@@ -143,6 +145,7 @@ __global__ void export_blocks_kernel(VolumeDev v, long long *bkeys, long long ca
 
 extern "C" int b200tsdf_export_blocks(b200tsdf_t *h, int64_t *bkeys_dev, int64_t cap,
                                       int64_t *n_host, void *stream) {
+  B200_NVTX("b200tsdf_export_blocks");
   if (!h || !n_host || (cap > 0 && !bkeys_dev)) return B200TSDF_E_INVALID;
   cudaStream_t st = (cudaStream_t)stream;
   B200_CUDA(cudaSetDevice(h->cfg.device));
@@ -297,6 +300,7 @@ __global__ void query_kernel(VolumeDev v, int which, const T *__restrict__ pts, 
 extern "C" int b200tsdf_query(b200tsdf_t *h, int which, const void *pts_dev, int dtype, int64_t m,
                               double *tsdf_dev, double *grad_dev, uint8_t *flags_dev,
                               void *stream) {
+  B200_NVTX("b200tsdf_query");
   if (!h || m < 0 || (which != 0 && which != 1) ||
       (m > 0 && (!pts_dev || !tsdf_dev || !grad_dev || !flags_dev)) ||
       (dtype != B200TSDF_F32 && dtype != B200TSDF_F64)) {
@@ -429,6 +433,7 @@ extern "C" int b200tsdf_pose_normal_equations(b200tsdf_t *h, int which, const fl
                                               const float *pose_host, double lambda,
                                               double *H_host, double *b_host, int64_t *used_host,
                                               void *stream) {
+  B200_NVTX("b200tsdf_pose_normal_equations");
   return pose_normal_equations_impl(h, which, pts_cam_dev, conf_dev, n, pose_host, lambda, H_host,
                                     b_host, used_host, stream, nullptr);
 }
@@ -596,6 +601,7 @@ extern "C" int b200tsdf_pose_optimize(b200tsdf_t *h, int which, const float *pts
                                       double lambda, double damping, int32_t iterations,
                                       int64_t *used_host, int32_t *iterations_done_host,
                                       void *stream) {
+  B200_NVTX("b200tsdf_pose_optimize");
   if (!h || n < 0 || (which != 0 && which != 1) || !pose_inout_host || iterations < 0 ||
       (n > 0 && (!pts_cam_dev || !conf_dev))) {
     b200_set_error("b200tsdf_pose_optimize: invalid argument");
@@ -672,6 +678,7 @@ __global__ void query_finish_kernel(float min_weight, double voxel_size,
 extern "C" int b200tsdf_query_taps(b200tsdf_t *h, int which, const void *pts_dev, int dtype,
                                    int64_t m, const float *pose_host, float *taps_dev,
                                    void *stream) {
+  B200_NVTX("b200tsdf_query_taps");
   if (!h || m < 0 || (which != 0 && which != 1) || (m > 0 && (!pts_dev || !taps_dev)) ||
       (dtype != B200TSDF_F32 && dtype != B200TSDF_F64) || (pose_host && dtype != B200TSDF_F32) ||
       ((uintptr_t)taps_dev & 15)) {
@@ -705,6 +712,7 @@ extern "C" int b200tsdf_query_taps(b200tsdf_t *h, int which, const void *pts_dev
 extern "C" int b200tsdf_query_finish(b200tsdf_t *h, const float *taps_dev, int64_t m,
                                      double *tsdf_dev, double *grad_dev, uint8_t *flags_dev,
                                      void *stream) {
+  B200_NVTX("b200tsdf_query_finish");
   if (!h || m < 0 || (m > 0 && (!taps_dev || !tsdf_dev || !grad_dev || !flags_dev)) ||
       ((uintptr_t)taps_dev & 15)) {
     b200_set_error("b200tsdf_query_finish: invalid argument");
@@ -726,6 +734,7 @@ extern "C" int b200tsdf_pose_normal_equations_taps(b200tsdf_t *h, const float *t
                                                    const float *pose_host, double lambda,
                                                    double *H_host, double *b_host,
                                                    int64_t *used_host, void *stream) {
+  B200_NVTX("b200tsdf_pose_normal_equations_taps");
   if ((n > 0 && !taps_dev) || ((uintptr_t)taps_dev & 15)) {
     b200_set_error("b200tsdf_pose_normal_equations_taps: invalid argument");
     return B200TSDF_E_INVALID;
@@ -795,12 +804,14 @@ static int export_block_payload(b200tsdf_t *h, int64_t *bkeys_dev, float *vox_de
 extern "C" int b200tsdf_export_seam_blocks(b200tsdf_t *h, int64_t *bkeys_dev, float *vox_dev,
                                            uint64_t *cnt_dev, int64_t cap, int64_t *n_host,
                                            void *stream) {
+  B200_NVTX("b200tsdf_export_seam_blocks");
   return export_block_payload(h, bkeys_dev, vox_dev, cnt_dev, cap, n_host, stream, 0);
 }
 
 extern "C" int b200tsdf_export_block_data(b200tsdf_t *h, int64_t *bkeys_dev, float *vox_dev,
                                           uint64_t *cnt_dev, int64_t cap, int64_t *n_host,
                                           void *stream) {
+  B200_NVTX("b200tsdf_export_block_data");
   return export_block_payload(h, bkeys_dev, vox_dev, cnt_dev, cap, n_host, stream, 1);
 }
 
@@ -872,11 +883,13 @@ static int import_block_payload(b200tsdf_t *h, const int64_t *bkeys_dev, const f
 extern "C" int b200tsdf_import_halo_blocks(b200tsdf_t *h, const int64_t *bkeys_dev,
                                            const float *vox_dev, const uint64_t *cnt_dev,
                                            int64_t n, void *stream) {
+  B200_NVTX("b200tsdf_import_halo_blocks");
   return import_block_payload(h, bkeys_dev, vox_dev, cnt_dev, n, stream, 0);
 }
 
 extern "C" int b200tsdf_import_blocks(b200tsdf_t *h, const int64_t *bkeys_dev,
                                       const float *vox_dev, const uint64_t *cnt_dev, int64_t n,
                                       void *stream) {
+  B200_NVTX("b200tsdf_import_blocks");
   return import_block_payload(h, bkeys_dev, vox_dev, cnt_dev, n, stream, 1);
 }

@@ -27,6 +27,7 @@ static int clamp_i32(int64_t v) {
 }
 
 extern "C" int b200tsdf_create(const b200tsdf_config *cfg, b200tsdf_t **out) {
+  B200_NVTX("b200tsdf_create");
   if (!cfg || !out) {
     b200_set_error("b200tsdf_create: null argument");
     return B200TSDF_E_INVALID;
@@ -129,6 +130,7 @@ extern "C" int b200tsdf_create(const b200tsdf_config *cfg, b200tsdf_t **out) {
 }
 
 extern "C" int b200tsdf_destroy(b200tsdf_t *h) {
+  B200_NVTX("b200tsdf_destroy");
   if (!h) return B200TSDF_OK;
   cudaSetDevice(h->cfg.device);
   cudaFree(h->d.keys);
@@ -153,6 +155,7 @@ extern "C" int b200tsdf_destroy(b200tsdf_t *h) {
 }
 
 extern "C" int b200tsdf_reset(b200tsdf_t *h, void *stream) {
+  B200_NVTX("b200tsdf_reset");
   if (!h) return B200TSDF_E_INVALID;
   cudaStream_t st = (cudaStream_t)stream;
   B200_CUDA(cudaSetDevice(h->cfg.device));
@@ -166,6 +169,7 @@ extern "C" int b200tsdf_reset(b200tsdf_t *h, void *stream) {
 }
 
 extern "C" int b200tsdf_counters(b200tsdf_t *h, int64_t out_host[8], void *stream) {
+  B200_NVTX("b200tsdf_counters");
   if (!h || !out_host) return B200TSDF_E_INVALID;
   cudaStream_t st = (cudaStream_t)stream;
   unsigned long long tmp[CTR_COUNT];

@@ -194,6 +194,7 @@ static int weld_impl(int device, const float *soup_dev, int64_t n_tris, float *v
 extern "C" int b200tsdf_weld_mesh(int32_t device, const float *soup_dev, int64_t n_tris,
                                   float *verts_dev, int64_t vert_cap, int32_t *faces_dev,
                                   int64_t *n_verts_host, void *stream) {
+  B200_NVTX("b200tsdf_weld_mesh");
   if (n_tris < 0 || !n_verts_host || (n_tris > 0 && !soup_dev) || vert_cap < 0) {
     b200_set_error("b200tsdf_weld_mesh: invalid argument");
     return B200TSDF_E_INVALID;
@@ -206,6 +207,7 @@ extern "C" int b200tsdf_extract_mesh_indexed(b200tsdf_t *h, int which, float *ve
                                              int64_t vert_cap, int32_t *faces_dev,
                                              int64_t tri_cap, int64_t *n_verts_host,
                                              int64_t *n_tris_host, void *stream) {
+  B200_NVTX("b200tsdf_extract_mesh_indexed");
   if (!h || !n_verts_host || !n_tris_host || vert_cap < 0 || tri_cap < 0) {
     b200_set_error("b200tsdf_extract_mesh_indexed: invalid argument");
     return B200TSDF_E_INVALID;

@@ -4,10 +4,10 @@ N=${1:-2}
 mkdir -p gpurun_out
 TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1"
 for s in sharded_mesh_check sharded_query_check sharded_reintegrate_check; do
-  timeout 600 $TR --master-port 296$((RANDOM % 90 + 10)) scripts/$s.py > gpurun_out/${s}_n$N.log 2>&1
+  timeout 300 $TR --master-port 296$((RANDOM % 90 + 10)) scripts/$s.py > gpurun_out/${s}_n$N.log 2>&1
   echo "$s N=$N rc=$?"; tail -2 gpurun_out/${s}_n$N.log | cut -c1-600
 done
-timeout 900 $TR --master-port 29577 bench.py --gpus $N --steps 4 --warmup 2 > gpurun_out/bench_n$N.json 2> gpurun_out/bench_n$N.err
+timeout 600 $TR --master-port 29577 bench.py --gpus $N --steps 4 --warmup 2 > gpurun_out/bench_n$N.json 2> gpurun_out/bench_n$N.err
 echo "bench N=$N rc=$?"
 python - <<P
 import json

@@ -8,9 +8,12 @@ Every rank fuses the same synthetic keyframes into its interleaved z-slabs
 (broadcast from rank 0), the ranks exchange their seam block layers over NCCL
 (`exchange_seams`: isend / irecv of the packed blocks) and extract the mesh of
 BOTH volumes; rank 0 gathers the per-rank soups and compares the triangle
-multiset with the mesh of ONE volume fused with the same keyframes -- bit for
-bit -- and welds the gathered soup on the device (seam vertices must merge:
-same vertex count as the single-volume indexed mesh).
+multiset -- bit for bit -- with the mesh of ONE volume holding exactly the
+ranks' voxel data (their exported blocks merged by `import_blocks`; a second
+fusion would differ in the last bits, float32 reductions are unordered), and
+welds the gathered soup on the device (seam vertices must merge: same vertex
+count as the single-volume indexed mesh).  The merged volume is also compared
+with a volume fused directly on one GPU (keys and hit counts exact).
 Writes gpurun_out/sharded_mesh_n<N>.json."""
 import json
 import os
@@ -52,6 +55,24 @@ def main():
     sv.integrate_keyframes(src["X"], src["C"], src["pose"], src["q"], 0.05, H, W, src=0)
     res = {"world": world, "slab_width": width, "volumes": {}}
     ok = True
+    # the ranks' voxel blocks, merged on rank 0 into ONE volume
+    bk, vox, cnt = sv.vol.export_block_data()
+    parts = [None] * world
+    dist.all_gather_object(parts, (bk.cpu().numpy(), vox.cpu().numpy(), cnt.cpu().numpy()))
+    one = None
+    if rank == 0:
+        one = TSDFVolume(VOXEL, TRUNC, capacity_log2=16, bounds=(lo, hi), device=dev)
+        for pb, pv, pc in parts:
+            one.import_blocks(torch.from_numpy(pb), torch.from_numpy(pv), torch.from_numpy(pc))
+        direct = TSDFVolume(VOXEL, TRUNC, capacity_log2=16, bounds=(lo, hi), device=dev)
+        direct.integrate_keyframes(t["X"], t["C"], t["pose"], t["q"], 0.05, H, W)
+        a, b = one.export(0), direct.export(0)
+        same_keys = a[0].shape == b[0].shape and np.array_equal(a[0], b[0]) and \
+            np.array_equal(a[3], b[3])
+        res["union_equals_direct_fusion"] = {
+            "keys_and_hit_counts_exact": bool(same_keys),
+            "max_abs_dtsdf": float(np.abs(a[1] - b[1]).max()) if same_keys else None}
+        ok = ok and same_keys
     for which, name in ((0, "primary"), (1, "quality")):
         torch.cuda.synchronize()
         dist.barrier()
@@ -60,8 +81,6 @@ def main():
         torch.cuda.synchronize()
         dt = time.perf_counter() - t0
         if rank == 0:
-            one = TSDFVolume(VOXEL, TRUNC, capacity_log2=16, bounds=(lo, hi), device=dev)
-            one.integrate_keyframes(t["X"], t["C"], t["pose"], t["q"], 0.05, H, W)
             want = one.extract_mesh(which)
             a, b = canon(soup.cpu().numpy()), canon(want.cpu().numpy())
             same = a.shape == b.shape and np.array_equal(a, b)
