@@ -37,6 +37,7 @@ enum {
 };
 
 enum { B200TSDF_F32 = 0, B200TSDF_F64 = 1 };
+#define B200TSDF_MAX_SEGMENTS 16 /* source ranks of one keyframe batch (one NVSwitch box: 8) */
 
 typedef struct b200tsdf b200tsdf_t;
 
@@ -159,6 +160,44 @@ typedef struct {
 } b200tsdf_kf_batch;
 int b200tsdf_integrate_keyframes_ex(b200tsdf_t *h, const b200tsdf_kf_batch *batch,
                                     void *stream);
+
+/* ---- multi-GPU peer pull (no reference counterpart) ------------
+ * A z-slab rank needs only the 32 x 8 pixel tiles of a batch whose +-truncation
+ * band reaches its slabs (~1.4 / N of them).  Instead of broadcasting 3.1 MB per
+ * keyframe to every rank, the rank that holds a keyframe (its OWNER) describes it
+ * by a meta record -- per tile the conservative z range of its bands in voxel
+ * layers and its ray count, the pose, the quality grid: ~28 KB -- and the ranks
+ * all-gather the records (one small collective).  b200tsdf_integrate_keyframes_pull
+ * then lists the tiles that reach this handle's slabs, accounts for the rays of the
+ * others (counted + culled, exactly as the broadcast path does), and its fuse
+ * kernel TMA-loads the listed tiles straight from the owner's HBM over NVLink:
+ * X_seg_dev[s] / C_seg_dev[s] are the bases of source rank s's seg_kf pointmaps /
+ * confidences in THIS process's address space (own memory, or a peer buffer mapped
+ * with b200tsdf_ipc_open).  meta_dev: n_seg gathered records, meta_stride 32-bit
+ * words apart, each of b200tsdf_keyframe_meta_words(seg_kf, H, W, gh, gw) words as
+ * b200tsdf_keyframe_meta writes them.  Bounded volumes with a block directory
+ * only; no max_points (the owner would have to ship its selection). */
+typedef struct {
+  const float *X_seg_dev[B200TSDF_MAX_SEGMENTS];
+  const float *C_seg_dev[B200TSDF_MAX_SEGMENTS];
+  const uint32_t *meta_dev;
+  int64_t meta_stride;
+  int32_t n_seg, seg_kf, H, W, gh, gw;
+  float min_conf;
+  int32_t negate;
+  double step_scale;
+} b200tsdf_kf_pull;
+int64_t b200tsdf_keyframe_meta_words(int32_t seg_kf, int32_t H, int32_t W, int32_t gh, int32_t gw);
+int b200tsdf_keyframe_meta(b200tsdf_t *h, const float *X_dev, const float *C_dev,
+                           const float *q_grid_dev, const float *pose_dev, int32_t B, int32_t H,
+                           int32_t W, int32_t gh, int32_t gw, float min_conf, uint32_t *meta_dev,
+                           void *stream);
+int b200tsdf_integrate_keyframes_pull(b200tsdf_t *h, const b200tsdf_kf_pull *pull, void *stream);
+/* CUDA IPC plumbing for the peer buffers (one process per GPU): handle64 = the 64
+ * bytes of a cudaIpcMemHandle_t exported by the owner, offset_bytes = offset of the
+ * buffer inside that allocation.  ipc_close takes the pointer ipc_open returned. */
+int b200tsdf_ipc_open(int32_t device, const void *handle64, int64_t offset_bytes, void **ptr_out);
+int b200tsdf_ipc_close(int32_t device, void *ptr, int64_t offset_bytes);
 
 /* Same call with HOST buffers (pinned or pageable): copies H2D in chunks on an
  * internal copy stream into a staging area while the chunks already there are

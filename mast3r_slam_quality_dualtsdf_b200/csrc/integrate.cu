@@ -468,6 +468,12 @@ struct KfArgs { // one keyframe batch (device pointers)
   // tsdf_global.max_points_per_kf: per keyframe {hash threshold, salt}; a valid pixel
   // is fused iff sub_hash(pixel, salt) <= threshold (nullptr: every valid pixel)
   const uint2 *sub;
+  // peer pull (multi-GPU): pointmaps / confidences of segment s live at segX[s] /
+  // segC[s] -- the OWNER rank's HBM, mapped into this process (NVLink) -- instead of
+  // X + s * seg_stride; quality grids and poses come from the gathered meta records
+  // through qg / poses + s * seg_stride as before.  n_ptr = 0: not used.
+  const float *segX[B200TSDF_MAX_SEGMENTS], *segC[B200TSDF_MAX_SEGMENTS];
+  int n_ptr;
 };
 
 // Seeded bijective 32-bit hash of the pixel index (murmur3 finaliser: xor-shifts
@@ -504,8 +510,14 @@ __device__ __forceinline__ KfPtrs kf_ptrs(const KfArgs &a, int kf) {
   }
   const long long npix = (long long)a.H * a.W;
   KfPtrs p;
-  p.X = a.X + so + (long long)loc * npix * 3;
-  p.C = a.C + so + (long long)loc * npix;
+  if (a.n_ptr > 0) {
+    const int seg = kf / a.seg_kf;
+    p.X = a.segX[seg] + (long long)loc * npix * 3;
+    p.C = a.segC[seg] + (long long)loc * npix;
+  } else {
+    p.X = a.X + so + (long long)loc * npix * 3;
+    p.C = a.C + so + (long long)loc * npix;
+  }
   p.qg = a.qg ? a.qg + so + (long long)loc * a.gh * a.gw : nullptr;
   p.P = a.poses + so + (long long)loc * 8;
   return p;
@@ -943,8 +955,11 @@ static int fuse_keyframes(b200tsdf_t *h, const b200tsdf_kf_batch *kb, void *stre
   const int mode = !use_bounded(h) ? 0 : (h->d.dir_on ? 2 : 1);
   // TMA staging needs full tiles and 16-byte aligned row segments
   const bool tma = (W % TILE_W == 0) && (H % TILE_H == 0) && aligned;
-  KfArgs ka = {X_dev, C_dev, q_grid_dev, pose_dev, (long long)kb->seg_stride,
-               kb->seg_kf > 0 ? kb->seg_kf : 1, H, W, gh, gw, kb->min_conf, (float)step_d, nullptr};
+  KfArgs ka;
+  memset(&ka, 0, sizeof(ka));
+  ka.X = X_dev, ka.C = C_dev, ka.qg = q_grid_dev, ka.poses = pose_dev;
+  ka.seg_stride = (long long)kb->seg_stride, ka.seg_kf = kb->seg_kf > 0 ? kb->seg_kf : 1;
+  ka.H = H, ka.W = W, ka.gh = gh, ka.gw = gw, ka.min_conf = kb->min_conf, ka.step = (float)step_d;
   if (kb->max_points > 0 && (long long)kb->max_points < (long long)H * W) {
     // the reference's per-keyframe cap (global_manager.py:94-99), seeded and exact-size
     if ((size_t)B > h->sub_cap) {
@@ -1107,6 +1122,271 @@ extern "C" int b200tsdf_integrate_keyframes_host(b200tsdf_t *h, const float *X_h
   // the host buffers are the caller's again when this returns: wait for the copies
   // (not for the fuse, which stays queued on `stream`)
   B200_CUDA(cudaStreamSynchronize(h->copy_stream));
+  return B200TSDF_OK;
+}
+
+// ---------------------------------------------------------------- peer pull
+// Multi-GPU ingest without broadcasting the pointmaps:
+// a z-slab rank needs only the ~1.4 / N of the batch's 32 x 8 pixel tiles whose
+// +-truncation band reaches its slabs.  The OWNER of a keyframe (the rank whose HBM
+// holds it) runs keyframe_meta_kernel once: per tile the conservative z range of
+// the bands of its rays (voxel layers) and the number of rays, plus copies of the
+// pose and the quality grid -- ~28 KB per keyframe instead of 3.1 MB.  ONE small
+// all-gather moves the meta records; every rank then lists the tiles that reach
+// its slabs (tiles_from_meta_kernel, which also does the accounting of the
+// skipped tiles' rays) and the persistent fuse kernel TMA-loads exactly those
+// tiles straight from the owner's memory over NVLink (KfArgs::segX / segC are
+// peer-mapped pointers): the staging of the fuse IS the collective.
+struct TileMeta {
+  int zlo, zhi;    // voxel layers the tile's bands can touch; zlo > zhi: no ray in the tile
+  uint32_t rays;   // rays of the tile the reference would fuse (global_volume.py:56)
+  uint32_t pad;
+};
+
+static long long meta_words(int seg_kf, int H, int W, int gh, int gw) {
+  const long long tiles = (long long)((W + TILE_W - 1) / TILE_W) * ((H + TILE_H - 1) / TILE_H);
+  long long w = (long long)seg_kf * tiles * 4 + (long long)seg_kf * 8 + (long long)seg_kf * gh * gw;
+  return (w + 63) & ~63ll;
+}
+
+// CTA = CLS_TILES consecutive tiles of one tile row of one keyframe (as slab_classify_kernel).
+__global__ void __launch_bounds__(256)
+    keyframe_meta_kernel(KfArgs a, MarchConst mc, TileMeta *__restrict__ table, int tiles_x,
+                         int tiles_y) {
+  __shared__ int s_lo[8], s_hi[8];
+  __shared__ uint32_t s_rays[8];
+  const int lx = threadIdx.x & 31, warp = threadIdx.x >> 5, py = blockIdx.y * TILE_H + warp;
+  const int kf = blockIdx.z;
+  const KfPtrs k = kf_ptrs(a, kf);
+  const float *P = k.P;
+  const long long row = (long long)py * a.W;
+  float c[CLS_TILES], x0[CLS_TILES], x1[CLS_TILES], x2[CLS_TILES];
+#pragma unroll
+  for (int t = 0; t < CLS_TILES; ++t) {
+    const int px = (blockIdx.x * CLS_TILES + t) * TILE_W + lx;
+    c[t] = 0.f, x0[t] = x1[t] = x2[t] = 0.f;
+    if (px < a.W && py < a.H) {
+      c[t] = k.C[row + px];
+      const float *x = k.X + (row + px) * 3;
+      x0[t] = x[0], x1[t] = x[1], x2[t] = x[2];
+    }
+  }
+  const float q0 = P[3], q1 = P[4], q2 = P[5], q3 = P[6], sv = P[7] * mc.inv_vs;
+  const float k0 = 2.0f * (q0 * q2 - q1 * q3) * sv, k1 = 2.0f * (q1 * q2 + q0 * q3) * sv,
+              k2 = (1.0f - 2.0f * (q0 * q0 + q1 * q1)) * sv, tzv = P[2] * mc.inv_vs;
+  const float s2 = P[7] * P[7], tv = mc.trunc * mc.inv_vs;
+#pragma unroll
+  for (int t = 0; t < CLS_TILES; ++t) {
+    const int bx = blockIdx.x * CLS_TILES + t;
+    if (bx >= tiles_x) break; // uniform
+    const int px = bx * TILE_W + lx;
+    const bool take = px < a.W && py < a.H && c[t] > a.min_conf;
+    int zlo = 0x7FFFFFFF, zhi = (int)0x80000000;
+    uint32_t ray = 0;
+    if (take) {
+      // the conservative z test of slab_classify_kernel, kept as a RANGE
+      const float zc = fmaf(x0[t], k0, fmaf(x1[t], k1, fmaf(x2[t], k2, tzv)));
+      const float mag = fmaf(fabsf(x0[t]), fabsf(k0),
+                             fmaf(fabsf(x1[t]), fabsf(k1), fmaf(fabsf(x2[t]), fabsf(k2), fabsf(tzv))));
+      const float d2 = s2 * fmaf(x0[t], x0[t], fmaf(x1[t], x1[t], x2[t] * x2[t]));
+      float dz = fmaf(fabsf(zc - tzv) * mc.vs * rsqrtf(d2), 1.01f, 1.0e-3f);
+      if (!(dz < 1.0f)) dz = 1.0f;
+      const float ext = fmaf(tv, dz, fmaf(mag, 4.0e-6f, 3.5f));
+      if (fabsf(zc) < 1.0e9f && ext < 1.0e9f) {
+        zlo = (int)floorf(zc - ext), zhi = (int)floorf(zc + ext);
+      } else { // the per-voxel test decides: every rank takes the tile
+        zlo = (int)0x80000000, zhi = 0x7FFFFFFF;
+      }
+      bool is_ray = d2 > 4.0e-6f && d2 < 1.0e36f; // certainly a ray when 2e-3 < len < 1e18
+      if (!is_ray) {
+        float wx, wy, wz, rx, ry, rz;
+        sim3_act(P, x0[t], x1[t], x2[t], wx, wy, wz);
+        Ray<float> r;
+        is_ray = ray_length<float>(r, wx, wy, wz, P[0], P[1], P[2], rx, ry, rz);
+      }
+      ray = is_ray ? 1u : 0u;
+    }
+    zlo = __reduce_min_sync(0xFFFFFFFFu, zlo);
+    zhi = __reduce_max_sync(0xFFFFFFFFu, zhi);
+    ray = __reduce_add_sync(0xFFFFFFFFu, ray);
+    __syncthreads(); // the previous tile's totals have been read
+    if (lx == 0) s_lo[warp] = zlo, s_hi[warp] = zhi, s_rays[warp] = ray;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      TileMeta m = {0x7FFFFFFF, (int)0x80000000, 0u, 0u};
+      for (int w = 0; w < 8; ++w) {
+        m.zlo = min(m.zlo, s_lo[w]), m.zhi = max(m.zhi, s_hi[w]);
+        m.rays += s_rays[w];
+      }
+      table[((long long)kf * tiles_y + blockIdx.y) * tiles_x + bx] = m;
+    }
+  }
+}
+
+// One thread per tile of the gathered batch: list it if its z range reaches a slab
+// of this rank, else account for its rays (counted, culled) right here.
+__global__ void __launch_bounds__(256)
+    tiles_from_meta_kernel(VolumeDev v, const uint32_t *__restrict__ meta, long long meta_stride,
+                           int seg_kf, int n_kf, int tiles_kf, int *__restrict__ list,
+                           unsigned int *sched) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  Tally tl = {0, 0, 0, 0, 0, 0, 0};
+  if (i < (long long)n_kf * tiles_kf) {
+    const int kf = (int)(i / tiles_kf), tile = (int)(i - (long long)kf * tiles_kf);
+    const int seg = kf / seg_kf, loc = kf - seg * seg_kf;
+    const TileMeta m = reinterpret_cast<const TileMeta *>(meta + (long long)seg * meta_stride)
+        [(long long)loc * tiles_kf + tile];
+    if (m.zlo <= m.zhi) {
+      bool hit = true;
+      if (v.slab_count > 1 && m.zlo > -1000000000 && m.zhi < 1000000000) {
+        const int s_lo = (m.zlo - v.slab_z0) >> v.slab_shift, s_hi = (m.zhi - v.slab_z0) >> v.slab_shift;
+        int need = v.slab_index - slab_owner_of(v, s_lo);
+        if (need < 0) need += v.slab_count;
+        hit = need <= s_hi - s_lo;
+      }
+      if (hit) {
+        list[atomicAdd(sched, 1u)] = (int)i;
+      } else {
+        tl.rays = m.rays, tl.culled = m.rays;
+      }
+    }
+  }
+  commit_tally(v, tl);
+}
+
+extern "C" int64_t b200tsdf_keyframe_meta_words(int32_t seg_kf, int32_t H, int32_t W, int32_t gh,
+                                                int32_t gw) {
+  return (int64_t)meta_words(seg_kf, H, W, gh, gw);
+}
+
+extern "C" int b200tsdf_keyframe_meta(b200tsdf_t *h, const float *X_dev, const float *C_dev,
+                                      const float *q_grid_dev, const float *pose_dev, int32_t B,
+                                      int32_t H, int32_t W, int32_t gh, int32_t gw, float min_conf,
+                                      uint32_t *meta_dev, void *stream) {
+  B200_NVTX("b200tsdf_keyframe_meta");
+  if (!h || B < 0 || H <= 0 || W <= 0 || gh < 0 || gw < 0 ||
+      (B > 0 && (!X_dev || !C_dev || !pose_dev || !meta_dev)) || (q_grid_dev && (gh == 0 || gw == 0))) {
+    b200_set_error("b200tsdf_keyframe_meta: invalid argument");
+    return B200TSDF_E_INVALID;
+  }
+  if (B == 0) return B200TSDF_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  B200_CUDA(cudaSetDevice(h->cfg.device));
+  const int tiles_x = (W + TILE_W - 1) / TILE_W, tiles_y = (H + TILE_H - 1) / TILE_H;
+  KfArgs ka;
+  memset(&ka, 0, sizeof(ka));
+  ka.X = X_dev, ka.C = C_dev, ka.qg = q_grid_dev, ka.poses = pose_dev;
+  ka.seg_kf = B, ka.H = H, ka.W = W, ka.gh = gh, ka.gw = gw, ka.min_conf = min_conf;
+  const MarchConst mc = make_consts(h);
+  const dim3 grid((unsigned)((tiles_x + CLS_TILES - 1) / CLS_TILES), (unsigned)tiles_y, (unsigned)B);
+  keyframe_meta_kernel<<<grid, 256, 0, st>>>(ka, mc, (TileMeta *)meta_dev, tiles_x, tiles_y);
+  B200_CUDA(cudaGetLastError());
+  // [tile table | poses | quality grids]: what the fuse needs beside the tiles themselves
+  uint32_t *p = meta_dev + (size_t)B * tiles_x * tiles_y * 4;
+  B200_CUDA(cudaMemcpyAsync(p, pose_dev, (size_t)B * 8 * sizeof(float), cudaMemcpyDeviceToDevice, st));
+  if (q_grid_dev)
+    B200_CUDA(cudaMemcpyAsync(p + (size_t)B * 8, q_grid_dev, (size_t)B * gh * gw * sizeof(float),
+                              cudaMemcpyDeviceToDevice, st));
+  return B200TSDF_OK;
+}
+
+extern "C" int b200tsdf_integrate_keyframes_pull(b200tsdf_t *h, const b200tsdf_kf_pull *kp,
+                                                 void *stream) {
+  B200_NVTX("b200tsdf_integrate_keyframes_pull");
+  if (!h || !kp || kp->n_seg <= 0 || kp->n_seg > B200TSDF_MAX_SEGMENTS || kp->seg_kf <= 0 ||
+      kp->H <= 0 || kp->W <= 0 || !kp->meta_dev || kp->meta_stride <= 0) {
+    b200_set_error("b200tsdf_integrate_keyframes_pull: invalid argument");
+    return B200TSDF_E_INVALID;
+  }
+  if (!use_bounded(h) || !h->d.dir_on) {
+    b200_set_error("b200tsdf_integrate_keyframes_pull: needs a bounded volume with a block directory");
+    return B200TSDF_E_INVALID;
+  }
+  const int H = kp->H, W = kp->W, gh = kp->gh, gw = kp->gw, B = kp->n_seg * kp->seg_kf;
+  if (gh > 0 && (gw <= 0 || H % gh || W % gw)) {
+    b200_set_error("b200tsdf_integrate_keyframes_pull: quality grid %dx%d does not tile %dx%d", gh,
+                   gw, H, W);
+    return B200TSDF_E_INVALID;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  B200_CUDA(cudaSetDevice(h->cfg.device));
+  double step_d = h->cfg.voxel_size * kp->step_scale;
+  if (step_d < 1.0e-4) step_d = 1.0e-4;
+  const int tiles_x = (W + TILE_W - 1) / TILE_W, tiles_y = (H + TILE_H - 1) / TILE_H;
+  const int tiles_kf = tiles_x * tiles_y;
+  const long long n_tiles = (long long)tiles_kf * B;
+  if (n_tiles >= (1ll << 31)) {
+    b200_set_error("b200tsdf_integrate_keyframes_pull: batch too large");
+    return B200TSDF_E_INVALID;
+  }
+  MarchConst mc = gh > 0 ? make_consts(h, H / gh, W / gw) : make_consts(h);
+  mc.negate = kp->negate ? 1 : 0;
+  const FastConst fc = make_fast_consts(h, step_d);
+  KfArgs ka;
+  memset(&ka, 0, sizeof(ka));
+  const float *meta_f = reinterpret_cast<const float *>(kp->meta_dev);
+  const size_t tab = (size_t)kp->seg_kf * tiles_kf * 4;
+  ka.poses = meta_f + tab;
+  ka.qg = gh > 0 ? meta_f + tab + (size_t)kp->seg_kf * 8 : nullptr;
+  ka.seg_stride = (long long)kp->meta_stride, ka.seg_kf = kp->seg_kf;
+  ka.H = H, ka.W = W, ka.gh = gh, ka.gw = gw, ka.min_conf = kp->min_conf, ka.step = (float)step_d;
+  bool aligned = true;
+  for (int s = 0; s < kp->n_seg; ++s) {
+    if (!kp->X_seg_dev[s] || !kp->C_seg_dev[s]) {
+      b200_set_error("b200tsdf_integrate_keyframes_pull: segment %d has no pointers", s);
+      return B200TSDF_E_INVALID;
+    }
+    ka.segX[s] = kp->X_seg_dev[s], ka.segC[s] = kp->C_seg_dev[s];
+    aligned = aligned && (((uintptr_t)kp->X_seg_dev[s] & 15) == 0) &&
+              (((uintptr_t)kp->C_seg_dev[s] & 15) == 0);
+  }
+  ka.n_ptr = kp->n_seg;
+  ka.X = ka.segX[0], ka.C = ka.segC[0];
+  const bool tma = (W % TILE_W == 0) && (H % TILE_H == 0) && aligned && ((H * (long long)W) % 4 == 0);
+  if ((size_t)n_tiles > h->tile_cap) {
+    cudaFree(h->tile_list);
+    h->tile_list = nullptr, h->tile_cap = 0;
+    B200_CUDA(cudaMalloc(&h->tile_list, (size_t)n_tiles * sizeof(int)));
+    h->tile_cap = (size_t)n_tiles;
+  }
+  B200_CUDA(cudaMemsetAsync(h->sched, 0, 2 * sizeof(unsigned int), st));
+  tiles_from_meta_kernel<<<(unsigned)((n_tiles + 255) / 256), 256, 0, st>>>(
+      h->d, kp->meta_dev, (long long)kp->meta_stride, kp->seg_kf, B, tiles_kf, h->tile_list, h->sched);
+  const long long cap = (long long)h->sm_count * FUSE_MINB;
+  const unsigned ctas = (unsigned)(n_tiles < cap ? n_tiles : cap);
+  if (tma)
+    integrate_keyframes_listed_kernel<true, true, true><<<ctas, 256, 0, st>>>(
+        h->d, ka, mc, fc, h->tile_list, h->sched, tiles_x, tiles_y);
+  else
+    integrate_keyframes_listed_kernel<true, true, false><<<ctas, 256, 0, st>>>(
+        h->d, ka, mc, fc, h->tile_list, h->sched, tiles_x, tiles_y);
+  B200_CUDA(cudaGetLastError());
+  return B200TSDF_OK;
+}
+
+// ---- CUDA IPC: map another rank's keyframe buffer into this process (one process
+// per GPU; NVSwitch gives every peer full NVLink bandwidth).
+extern "C" int b200tsdf_ipc_open(int32_t device, const void *handle64, int64_t offset_bytes,
+                                 void **ptr_out) {
+  B200_NVTX("b200tsdf_ipc_open");
+  if (!handle64 || !ptr_out || offset_bytes < 0) {
+    b200_set_error("b200tsdf_ipc_open: invalid argument");
+    return B200TSDF_E_INVALID;
+  }
+  B200_CUDA(cudaSetDevice(device));
+  cudaIpcMemHandle_t hnd;
+  memcpy(&hnd, handle64, sizeof(hnd));
+  void *base = nullptr;
+  B200_CUDA(cudaIpcOpenMemHandle(&base, hnd, cudaIpcMemLazyEnablePeerAccess));
+  *ptr_out = (char *)base + offset_bytes;
+  return B200TSDF_OK;
+}
+
+extern "C" int b200tsdf_ipc_close(int32_t device, void *ptr, int64_t offset_bytes) {
+  B200_NVTX("b200tsdf_ipc_close");
+  if (!ptr) return B200TSDF_OK;
+  B200_CUDA(cudaSetDevice(device));
+  B200_CUDA(cudaIpcCloseMemHandle((char *)ptr - offset_bytes));
   return B200TSDF_OK;
 }
 
