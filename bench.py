@@ -62,6 +62,11 @@ def parse():
     ap.add_argument("--kf-per-launch", type=int, default=KF_PER_LAUNCH)
     ap.add_argument("--launches-per-step", type=int, default=ORBIT_TOTAL // KF_PER_LAUNCH)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--ingest", default="pull", choices=["pull", "gather"],
+                    help="N > 1: how a launch's keyframes reach the ranks -- pull: ONE small "
+                         "all-gather of meta records, the fuse kernel TMA-loads the tiles it needs "
+                         "from the owners' HBM over NVLink; gather: ONE all-gather of the packed "
+                         "keyframes (= N broadcasts), double-buffered against the fuse")
     ap.add_argument("--no-sections", action="store_true",
                     help="skip the secondary sections (config2, extract, sweep, quality, manager, "
                          "reintegrate): headline value / e2e / roofline only")
@@ -288,6 +293,34 @@ def run_b200(args):
     torch.cuda.synchronize()
 
     main = torch.cuda.current_stream(dev)
+    pull = world > 1 and args.ingest == "pull"
+    peers = sh_pull = None
+    if pull:
+        from mast3r_slam_quality_dualtsdf_b200 import parallel
+
+        # every rank's shares of the L launches in ONE buffer the other ranks map (CUDA IPC)
+        peers = parallel.PeerKeyframes(L, share, H, W, GH, GW, device=dev)
+        for l in range(L):
+            peers.slot(l).copy_(res_seg[l])
+        res_seg = [peers.slot(l) for l in range(L)]
+        torch.cuda.synchronize()
+        dist.barrier()
+        sh_pull = {}
+
+    def pull_volume(v):
+        """ShardedTSDFVolume view of the TSDFVolume v (integrate_slot lives there)."""
+        if id(v) not in sh_pull:
+            from mast3r_slam_quality_dualtsdf_b200 import parallel
+
+            sh_pull[id(v)] = parallel.ShardedTSDFVolume(
+                VOXEL, TRUNC, slab_width=slabs[2], bounds=bounds, device=dev,
+                volume_factory=lambda **kw: v)
+        return sh_pull[id(v)]
+
+    words = TSDFVolume.keyframe_meta_words(share, H, W, GH, GW) if pull else 0
+    meta_bufs = [(torch.empty(words, dtype=torch.int32, device=dev),
+                  torch.empty(words * world, dtype=torch.int32, device=dev)) for _ in range(2)] \
+        if pull else None
 
     def fuse_packed(v, buf, n_seg):
         v.integrate_keyframes_packed(buf, n_seg, share, H, W, GH, GW, MIN_CONF)
@@ -309,6 +342,11 @@ def run_b200(args):
             for l in range(L):
                 fuse_packed(v, res_seg[l], 1)
             return
+        if pull:  # meta record + ONE small all-gather + fuse pulling its tiles from the owners
+            sv = pull_volume(v)
+            for l in range(L):
+                sv.integrate_slot(peers, l, MIN_CONF, meta_bufs=meta_bufs[l & 1])
+            return
         for l in range(L + 1):
             b = l & 1
             if l < L:
@@ -327,6 +365,17 @@ def run_b200(args):
             for l in range(L):  # *_host entry: chunked H2D inside the C ABI call
                 t = host_sep[l]
                 v.integrate_keyframes(t["X"], t["C"], t["pose"], t["q"], MIN_CONF, H, W)
+        elif pull:  # one H2D of my share per launch into its ring slot, then as step_value
+            sv = pull_volume(v)
+            for l in range(L):
+                with torch.cuda.stream(cs):
+                    peers.slot(l).copy_(host_seg[l], non_blocking=True)
+                    copy_done[l & 1].record(cs)
+                main.wait_event(copy_done[l & 1])
+                sv.integrate_slot(peers, l, MIN_CONF, meta_bufs=meta_bufs[l & 1])
+            v.counters()
+            dist.barrier()  # every rank has pulled from my slots: the next step may overwrite them
+            return
         else:  # one H2D + one all-gather + one fuse per launch, three-stage pipeline
             for l in range(L + 2):
                 if l < L:
@@ -397,14 +446,22 @@ def run_b200(args):
         scratch.reset()
         if world == 1:
             fuse_packed(scratch, res_seg[l], 1)
+        elif pull:
+            pull_volume(scratch).integrate_slot(peers, l, MIN_CONF, meta_bufs=meta_bufs[0])
         else:
             dist.all_gather_into_tensor(full[0], res_seg[l])
             fuse_packed(scratch, full[0], world)
         touched_v += scratch.stats(0)["total_voxels"]
         touched_b += scratch.counters()["blocks"]
     del scratch
-    # the launch on this rank reads the whole batch and writes its slabs
-    alg_bytes_launch = B * KF_BYTES + (touched_v * 32 + touched_b * 8) / L
+    # the launch on this rank reads the whole batch and writes its slabs; with the peer pull
+    # it reads its own share (meta pass), the gathered meta records and the tiles it lists
+    # (bounded from above by the share of the batch's rays it does not cull)
+    kf_read = B * KF_BYTES
+    if pull:
+        frac = 1.0 - ctr["culled_rays"] / max(1, ctr["rays"])
+        kf_read = share * KF_BYTES + world * words * 4 + frac * B * KF_BYTES
+    alg_bytes_launch = kf_read + (touched_v * 32 + touched_b * 8) / L
     launch_ms = float(np.mean(step_ms)) / L
     peaks = {}
     try:
@@ -448,25 +505,34 @@ def run_b200(args):
         "config": workload_config(args),
         "partition": "single volume" if world == 1 else
         f"interleaved z-slabs of {slab_width_for(world, wl['dim'])} voxel layers over {world} "
-        f"ranks; every rank holds {share} keyframes of each launch; ONE packed NCCL all-gather "
-        f"(= {world} broadcasts over NVLink) per launch inside the timed region, double-buffered "
-        "against the fuse",
+        f"ranks; every rank holds {share} keyframes of each launch; " +
+        ("peer pull: per launch ONE NCCL all-gather of the meta records (tile z ranges, poses, "
+         "quality grids: ~28 KB per keyframe) inside the timed region, then every rank's fuse "
+         "kernel TMA-loads the tiles that reach its slabs from the owners' HBM over NVLink "
+         "(CUDA IPC mapped buffers)" if pull else
+         f"ONE packed NCCL all-gather (= {world} broadcasts over NVLink) per launch inside the "
+         "timed region, double-buffered against the fuse"),
         "e2e": {"value": e2e_value, "unit": "voxel updates/s",
                 "h2d_bytes_per_step": n_kf_step * KF_BYTES, "d2h_bytes_per_step": 64,
                 "keyframes_per_s": n_kf_step * args.steps / (e2e_ms * 1e-3),
                 "ms_per_step": e2e_ms / args.steps,
                 "ingest": ("b200tsdf_integrate_keyframes_host per launch (chunked H2D overlapped "
                            "with the fuse), one counters read per step" if world == 1 else
-                           "per launch ONE packed H2D of the rank's share, ONE all-gather, one "
-                           "fuse (classify + listed-tile march); copy / gather / fuse of "
-                           "consecutive launches overlap on three streams; one counters read "
-                           "per step")},
+                           ("per launch ONE packed H2D of the rank's share into its ring slot, "
+                            "meta record + ONE small all-gather, fuse pulling its tiles from the "
+                            "owners' slots; one counters read + one barrier per step" if pull else
+                            "per launch ONE packed H2D of the rank's share, ONE all-gather, one "
+                            "fuse (classify + listed-tile march); copy / gather / fuse of "
+                            "consecutive launches overlap on three streams; one counters read "
+                            "per step"))},
         # kernels of this library inside the timed `value` region, all ranks: one fused launch
         # per 40 keyframes and rank; from 3 ranks up the classify pass + the listed-tile fuse
-        "gpu_launches": args.steps * L * world * (2 if world > 2 else 1),
+        "gpu_launches": args.steps * L * world * (3 if pull else 2 if world > 2 else 1),
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": traffic,
-                     "kernel": "integrate_keyframes_kernel" if world <= 2 else
+                     "kernel": "integrate_keyframes_kernel" if world <= 2 and not pull else
+                     "keyframe_meta_kernel + tiles_from_meta_kernel + "
+                     "integrate_keyframes_listed_kernel" if pull else
                      "slab_classify_kernel + integrate_keyframes_listed_kernel",
                      "peak_source": "measured (MEASURED_PEAKS.json hbm_gbs)" if peaks else "fallback",
                      "algorithmic_bytes_per_launch": alg_bytes_launch,

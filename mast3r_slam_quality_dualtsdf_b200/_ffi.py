@@ -19,7 +19,9 @@ SYMBOLS = [
     "b200tsdf_last_error", "b200tsdf_abi_version", "b200tsdf_create", "b200tsdf_destroy",
     "b200tsdf_reset", "b200tsdf_integrate_points", "b200tsdf_integrate_keyframes",
     "b200tsdf_integrate_keyframes_host", "b200tsdf_deintegrate_keyframes",
-    "b200tsdf_integrate_keyframes_ex", "b200tsdf_selftest_div", "b200tsdf_counters", "b200tsdf_stats",
+    "b200tsdf_integrate_keyframes_ex", "b200tsdf_selftest_div",
+    "b200tsdf_keyframe_meta_words", "b200tsdf_keyframe_meta", "b200tsdf_integrate_keyframes_pull",
+    "b200tsdf_ipc_open", "b200tsdf_ipc_close", "b200tsdf_counters", "b200tsdf_stats",
     "b200tsdf_query", "b200tsdf_export_voxels", "b200tsdf_export_blocks",
     "b200tsdf_extract_mesh", "b200tsdf_extract_mesh_indexed", "b200tsdf_weld_mesh",
     "b200tsdf_export_seam_blocks", "b200tsdf_import_halo_blocks",
@@ -52,6 +54,20 @@ class KfBatch(C.Structure):
         ("min_conf", C.c_float), ("negate", C.c_int32), ("step_scale", C.c_double),
         ("max_points", C.c_int32), ("reserved", C.c_int32), ("seed", C.c_uint64),
         ("kf_ids_dev", C.c_void_p),
+    ]
+
+
+MAX_SEGMENTS = 16
+
+
+class KfPull(C.Structure):
+    """b200tsdf_kf_pull (include/b200tsdf.h)."""
+    _fields_ = [
+        ("X_seg_dev", C.c_void_p * MAX_SEGMENTS), ("C_seg_dev", C.c_void_p * MAX_SEGMENTS),
+        ("meta_dev", C.c_void_p), ("meta_stride", C.c_int64),
+        ("n_seg", C.c_int32), ("seg_kf", C.c_int32), ("H", C.c_int32), ("W", C.c_int32),
+        ("gh", C.c_int32), ("gw", C.c_int32), ("min_conf", C.c_float), ("negate", C.c_int32),
+        ("step_scale", C.c_double),
     ]
 
 
@@ -92,6 +108,11 @@ def lib():
     L.b200tsdf_deintegrate_keyframes.argtypes = L.b200tsdf_integrate_keyframes.argtypes
     L.b200tsdf_integrate_keyframes_ex.argtypes = [vp, C.POINTER(KfBatch), vp]
     L.b200tsdf_selftest_div.argtypes = [i32, i64, C.c_uint64, vp, vp]
+    L.b200tsdf_keyframe_meta_words.argtypes = [i32] * 5
+    L.b200tsdf_keyframe_meta.argtypes = [vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, C.c_float, vp, vp]
+    L.b200tsdf_integrate_keyframes_pull.argtypes = [vp, C.POINTER(KfPull), vp]
+    L.b200tsdf_ipc_open.argtypes = [i32, vp, i64, C.POINTER(vp)]
+    L.b200tsdf_ipc_close.argtypes = [i32, vp, i64]
     L.b200tsdf_counters.argtypes = [vp, vp, vp]
     L.b200tsdf_stats.argtypes = [vp, C.c_int, vp, vp, vp]
     L.b200tsdf_query.argtypes = [vp, C.c_int, vp, C.c_int, i64, vp, vp, vp, vp]
@@ -124,6 +145,7 @@ def lib():
     for s in SYMBOLS:
         if s != "b200tsdf_last_error":
             getattr(L, s).restype = C.c_int
+    L.b200tsdf_keyframe_meta_words.restype = C.c_int64
     _lib = L
     return L
 

@@ -41,6 +41,81 @@ def slab_owner(kz, z0, slab_width, world):
     return slab_of(kz, z0, slab_width) % world
 
 
+class PeerKeyframes:
+    """Keyframe batches that are NOT broadcast (DESIGN.md 6 "peer
+    pull").  Every rank keeps ITS share of each batch -- `seg_kf` keyframes as one
+    packed segment (`tsdf.global_volume.packed_layout`) per slot -- in one device
+    buffer of `n_slots` segments, and maps the buffers of all other ranks into
+    its address space with CUDA IPC (one process per GPU; NVSwitch gives every
+    peer full NVLink bandwidth).  `ShardedTSDFVolume.integrate_slot` then moves
+    ~28 KB of meta per keyframe through ONE all-gather and lets the fuse kernel
+    TMA-load just the tiles that reach this rank's slabs from the owners' HBM.
+    With one rank (or `local_only`) nothing is mapped: the same code path runs on
+    local pointers (tests)."""
+
+    def __init__(self, n_slots, seg_kf, H, W, gh=0, gw=0, device=None, group=None,
+                 local_only=False):
+        from . import _ffi
+        from .tsdf.global_volume import packed_layout
+
+        self.group = group
+        self.rank = dist.get_rank(group) if dist.is_initialized() and not local_only else 0
+        self.world = dist.get_world_size(group) if dist.is_initialized() and not local_only else 1
+        self.n_slots, self.seg_kf, self.H, self.W, self.gh, self.gw = n_slots, seg_kf, H, W, gh, gw
+        self.lay = packed_layout(seg_kf, H, W, gh, gw)
+        self.seg_len = self.lay["seg_len"]
+        self.device = torch.device(device)
+        self.buf = torch.zeros(n_slots * self.seg_len, dtype=torch.float32, device=self.device)
+        self._opened = []
+        self.base = [0] * self.world  # device address of rank r's buffer in THIS process
+        self.base[self.rank] = self.buf.data_ptr()
+        if self.world > 1:
+            import ctypes as C
+
+            # (device, handle, size, offset, ...) of the allocation that holds the buffer
+            meta = self.buf.untyped_storage()._share_cuda_()
+            mine = (bytes(meta[1]), int(meta[3]) + self.buf.storage_offset() * 4)
+            handles = [None] * self.world
+            dist.all_gather_object(handles, mine, group=group)
+            for r, (hnd, off) in enumerate(handles):
+                if r == self.rank:
+                    continue
+                ptr = C.c_void_p()
+                _ffi.check(_ffi.lib().b200tsdf_ipc_open(self.device.index or 0, hnd, off,
+                                                       C.byref(ptr)), "ipc_open")
+                self.base[r] = int(ptr.value)
+                self._opened.append((int(ptr.value), off))
+            dist.barrier(group=group)
+
+    def slot(self, i):
+        """This rank's packed segment of slot i (1-D float32 view)."""
+        return self.buf[i * self.seg_len:(i + 1) * self.seg_len]
+
+    def views(self, i):
+        """(X (k,HW,3), C (k,HW), q (k,gh,gw) or None, pose (k,8)) views of my slot i."""
+        sg, lay, k, n = self.slot(i), self.lay, self.seg_kf, self.H * self.W
+        X = sg[lay["X"]:lay["X"] + k * n * 3].view(k, n, 3)
+        Cf = sg[lay["C"]:lay["C"] + k * n].view(k, n)
+        q = sg[lay["q"]:lay["q"] + k * self.gh * self.gw].view(k, self.gh, self.gw) \
+            if self.gh and self.gw else None
+        P = sg[lay["pose"]:lay["pose"] + k * 8].view(k, 8)
+        return X, Cf, q, P
+
+    def pointers(self, i):
+        """Per source rank: device addresses of its slot-i pointmaps / confidences."""
+        off = i * self.seg_len * 4
+        xs = [b + off + 4 * self.lay["X"] for b in self.base]
+        cs = [b + off + 4 * self.lay["C"] for b in self.base]
+        return xs, cs
+
+    def close(self):
+        from . import _ffi
+
+        for ptr, off in self._opened:
+            _ffi.lib().b200tsdf_ipc_close(self.device.index or 0, ptr, off)
+        self._opened = []
+
+
 class ShardedTSDFVolume:
     def __init__(self, voxel_size, truncation, max_weight=100.0, min_weight=1.0e-3, *,
                  slab_width, bounds=None, capacity_log2=17, device=None, group=None,
@@ -116,6 +191,30 @@ class ShardedTSDFVolume:
                     "X": X[b].clone(), "C": Cf[b].clone(), "pose": poses[b].reshape(8).clone(),
                     "q": None if q_grid is None else q_grid[b].clone(),
                     "args": (float(min_conf), int(H), int(W), float(step_scale))}
+
+    def integrate_slot(self, peers, i, min_conf=0.05, step_scale=0.5, meta_bufs=None):
+        """Fuse slot i of a `PeerKeyframes` ring on every rank WITHOUT moving the
+        pointmaps: meta record of my share (one kernel), ONE all-gather of the
+        records (tile z ranges, poses, quality grids: ~28 KB per keyframe), then
+        the fuse kernel pulls the tiles that reach my slabs from the owners' HBM.
+        Everything is queued on the current stream; the all-gather also orders the
+        owners' writes to slot i (queued before it) ahead of the peers' reads.
+        meta_bufs: optional (share, full) int32 tensors to reuse."""
+        X, Cf, q, P = peers.views(i)
+        words = self.vol.keyframe_meta_words(peers.seg_kf, peers.H, peers.W, peers.gh, peers.gw)
+        if meta_bufs is None:
+            meta_bufs = (torch.empty(words, dtype=torch.int32, device=self.device),
+                         torch.empty(words * self.world, dtype=torch.int32, device=self.device))
+        share, full = meta_bufs
+        self.vol.keyframe_meta(X, Cf, P, q, min_conf, peers.H, peers.W, out=share)
+        if self.world > 1:
+            dist.all_gather_into_tensor(full, share, group=self.group)
+        else:
+            full = share
+        xs, cs = peers.pointers(i)
+        self.vol.integrate_keyframes_pull(xs, cs, full, peers.seg_kf, peers.H, peers.W, peers.gh,
+                                          peers.gw, min_conf, step_scale)
+        return meta_bufs
 
     # -- re-integration after a backend solve (SURVEY 8(e), config 5) ------------
     def stored_ids(self):

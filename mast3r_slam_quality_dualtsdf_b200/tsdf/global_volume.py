@@ -303,6 +303,54 @@ class TSDFVolume:
             _ffi.check(_ffi.lib().b200tsdf_integrate_keyframes_ex(
                 self._h, C.byref(kb), _stream_ptr(self.device)), "integrate_keyframes_ex")
 
+    # -- multi-GPU peer pull (parallel.PeerKeyframes drives these) ---------------
+    @staticmethod
+    def keyframe_meta_words(seg_kf, H, W, gh=0, gw=0):
+        return int(_ffi.lib().b200tsdf_keyframe_meta_words(seg_kf, H, W, gh, gw))
+
+    def keyframe_meta(self, X, Cf, poses, q_grid=None, min_conf=0.05, H=None, W=None, out=None):
+        """OWNER side of the peer pull: the meta record of the keyframes this rank
+        holds -- per 32 x 8 tile the z range of its bands (voxel layers) and its
+        ray count, then the poses and quality grids (int32 device tensor of
+        `keyframe_meta_words` words; ~28 KB per keyframe instead of 3.1 MB)."""
+        B, N = X.shape[0], X.shape[1]
+        gh = gw = 0
+        if q_grid is not None:
+            gh, gw = int(q_grid.shape[-2]), int(q_grid.shape[-1])
+        words = self.keyframe_meta_words(B, H, W, gh, gw)
+        if out is None:
+            out = torch.zeros(words, dtype=torch.int32, device=self.device)
+        with self._reading():
+            _ffi.check(_ffi.lib().b200tsdf_keyframe_meta(
+                self._h, X.data_ptr(), Cf.data_ptr(),
+                q_grid.data_ptr() if q_grid is not None else None, poses.data_ptr(), B, H, W, gh,
+                gw, float(min_conf), out.data_ptr(), _stream_ptr(self.device)), "keyframe_meta")
+        return out
+
+    def integrate_keyframes_pull(self, x_ptrs, c_ptrs, meta, seg_kf, H, W, gh=0, gw=0,
+                                 min_conf=0.05, step_scale=0.5, negate=False):
+        """Fuse a batch whose pointmaps / confidences stay where they are: segment
+        s (seg_kf keyframes of source rank s) is read tile by tile from the device
+        addresses x_ptrs[s] / c_ptrs[s] (ints: this GPU's memory or a peer buffer
+        mapped over NVLink); `meta` = the gathered meta records (n_seg x
+        keyframe_meta_words int32).  Only tiles whose band reaches this volume's
+        slabs are loaded."""
+        n_seg = len(x_ptrs)
+        if n_seg != len(c_ptrs) or not 0 < n_seg <= _ffi.MAX_SEGMENTS:
+            raise ValueError(f"1..{_ffi.MAX_SEGMENTS} segments, X and C pointers for each")
+        stride = self.keyframe_meta_words(seg_kf, H, W, gh, gw)
+        if meta.dtype != torch.int32 or not meta.is_cuda or meta.numel() < n_seg * stride:
+            raise ValueError("meta must be an int32 device tensor of n_seg meta records")
+        kp = _ffi.KfPull()
+        for s_ in range(n_seg):
+            kp.X_seg_dev[s_], kp.C_seg_dev[s_] = int(x_ptrs[s_]), int(c_ptrs[s_])
+        kp.meta_dev, kp.meta_stride = meta.data_ptr(), stride
+        kp.n_seg, kp.seg_kf, kp.H, kp.W, kp.gh, kp.gw = n_seg, seg_kf, H, W, gh, gw
+        kp.min_conf, kp.negate, kp.step_scale = float(min_conf), int(bool(negate)), float(step_scale)
+        with self._writing():
+            _ffi.check(_ffi.lib().b200tsdf_integrate_keyframes_pull(
+                self._h, C.byref(kp), _stream_ptr(self.device)), "integrate_keyframes_pull")
+
     # ------------------------------------------------------------------
     # Query helpers
     # ------------------------------------------------------------------

@@ -3,7 +3,7 @@
 N=${1:-2}
 mkdir -p gpurun_out
 TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1"
-for s in sharded_mesh_check sharded_query_check sharded_reintegrate_check; do
+for s in sharded_pull_check sharded_mesh_check sharded_query_check sharded_reintegrate_check; do
   timeout 300 $TR --master-port 296$((RANDOM % 90 + 10)) scripts/$s.py > gpurun_out/${s}_n$N.log 2>&1
   echo "$s N=$N rc=$?"; tail -2 gpurun_out/${s}_n$N.log | cut -c1-600
 done

@@ -213,3 +213,52 @@ def test_target_1024_slab_union_matches_oracle(cuda_device, target_case, R):
         got = tuple(np.concatenate([p[i] for p in parts[which]])[order] for i in range(4))
         assert len(np.unique(got[0], axis=0)) == len(got[0]), "a voxel has two owners"
         assert_volume_matches(got, orc_vol.export(), f"R={R} slab union {name}")
+
+
+@pytest.mark.parametrize("R", [1, 2, 8])
+def test_target_1024_peer_pull_matches_oracle(cuda_device, target_case, R):
+    """The peer-pull ingest (b200tsdf_keyframe_meta -> gathered meta records ->
+    b200tsdf_integrate_keyframes_pull reading the tiles through per-segment
+    pointers) with one GPU emulating the R ranks in turn: segments are separate
+    buffers, every emulated rank lists and loads only the tiles whose band
+    reaches its slabs.  Union == sequential oracle; ray / culled accounting
+    equals the broadcast path's."""
+    from mast3r_slam_quality_dualtsdf_b200.tsdf import TSDFVolume
+
+    kfs, vp, vq, rays = target_case
+    lo, hi = synth.bounds_for(TARGET_SCENE, VOXEL, TARGET_DIM)
+    share = 8 // R
+    seg = []
+    for r in range(R):
+        sl = slice(r * share, (r + 1) * share)
+        seg.append({k: torch.from_numpy(np.ascontiguousarray(kfs[k][sl])).to(cuda_device)
+                    for k in ("X", "C", "pose", "q")})
+    width = max(8, TARGET_DIM // (4 * R))
+    owner = TSDFVolume(VOXEL, TRUNC, capacity_log2=10, bounds=(lo, hi), device=cuda_device)
+    words = owner.keyframe_meta_words(share, H, W, 24, 32)
+    meta = torch.cat([owner.keyframe_meta(s["X"], s["C"], s["pose"], s["q"], 0.05, H, W)
+                      for s in seg])
+    assert meta.numel() == R * words
+    xs, cs = [s["X"].data_ptr() for s in seg], [s["C"].data_ptr() for s in seg]
+    parts = {0: [], 1: []}
+    upd_p = upd_q = culled = 0
+    for r in range(R):
+        vol = TSDFVolume(VOXEL, TRUNC, capacity_log2=18, bounds=(lo, hi),
+                         slabs=(R, r, width) if R > 1 else None, device=cuda_device)
+        vol.integrate_keyframes_pull(xs, cs, meta, share, H, W, 24, 32, 0.05)
+        c = vol.counters()
+        assert c["rays"] == rays and c["overflow"] == 0
+        upd_p += c["updates_primary"]
+        upd_q += c["updates_quality"]
+        culled += c["culled_rays"]
+        for which in (0, 1):
+            parts[which].append(vol.export(which))
+        vol.close()
+    assert upd_p == vp.events and upd_q == vq.events
+    assert (culled > 0) == (R > 1)
+    for which, orc_vol, name in ((0, vp, "primary"), (1, vq, "quality")):
+        k = np.concatenate([p[0] for p in parts[which]])
+        order = np.lexsort((k[:, 2], k[:, 1], k[:, 0]))
+        got = tuple(np.concatenate([p[i] for p in parts[which]])[order] for i in range(4))
+        assert len(np.unique(got[0], axis=0)) == len(got[0]), "a voxel has two owners"
+        assert_volume_matches(got, orc_vol.export(), f"R={R} peer pull {name}")
