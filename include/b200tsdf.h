@@ -193,9 +193,14 @@ int b200tsdf_keyframe_meta(b200tsdf_t *h, const float *X_dev, const float *C_dev
                            int32_t W, int32_t gh, int32_t gw, float min_conf, uint32_t *meta_dev,
                            void *stream);
 int b200tsdf_integrate_keyframes_pull(b200tsdf_t *h, const b200tsdf_kf_pull *pull, void *stream);
-/* CUDA IPC plumbing for the peer buffers (one process per GPU): handle64 = the 64
- * bytes of a cudaIpcMemHandle_t exported by the owner, offset_bytes = offset of the
- * buffer inside that allocation.  ipc_close takes the pointer ipc_open returned. */
+/* CUDA IPC plumbing for the peer buffers (one process per GPU).  peer_alloc: a
+ * zeroed device buffer as its own allocation plus the 64 bytes of its
+ * cudaIpcMemHandle_t (ship them to the other ranks); ipc_open maps a buffer from
+ * those bytes (offset_bytes = offset of the data inside the exported allocation, 0
+ * for peer_alloc buffers) with peer access enabled; ipc_close takes the pointer
+ * ipc_open returned. */
+int b200tsdf_peer_alloc(int32_t device, int64_t bytes, void **ptr_out, void *handle64_out);
+int b200tsdf_peer_free(int32_t device, void *ptr);
 int b200tsdf_ipc_open(int32_t device, const void *handle64, int64_t offset_bytes, void **ptr_out);
 int b200tsdf_ipc_close(int32_t device, void *ptr, int64_t offset_bytes);
 

@@ -21,7 +21,7 @@ SYMBOLS = [
     "b200tsdf_integrate_keyframes_host", "b200tsdf_deintegrate_keyframes",
     "b200tsdf_integrate_keyframes_ex", "b200tsdf_selftest_div",
     "b200tsdf_keyframe_meta_words", "b200tsdf_keyframe_meta", "b200tsdf_integrate_keyframes_pull",
-    "b200tsdf_ipc_open", "b200tsdf_ipc_close", "b200tsdf_counters", "b200tsdf_stats",
+    "b200tsdf_ipc_open", "b200tsdf_ipc_close", "b200tsdf_peer_alloc", "b200tsdf_peer_free", "b200tsdf_counters", "b200tsdf_stats",
     "b200tsdf_query", "b200tsdf_export_voxels", "b200tsdf_export_blocks",
     "b200tsdf_extract_mesh", "b200tsdf_extract_mesh_indexed", "b200tsdf_weld_mesh",
     "b200tsdf_export_seam_blocks", "b200tsdf_import_halo_blocks",
@@ -113,6 +113,8 @@ def lib():
     L.b200tsdf_integrate_keyframes_pull.argtypes = [vp, C.POINTER(KfPull), vp]
     L.b200tsdf_ipc_open.argtypes = [i32, vp, i64, C.POINTER(vp)]
     L.b200tsdf_ipc_close.argtypes = [i32, vp, i64]
+    L.b200tsdf_peer_alloc.argtypes = [i32, i64, C.POINTER(vp), vp]
+    L.b200tsdf_peer_free.argtypes = [i32, vp]
     L.b200tsdf_counters.argtypes = [vp, vp, vp]
     L.b200tsdf_stats.argtypes = [vp, C.c_int, vp, vp, vp]
     L.b200tsdf_query.argtypes = [vp, C.c_int, vp, C.c_int, i64, vp, vp, vp, vp]

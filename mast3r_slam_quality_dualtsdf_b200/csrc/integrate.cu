@@ -1366,6 +1366,42 @@ extern "C" int b200tsdf_integrate_keyframes_pull(b200tsdf_t *h, const b200tsdf_k
 
 // ---- CUDA IPC: map another rank's keyframe buffer into this process (one process
 // per GPU; NVSwitch gives every peer full NVLink bandwidth).
+// The shareable buffer itself: its own cudaMalloc allocation (offset 0 in its IPC
+// handle), so nothing depends on how a framework's caching allocator carves blocks.
+extern "C" int b200tsdf_peer_alloc(int32_t device, int64_t bytes, void **ptr_out, void *handle64_out) {
+  B200_NVTX("b200tsdf_peer_alloc");
+  if (bytes <= 0 || !ptr_out || !handle64_out) {
+    b200_set_error("b200tsdf_peer_alloc: invalid argument");
+    return B200TSDF_E_INVALID;
+  }
+  B200_CUDA(cudaSetDevice(device));
+  void *p = nullptr;
+  if (cudaMalloc(&p, (size_t)bytes) != cudaSuccess) {
+    (void)cudaGetLastError();
+    b200_set_error("b200tsdf_peer_alloc: cudaMalloc of %lld bytes failed", (long long)bytes);
+    return B200TSDF_E_NOMEM;
+  }
+  cudaIpcMemHandle_t hnd;
+  cudaError_t e = cudaMemset(p, 0, (size_t)bytes);
+  if (e == cudaSuccess) e = cudaIpcGetMemHandle(&hnd, p);
+  if (e != cudaSuccess) {
+    cudaFree(p);
+    b200_set_error("b200tsdf_peer_alloc: %s", cudaGetErrorString(e));
+    return B200TSDF_E_CUDA;
+  }
+  memcpy(handle64_out, &hnd, sizeof(hnd));
+  *ptr_out = p;
+  return B200TSDF_OK;
+}
+
+extern "C" int b200tsdf_peer_free(int32_t device, void *ptr) {
+  B200_NVTX("b200tsdf_peer_free");
+  if (!ptr) return B200TSDF_OK;
+  B200_CUDA(cudaSetDevice(device));
+  B200_CUDA(cudaFree(ptr));
+  return B200TSDF_OK;
+}
+
 extern "C" int b200tsdf_ipc_open(int32_t device, const void *handle64, int64_t offset_bytes,
                                  void **ptr_out) {
   B200_NVTX("b200tsdf_ipc_open");

@@ -64,27 +64,39 @@ class PeerKeyframes:
         self.n_slots, self.seg_kf, self.H, self.W, self.gh, self.gw = n_slots, seg_kf, H, W, gh, gw
         self.lay = packed_layout(seg_kf, H, W, gh, gw)
         self.seg_len = self.lay["seg_len"]
+        import ctypes as C
+
         self.device = torch.device(device)
-        self.buf = torch.zeros(n_slots * self.seg_len, dtype=torch.float32, device=self.device)
+        self._dev_index = self.device.index if self.device.index is not None else \
+            torch.cuda.current_device()
+        n = n_slots * self.seg_len
+        # the buffer is its own cudaMalloc allocation owned by libb200tsdf (offset 0 in its
+        # IPC handle); torch sees it through __cuda_array_interface__ (zero copy)
+        ptr, hnd = C.c_void_p(), (C.c_ubyte * 64)()
+        _ffi.check(_ffi.lib().b200tsdf_peer_alloc(self._dev_index, n * 4, C.byref(ptr), hnd),
+                   "peer_alloc")
+        self._own = int(ptr.value)
+
+        class _Raw:
+            __cuda_array_interface__ = {"shape": (n,), "typestr": "<f4", "version": 2,
+                                        "data": (self._own, False)}
+
+        self.buf = torch.as_tensor(_Raw(), device=self.device)
+        assert self.buf.data_ptr() == self._own
         self._opened = []
         self.base = [0] * self.world  # device address of rank r's buffer in THIS process
-        self.base[self.rank] = self.buf.data_ptr()
+        self.base[self.rank] = self._own
         if self.world > 1:
-            import ctypes as C
-
-            # (device, handle, size, offset, ...) of the allocation that holds the buffer
-            meta = self.buf.untyped_storage()._share_cuda_()
-            mine = (bytes(meta[1]), int(meta[3]) + self.buf.storage_offset() * 4)
             handles = [None] * self.world
-            dist.all_gather_object(handles, mine, group=group)
-            for r, (hnd, off) in enumerate(handles):
+            dist.all_gather_object(handles, bytes(hnd), group=group)
+            for r, hb in enumerate(handles):
                 if r == self.rank:
                     continue
-                ptr = C.c_void_p()
-                _ffi.check(_ffi.lib().b200tsdf_ipc_open(self.device.index or 0, hnd, off,
-                                                       C.byref(ptr)), "ipc_open")
-                self.base[r] = int(ptr.value)
-                self._opened.append((int(ptr.value), off))
+                p2 = C.c_void_p()
+                _ffi.check(_ffi.lib().b200tsdf_ipc_open(self._dev_index, hb, 0, C.byref(p2)),
+                           "ipc_open")
+                self.base[r] = int(p2.value)
+                self._opened.append((int(p2.value), 0))
             dist.barrier(group=group)
 
     def slot(self, i):
@@ -112,8 +124,25 @@ class PeerKeyframes:
         from . import _ffi
 
         for ptr, off in self._opened:
-            _ffi.lib().b200tsdf_ipc_close(self.device.index or 0, ptr, off)
+            _ffi.lib().b200tsdf_ipc_close(self._dev_index, ptr, off)
         self._opened = []
+        if dist.is_initialized() and self.world > 1:
+            dist.barrier(group=self.group)  # nobody reads my buffer any more
+        if self._own:
+            self.buf = None
+            _ffi.lib().b200tsdf_peer_free(self._dev_index, self._own)
+            self._own = 0
+
+    def __del__(self):
+        try:
+            if getattr(self, "_own", 0) and not self._opened:
+                from . import _ffi
+
+                self.buf = None
+                _ffi.lib().b200tsdf_peer_free(self._dev_index, self._own)
+                self._own = 0
+        except Exception:  # noqa: BLE001
+            pass
 
 
 class ShardedTSDFVolume:

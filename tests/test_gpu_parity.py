@@ -270,3 +270,30 @@ def test_against_reference_golden(cuda_device, case):
         assert np.array_equal(fl & 1, g[f"{name}_qfl"] & 1)
         has = (fl & 1) > 0
         assert np.abs(t[has] - g[f"{name}_qt"][has]).max() <= 1e-5
+
+
+def test_peer_keyframes_ring_one_rank(cuda_device):
+    """parallel.PeerKeyframes / ShardedTSDFVolume.integrate_slot with one rank:
+    the ring buffer is libb200tsdf's own allocation seen by torch through
+    __cuda_array_interface__; the pull path (meta record -> tile list -> fuse
+    through per-segment pointers) equals the plain batch fuse bit for bit in
+    keys and counts."""
+    from mast3r_slam_quality_dualtsdf_b200 import parallel
+    from mast3r_slam_quality_dualtsdf_b200.tsdf.global_volume import pack_keyframes
+
+    kf = synth.make_keyframes(synth.SCENES["sphere"], 4, H=48, W=64, seed=2, f=50.0, total=12)
+    bounds = ((-128, -128, -64), (128, 128, 192))
+    peers = parallel.PeerKeyframes(2, 2, 48, 64, 3, 4, device=cuda_device, local_only=True)
+    for s in range(2):
+        sl = slice(2 * s, 2 * s + 2)
+        pack_keyframes(kf["X"][sl], kf["C"][sl], kf["pose"][sl], kf["q"][sl], out=peers.slot(s))
+    X, Cf, q, P = peers.views(1)
+    assert np.array_equal(X.cpu().numpy(), kf["X"][2:4]) and np.array_equal(q.cpu().numpy(), kf["q"][2:4])
+    sv = parallel.ShardedTSDFVolume(0.03, 0.12, slab_width=8, bounds=bounds, device=cuda_device)
+    for s in range(2):
+        sv.integrate_slot(peers, s, 0.05)
+    vp, vq, rays = oracle_dual(kf, 0.03, 0.12)
+    assert sv.vol.counters()["rays"] == rays
+    assert_volume_matches(sv.vol.export(0), vp.export(), "ring primary")
+    assert_volume_matches(sv.vol.export(1), vq.export(), "ring quality")
+    peers.close()
