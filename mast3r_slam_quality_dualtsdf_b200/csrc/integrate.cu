@@ -682,8 +682,11 @@ __global__ void __launch_bounds__(256)
 // the TMA copies of tile k+1 are in flight, the list entry of tile k+2 is being
 // read and the ticket after that is being fetched (thread 0 keeps them in
 // registers and never waits on a value it requested in the same iteration).
+#ifndef FUSE_MINB_LISTED
+#define FUSE_MINB_LISTED FUSE_MINB
+#endif
 template <bool BOUNDED, bool DIR, bool TMA>
-__global__ void __launch_bounds__(256, FUSE_MINB)
+__global__ void __launch_bounds__(256, FUSE_MINB_LISTED)
     integrate_keyframes_listed_kernel(const __grid_constant__ VolumeDev v,
                                       const __grid_constant__ KfArgs a,
                                       const __grid_constant__ MarchConst mc,
@@ -1001,7 +1004,7 @@ static int fuse_keyframes(b200tsdf_t *h, const b200tsdf_kf_batch *kb, void *stre
     const dim3 cgrid((grid.x + CLS_TILES - 1) / CLS_TILES, grid.y, grid.z);
     slab_classify_kernel<<<cgrid, 256, 0, st>>>(h->d, ka, mc, h->tile_list, h->sched, (int)grid.x,
                                                 (int)grid.y);
-    const long long cap = (long long)h->sm_count * FUSE_MINB;
+    const long long cap = (long long)h->sm_count * FUSE_MINB_LISTED;
     const unsigned ctas = (unsigned)(n_tiles < cap ? n_tiles : cap);
 #define LAUNCH_LISTED(BD, DR, TM)                                                              \
   integrate_keyframes_listed_kernel<BD, DR, TM><<<ctas, 256, 0, st>>>(                          \
@@ -1352,7 +1355,7 @@ extern "C" int b200tsdf_integrate_keyframes_pull(b200tsdf_t *h, const b200tsdf_k
   B200_CUDA(cudaMemsetAsync(h->sched, 0, 2 * sizeof(unsigned int), st));
   tiles_from_meta_kernel<<<(unsigned)((n_tiles + 255) / 256), 256, 0, st>>>(
       h->d, kp->meta_dev, (long long)kp->meta_stride, kp->seg_kf, B, tiles_kf, h->tile_list, h->sched);
-  const long long cap = (long long)h->sm_count * FUSE_MINB;
+  const long long cap = (long long)h->sm_count * FUSE_MINB_LISTED;
   const unsigned ctas = (unsigned)(n_tiles < cap ? n_tiles : cap);
   if (tma)
     integrate_keyframes_listed_kernel<true, true, true><<<ctas, 256, 0, st>>>(
