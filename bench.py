@@ -67,6 +67,9 @@ def parse():
                          "all-gather of meta records, the fuse kernel TMA-loads the tiles it needs "
                          "from the owners' HBM over NVLink; gather: ONE all-gather of the packed "
                          "keyframes (= N broadcasts), double-buffered against the fuse")
+    ap.add_argument("--no-pipeline", action="store_true",
+                    help="N > 1, pull ingest: meta pass, all-gather and fuse of a launch in series "
+                         "on one stream (A/B against the default software pipeline)")
     ap.add_argument("--no-sections", action="store_true",
                     help="skip the secondary sections (config2, extract, sweep, quality, manager, "
                          "reintegrate): headline value / e2e / roofline only")
@@ -335,6 +338,7 @@ def run_b200(args):
     fuse_done = [torch.cuda.Event() for _ in range(2)]
     copy_done = [torch.cuda.Event() for _ in range(2)]
     gath_done = [torch.cuda.Event() for _ in range(2)]
+    slot_ready = [torch.cuda.Event() for _ in range(L)]
 
     def step_value(v):
         """One pass over the orbit from HBM-resident shares."""
@@ -344,8 +348,11 @@ def run_b200(args):
             return
         if pull:  # meta record + ONE small all-gather + fuse pulling its tiles from the owners
             sv = pull_volume(v)
-            for l in range(L):
-                sv.integrate_slot(peers, l, MIN_CONF, meta_bufs=meta_bufs[l & 1])
+            if args.no_pipeline:
+                for l in range(L):
+                    sv.integrate_slot(peers, l, MIN_CONF, meta_bufs=meta_bufs[l & 1])
+            else:  # meta + all-gather of launch l+1 behind the fuse of launch l
+                sv.integrate_slots(peers, range(L), MIN_CONF, meta_bufs=meta_bufs)
             return
         for l in range(L + 1):
             b = l & 1
@@ -367,12 +374,21 @@ def run_b200(args):
                 v.integrate_keyframes(t["X"], t["C"], t["pose"], t["q"], MIN_CONF, H, W)
         elif pull:  # one H2D of my share per launch into its ring slot, then as step_value
             sv = pull_volume(v)
-            for l in range(L):
+            if args.no_pipeline:
+                for l in range(L):
+                    with torch.cuda.stream(cs):
+                        peers.slot(l).copy_(host_seg[l], non_blocking=True)
+                        copy_done[l & 1].record(cs)
+                    main.wait_event(copy_done[l & 1])
+                    sv.integrate_slot(peers, l, MIN_CONF, meta_bufs=meta_bufs[l & 1])
+            else:
+                cs.wait_stream(main)
                 with torch.cuda.stream(cs):
-                    peers.slot(l).copy_(host_seg[l], non_blocking=True)
-                    copy_done[l & 1].record(cs)
-                main.wait_event(copy_done[l & 1])
-                sv.integrate_slot(peers, l, MIN_CONF, meta_bufs=meta_bufs[l & 1])
+                    for l in range(L):
+                        peers.slot(l).copy_(host_seg[l], non_blocking=True)
+                        slot_ready[l].record(cs)
+                sv.integrate_slots(peers, range(L), MIN_CONF, meta_bufs=meta_bufs,
+                                   ready=slot_ready)
             v.counters()
             dist.barrier()  # every rank has pulled from my slots: the next step may overwrite them
             return
@@ -408,9 +424,11 @@ def run_b200(args):
         v.reset()
         for _ in range(warmup):
             step_fn(v)
-        barrier()
-        c0 = v.counters()
+        # started BEFORE the barrier: its start-up (NVML + a thread) on rank 0 would otherwise
+        # sit inside the other ranks' timed region (they wait for rank 0 at the first collective)
         sampler = ClockSampler(local) if (rank == 0 and sample_clocks) else None
+        c0 = v.counters()
+        barrier()
         ev = [torch.cuda.Event(enable_timing=True) for _ in range(steps + 1)]
         ev[0].record()
         for i in range(steps):

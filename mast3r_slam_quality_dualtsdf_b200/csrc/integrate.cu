@@ -457,6 +457,9 @@ __device__ __forceinline__ void fuse_pixels_warp_fast(const VolumeDev &v, const 
 #define SX_ROW 104 // floats per staged X row: 96 + 8 pad (bank-conflict-free, 16 B multiple)
 #define SC_ROW 40  // floats per staged C row: 32 + 8 pad
 
+#ifndef FUSE_KF_ORDER
+#define FUSE_KF_ORDER 1
+#endif
 struct KfArgs { // one keyframe batch (device pointers)
   const float *X, *C, *qg, *poses; // bases of segment 0
   // packed multi-GPU ingest: the batch is n segments (one per source rank) of
@@ -474,6 +477,12 @@ struct KfArgs { // one keyframe batch (device pointers)
   // through qg / poses + s * seg_stride as before.  n_ptr = 0: not used.
   const float *segX[B200TSDF_MAX_SEGMENTS], *segC[B200TSDF_MAX_SEGMENTS];
   int n_ptr;
+  // CTA order of the one-CTA-per-tile launch: `order` keyframes of the SAME tile
+  // position are adjacent in the block schedule (grid.x = order * tiles_x, grid.z =
+  // keyframes / order).  Consecutive keyframes of a trajectory see nearly the same
+  // surface through the same tile, so the voxels the resident CTAs reduce into are a
+  // few MB instead of a whole view's band and stay in L2 between their updates.
+  int order;
 };
 
 // Seeded bijective 32-bit hash of the pixel index (murmur3 finaliser: xor-shifts
@@ -590,15 +599,16 @@ __global__ void __launch_bounds__(256, FUSE_MINB)
   __shared__ __align__(8) unsigned long long s_bar;
   WarpCache &wc = wcs[DIR ? 0 : (threadIdx.x >> 5)];
   const uint32_t bar = smem_u32(&s_bar);
+  int bx = blockIdx.x, kf = blockIdx.z;
+  if (a.order > 1) kf = kf * a.order + bx % a.order, bx /= a.order;
   if (TMA && threadIdx.x == 0) {
     mbar_init(bar, 1);
-    tile_issue(a, sX, sC, bar, blockIdx.x, blockIdx.y, blockIdx.z);
+    tile_issue(a, sX, sC, bar, bx, blockIdx.y, kf);
   }
   if (!DIR) warp_cache_init(wc);
   if (TMA) __syncthreads(); // mbarrier init visible to the waiters
   Tally tl = {0, 0, 0, 0, 0, 0, 0};
-  tile_consume<BOUNDED, DIR, TMA>(v, wc, a, mc, fc, d_sh, sX, sC, bar, 0, blockIdx.x, blockIdx.y,
-                                  blockIdx.z, tl);
+  tile_consume<BOUNDED, DIR, TMA>(v, wc, a, mc, fc, d_sh, sX, sC, bar, 0, bx, blockIdx.y, kf, tl);
   commit_tally(v, tl);
 }
 
@@ -1012,7 +1022,15 @@ static int fuse_keyframes(b200tsdf_t *h, const b200tsdf_kf_batch *kb, void *stre
     DISPATCH_KF(LAUNCH_LISTED)
 #undef LAUNCH_LISTED
   } else {
-#define LAUNCH_KF(BD, DR, TM) integrate_keyframes_kernel<BD, DR, TM><<<grid, 256, 0, st>>>(h->d, ka, mc, fc)
+    static const int kf_order = [] {
+      const char *e = getenv("B200TSDF_KF_ORDER"); // A/B knob, see KfArgs::order
+      return e ? atoi(e) : FUSE_KF_ORDER;
+    }();
+    int order = kf_order < 1 ? 1 : kf_order;
+    while (order > 1 && (B % order) != 0) --order; // largest divisor of the batch <= the knob
+    ka.order = order;
+    const dim3 ogrid(grid.x * (unsigned)order, grid.y, (unsigned)(B / order));
+#define LAUNCH_KF(BD, DR, TM) integrate_keyframes_kernel<BD, DR, TM><<<ogrid, 256, 0, st>>>(h->d, ka, mc, fc)
     DISPATCH_KF(LAUNCH_KF)
 #undef LAUNCH_KF
   }
@@ -1224,6 +1242,16 @@ __global__ void __launch_bounds__(256)
       table[((long long)kf * tiles_y + blockIdx.y) * tiles_x + bx] = m;
     }
   }
+  // the first CTA of a keyframe also copies its pose and quality grid behind the
+  // tile table: [tile table | poses | quality grids]
+  if (blockIdx.x == 0 && blockIdx.y == 0) {
+    float *tail = reinterpret_cast<float *>(table + (long long)gridDim.z * tiles_y * tiles_x);
+    if (threadIdx.x < 8) tail[kf * 8 + threadIdx.x] = P[threadIdx.x];
+    if (k.qg) {
+      float *q = tail + (long long)gridDim.z * 8 + (long long)kf * a.gh * a.gw;
+      for (int i = threadIdx.x; i < a.gh * a.gw; i += 256) q[i] = k.qg[i];
+    }
+  }
 }
 
 // One thread per tile of the gathered batch: list it if its z range reaches a slab
@@ -1284,12 +1312,6 @@ extern "C" int b200tsdf_keyframe_meta(b200tsdf_t *h, const float *X_dev, const f
   const dim3 grid((unsigned)((tiles_x + CLS_TILES - 1) / CLS_TILES), (unsigned)tiles_y, (unsigned)B);
   keyframe_meta_kernel<<<grid, 256, 0, st>>>(ka, mc, (TileMeta *)meta_dev, tiles_x, tiles_y);
   B200_CUDA(cudaGetLastError());
-  // [tile table | poses | quality grids]: what the fuse needs beside the tiles themselves
-  uint32_t *p = meta_dev + (size_t)B * tiles_x * tiles_y * 4;
-  B200_CUDA(cudaMemcpyAsync(p, pose_dev, (size_t)B * 8 * sizeof(float), cudaMemcpyDeviceToDevice, st));
-  if (q_grid_dev)
-    B200_CUDA(cudaMemcpyAsync(p + (size_t)B * 8, q_grid_dev, (size_t)B * gh * gw * sizeof(float),
-                              cudaMemcpyDeviceToDevice, st));
   return B200TSDF_OK;
 }
 

@@ -244,21 +244,24 @@ __global__ void __launch_bounds__(MC_THREADS, MC_CTAS_PER_SM)
 // stores are coalesced and no lane idles behind a 5-triangle cube.  Blocks
 // without a sign change (most of a band's blocks) stop after the row pass.
 #define MC2_CUBE_CAP 512
+#ifndef MC2_STAGES
+#define MC2_STAGES 3 // raw-word buffers: the block being processed + MC2_STAGES - 1 in flight
+#endif
 template <bool WRITE>
 __global__ void __launch_bounds__(MC_THREADS, MC_CTAS_PER_SM)
     mc_kernel2(VolumeDev v, const uint32_t *__restrict__ nbr, int which, float vs,
                float *__restrict__ verts, long long tri_cap, unsigned long long *n_tris) {
   __shared__ float tv[9 * 9 * 9 + 7];
-  __shared__ __align__(16) float2 r_sw[2][9 * 9 * 9 + 7];
-  __shared__ uint32_t r_h[2][9 * 9 * 9 + 7];
+  __shared__ __align__(16) float2 r_sw[MC2_STAGES][9 * 9 * 9 + 7];
+  __shared__ uint32_t r_h[MC2_STAGES][9 * 9 * 9 + 7];
   __shared__ uint32_t s_nb[8];
-  __shared__ unsigned long long s_key[2], s_base; // s_key[it & 1]: emission of block b reads it
-                                                 // while thread 0 already stores the next key
+  __shared__ __align__(8) unsigned long long s_key[MC2_STAGES], s_base; // block key per stage
   __shared__ __align__(16) signed char s_tri[256 * 16];
   __shared__ unsigned char s_num[256];
   __shared__ uint32_t p_sgn[24], p_val[24]; // bit planes over the lattice index z*81 + y*9 + x
-  __shared__ uint32_t s_cube[MC2_CUBE_CAP];       // active cubes: id | case << 9
-  __shared__ uint32_t s_scan[MC2_CUBE_CAP + 1];   // exclusive scan of their triangle counts
+  __shared__ uint16_t s_cube[MC2_CUBE_CAP];       // active cubes: cube id (9 bits)
+  __shared__ unsigned char s_case[MC2_CUBE_CAP];  // ... and their case index
+  __shared__ uint16_t s_scan[MC2_CUBE_CAP + 2];   // exclusive scan of their triangle counts
   __shared__ uint32_t s_w0, s_tot;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   if (tid < 256) {
@@ -275,19 +278,24 @@ __global__ void __launch_bounds__(MC_THREADS, MC_CTAS_PER_SM)
   }
   const char *vox_b = reinterpret_cast<const char *>(v.vox) + which * 8;
   const char *cnt_b = reinterpret_cast<const char *>(v.cnt) + which * 4;
-  auto prefetch = [&](int buf) {
+  // raw words + key of the block whose neighbour slots are in s_nb -> stage `buf`
+  // (always one commit group per call, empty when there is no such block)
+  auto prefetch = [&](int buf, bool live) {
+    if (live) {
 #pragma unroll
-    for (int j = 0; j < MC_PTS; ++j) {
-      if (pk[j] < 0) continue;
-      const int i = tid + j * MC_THREADS;
-      const uint32_t s = s_nb[pk[j] >> 9];
-      if (s != B200_NO_SLOT) {
-        const size_t off = (size_t)s * B200_BLOCK_VOX + (pk[j] & 511);
-        cp_async8(&r_sw[buf][i], vox_b + off * sizeof(float4));
-        cp_async4(&r_h[buf][i], cnt_b + off * sizeof(unsigned long long));
-      } else {
-        r_h[buf][i] = 0u;
+      for (int j = 0; j < MC_PTS; ++j) {
+        if (pk[j] < 0) continue;
+        const int i = tid + j * MC_THREADS;
+        const uint32_t s = s_nb[pk[j] >> 9];
+        if (s != B200_NO_SLOT) {
+          const size_t off = (size_t)s * B200_BLOCK_VOX + (pk[j] & 511);
+          cp_async8(&r_sw[buf][i], vox_b + off * sizeof(float4));
+          cp_async4(&r_h[buf][i], cnt_b + off * sizeof(unsigned long long));
+        } else {
+          r_h[buf][i] = 0u;
+        }
       }
+      if (tid == 0) cp_async8(&s_key[buf], v.keys + s_nb[0]);
     }
     cp_async_commit();
   };
@@ -295,37 +303,38 @@ __global__ void __launch_bounds__(MC_THREADS, MC_CTAS_PER_SM)
   const uint32_t g = gridDim.x;
   uint32_t b = blockIdx.x;
   if (b >= nb) return;
-  uint32_t nbA = B200_NO_SLOT;
-  unsigned long long keyA = 0;
-  if (tid < 8) s_nb[tid] = nbr[(size_t)b * 8 + tid];
-  __syncthreads();
-  prefetch(0);
-  if (tid == 0) keyA = v.keys[s_nb[0]];
-  if (tid < 8 && b + g < nb) nbA = nbr[(size_t)(b + g) * 8 + tid];
-  __syncthreads();
-  for (uint32_t it = 0; b < nb; b += g, ++it) {
-    const int buf = it & 1;
+  // prologue: blocks b, b + g, ... of this CTA into stages 0 .. MC2_STAGES - 2
+#pragma unroll 1
+  for (int pre = 0; pre < MC2_STAGES - 1; ++pre) {
+    const uint32_t bb = b + (uint32_t)pre * g;
+    if (tid < 8 && bb < nb) s_nb[tid] = nbr[(size_t)bb * 8 + tid];
+    __syncthreads();
+    prefetch(pre, bb < nb);
+    __syncthreads(); // s_nb is rewritten next
+  }
+  uint32_t nbA = B200_NO_SLOT; // threads 0..7: neighbour slots of the block MC2_STAGES - 1 ahead
+  if (tid < 8 && b + (MC2_STAGES - 1) * g < nb) nbA = nbr[(size_t)(b + (MC2_STAGES - 1) * g) * 8 + tid];
+  int buf = 0, pbuf = MC2_STAGES - 1;
+  for (; b < nb; b += g) {
     if (tid < 8) s_nb[tid] = nbA;
-    if (tid == 0) s_key[buf] = keyA;
-    __syncthreads(); // previous block fully emitted; s_nb / s_key of this iteration visible
-    if (b + g < nb) {
-      prefetch(buf ^ 1);
-      if (tid == 0) keyA = v.keys[s_nb[0]];
-      if (tid < 8) nbA = b + 2 * g < nb ? nbr[(size_t)(b + 2 * g) * 8 + tid] : B200_NO_SLOT;
-      cp_async_wait<1>();
-    } else {
-      cp_async_wait<0>();
-    }
+    __syncthreads(); // previous block fully emitted (its stage is free); s_nb visible
+    prefetch(pbuf, b + (MC2_STAGES - 1) * g < nb);
+    if (tid < 8)
+      nbA = b + MC2_STAGES * g < nb ? nbr[(size_t)(b + MC2_STAGES * g) * 8 + tid] : B200_NO_SLOT;
+    cp_async_wait<MC2_STAGES - 1>();
     __syncthreads(); // raw words of block b have landed for every thread
+    const int cur = buf;
+    buf = buf + 1 == MC2_STAGES ? 0 : buf + 1;
+    pbuf = pbuf + 1 == MC2_STAGES ? 0 : pbuf + 1;
     // ---- conversion: VoxelData view of every lattice point + the two bit planes
 #pragma unroll
     for (int j = 0; j < MC_PTS; ++j) {
       const int i = tid + j * MC_THREADS;
       float val = NAN;
       if (pk[j] >= 0) {
-        const uint32_t hits = r_h[buf][i];
+        const uint32_t hits = r_h[cur][i];
         if (hits != 0) { // voxel_view (common.cuh) on the staged words
-          const float2 sw = r_sw[buf][i];
+          const float2 sw = r_sw[cur][i];
           const float w = (hits == 1) ? sw.y : fminf(sw.y, v.max_weight);
           if (w >= v.min_weight) val = sw.x / fmaxf(1.0e-9f, w);
         }
@@ -375,14 +384,15 @@ __global__ void __launch_bounds__(MC_THREADS, MC_CTAS_PER_SM)
         const int x = __ffs(a) - 1;
         const uint32_t m = ((s0 >> x) & 3u) | (((s1 >> x) & 3u) << 2) | (((s2 >> x) & 3u) << 4) |
                            (((s3 >> x) & 3u) << 6);
-        s_cube[co] = (uint32_t)(tid * 8 + x) | (m << 9);
-        s_scan[co] = to;
+        s_cube[co] = (uint16_t)(tid * 8 + x);
+        s_case[co] = (unsigned char)m;
+        s_scan[co] = (uint16_t)to;
         ++co;
         to += s_num[m];
       }
       if (tid == 63) { // totals: ONE atomicAdd reserves the block's output run
         const uint32_t A = incl >> 16, T = incl & 0xFFFFu;
-        s_scan[A] = T;
+        s_scan[A] = (uint16_t)T;
         s_tot = incl;
         if (T) s_base = atomicAdd(n_tris, (unsigned long long)T);
       }
@@ -392,7 +402,7 @@ __global__ void __launch_bounds__(MC_THREADS, MC_CTAS_PER_SM)
     const uint32_t A = s_tot >> 16, T = s_tot & 0xFFFFu;
     if (T == 0) continue;
     int bx, by, bz;
-    unpack_block_key(s_key[buf], bx, by, bz);
+    unpack_block_key(s_key[cur], bx, by, bz);
     const unsigned long long base_o = s_base;
     // ---- emission: one triangle per thread
     for (uint32_t k = tid; k < T; k += MC_THREADS) {
@@ -401,8 +411,7 @@ __global__ void __launch_bounds__(MC_THREADS, MC_CTAS_PER_SM)
         const uint32_t mid = (lo + hi) >> 1;
         if (s_scan[mid] <= k) lo = mid; else hi = mid;
       }
-      const uint32_t ent = s_cube[lo];
-      const int q = (int)(k - s_scan[lo]), c = (int)(ent & 511u), m = (int)(ent >> 9);
+      const int q = (int)(k - s_scan[lo]), c = (int)s_cube[lo], m = (int)s_case[lo];
       const int x = c & 7, y = (c >> 3) & 7, z = c >> 6;
       const long long o = (long long)base_o + k;
       if (o >= tri_cap) continue;

@@ -320,7 +320,7 @@ class TSDFVolume:
         words = self.keyframe_meta_words(B, H, W, gh, gw)
         if out is None:
             out = torch.zeros(words, dtype=torch.int32, device=self.device)
-        with self._reading():
+        with self._lock:  # reads the volume's geometry only, not its voxels: no stream ordering
             _ffi.check(_ffi.lib().b200tsdf_keyframe_meta(
                 self._h, X.data_ptr(), Cf.data_ptr(),
                 q_grid.data_ptr() if q_grid is not None else None, poses.data_ptr(), B, H, W, gh,

@@ -13,8 +13,9 @@ except Exception as e: print('$name failed', e)"
 }
 run default X=1
 run nofast B200TSDF_NO_FAST=1
+for o in ${AB_ORDERS:-2 4 8 20 40}; do run order$o B200TSDF_KF_ORDER=$o; done
 for f in build/variants/lib_*.so; do
-  [ -e "$f" ] || continue
+  [ -e "$f" ] && [ "${AB_LIBS:-1}" = "1" ] || continue
   n=$(basename $f .so)
   run $n B200TSDF_LIB=$PWD/$f
 done

@@ -296,4 +296,15 @@ def test_peer_keyframes_ring_one_rank(cuda_device):
     assert sv.vol.counters()["rays"] == rays
     assert_volume_matches(sv.vol.export(0), vp.export(), "ring primary")
     assert_volume_matches(sv.vol.export(1), vq.export(), "ring quality")
+    # the software-pipelined run of slots (meta + gather of slot j+1 on a side stream
+    # behind the fuse of slot j) is the same fusion
+    sv2 = parallel.ShardedTSDFVolume(0.03, 0.12, slab_width=8, bounds=bounds, device=cuda_device)
+    ready = [torch.cuda.Event() for _ in range(2)]
+    for e in ready:
+        e.record()
+    sv2.integrate_slots(peers, [0, 1], 0.05, ready=ready)
+    bufs = sv2.integrate_slots(peers, [], 0.05)
+    assert bufs is None and sv2.vol.counters()["rays"] == rays
+    assert_volume_matches(sv2.vol.export(0), vp.export(), "pipelined ring primary")
+    assert_volume_matches(sv2.vol.export(1), vq.export(), "pipelined ring quality")
     peers.close()
