@@ -455,10 +455,10 @@ __global__ void __launch_bounds__(MC_THREADS, MC_CTAS_PER_SM)
 //   emit     one triangle per lane and iteration (binary search over the scan)
 #define MC3_WARPS 8
 #ifndef MC3_CTAS_PER_SM
-#define MC3_CTAS_PER_SM 4
+#define MC3_CTAS_PER_SM 3 // 80 registers: 12 points (24 loads) in flight per lane without spills
 #endif
 #ifndef MC3_CHUNK
-#define MC3_CHUNK 8
+#define MC3_CHUNK 12
 #endif
 struct Mc3Warp {
   float tv[736];
@@ -474,15 +474,29 @@ struct Mc3Smem {
   Mc3Warp w[MC3_WARPS];
 };
 
+// Plain read-only loads.  With `.L1::no_allocate` the halo faces (re-read by up to 7
+// neighbour blocks) stopped hitting in L2: 1.06 GB of DRAM reads for a 594 MB volume
+// (profiles/r02r_mc3_*.txt), i.e. the hint also makes the line evict-first in L2.
+#ifndef MC3_LD_NA
+#define MC3_LD_NA 0
+#endif
 __device__ __forceinline__ float2 ldg_nc_f2(const void *p) {
+#if MC3_LD_NA
   float2 r;
   asm volatile("ld.global.nc.L1::no_allocate.v2.f32 {%0, %1}, [%2];" : "=f"(r.x), "=f"(r.y) : "l"(p));
   return r;
+#else
+  return __ldg(reinterpret_cast<const float2 *>(p));
+#endif
 }
 __device__ __forceinline__ uint32_t ldg_nc_u32(const void *p) {
+#if MC3_LD_NA
   uint32_t r;
   asm volatile("ld.global.nc.L1::no_allocate.u32 %0, [%1];" : "=r"(r) : "l"(p));
   return r;
+#else
+  return __ldg(reinterpret_cast<const uint32_t *>(p));
+#endif
 }
 
 template <bool WRITE>
