@@ -435,224 +435,7 @@ __global__ void __launch_bounds__(MC_THREADS, MC_CTAS_PER_SM)
   }
 }
 
-// ---------------------------------------------------------------------------
-// mc_kernel3: ONE WARP per voxel block, no CTA barrier in the loop.
-// mc_kernel2's profile (profiles/r02i_mc2_ncu_full.txt) is a barrier profile:
-// 7.9 stalled warps per issue at `bar.sync`, 54 % issue utilisation, and a
-// deeper prefetch does not help (3 stages: 0.371 ms, 2 stages: 0.350 ms).  A
-// block's work is too small and too uneven for 8 warps: the row pass occupies 2
-// of them, the emission of a typical block (~100 triangles) fills 3 of 8 warps.
-// Here every warp owns a block from the first load to the last store, so the
-// only synchronisation is __syncwarp and DRAM latency is hidden the ordinary
-// way, by the 32 independent warps of an SM:
-//   load     23 lattice points per lane (index lane + 32 j), straight into
-//            registers in chunks of MC3_CHUNK (8-byte sums + 4-byte hit counter
-//            of the selected volume; up to 2 * MC3_CHUNK loads in flight per lane)
-//   convert  VoxelData view -> tv[] (per-warp shared), sign / validity planes by
-//            ballot: word j of a plane IS the ballot of chunk element j
-//   rows     2 cube rows per lane on the bit planes, warp scan of (cubes, triangles),
-//            active-cube list; ONE atomicAdd per block reserves the output run
-//   emit     one triangle per lane and iteration (binary search over the scan)
-#define MC3_WARPS 8
-#ifndef MC3_CTAS_PER_SM
-#define MC3_CTAS_PER_SM 3 // 80 registers: 12 points (24 loads) in flight per lane without spills
-#endif
-#ifndef MC3_CHUNK
-#define MC3_CHUNK 12
-#endif
-struct Mc3Warp {
-  float tv[736];
-  uint32_t p_sgn[24], p_val[24];
-  uint16_t cube[512];  // active cubes: cube id
-  uint16_t scan[516];  // exclusive scan of their triangle counts (+ total)
-  unsigned char kase[512];
-};
-struct Mc3Smem {
-  signed char tri[256 * 16];
-  unsigned char num[256];
-  uint16_t pk[736]; // lattice point -> local voxel index | neighbour id << 9
-  Mc3Warp w[MC3_WARPS];
-};
-
-// Plain read-only loads.  With `.L1::no_allocate` the halo faces (re-read by up to 7
-// neighbour blocks) stopped hitting in L2: 1.06 GB of DRAM reads for a 594 MB volume
-// (profiles/r02r_mc3_*.txt), i.e. the hint also makes the line evict-first in L2.
-#ifndef MC3_LD_NA
-#define MC3_LD_NA 0
-#endif
-__device__ __forceinline__ float2 ldg_nc_f2(const void *p) {
-#if MC3_LD_NA
-  float2 r;
-  asm volatile("ld.global.nc.L1::no_allocate.v2.f32 {%0, %1}, [%2];" : "=f"(r.x), "=f"(r.y) : "l"(p));
-  return r;
-#else
-  return __ldg(reinterpret_cast<const float2 *>(p));
-#endif
-}
-__device__ __forceinline__ uint32_t ldg_nc_u32(const void *p) {
-#if MC3_LD_NA
-  uint32_t r;
-  asm volatile("ld.global.nc.L1::no_allocate.u32 %0, [%1];" : "=r"(r) : "l"(p));
-  return r;
-#else
-  return __ldg(reinterpret_cast<const uint32_t *>(p));
-#endif
-}
-
-template <bool WRITE>
-__global__ void __launch_bounds__(MC3_WARPS * 32, MC3_CTAS_PER_SM)
-    mc_kernel3(const __grid_constant__ VolumeDev v, const uint32_t *__restrict__ nbr, int which,
-               float vs, float *__restrict__ verts, long long tri_cap, unsigned long long *n_tris) {
-  extern __shared__ __align__(16) unsigned char mc3_raw[];
-  Mc3Smem &sm = *reinterpret_cast<Mc3Smem *>(mc3_raw);
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  reinterpret_cast<int4 *>(sm.tri)[tid] = reinterpret_cast<const int4 *>(MC_TRI_TABLE)[tid];
-  sm.num[tid] = MC_NUM_TRIS[tid];
-  for (int i = tid; i < 736; i += MC3_WARPS * 32) {
-    const int x = i % 9, y = (i / 9) % 9, z = i / 81;
-    const int nbk = (x == 8) | ((y == 8) << 1) | ((z == 8) << 2);
-    sm.pk[i] = (uint16_t)((((z & 7) << 6) | ((y & 7) << 3) | (x & 7)) | (nbk << 9));
-  }
-  __syncthreads(); // the only CTA barrier: tables ready
-  Mc3Warp &w = sm.w[warp];
-  const char *vox_b = reinterpret_cast<const char *>(v.vox) + which * 8;
-  const char *cnt_b = reinterpret_cast<const char *>(v.cnt) + which * 4;
-  const uint32_t nb = (uint32_t)v.ctr[CTR_BLOCKS];
-  const uint32_t stride = gridDim.x * MC3_WARPS;
-  uint32_t b = blockIdx.x * MC3_WARPS + warp;
-  uint32_t slot_n = (b < nb && lane < 8) ? nbr[(size_t)b * 8 + lane] : B200_NO_SLOT;
-  for (; b < nb; b += stride) {
-    const uint32_t myslot = slot_n; // lanes 0..7: the 8 block slots of this lattice
-    slot_n = (b + stride < nb && lane < 8) ? nbr[(size_t)(b + stride) * 8 + lane] : B200_NO_SLOT;
-    unsigned long long key = 0;
-    if (lane == 0) key = v.keys[myslot];
-    // ---- load + convert, MC3_CHUNK lattice points per lane at a time
-#pragma unroll 1
-    for (int j0 = 0; j0 < 23; j0 += MC3_CHUNK) {
-      float2 sw[MC3_CHUNK];
-      uint32_t hh[MC3_CHUNK];
-#pragma unroll
-      for (int u = 0; u < MC3_CHUNK; ++u) {
-        const int i = lane + 32 * (j0 + u);
-        const bool in = (j0 + u < 23) && i < 729;
-        const uint32_t pk = in ? sm.pk[i] : 0u;
-        const uint32_t s = __shfl_sync(0xFFFFFFFFu, myslot, pk >> 9);
-        hh[u] = 0u, sw[u] = make_float2(0.f, 0.f);
-        if (in && s != B200_NO_SLOT) {
-          const size_t off = (size_t)s * B200_BLOCK_VOX + (pk & 511u);
-          sw[u] = ldg_nc_f2(vox_b + off * sizeof(float4));
-          hh[u] = ldg_nc_u32(cnt_b + off * sizeof(unsigned long long));
-        }
-      }
-#pragma unroll
-      for (int u = 0; u < MC3_CHUNK; ++u) {
-        if (j0 + u >= 23) break; // uniform
-        const int i = lane + 32 * (j0 + u);
-        float val = NAN;
-        if (hh[u] != 0u) { // voxel_view (common.cuh)
-          const float wt = (hh[u] == 1u) ? sw[u].y : fminf(sw[u].y, v.max_weight);
-          if (wt >= v.min_weight) val = sw[u].x / fmaxf(1.0e-9f, wt);
-        }
-        if (WRITE && i < 729) w.tv[i] = val;
-        const unsigned bs = __ballot_sync(0xFFFFFFFFu, val < 0.0f);
-        const unsigned bv = __ballot_sync(0xFFFFFFFFu, !isnan(val));
-        if (lane == 0) w.p_sgn[j0 + u] = bs, w.p_val[j0 + u] = bv;
-      }
-    }
-    if (lane == 0) w.p_sgn[23] = 0u, w.p_val[23] = 0u;
-    __syncwarp();
-    // ---- rows: lane owns rows r = lane and lane + 32 (y = r & 7, z = r >> 3)
-    uint32_t act[2], sg[2][4];
-    uint32_t ta = 0;
-#pragma unroll
-    for (int h2 = 0; h2 < 2; ++h2) {
-      const int r = lane + 32 * h2, base = 81 * (r >> 3) + 9 * (r & 7);
-      auto ext = [&](const uint32_t *a, int pos) {
-        const int wd = pos >> 5;
-        return __funnelshift_r(a[wd], a[wd + 1], pos & 31) & 0x1FFu; // wd + 1 <= 23
-      };
-      const uint32_t s0 = ext(w.p_sgn, base), s1 = ext(w.p_sgn, base + 9), s2 = ext(w.p_sgn, base + 81),
-                     s3 = ext(w.p_sgn, base + 90);
-      const uint32_t v0 = ext(w.p_val, base), v1 = ext(w.p_val, base + 9), v2 = ext(w.p_val, base + 81),
-                     v3 = ext(w.p_val, base + 90);
-      const uint32_t vc = (v0 & (v0 >> 1)) & (v1 & (v1 >> 1)) & (v2 & (v2 >> 1)) & (v3 & (v3 >> 1));
-      const uint32_t in1 = (s0 & (s0 >> 1)) & (s1 & (s1 >> 1)) & (s2 & (s2 >> 1)) & (s3 & (s3 >> 1));
-      const uint32_t o0 = ~s0, o1 = ~s1, o2 = ~s2, o3 = ~s3;
-      const uint32_t in0 = (o0 & (o0 >> 1)) & (o1 & (o1 >> 1)) & (o2 & (o2 >> 1)) & (o3 & (o3 >> 1));
-      act[h2] = vc & ~(in1 | in0) & 0xFFu; // all 8 corners observed, signs mixed
-      sg[h2][0] = s0, sg[h2][1] = s1, sg[h2][2] = s2, sg[h2][3] = s3;
-      for (uint32_t a = act[h2]; a; a &= a - 1) {
-        const int x = __ffs(a) - 1;
-        const uint32_t m = ((s0 >> x) & 3u) | (((s1 >> x) & 3u) << 2) | (((s2 >> x) & 3u) << 4) |
-                           (((s3 >> x) & 3u) << 6);
-        ta += sm.num[m];
-      }
-    }
-    const uint32_t mine = ((uint32_t)(__popc(act[0]) + __popc(act[1])) << 16) | ta;
-    uint32_t incl = mine;
-#pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-      const uint32_t o = __shfl_up_sync(0xFFFFFFFFu, incl, d);
-      if (lane >= d) incl += o;
-    }
-    const uint32_t tot = __shfl_sync(0xFFFFFFFFu, incl, 31);
-    const uint32_t A = tot >> 16, T = tot & 0xFFFFu;
-    if (T == 0) continue; // (warp-uniform) most blocks of a band have no sign change
-    unsigned long long base_o = 0;
-    if (lane == 0) base_o = atomicAdd(n_tris, (unsigned long long)T);
-    if (!WRITE) continue;
-    base_o = __shfl_sync(0xFFFFFFFFu, base_o, 0);
-    key = __shfl_sync(0xFFFFFFFFu, key, 0);
-    uint32_t co = (incl - mine) >> 16, to = (incl - mine) & 0xFFFFu;
-#pragma unroll
-    for (int h2 = 0; h2 < 2; ++h2) {
-      const int r = lane + 32 * h2;
-      for (uint32_t a = act[h2]; a; a &= a - 1) {
-        const int x = __ffs(a) - 1;
-        const uint32_t m = ((sg[h2][0] >> x) & 3u) | (((sg[h2][1] >> x) & 3u) << 2) |
-                           (((sg[h2][2] >> x) & 3u) << 4) | (((sg[h2][3] >> x) & 3u) << 6);
-        w.cube[co] = (uint16_t)(r * 8 + x);
-        w.kase[co] = (unsigned char)m;
-        w.scan[co] = (uint16_t)to;
-        ++co;
-        to += sm.num[m];
-      }
-    }
-    if (lane == 31) w.scan[A] = (uint16_t)T;
-    __syncwarp();
-    int bx, by, bz;
-    unpack_block_key(key, bx, by, bz);
-    // ---- emission: one triangle per lane and iteration
-    for (uint32_t k = lane; k < T; k += 32) {
-      uint32_t lo = 0, hi = A; // largest c with scan[c] <= k
-      while (hi - lo > 1) {
-        const uint32_t mid = (lo + hi) >> 1;
-        if (w.scan[mid] <= k) lo = mid; else hi = mid;
-      }
-      const int q = (int)(k - w.scan[lo]), c = (int)w.cube[lo], m = (int)w.kase[lo];
-      const int x = c & 7, y = (c >> 3) & 7, z = c >> 6;
-      const long long o = (long long)base_o + k;
-      if (o >= tri_cap) continue;
-#pragma unroll
-      for (int vtx = 0; vtx < 3; ++vtx) {
-        const int e = sm.tri[m * 16 + 3 * q + vtx];
-        const int a = MC_EDGE_CORNERS[e][0], bb = MC_EDGE_CORNERS[e][1];
-        const int ax = x + (a & 1), ay = y + ((a >> 1) & 1), az = z + (a >> 2);
-        const int cx = x + (bb & 1), cy = y + ((bb >> 1) & 1), cz = z + (bb >> 2);
-        const float fa = w.tv[az * 81 + ay * 9 + ax], fb = w.tv[cz * 81 + cy * 9 + cx];
-        const float mu = __fdiv_rn(fa, __fsub_rn(fa, fb));
-        const float pa[3] = {__fmul_rn((float)(bx * 8 + ax), vs), __fmul_rn((float)(by * 8 + ay), vs),
-                             __fmul_rn((float)(bz * 8 + az), vs)};
-        const float pb[3] = {__fmul_rn((float)(bx * 8 + cx), vs), __fmul_rn((float)(by * 8 + cy), vs),
-                             __fmul_rn((float)(bz * 8 + cz), vs)};
-#pragma unroll
-        for (int d = 0; d < 3; ++d)
-          verts[o * 9 + vtx * 3 + d] = __fadd_rn(pa[d], __fmul_rn(__fsub_rn(pb[d], pa[d]), mu));
-      }
-    }
-    __syncwarp(); // tv / list are rewritten by the next block
-  }
-}
+#include "mc3.cuh" // mc_kernel3: one warp per voxel block (the default)
 
 extern "C" int b200tsdf_extract_mesh(b200tsdf_t *h, int which, float *verts_dev, int64_t tri_cap,
                                      int64_t *n_tris_host, void *stream) {

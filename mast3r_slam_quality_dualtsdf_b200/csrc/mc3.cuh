@@ -1,0 +1,278 @@
+// mc3.cuh -- mc_kernel3: marching cubes with ONE WARP per voxel block (included by mc.cu).
+//
+// mc_kernel2's profile (profiles/r02i_mc2_ncu_full.txt) is a barrier profile: 7.9
+// stalled warps per issue at `bar.sync`, 54 % issue utilisation, and a deeper
+// prefetch does not help (3 stages: 0.371 ms, 2 stages: 0.350 ms).  A block's work
+// is too small and too uneven for 8 warps: the row pass occupies 2 of them, the
+// emission of a typical block (~100 triangles) fills 3 of 8 warps.  Here every
+// warp owns a block from the first load to the last store, so the only
+// synchronisation is __syncwarp and DRAM latency is hidden the ordinary way, by
+// the 24 independent warps of an SM:
+//   load     23 lattice points per lane straight into registers, 12 + 11 at a
+//            time (8-byte sums + 4-byte hit counter of the selected volume).  The
+//            lattice is split so that every address is a per-block base plus an
+//            immediate: 16 steps of the block itself (voxel 32 j + lane), two
+//            steps per +x / +y / +z face, one step for the edges and the corner;
+//            a missing neighbour block is a warp-uniform skip.
+//   convert  VoxelData view -> tv[] (per-warp shared), sign / validity ballots;
+//            81 nine-bit lattice rows are then assembled from the ballot words
+//   rows     2 cube rows per lane on the packed rows, warp scan of (cubes,
+//            triangles), active-cube list; ONE atomicAdd per block
+//   emit     one triangle per lane and iteration; its cube comes from a
+//            triangle -> cube table written with the list (binary search over
+//            the scan only for blocks with more than MC3_SRC_CAP triangles)
+// Loads are plain read-only loads: with `.L1::no_allocate` the halo faces (re-read
+// by up to 7 neighbour blocks) stopped hitting in L2 -- 1.06 GB of DRAM reads for
+// a 594 MB volume (profiles/r02r_mc3_na_ncu_full.txt).
+#pragma once
+
+#define MC3_WARPS 8
+#ifndef MC3_CTAS_PER_SM
+#define MC3_CTAS_PER_SM 3 // 80 registers: 12 points (24 loads) in flight per lane without spills
+#endif
+#define MC3_SRC_CAP 512
+struct Mc3Warp {
+  float tv[736];
+  // ballot words of the 23 load steps: [0..15] main block (word j: z = j >> 1, four y rows
+  // of 8 x bits), [16, 17] +x face, [18, 19] +y face, [20, 21] +z face, [22] edges + corner
+  uint32_t p_sgn[24], p_val[24];
+  uint32_t row[84];   // index z * 9 + y: 9-bit sign row | 9-bit validity row << 16
+  uint16_t cube[512]; // active cubes: cube id
+  uint16_t scan[516]; // exclusive scan of their triangle counts (+ total)
+  unsigned char kase[512];
+  uint16_t src[MC3_SRC_CAP]; // triangle -> entry of the cube list
+};
+struct Mc3Smem {
+  signed char tri[256 * 16];
+  unsigned char num[256];
+  unsigned char ec[16]; // edge -> corner a | corner b << 4
+  Mc3Warp w[MC3_WARPS];
+};
+
+// Where the 9 bits of lattice row (y, z) sit in the ballot words: word / shift of
+// its x = 0..7 byte, word / bit of its x = 8 bit (packed 5 bits each).
+__device__ __forceinline__ uint32_t mc3_row_desc(int r) {
+  const int z = r / 9, y = r - 9 * z;
+  int wl, sl, w8, s8;
+  if (y < 8 && z < 8) wl = 2 * z + (y >> 2), sl = 8 * (y & 3), w8 = 16 + (z >> 2), s8 = 8 * (z & 3) + y;
+  else if (z < 8) wl = 18 + (z >> 2), sl = 8 * (z & 3), w8 = 22, s8 = z;      // y == 8: +y face, xy edge
+  else if (y < 8) wl = 20 + (y >> 2), sl = 8 * (y & 3), w8 = 22, s8 = 8 + y;  // z == 8: +z face, xz edge
+  else wl = 22, sl = 16, w8 = 22, s8 = 24;                                    // yz edge, corner
+  return (uint32_t)(wl | (sl << 5) | (w8 << 10) | (s8 << 15));
+}
+
+template <bool WRITE>
+__global__ void __launch_bounds__(MC3_WARPS * 32, MC3_CTAS_PER_SM)
+    mc_kernel3(const __grid_constant__ VolumeDev v, const uint32_t *__restrict__ nbr, int which,
+               float vs, float *__restrict__ verts, long long tri_cap, unsigned long long *n_tris) {
+  extern __shared__ __align__(16) unsigned char mc3_raw[];
+  Mc3Smem &sm = *reinterpret_cast<Mc3Smem *>(mc3_raw);
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  reinterpret_cast<int4 *>(sm.tri)[tid] = reinterpret_cast<const int4 *>(MC_TRI_TABLE)[tid];
+  sm.num[tid] = MC_NUM_TRIS[tid];
+  if (tid < 12) sm.ec[tid] = (unsigned char)(MC_EDGE_CORNERS[tid][0] | (MC_EDGE_CORNERS[tid][1] << 4));
+  __syncthreads(); // the only CTA barrier: tables ready
+  Mc3Warp &w = sm.w[warp];
+  // block-invariant lane geometry (see the load steps below)
+  const int l7 = lane & 7, l3 = lane >> 3;
+  const int tv0 = l3 * 9 + l7, tv1 = l3 * 81 + l7 * 9 + 8, tv2 = l3 * 81 + 72 + l7;
+  const int tvE = lane < 8 ? lane * 81 + 80 : lane < 16 ? 648 + (lane - 8) * 9 + 8 : lane < 24 ? 704 + lane : 728;
+  const int locE = lane < 8 ? lane * 64 : lane < 16 ? (lane - 8) * 8 : lane < 24 ? lane - 16 : 0;
+  const int nbE = lane < 8 ? 3 : lane < 16 ? 5 : lane < 24 ? 6 : 7;
+  const uint32_t rd0 = mc3_row_desc(lane), rd1 = mc3_row_desc(lane + 32),
+                 rd2 = mc3_row_desc(lane + 64 < 81 ? lane + 64 : 80);
+  const char *vox_b = reinterpret_cast<const char *>(v.vox) + which * 8;
+  const char *cnt_b = reinterpret_cast<const char *>(v.cnt) + which * 4;
+  const float max_w = v.max_weight, min_w = v.min_weight;
+  const uint32_t nb = (uint32_t)v.ctr[CTR_BLOCKS];
+  const uint32_t stride = gridDim.x * MC3_WARPS;
+  uint32_t b = blockIdx.x * MC3_WARPS + warp;
+  uint32_t slot_n = (b < nb && lane < 8) ? nbr[(size_t)b * 8 + lane] : B200_NO_SLOT;
+
+  // VoxelData view of one lattice point (voxel_view, common.cuh) -> tv, sign / validity ballots
+  auto conv = [&](float2 sw, uint32_t hh, int tvi, int word, bool st) {
+    float val = NAN;
+    if (hh != 0u) {
+      const float wt = (hh == 1u) ? sw.y : fminf(sw.y, max_w);
+      if (wt >= min_w) val = sw.x / fmaxf(1.0e-9f, wt);
+    }
+    if (WRITE && st) w.tv[tvi] = val;
+    const unsigned bs = __ballot_sync(0xFFFFFFFFu, val < 0.0f);
+    const unsigned bv = __ballot_sync(0xFFFFFFFFu, !isnan(val));
+    if (lane == 0) w.p_sgn[word] = bs, w.p_val[word] = bv;
+  };
+
+  for (; b < nb; b += stride) {
+    const uint32_t myslot = slot_n; // lanes 0..7: the 8 block slots of this lattice
+    slot_n = (b + stride < nb && lane < 8) ? nbr[(size_t)(b + stride) * 8 + lane] : B200_NO_SLOT;
+    const uint32_t s0 = __shfl_sync(0xFFFFFFFFu, myslot, 0), s1 = __shfl_sync(0xFFFFFFFFu, myslot, 1),
+                   s2 = __shfl_sync(0xFFFFFFFFu, myslot, 2), s4 = __shfl_sync(0xFFFFFFFFu, myslot, 4),
+                   sE = __shfl_sync(0xFFFFFFFFu, myslot, nbE);
+    unsigned long long key = 0;
+    if (lane == 0) key = v.keys[s0];
+    // ---- main block, steps j = 0..15: voxel index 32 j + lane (x = lane & 7, y = 4 (j & 1) +
+    // (lane >> 3), z = j >> 1): every address is one base + an immediate
+    const char *pv = vox_b + ((size_t)s0 * B200_BLOCK_VOX + lane) * sizeof(float4);
+    const char *pc = cnt_b + ((size_t)s0 * B200_BLOCK_VOX + lane) * sizeof(unsigned long long);
+    {
+      float2 sw[12];
+      uint32_t hh[12];
+#pragma unroll
+      for (int j = 0; j < 12; ++j) {
+        sw[j] = __ldg(reinterpret_cast<const float2 *>(pv + j * 32 * sizeof(float4)));
+        hh[j] = __ldg(reinterpret_cast<const uint32_t *>(pc + j * 32 * sizeof(unsigned long long)));
+      }
+#pragma unroll
+      for (int j = 0; j < 12; ++j) conv(sw[j], hh[j], tv0 + (j >> 1) * 81 + (j & 1) * 36, j, true);
+    }
+    {
+      // steps 12..15 of the main block, then the halo: +x face (block 1: x = 0, y = lane & 7,
+      // z = (lane >> 3) + 4 jj), +y face (block 2: y = 0), +z face (block 4: z = 0), and one
+      // step for the three edges (blocks 3, 5, 6) and the corner (block 7)
+      float2 sw[11];
+      uint32_t hh[11];
+#pragma unroll
+      for (int u = 0; u < 11; ++u) sw[u] = make_float2(0.f, 0.f), hh[u] = 0u;
+#pragma unroll
+      for (int j = 12; j < 16; ++j) {
+        sw[j - 12] = __ldg(reinterpret_cast<const float2 *>(pv + j * 32 * sizeof(float4)));
+        hh[j - 12] = __ldg(reinterpret_cast<const uint32_t *>(pc + j * 32 * sizeof(unsigned long long)));
+      }
+      auto face = [&](uint32_t s, int loc, int step, int u) { // two steps, `step` voxels apart
+        if (s == B200_NO_SLOT) return;                        // (warp-uniform)
+        const size_t off = (size_t)s * B200_BLOCK_VOX + loc;
+        const char *fv = vox_b + off * sizeof(float4);
+        const char *fc = cnt_b + off * sizeof(unsigned long long);
+        sw[u] = __ldg(reinterpret_cast<const float2 *>(fv));
+        hh[u] = __ldg(reinterpret_cast<const uint32_t *>(fc));
+        sw[u + 1] = __ldg(reinterpret_cast<const float2 *>(fv + (size_t)step * sizeof(float4)));
+        hh[u + 1] = __ldg(reinterpret_cast<const uint32_t *>(fc + (size_t)step * sizeof(unsigned long long)));
+      };
+      face(s1, l3 * 64 + l7 * 8, 256, 4);
+      face(s2, l3 * 64 + l7, 256, 6);
+      face(s4, lane, 32, 8);
+      if (lane < 25 && sE != B200_NO_SLOT) {
+        const size_t off = (size_t)sE * B200_BLOCK_VOX + locE;
+        sw[10] = __ldg(reinterpret_cast<const float2 *>(vox_b + off * sizeof(float4)));
+        hh[10] = __ldg(reinterpret_cast<const uint32_t *>(cnt_b + off * sizeof(unsigned long long)));
+      }
+#pragma unroll
+      for (int j = 12; j < 16; ++j) conv(sw[j - 12], hh[j - 12], tv0 + (j >> 1) * 81 + (j & 1) * 36, j, true);
+      conv(sw[4], hh[4], tv1, 16, true);
+      conv(sw[5], hh[5], tv1 + 324, 17, true);
+      conv(sw[6], hh[6], tv2, 18, true);
+      conv(sw[7], hh[7], tv2 + 324, 19, true);
+      conv(sw[8], hh[8], tv0 + 648, 20, true);
+      conv(sw[9], hh[9], tv0 + 648 + 36, 21, true);
+      conv(sw[10], hh[10], tvE, 22, lane < 25);
+    }
+    __syncwarp();
+    // ---- the 81 lattice rows (9 bits each) from the ballot words
+    {
+      auto build = [&](uint32_t d, int r) {
+        const uint32_t wl = d & 31u, sl = (d >> 5) & 31u, w8 = (d >> 10) & 31u, s8 = d >> 15;
+        const uint32_t sg = ((w.p_sgn[wl] >> sl) & 0xFFu) | (((w.p_sgn[w8] >> s8) & 1u) << 8);
+        const uint32_t va = ((w.p_val[wl] >> sl) & 0xFFu) | (((w.p_val[w8] >> s8) & 1u) << 8);
+        w.row[r] = sg | (va << 16);
+      };
+      build(rd0, lane);
+      build(rd1, lane + 32);
+      if (lane + 64 < 81) build(rd2, lane + 64);
+    }
+    __syncwarp();
+    // ---- cube rows: lane owns rows r = lane and lane + 32 (y = r & 7, z = r >> 3)
+    uint32_t act[2], sg[2][4];
+    uint32_t ta = 0;
+#pragma unroll
+    for (int h2 = 0; h2 < 2; ++h2) {
+      const int r = lane + 32 * h2, idx = 9 * (r >> 3) + (r & 7);
+      const uint32_t R0 = w.row[idx], R1 = w.row[idx + 1], R2 = w.row[idx + 9], R3 = w.row[idx + 10];
+      // x and x + 1 of all four rows at once, sign half and validity half of the packed word
+      const uint32_t all1 = (R0 & (R0 >> 1)) & (R1 & (R1 >> 1)) & (R2 & (R2 >> 1)) & (R3 & (R3 >> 1));
+      const uint32_t N0 = ~R0, N1 = ~R1, N2 = ~R2, N3 = ~R3;
+      const uint32_t all0 = (N0 & (N0 >> 1)) & (N1 & (N1 >> 1)) & (N2 & (N2 >> 1)) & (N3 & (N3 >> 1));
+      act[h2] = (all1 >> 16) & ~(all1 | all0) & 0xFFu; // all 8 corners observed, signs mixed
+      const uint32_t q0 = R0 & 0x1FFu, q1 = R1 & 0x1FFu, q2 = R2 & 0x1FFu, q3 = R3 & 0x1FFu;
+      sg[h2][0] = q0, sg[h2][1] = q1, sg[h2][2] = q2, sg[h2][3] = q3;
+      for (uint32_t a = act[h2]; a; a &= a - 1) {
+        const int x = __ffs(a) - 1;
+        const uint32_t m = ((q0 >> x) & 3u) | (((q1 >> x) & 3u) << 2) | (((q2 >> x) & 3u) << 4) |
+                           (((q3 >> x) & 3u) << 6);
+        ta += sm.num[m];
+      }
+    }
+    const uint32_t mine = ((uint32_t)(__popc(act[0]) + __popc(act[1])) << 16) | ta;
+    uint32_t incl = mine;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const uint32_t o = __shfl_up_sync(0xFFFFFFFFu, incl, d);
+      if (lane >= d) incl += o;
+    }
+    const uint32_t tot = __shfl_sync(0xFFFFFFFFu, incl, 31);
+    const uint32_t A = tot >> 16, T = tot & 0xFFFFu;
+    if (T == 0) continue; // (warp-uniform) most blocks of a band have no sign change
+    unsigned long long base_o = 0;
+    if (lane == 0) base_o = atomicAdd(n_tris, (unsigned long long)T);
+    if (!WRITE) continue;
+    base_o = __shfl_sync(0xFFFFFFFFu, base_o, 0);
+    key = __shfl_sync(0xFFFFFFFFu, key, 0);
+    const bool table = T <= MC3_SRC_CAP;
+    uint32_t co = (incl - mine) >> 16, to = (incl - mine) & 0xFFFFu;
+#pragma unroll
+    for (int h2 = 0; h2 < 2; ++h2) {
+      const int r = lane + 32 * h2;
+      for (uint32_t a = act[h2]; a; a &= a - 1) {
+        const int x = __ffs(a) - 1;
+        const uint32_t m = ((sg[h2][0] >> x) & 3u) | (((sg[h2][1] >> x) & 3u) << 2) |
+                           (((sg[h2][2] >> x) & 3u) << 4) | (((sg[h2][3] >> x) & 3u) << 6);
+        const uint32_t n = sm.num[m];
+        w.cube[co] = (uint16_t)(r * 8 + x);
+        w.kase[co] = (unsigned char)m;
+        w.scan[co] = (uint16_t)to;
+        if (table)
+          for (uint32_t q = 0; q < n; ++q) w.src[to + q] = (uint16_t)co;
+        ++co;
+        to += n;
+      }
+    }
+    if (lane == 31) w.scan[A] = (uint16_t)T;
+    __syncwarp();
+    int bx, by, bz;
+    unpack_block_key(key, bx, by, bz);
+    // ---- emission: one triangle per lane and iteration
+    for (uint32_t k = lane; k < T; k += 32) {
+      uint32_t lo = 0;
+      if (table) {
+        lo = w.src[k];
+      } else {
+        uint32_t hi = A; // largest c with scan[c] <= k
+        while (hi - lo > 1) {
+          const uint32_t mid = (lo + hi) >> 1;
+          if (w.scan[mid] <= k) lo = mid; else hi = mid;
+        }
+      }
+      const int q = (int)(k - w.scan[lo]), c = (int)w.cube[lo], m = (int)w.kase[lo];
+      const int x = c & 7, y = (c >> 3) & 7, z = c >> 6;
+      const long long o = (long long)base_o + k;
+      if (o >= tri_cap) continue;
+      float *out = verts + o * 9;
+#pragma unroll
+      for (int vtx = 0; vtx < 3; ++vtx) {
+        const int e = sm.tri[m * 16 + 3 * q + vtx];
+        const int ab = sm.ec[e], a = ab & 7, bb = ab >> 4;
+        const int ax = x + (a & 1), ay = y + ((a >> 1) & 1), az = z + (a >> 2);
+        const int cx = x + (bb & 1), cy = y + ((bb >> 1) & 1), cz = z + (bb >> 2);
+        const float fa = w.tv[az * 81 + ay * 9 + ax], fb = w.tv[cz * 81 + cy * 9 + cx];
+        const float mu = __fdiv_rn(fa, __fsub_rn(fa, fb));
+        const float pa[3] = {__fmul_rn((float)(bx * 8 + ax), vs), __fmul_rn((float)(by * 8 + ay), vs),
+                             __fmul_rn((float)(bz * 8 + az), vs)};
+        const float pb[3] = {__fmul_rn((float)(bx * 8 + cx), vs), __fmul_rn((float)(by * 8 + cy), vs),
+                             __fmul_rn((float)(bz * 8 + cz), vs)};
+#pragma unroll
+        for (int d = 0; d < 3; ++d)
+          out[vtx * 3 + d] = __fadd_rn(pa[d], __fmul_rn(__fsub_rn(pb[d], pa[d]), mu));
+      }
+    }
+    __syncwarp(); // tv / lists are rewritten by the next block
+  }
+}
