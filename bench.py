@@ -648,20 +648,32 @@ def secondary_sections(args, vol, dev, rank, world, peak, bounds, slabs):
     seam_ms = 0.0
     if sharded is not None:
         seam_ms, halo = dev_ms(sharded.exchange_seams, reps=2)
-    extract = {"kernel": "mc_kernel<write>, one optimistic write pass per volume (incl. counter "
-                         "memset + D2H of the triangle count)", "volumes": {}}
+    extract = {"kernel": "mc_neighbors_kernel + mc_kernel3<write> (one warp per voxel block), one "
+                         "optimistic write pass per volume",
+               "ms_means": "device time of one pass (CUDA events around %d passes queued back to "
+                           "back through b200tsdf_extract_mesh_async, count left on the device); "
+                           "api_ms = one synchronous b200tsdf_extract_mesh call incl. the read-back "
+                           "of the triangle count and the host wake-up" % 8, "volumes": {}}
     tot_ms = 0.0
     for which, name in ((0, "primary"), (1, "quality")):
         verts = vol.extract_mesh(which)
         n_tris = int(verts.shape[0] // 3)
         buf = torch.empty(max(n_tris, 1) * 3, 3, dtype=torch.float32, device=dev)
         del verts
-        mc_ms, _ = dev_ms(lambda w=which, b=buf: vol.extract_mesh(w, out=b))
+        api_ms, _ = dev_ms(lambda w=which, b=buf: vol.extract_mesh(w, out=b))
+        cnt = torch.empty(1, dtype=torch.int64, device=dev)
+
+        def passes(w=which, b=buf, c=cnt):
+            for _ in range(8):
+                vol.extract_mesh_async(w, b, c)
+        mc_ms, _ = dev_ms(passes)
+        mc_ms /= 8
+        assert int(cnt.item()) == n_tris
         tot_ms += mc_ms
         vox_bytes = nblk * 512 * 24  # packed voxel (16 B) + hit counters (8 B)
         alg = vox_bytes + n_tris * 36
         extract["volumes"][name] = {
-            "ms": mc_ms, "triangles": allsum(n_tris), "blocks": allsum(nblk),
+            "ms": mc_ms, "api_ms": api_ms, "triangles": allsum(n_tris), "blocks": allsum(nblk),
             "triangles_per_s": allsum(n_tris) / (mc_ms * 1e-3),
             "algorithmic_bytes_this_rank": alg,
             "achieved_gbs": alg / (mc_ms * 1e-3) / 1e9, "frac": alg / (mc_ms * 1e-3) / 1e9 / peak}

@@ -263,6 +263,13 @@ int b200tsdf_export_blocks(b200tsdf_t *h, int64_t *bkeys_dev, int64_t cap,
 int b200tsdf_extract_mesh(b200tsdf_t *h, int which, float *verts_dev,
                           int64_t tri_cap, int64_t *n_tris_host, void *stream);
 
+/* The same pass without the host round trip: the triangle count stays on the
+ * device (n_tris_dev, 8 bytes, zeroed by the call), nothing is synchronised, so
+ * extractions can be queued back to back or feed a device consumer (the weld).
+ * The count can exceed tri_cap: triangles beyond it were not written. */
+int b200tsdf_extract_mesh_async(b200tsdf_t *h, int which, float *verts_dev,
+                                int64_t tri_cap, uint64_t *n_tris_dev, void *stream);
+
 /* The same mesh INDEXED: unique vertices + int32 faces.  Vertices
  * that marching cubes computes on a shared cube edge are bit-identical, so the
  * weld is an exact de-duplication, done on the device (csrc/weld.cu: hash table

@@ -22,7 +22,9 @@
 // Pass 0: the 8 block slots every block's 9^3 corner lattice draws from (itself
 // and its +x/+y/+z neighbours), one thread per (block, neighbour): the
 // dependent hash probes run massively parallel instead of serially per CTA.
-__global__ void mc_neighbors_kernel(VolumeDev v, uint32_t *__restrict__ nbr) {
+__global__ void mc_neighbors_kernel(VolumeDev v, uint32_t *__restrict__ nbr,
+                                    unsigned long long *__restrict__ n_tris) {
+  if (blockIdx.x == 0 && threadIdx.x == 0) *n_tris = 0ull; // the triangle counter of the pass after
   const uint32_t nb = (uint32_t)v.ctr[CTR_BLOCKS];
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < (long long)nb * 8;
        i += (long long)gridDim.x * blockDim.x) {
@@ -437,20 +439,13 @@ __global__ void __launch_bounds__(MC_THREADS, MC_CTAS_PER_SM)
 
 #include "mc3.cuh" // mc_kernel3: one warp per voxel block (the default)
 
-extern "C" int b200tsdf_extract_mesh(b200tsdf_t *h, int which, float *verts_dev, int64_t tri_cap,
-                                     int64_t *n_tris_host, void *stream) {
-  B200_NVTX("b200tsdf_extract_mesh");
-  if (!h || !n_tris_host || (which != 0 && which != 1) || tri_cap < 0) {
-    b200_set_error("b200tsdf_extract_mesh: invalid argument");
-    return B200TSDF_E_INVALID;
-  }
-  cudaStream_t st = (cudaStream_t)stream;
+static int mc_launch(b200tsdf_t *h, int which, float *verts_dev, int64_t tri_cap,
+                     unsigned long long *n_tris_dev, cudaStream_t st) {
   B200_CUDA(cudaSetDevice(h->cfg.device));
-  B200_CUDA(cudaMemsetAsync(h->scratch, 0, 8, st));
   const float vs = (float)h->cfg.voxel_size;
   if (!h->nbr) B200_CUDA(cudaMalloc(&h->nbr, h->cap * 8 * sizeof(uint32_t)));
   const unsigned sms = (unsigned)(h->sm_count > 0 ? h->sm_count : 148);
-  mc_neighbors_kernel<<<sms * 8, 256, 0, st>>>(h->d, h->nbr);
+  mc_neighbors_kernel<<<sms * 8, 256, 0, st>>>(h->d, h->nbr, n_tris_dev);
   static const int ver = [] {
     // A/B knob: B200TSDF_MC = 1 per-cube kernel, 2 bit-plane kernel (CTA per block), 3 warp per block
     const char *e = getenv("B200TSDF_MC");
@@ -462,15 +457,15 @@ extern "C" int b200tsdf_extract_mesh(b200tsdf_t *h, int which, float *verts_dev,
   if (ver == 1) {
     if (wr)
       mc_kernel<true><<<grid, MC_THREADS, 0, st>>>(h->d, h->nbr, which, vs, verts_dev,
-                                                   (long long)tri_cap, h->scratch);
+                                                   (long long)tri_cap, n_tris_dev);
     else
-      mc_kernel<false><<<grid, MC_THREADS, 0, st>>>(h->d, h->nbr, which, vs, nullptr, 0, h->scratch);
+      mc_kernel<false><<<grid, MC_THREADS, 0, st>>>(h->d, h->nbr, which, vs, nullptr, 0, n_tris_dev);
   } else if (ver == 2) {
     if (wr)
       mc_kernel2<true><<<grid, MC_THREADS, 0, st>>>(h->d, h->nbr, which, vs, verts_dev,
-                                                    (long long)tri_cap, h->scratch);
+                                                    (long long)tri_cap, n_tris_dev);
     else
-      mc_kernel2<false><<<grid, MC_THREADS, 0, st>>>(h->d, h->nbr, which, vs, nullptr, 0, h->scratch);
+      mc_kernel2<false><<<grid, MC_THREADS, 0, st>>>(h->d, h->nbr, which, vs, nullptr, 0, n_tris_dev);
   } else {
     static bool attr_set = false;
     if (!attr_set) {
@@ -483,12 +478,35 @@ extern "C" int b200tsdf_extract_mesh(b200tsdf_t *h, int which, float *verts_dev,
     const unsigned g3 = sms * MC3_CTAS_PER_SM;
     if (wr)
       mc_kernel3<true><<<g3, MC3_WARPS * 32, sizeof(Mc3Smem), st>>>(
-          h->d, h->nbr, which, vs, verts_dev, (long long)tri_cap, h->scratch);
+          h->d, h->nbr, which, vs, verts_dev, (long long)tri_cap, n_tris_dev);
     else
       mc_kernel3<false><<<g3, MC3_WARPS * 32, sizeof(Mc3Smem), st>>>(h->d, h->nbr, which, vs, nullptr,
-                                                                    0, h->scratch);
+                                                                    0, n_tris_dev);
   }
   B200_CUDA(cudaGetLastError());
+  return B200TSDF_OK;
+}
+
+extern "C" int b200tsdf_extract_mesh_async(b200tsdf_t *h, int which, float *verts_dev,
+                                           int64_t tri_cap, uint64_t *n_tris_dev, void *stream) {
+  B200_NVTX("b200tsdf_extract_mesh_async");
+  if (!h || !n_tris_dev || (which != 0 && which != 1) || tri_cap < 0) {
+    b200_set_error("b200tsdf_extract_mesh_async: invalid argument");
+    return B200TSDF_E_INVALID;
+  }
+  return mc_launch(h, which, verts_dev, tri_cap, (unsigned long long *)n_tris_dev, (cudaStream_t)stream);
+}
+
+extern "C" int b200tsdf_extract_mesh(b200tsdf_t *h, int which, float *verts_dev, int64_t tri_cap,
+                                     int64_t *n_tris_host, void *stream) {
+  B200_NVTX("b200tsdf_extract_mesh");
+  if (!h || !n_tris_host || (which != 0 && which != 1) || tri_cap < 0) {
+    b200_set_error("b200tsdf_extract_mesh: invalid argument");
+    return B200TSDF_E_INVALID;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  int rc = mc_launch(h, which, verts_dev, tri_cap, h->scratch, st);
+  if (rc) return rc;
   unsigned long long n;
   B200_CUDA(cudaMemcpyAsync(&n, h->scratch, 8, cudaMemcpyDeviceToHost, st));
   B200_CUDA(cudaStreamSynchronize(st));

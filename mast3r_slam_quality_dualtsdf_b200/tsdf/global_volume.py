@@ -568,6 +568,20 @@ class TSDFVolume:
             self._last_tris = n.value
         return out[: n.value * 3]
 
+    def extract_mesh_async(self, which: int, out, count=None):
+        """Marching cubes into `out` (float32 (cap*3, 3) device tensor) without any
+        host synchronisation: returns `count`, a 1-element int64 device tensor
+        holding the triangle count (it can exceed the capacity: the triangles
+        beyond it were not written).  For device consumers and for timing the
+        pass itself; `extract_mesh` is this plus the read-back of the count."""
+        if count is None:
+            count = torch.empty(1, dtype=torch.int64, device=self.device)
+        with self._reading():
+            _ffi.check(_ffi.lib().b200tsdf_extract_mesh_async(
+                self._h, which, out.data_ptr(), out.shape[0] // 3, count.data_ptr(),
+                _stream_ptr(self.device)), "extract_mesh_async")
+        return count
+
     def extract_mesh_indexed(self, which: int = 0):
         """Marching cubes + weld on the device: (verts f32 (V,3), faces i32 (T,3))
         device tensors.  Shared vertices are stored once; vertex

@@ -65,12 +65,18 @@ def main():
     ntri = int(verts.shape[0] // 3)
     buf = torch.empty(max(ntri, 1) * 3, 3, dtype=torch.float32, device=dev)
     del verts
-    ms, _ = ms_of(lambda: vol.extract_mesh(0, out=buf))
+    api_ms, _ = ms_of(lambda: vol.extract_mesh(0, out=buf))
+    cnt = torch.empty(1, dtype=torch.int64, device=dev)
+
+    def passes():
+        for _ in range(8):
+            vol.extract_mesh_async(0, buf, cnt)
+    ms, _ = ms_of(passes)
+    ms /= 8
     b = vox_bytes + ntri * 36
-    out["extract_mesh"] = {"ms": ms, "triangles": ntri, "bytes": b, "gbs": b / ms / 1e6,
-                           "frac": b / ms / 1e6 / peak,
-                           "kernel": "mc_kernel" if os.environ.get("B200TSDF_MC_V1") == "1"
-                           else "mc_kernel2"}
+    out["extract_mesh"] = {"ms": ms, "api_ms": api_ms, "triangles": ntri, "bytes": b,
+                           "gbs": b / ms / 1e6, "frac": b / ms / 1e6 / peak,
+                           "kernel": "mc_kernel%s" % os.environ.get("B200TSDF_MC", "3")}
     ms, (iv, jf) = ms_of(lambda: vol.extract_mesh_indexed(0), reps=2)
     out["extract_mesh_indexed"] = {"ms": ms, "vertices": int(iv.shape[0]),
                                    "faces": int(jf.shape[0]),

@@ -33,6 +33,13 @@ def test_mesh_matches_cpu_marching_cubes(cuda_device, scene, voxel, n_kf):
         got = vol.extract_mesh(which).cpu().numpy().reshape(-1, 3, 3)
         assert len(got) == len(want) and len(want) > 100
         assert np.array_equal(_canon(got), _canon(want))
+        # the async entry leaves the count on the device and never synchronises
+        buf = torch.empty(len(want) * 3 + 30, 3, dtype=torch.float32, device=cuda_device)
+        cnt = vol.extract_mesh_async(which, buf)
+        small = torch.empty(30, 3, dtype=torch.float32, device=cuda_device)
+        cnt_small = vol.extract_mesh_async(which, small)  # capacity 10 triangles: count still exact
+        assert int(cnt.item()) == len(want) and int(cnt_small.item()) == len(want)
+        assert np.array_equal(_canon(buf[: len(want) * 3].cpu().numpy().reshape(-1, 3, 3)), _canon(want))
     # against the mesh of the ORACLE volume (float64 fold): same surface up to
     # sign flips of |tsdf| < 1e-6 voxels
     vp, vq, _ = oracle_dual(kf, voxel, trunc)
@@ -162,3 +169,20 @@ def test_indexed_mesh_equals_host_weld_of_the_soup(cuda_device, tmp_path):
     # empty volume: empty indexed mesh
     ev, ef = TSDFVolume(0.02, 0.08, device=cuda_device).extract_mesh_indexed(0)
     assert ev.shape == (0, 3) and ef.shape == (0, 3)
+
+
+@pytest.mark.parametrize("generation", ["1", "2"])
+def test_older_kernel_generations_stay_correct(cuda_device, generation):
+    """B200TSDF_MC=1 (per-cube classification) and =2 (bit planes, CTA per block) are kept as
+    the A/B baselines of mc_kernel3; the knob is read once per process, so the oracle
+    comparison above is re-run in a child process."""
+    import os
+    import subprocess
+    import sys
+
+    env = dict(os.environ, B200TSDF_MC=generation)
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-m", "pytest", "tests/test_gpu_mesh.py", "-m", "gpu", "-q", "-x",
+                        "-k", "matches_cpu_marching_cubes or stitched or empty"],
+                       cwd=root, env=env, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
