@@ -7,8 +7,8 @@
 // emission of a typical block (~100 triangles) fills 3 of 8 warps.  Here every
 // warp owns a block from the first load to the last store, so the only
 // synchronisation is __syncwarp and DRAM latency is hidden the ordinary way, by
-// the 24 independent warps of an SM:
-//   load     23 lattice points per lane straight into registers, 12 + 11 at a
+// the 32 independent warps of an SM:
+//   load     23 lattice points per lane straight into registers, 8 + 8 + 7 at a
 //            time (8-byte sums + 4-byte hit counter of the selected volume).  The
 //            lattice is split so that every address is a per-block base plus an
 //            immediate: 16 steps of the block itself (voxel 32 j + lane), two
@@ -28,18 +28,20 @@
 
 #define MC3_WARPS 8
 #ifndef MC3_CTAS_PER_SM
-#define MC3_CTAS_PER_SM 3 // 80 registers: 12 points (24 loads) in flight per lane without spills
+#define MC3_CTAS_PER_SM 4 // 64 registers, 32 warps per SM
 #endif
-#define MC3_SRC_CAP 512
+#define MC3_SRC_CAP 256
 struct Mc3Warp {
   float tv[736];
   // ballot words of the 23 load steps: [0..15] main block (word j: z = j >> 1, four y rows
   // of 8 x bits), [16, 17] +x face, [18, 19] +y face, [20, 21] +z face, [22] edges + corner
   uint32_t p_sgn[24], p_val[24];
   uint32_t row[84];   // index z * 9 + y: 9-bit sign row | 9-bit validity row << 16
-  uint16_t cube[512]; // active cubes: cube id
-  uint16_t scan[516]; // exclusive scan of their triangle counts (+ total)
-  unsigned char kase[512];
+  // lists of ONE HALF of the block (32 cube rows, <= 256 cubes): the two halves are emitted
+  // one after the other, which halves the shared memory of a warp (4 CTAs per SM)
+  uint16_t cube[256]; // active cubes: cube id
+  uint16_t scan[260]; // exclusive scan of their triangle counts (+ total)
+  unsigned char kase[256];
   uint16_t src[MC3_SRC_CAP]; // triangle -> entry of the cube list
 };
 struct Mc3Smem {
@@ -114,30 +116,29 @@ __global__ void __launch_bounds__(MC3_WARPS * 32, MC3_CTAS_PER_SM)
     // (lane >> 3), z = j >> 1): every address is one base + an immediate
     const char *pv = vox_b + ((size_t)s0 * B200_BLOCK_VOX + lane) * sizeof(float4);
     const char *pc = cnt_b + ((size_t)s0 * B200_BLOCK_VOX + lane) * sizeof(unsigned long long);
-    {
-      float2 sw[12];
-      uint32_t hh[12];
+#pragma unroll 1
+    for (int j0 = 0; j0 < 16; j0 += 8) {
+      float2 sw[8];
+      uint32_t hh[8];
+      const char *qv = pv + (size_t)j0 * 32 * sizeof(float4);
+      const char *qc = pc + (size_t)j0 * 32 * sizeof(unsigned long long);
 #pragma unroll
-      for (int j = 0; j < 12; ++j) {
-        sw[j] = __ldg(reinterpret_cast<const float2 *>(pv + j * 32 * sizeof(float4)));
-        hh[j] = __ldg(reinterpret_cast<const uint32_t *>(pc + j * 32 * sizeof(unsigned long long)));
+      for (int u = 0; u < 8; ++u) {
+        sw[u] = __ldg(reinterpret_cast<const float2 *>(qv + u * 32 * sizeof(float4)));
+        hh[u] = __ldg(reinterpret_cast<const uint32_t *>(qc + u * 32 * sizeof(unsigned long long)));
       }
+      const int tvj = tv0 + (j0 >> 1) * 81;
 #pragma unroll
-      for (int j = 0; j < 12; ++j) conv(sw[j], hh[j], tv0 + (j >> 1) * 81 + (j & 1) * 36, j, true);
+      for (int u = 0; u < 8; ++u) conv(sw[u], hh[u], tvj + (u >> 1) * 81 + (u & 1) * 36, j0 + u, true);
     }
     {
-      // steps 12..15 of the main block, then the halo: +x face (block 1: x = 0, y = lane & 7,
-      // z = (lane >> 3) + 4 jj), +y face (block 2: y = 0), +z face (block 4: z = 0), and one
-      // step for the three edges (blocks 3, 5, 6) and the corner (block 7)
-      float2 sw[11];
-      uint32_t hh[11];
+      // the halo: +x face (block 1: x = 0, y = lane & 7, z = (lane >> 3) + 4 jj), +y face
+      // (block 2: y = 0), +z face (block 4: z = 0), and one step for the three edges
+      // (blocks 3, 5, 6) and the corner (block 7)
+      float2 sw[7];
+      uint32_t hh[7];
 #pragma unroll
-      for (int u = 0; u < 11; ++u) sw[u] = make_float2(0.f, 0.f), hh[u] = 0u;
-#pragma unroll
-      for (int j = 12; j < 16; ++j) {
-        sw[j - 12] = __ldg(reinterpret_cast<const float2 *>(pv + j * 32 * sizeof(float4)));
-        hh[j - 12] = __ldg(reinterpret_cast<const uint32_t *>(pc + j * 32 * sizeof(unsigned long long)));
-      }
+      for (int u = 0; u < 7; ++u) sw[u] = make_float2(0.f, 0.f), hh[u] = 0u;
       auto face = [&](uint32_t s, int loc, int step, int u) { // two steps, `step` voxels apart
         if (s == B200_NO_SLOT) return;                        // (warp-uniform)
         const size_t off = (size_t)s * B200_BLOCK_VOX + loc;
@@ -148,23 +149,21 @@ __global__ void __launch_bounds__(MC3_WARPS * 32, MC3_CTAS_PER_SM)
         sw[u + 1] = __ldg(reinterpret_cast<const float2 *>(fv + (size_t)step * sizeof(float4)));
         hh[u + 1] = __ldg(reinterpret_cast<const uint32_t *>(fc + (size_t)step * sizeof(unsigned long long)));
       };
-      face(s1, l3 * 64 + l7 * 8, 256, 4);
-      face(s2, l3 * 64 + l7, 256, 6);
-      face(s4, lane, 32, 8);
+      face(s1, l3 * 64 + l7 * 8, 256, 0);
+      face(s2, l3 * 64 + l7, 256, 2);
+      face(s4, lane, 32, 4);
       if (lane < 25 && sE != B200_NO_SLOT) {
         const size_t off = (size_t)sE * B200_BLOCK_VOX + locE;
-        sw[10] = __ldg(reinterpret_cast<const float2 *>(vox_b + off * sizeof(float4)));
-        hh[10] = __ldg(reinterpret_cast<const uint32_t *>(cnt_b + off * sizeof(unsigned long long)));
+        sw[6] = __ldg(reinterpret_cast<const float2 *>(vox_b + off * sizeof(float4)));
+        hh[6] = __ldg(reinterpret_cast<const uint32_t *>(cnt_b + off * sizeof(unsigned long long)));
       }
-#pragma unroll
-      for (int j = 12; j < 16; ++j) conv(sw[j - 12], hh[j - 12], tv0 + (j >> 1) * 81 + (j & 1) * 36, j, true);
-      conv(sw[4], hh[4], tv1, 16, true);
-      conv(sw[5], hh[5], tv1 + 324, 17, true);
-      conv(sw[6], hh[6], tv2, 18, true);
-      conv(sw[7], hh[7], tv2 + 324, 19, true);
-      conv(sw[8], hh[8], tv0 + 648, 20, true);
-      conv(sw[9], hh[9], tv0 + 648 + 36, 21, true);
-      conv(sw[10], hh[10], tvE, 22, lane < 25);
+      conv(sw[0], hh[0], tv1, 16, true);
+      conv(sw[1], hh[1], tv1 + 324, 17, true);
+      conv(sw[2], hh[2], tv2, 18, true);
+      conv(sw[3], hh[3], tv2 + 324, 19, true);
+      conv(sw[4], hh[4], tv0 + 648, 20, true);
+      conv(sw[5], hh[5], tv0 + 648 + 36, 21, true);
+      conv(sw[6], hh[6], tvE, 22, lane < 25);
     }
     __syncwarp();
     // ---- the 81 lattice rows (9 bits each) from the ballot words
@@ -181,8 +180,7 @@ __global__ void __launch_bounds__(MC3_WARPS * 32, MC3_CTAS_PER_SM)
     }
     __syncwarp();
     // ---- cube rows: lane owns rows r = lane and lane + 32 (y = r & 7, z = r >> 3)
-    uint32_t act[2], sg[2][4];
-    uint32_t ta = 0;
+    uint32_t act[2], sg[2][4], ta[2];
 #pragma unroll
     for (int h2 = 0; h2 < 2; ++h2) {
       const int r = lane + 32 * h2, idx = 9 * (r >> 3) + (r & 7);
@@ -194,37 +192,47 @@ __global__ void __launch_bounds__(MC3_WARPS * 32, MC3_CTAS_PER_SM)
       act[h2] = (all1 >> 16) & ~(all1 | all0) & 0xFFu; // all 8 corners observed, signs mixed
       const uint32_t q0 = R0 & 0x1FFu, q1 = R1 & 0x1FFu, q2 = R2 & 0x1FFu, q3 = R3 & 0x1FFu;
       sg[h2][0] = q0, sg[h2][1] = q1, sg[h2][2] = q2, sg[h2][3] = q3;
+      ta[h2] = 0;
       for (uint32_t a = act[h2]; a; a &= a - 1) {
         const int x = __ffs(a) - 1;
         const uint32_t m = ((q0 >> x) & 3u) | (((q1 >> x) & 3u) << 2) | (((q2 >> x) & 3u) << 4) |
                            (((q3 >> x) & 3u) << 6);
-        ta += sm.num[m];
+        ta[h2] += sm.num[m];
       }
     }
-    const uint32_t mine = ((uint32_t)(__popc(act[0]) + __popc(act[1])) << 16) | ta;
-    uint32_t incl = mine;
-#pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-      const uint32_t o = __shfl_up_sync(0xFFFFFFFFu, incl, d);
-      if (lane >= d) incl += o;
-    }
-    const uint32_t tot = __shfl_sync(0xFFFFFFFFu, incl, 31);
-    const uint32_t A = tot >> 16, T = tot & 0xFFFFu;
+    // triangles of the lower half (rows 0..31) and of the block: ONE atomicAdd per block
+    const uint32_t T01 = __reduce_add_sync(0xFFFFFFFFu, ta[0] | (ta[1] << 16));
+    const uint32_t T0 = T01 & 0xFFFFu, T = T0 + (T01 >> 16);
     if (T == 0) continue; // (warp-uniform) most blocks of a band have no sign change
     unsigned long long base_o = 0;
     if (lane == 0) base_o = atomicAdd(n_tris, (unsigned long long)T);
     if (!WRITE) continue;
     base_o = __shfl_sync(0xFFFFFFFFu, base_o, 0);
     key = __shfl_sync(0xFFFFFFFFu, key, 0);
-    const bool table = T <= MC3_SRC_CAP;
-    uint32_t co = (incl - mine) >> 16, to = (incl - mine) & 0xFFFFu;
-#pragma unroll
+    int bx, by, bz;
+    unpack_block_key(key, bx, by, bz);
+#pragma unroll 1
     for (int h2 = 0; h2 < 2; ++h2) {
+      const uint32_t Th = h2 ? T - T0 : T0;
+      if (Th == 0) continue;
+      const uint32_t ac = h2 ? act[1] : act[0];
+      const uint32_t mine = ((uint32_t)__popc(ac) << 16) | (h2 ? ta[1] : ta[0]);
+      uint32_t incl = mine;
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        const uint32_t o = __shfl_up_sync(0xFFFFFFFFu, incl, d);
+        if (lane >= d) incl += o;
+      }
+      const uint32_t A = __shfl_sync(0xFFFFFFFFu, incl, 31) >> 16;
+      const bool table = Th <= MC3_SRC_CAP;
+      uint32_t co = (incl - mine) >> 16, to = (incl - mine) & 0xFFFFu;
+      const uint32_t g0 = h2 ? sg[1][0] : sg[0][0], g1 = h2 ? sg[1][1] : sg[0][1],
+                     g2 = h2 ? sg[1][2] : sg[0][2], g3 = h2 ? sg[1][3] : sg[0][3];
       const int r = lane + 32 * h2;
-      for (uint32_t a = act[h2]; a; a &= a - 1) {
+      for (uint32_t a = ac; a; a &= a - 1) {
         const int x = __ffs(a) - 1;
-        const uint32_t m = ((sg[h2][0] >> x) & 3u) | (((sg[h2][1] >> x) & 3u) << 2) |
-                           (((sg[h2][2] >> x) & 3u) << 4) | (((sg[h2][3] >> x) & 3u) << 6);
+        const uint32_t m = ((g0 >> x) & 3u) | (((g1 >> x) & 3u) << 2) | (((g2 >> x) & 3u) << 4) |
+                           (((g3 >> x) & 3u) << 6);
         const uint32_t n = sm.num[m];
         w.cube[co] = (uint16_t)(r * 8 + x);
         w.kase[co] = (unsigned char)m;
@@ -234,44 +242,44 @@ __global__ void __launch_bounds__(MC3_WARPS * 32, MC3_CTAS_PER_SM)
         ++co;
         to += n;
       }
-    }
-    if (lane == 31) w.scan[A] = (uint16_t)T;
-    __syncwarp();
-    int bx, by, bz;
-    unpack_block_key(key, bx, by, bz);
-    // ---- emission: one triangle per lane and iteration
-    for (uint32_t k = lane; k < T; k += 32) {
-      uint32_t lo = 0;
-      if (table) {
-        lo = w.src[k];
-      } else {
-        uint32_t hi = A; // largest c with scan[c] <= k
-        while (hi - lo > 1) {
-          const uint32_t mid = (lo + hi) >> 1;
-          if (w.scan[mid] <= k) lo = mid; else hi = mid;
+      if (lane == 31) w.scan[A] = (uint16_t)Th;
+      __syncwarp();
+      const unsigned long long base_h = base_o + (h2 ? T0 : 0u);
+      // ---- emission: one triangle per lane and iteration
+      for (uint32_t k = lane; k < Th; k += 32) {
+        uint32_t lo = 0;
+        if (table) {
+          lo = w.src[k];
+        } else {
+          uint32_t hi = A; // largest c with scan[c] <= k
+          while (hi - lo > 1) {
+            const uint32_t mid = (lo + hi) >> 1;
+            if (w.scan[mid] <= k) lo = mid; else hi = mid;
+          }
+        }
+        const int q = (int)(k - w.scan[lo]), c = (int)w.cube[lo], m = (int)w.kase[lo];
+        const int x = c & 7, y = (c >> 3) & 7, z = c >> 6;
+        const long long o = (long long)base_h + k;
+        if (o >= tri_cap) continue;
+        float *out = verts + o * 9;
+#pragma unroll
+        for (int vtx = 0; vtx < 3; ++vtx) {
+          const int e = sm.tri[m * 16 + 3 * q + vtx];
+          const int ab = sm.ec[e], a = ab & 7, bb = ab >> 4;
+          const int ax = x + (a & 1), ay = y + ((a >> 1) & 1), az = z + (a >> 2);
+          const int cx = x + (bb & 1), cy = y + ((bb >> 1) & 1), cz = z + (bb >> 2);
+          const float fa = w.tv[az * 81 + ay * 9 + ax], fb = w.tv[cz * 81 + cy * 9 + cx];
+          const float mu = __fdiv_rn(fa, __fsub_rn(fa, fb));
+          const float pa[3] = {__fmul_rn((float)(bx * 8 + ax), vs), __fmul_rn((float)(by * 8 + ay), vs),
+                               __fmul_rn((float)(bz * 8 + az), vs)};
+          const float pb[3] = {__fmul_rn((float)(bx * 8 + cx), vs), __fmul_rn((float)(by * 8 + cy), vs),
+                               __fmul_rn((float)(bz * 8 + cz), vs)};
+#pragma unroll
+          for (int d = 0; d < 3; ++d)
+            out[vtx * 3 + d] = __fadd_rn(pa[d], __fmul_rn(__fsub_rn(pb[d], pa[d]), mu));
         }
       }
-      const int q = (int)(k - w.scan[lo]), c = (int)w.cube[lo], m = (int)w.kase[lo];
-      const int x = c & 7, y = (c >> 3) & 7, z = c >> 6;
-      const long long o = (long long)base_o + k;
-      if (o >= tri_cap) continue;
-      float *out = verts + o * 9;
-#pragma unroll
-      for (int vtx = 0; vtx < 3; ++vtx) {
-        const int e = sm.tri[m * 16 + 3 * q + vtx];
-        const int ab = sm.ec[e], a = ab & 7, bb = ab >> 4;
-        const int ax = x + (a & 1), ay = y + ((a >> 1) & 1), az = z + (a >> 2);
-        const int cx = x + (bb & 1), cy = y + ((bb >> 1) & 1), cz = z + (bb >> 2);
-        const float fa = w.tv[az * 81 + ay * 9 + ax], fb = w.tv[cz * 81 + cy * 9 + cx];
-        const float mu = __fdiv_rn(fa, __fsub_rn(fa, fb));
-        const float pa[3] = {__fmul_rn((float)(bx * 8 + ax), vs), __fmul_rn((float)(by * 8 + ay), vs),
-                             __fmul_rn((float)(bz * 8 + az), vs)};
-        const float pb[3] = {__fmul_rn((float)(bx * 8 + cx), vs), __fmul_rn((float)(by * 8 + cy), vs),
-                             __fmul_rn((float)(bz * 8 + cz), vs)};
-#pragma unroll
-        for (int d = 0; d < 3; ++d)
-          out[vtx * 3 + d] = __fadd_rn(pa[d], __fmul_rn(__fsub_rn(pb[d], pa[d]), mu));
-      }
+      __syncwarp(); // the lists are rewritten by the other half
     }
     __syncwarp(); // tv / lists are rewritten by the next block
   }
