@@ -23,8 +23,10 @@
 // and its +x/+y/+z neighbours), one thread per (block, neighbour): the
 // dependent hash probes run massively parallel instead of serially per CTA.
 __global__ void mc_neighbors_kernel(VolumeDev v, uint32_t *__restrict__ nbr,
-                                    unsigned long long *__restrict__ n_tris) {
-  if (blockIdx.x == 0 && threadIdx.x == 0) *n_tris = 0ull; // the triangle counter of the pass after
+                                    unsigned long long *__restrict__ n_tris,
+                                    uint32_t *__restrict__ sched) {
+  // the triangle counter and the block ticket of the pass after
+  if (blockIdx.x == 0 && threadIdx.x == 0) *n_tris = 0ull, *sched = 0u;
   const uint32_t nb = (uint32_t)v.ctr[CTR_BLOCKS];
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < (long long)nb * 8;
        i += (long long)gridDim.x * blockDim.x) {
@@ -445,7 +447,8 @@ static int mc_launch(b200tsdf_t *h, int which, float *verts_dev, int64_t tri_cap
   const float vs = (float)h->cfg.voxel_size;
   if (!h->nbr) B200_CUDA(cudaMalloc(&h->nbr, h->cap * 8 * sizeof(uint32_t)));
   const unsigned sms = (unsigned)(h->sm_count > 0 ? h->sm_count : 148);
-  mc_neighbors_kernel<<<sms * 8, 256, 0, st>>>(h->d, h->nbr, n_tris_dev);
+  uint32_t *sched = reinterpret_cast<uint32_t *>(h->scratch + 8); // block ticket of mc_kernel3
+  mc_neighbors_kernel<<<sms * 8, 256, 0, st>>>(h->d, h->nbr, n_tris_dev, sched);
   static const int ver = [] {
     // A/B knob: B200TSDF_MC = 1 per-cube kernel, 2 bit-plane kernel (CTA per block), 3 warp per block
     const char *e = getenv("B200TSDF_MC");
@@ -478,10 +481,10 @@ static int mc_launch(b200tsdf_t *h, int which, float *verts_dev, int64_t tri_cap
     const unsigned g3 = sms * MC3_CTAS_PER_SM;
     if (wr)
       mc_kernel3<true><<<g3, MC3_WARPS * 32, sizeof(Mc3Smem), st>>>(
-          h->d, h->nbr, which, vs, verts_dev, (long long)tri_cap, n_tris_dev);
+          h->d, h->nbr, which, vs, verts_dev, (long long)tri_cap, n_tris_dev, sched);
     else
       mc_kernel3<false><<<g3, MC3_WARPS * 32, sizeof(Mc3Smem), st>>>(h->d, h->nbr, which, vs, nullptr,
-                                                                    0, n_tris_dev);
+                                                                    0, n_tris_dev, sched);
   }
   B200_CUDA(cudaGetLastError());
   return B200TSDF_OK;

@@ -18,9 +18,11 @@
 //            81 nine-bit lattice rows are then assembled from the ballot words
 //   rows     2 cube rows per lane on the packed rows, warp scan of (cubes,
 //            triangles), active-cube list; ONE atomicAdd per block
-//   emit     one triangle per lane and iteration; its cube comes from a
-//            triangle -> cube table written with the list (binary search over
-//            the scan only for blocks with more than MC3_SRC_CAP triangles)
+//   emit     one triangle per lane and step; its cube comes from a triangle ->
+//            cube table written with the list (binary search over the scan only
+//            for halves with more than MC3_SRC_CAP triangles); the 32 triangles
+//            of a step are staged in shared memory and stored as coalesced rows
+// Blocks are drawn from a global ticket in list order (no static stride).
 // Loads are plain read-only loads: with `.L1::no_allocate` the halo faces (re-read
 // by up to 7 neighbour blocks) stopped hitting in L2 -- 1.06 GB of DRAM reads for
 // a 594 MB volume (profiles/r02r_mc3_na_ncu_full.txt).
@@ -28,7 +30,7 @@
 
 #define MC3_WARPS 8
 #ifndef MC3_CTAS_PER_SM
-#define MC3_CTAS_PER_SM 4 // 64 registers, 32 warps per SM
+#define MC3_CTAS_PER_SM 3 // 80 registers, 24 warps per SM (4 x 64 registers: 0.240 vs 0.227 ms)
 #endif
 #define MC3_SRC_CAP 256
 struct Mc3Warp {
@@ -38,11 +40,12 @@ struct Mc3Warp {
   uint32_t p_sgn[24], p_val[24];
   uint32_t row[84];   // index z * 9 + y: 9-bit sign row | 9-bit validity row << 16
   // lists of ONE HALF of the block (32 cube rows, <= 256 cubes): the two halves are emitted
-  // one after the other, which halves the shared memory of a warp (4 CTAs per SM)
+  // one after the other, which halves the shared memory of the lists
   uint16_t cube[256]; // active cubes: cube id
   uint16_t scan[260]; // exclusive scan of their triangle counts (+ total)
   unsigned char kase[256];
   uint16_t src[MC3_SRC_CAP]; // triangle -> entry of the cube list
+  float stg[32 * 9];         // the 32 triangles of one emission step, stored coalesced
 };
 struct Mc3Smem {
   signed char tri[256 * 16];
@@ -66,7 +69,8 @@ __device__ __forceinline__ uint32_t mc3_row_desc(int r) {
 template <bool WRITE>
 __global__ void __launch_bounds__(MC3_WARPS * 32, MC3_CTAS_PER_SM)
     mc_kernel3(const __grid_constant__ VolumeDev v, const uint32_t *__restrict__ nbr, int which,
-               float vs, float *__restrict__ verts, long long tri_cap, unsigned long long *n_tris) {
+               float vs, float *__restrict__ verts, long long tri_cap, unsigned long long *n_tris,
+               uint32_t *__restrict__ sched) {
   extern __shared__ __align__(16) unsigned char mc3_raw[];
   Mc3Smem &sm = *reinterpret_cast<Mc3Smem *>(mc3_raw);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -87,9 +91,17 @@ __global__ void __launch_bounds__(MC3_WARPS * 32, MC3_CTAS_PER_SM)
   const char *cnt_b = reinterpret_cast<const char *>(v.cnt) + which * 4;
   const float max_w = v.max_weight, min_w = v.min_weight;
   const uint32_t nb = (uint32_t)v.ctr[CTR_BLOCKS];
-  const uint32_t stride = gridDim.x * MC3_WARPS;
-  uint32_t b = blockIdx.x * MC3_WARPS + warp;
-  uint32_t slot_n = (b < nb && lane < 8) ? nbr[(size_t)b * 8 + lane] : B200_NO_SLOT;
+  // blocks are handed out in list order by a global ticket (zeroed by the neighbour pass):
+  // no tail behind the warp that drew the blocks with the most triangles, and the blocks in
+  // flight are a contiguous window of the list (neighbours are mostly allocated together, so
+  // their halo reads hit in L2).  The ticket and the neighbour slots of the next block are
+  // fetched one block ahead.
+  uint32_t b = 0, bn_raw = 0, bn = 0;
+  if (lane == 0) b = atomicAdd(sched, 1u);
+  b = __shfl_sync(0xFFFFFFFFu, b, 0);
+  if (b >= nb) return;
+  uint32_t myslot = lane < 8 ? nbr[(size_t)b * 8 + lane] : B200_NO_SLOT, slot_n = B200_NO_SLOT;
+  if (lane == 0) bn_raw = atomicAdd(sched, 1u);
 
   // VoxelData view of one lattice point (voxel_view, common.cuh) -> tv, sign / validity ballots
   auto conv = [&](float2 sw, uint32_t hh, int tvi, int word, bool st) {
@@ -104,9 +116,10 @@ __global__ void __launch_bounds__(MC3_WARPS * 32, MC3_CTAS_PER_SM)
     if (lane == 0) w.p_sgn[word] = bs, w.p_val[word] = bv;
   };
 
-  for (; b < nb; b += stride) {
-    const uint32_t myslot = slot_n; // lanes 0..7: the 8 block slots of this lattice
-    slot_n = (b + stride < nb && lane < 8) ? nbr[(size_t)(b + stride) * 8 + lane] : B200_NO_SLOT;
+  for (; b < nb; b = bn, myslot = slot_n) { // myslot, lanes 0..7: the 8 block slots of this lattice
+    bn = __shfl_sync(0xFFFFFFFFu, bn_raw, 0);
+    slot_n = (bn < nb && lane < 8) ? nbr[(size_t)bn * 8 + lane] : B200_NO_SLOT;
+    if (lane == 0 && bn < nb) bn_raw = atomicAdd(sched, 1u);
     const uint32_t s0 = __shfl_sync(0xFFFFFFFFu, myslot, 0), s1 = __shfl_sync(0xFFFFFFFFu, myslot, 1),
                    s2 = __shfl_sync(0xFFFFFFFFu, myslot, 2), s4 = __shfl_sync(0xFFFFFFFFu, myslot, 4),
                    sE = __shfl_sync(0xFFFFFFFFu, myslot, nbE);
@@ -245,39 +258,51 @@ __global__ void __launch_bounds__(MC3_WARPS * 32, MC3_CTAS_PER_SM)
       if (lane == 31) w.scan[A] = (uint16_t)Th;
       __syncwarp();
       const unsigned long long base_h = base_o + (h2 ? T0 : 0u);
-      // ---- emission: one triangle per lane and iteration
-      for (uint32_t k = lane; k < Th; k += 32) {
-        uint32_t lo = 0;
-        if (table) {
-          lo = w.src[k];
-        } else {
-          uint32_t hi = A; // largest c with scan[c] <= k
-          while (hi - lo > 1) {
-            const uint32_t mid = (lo + hi) >> 1;
-            if (w.scan[mid] <= k) lo = mid; else hi = mid;
+      // ---- emission: one triangle per lane and step, staged in shared memory and stored
+      // as 9 coalesced rows (a lane's own 36 bytes would be 9 stores of stride 36)
+      for (uint32_t k0 = 0; k0 < Th; k0 += 32) {
+        const uint32_t k = k0 + lane;
+        if (k < Th) {
+          uint32_t lo = 0;
+          if (table) {
+            lo = w.src[k];
+          } else {
+            uint32_t hi = A; // largest c with scan[c] <= k
+            while (hi - lo > 1) {
+              const uint32_t mid = (lo + hi) >> 1;
+              if (w.scan[mid] <= k) lo = mid; else hi = mid;
+            }
+          }
+          const int q = (int)(k - w.scan[lo]), c = (int)w.cube[lo], m = (int)w.kase[lo];
+          const int x = c & 7, y = (c >> 3) & 7, z = c >> 6;
+          float *out = w.stg + lane * 9;
+#pragma unroll
+          for (int vtx = 0; vtx < 3; ++vtx) {
+            const int e = sm.tri[m * 16 + 3 * q + vtx];
+            const int ab = sm.ec[e], a = ab & 7, bb = ab >> 4;
+            const int ax = x + (a & 1), ay = y + ((a >> 1) & 1), az = z + (a >> 2);
+            const int cx = x + (bb & 1), cy = y + ((bb >> 1) & 1), cz = z + (bb >> 2);
+            const float fa = w.tv[az * 81 + ay * 9 + ax], fb = w.tv[cz * 81 + cy * 9 + cx];
+            const float mu = __fdiv_rn(fa, __fsub_rn(fa, fb));
+            const float pa[3] = {__fmul_rn((float)(bx * 8 + ax), vs), __fmul_rn((float)(by * 8 + ay), vs),
+                                 __fmul_rn((float)(bz * 8 + az), vs)};
+            const float pb[3] = {__fmul_rn((float)(bx * 8 + cx), vs), __fmul_rn((float)(by * 8 + cy), vs),
+                                 __fmul_rn((float)(bz * 8 + cz), vs)};
+#pragma unroll
+            for (int d = 0; d < 3; ++d)
+              out[vtx * 3 + d] = __fadd_rn(pa[d], __fmul_rn(__fsub_rn(pb[d], pa[d]), mu));
           }
         }
-        const int q = (int)(k - w.scan[lo]), c = (int)w.cube[lo], m = (int)w.kase[lo];
-        const int x = c & 7, y = (c >> 3) & 7, z = c >> 6;
-        const long long o = (long long)base_h + k;
-        if (o >= tri_cap) continue;
-        float *out = verts + o * 9;
+        __syncwarp();
+        const long long f0 = ((long long)base_h + k0) * 9;             // first float of the step
+        const long long fend = min((long long)base_h + Th, tri_cap) * 9; // triangles beyond the
+        const int nf = (int)min((long long)min(32u, Th - k0) * 9, fend - f0); // capacity are dropped
 #pragma unroll
-        for (int vtx = 0; vtx < 3; ++vtx) {
-          const int e = sm.tri[m * 16 + 3 * q + vtx];
-          const int ab = sm.ec[e], a = ab & 7, bb = ab >> 4;
-          const int ax = x + (a & 1), ay = y + ((a >> 1) & 1), az = z + (a >> 2);
-          const int cx = x + (bb & 1), cy = y + ((bb >> 1) & 1), cz = z + (bb >> 2);
-          const float fa = w.tv[az * 81 + ay * 9 + ax], fb = w.tv[cz * 81 + cy * 9 + cx];
-          const float mu = __fdiv_rn(fa, __fsub_rn(fa, fb));
-          const float pa[3] = {__fmul_rn((float)(bx * 8 + ax), vs), __fmul_rn((float)(by * 8 + ay), vs),
-                               __fmul_rn((float)(bz * 8 + az), vs)};
-          const float pb[3] = {__fmul_rn((float)(bx * 8 + cx), vs), __fmul_rn((float)(by * 8 + cy), vs),
-                               __fmul_rn((float)(bz * 8 + cz), vs)};
-#pragma unroll
-          for (int d = 0; d < 3; ++d)
-            out[vtx * 3 + d] = __fadd_rn(pa[d], __fmul_rn(__fsub_rn(pb[d], pa[d]), mu));
+        for (int i = 0; i < 9; ++i) {
+          const int f = i * 32 + lane;
+          if (f < nf) verts[f0 + f] = w.stg[f];
         }
+        __syncwarp(); // stg is rewritten by the next step
       }
       __syncwarp(); // the lists are rewritten by the other half
     }
