@@ -22,3 +22,10 @@ echo "ncu launches rc=$?"
 $PROF > gpurun_out/${tag}_plain2.log 2>&1 && \
 ncu --set full --clock-control none --import-source on -k regex:integrate_keyframes -s 16 -c 1 -o gpurun_out/${tag}_prof -f $PROF > gpurun_out/${tag}_ncu2.log 2>&1
 echo "ncu full rc=$?"
+python scripts/ncu_summary.py gpurun_out/${tag}_prof.ncu-rep 40 > gpurun_out/${tag}_integrate_ncu_full.txt 2>&1
+# marching cubes on the 594 MB Target volume: plain run, then the launch list and one full capture
+MC="python scripts/big_volume_sweeps.py --kf 600 --batch 40"
+$MC > gpurun_out/${tag}_big_volume.json 2> gpurun_out/${tag}_big_volume.err && \
+ncu --set full --clock-control none --import-source on -k regex:mc_kernel3 -s 2 -c 1 -o gpurun_out/${tag}_mc3 -f $MC > gpurun_out/${tag}_ncu3.log 2>&1
+echo "ncu mc rc=$?"; cat gpurun_out/${tag}_big_volume.json | cut -c1-900
+python scripts/ncu_summary.py gpurun_out/${tag}_mc3.ncu-rep 40 > gpurun_out/${tag}_mc3_ncu_full.txt 2>&1
