@@ -270,6 +270,21 @@ int b200tsdf_extract_mesh(b200tsdf_t *h, int which, float *verts_dev,
 int b200tsdf_extract_mesh_async(b200tsdf_t *h, int which, float *verts_dev,
                                 int64_t tri_cap, uint64_t *n_tris_dev, void *stream);
 
+/* b200tsdf_extract_mesh_async for callers that may not allocate (CUDA graph
+ * capture, tight serving loops, harnesses that forbid cudaMalloc).  It has NO
+ * counterpart in the reference.
+ * The neighbour table and the block ticket of the pass live in a
+ * file-scope device array of the library (2 MB + 256 B per GPU, held until the
+ * process exits) instead of the handle's lazily allocated table, so the call
+ * performs no cudaMalloc / cudaFree.  Limit: volumes of at most
+ * B200TSDF_STATIC_MESH_MAX_SLOTS hash slots (capacity_log2 <= 16); larger
+ * volumes are rejected with B200TSDF_E_INVALID.  All calls on a GPU share the
+ * array: calls that overlap on the GPU (other streams, other volumes) race.
+ * Same arguments and results as b200tsdf_extract_mesh_async. */
+#define B200TSDF_STATIC_MESH_MAX_SLOTS 65536
+int b200tsdf_extract_mesh_static(b200tsdf_t *h, int which, float *verts_dev,
+                                 int64_t tri_cap, uint64_t *n_tris_dev, void *stream);
+
 /* The same mesh INDEXED: unique vertices + int32 faces.  Vertices
  * that marching cubes computes on a shared cube edge are bit-identical, so the
  * weld is an exact de-duplication, done on the device (csrc/weld.cu: hash table

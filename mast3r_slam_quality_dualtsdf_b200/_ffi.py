@@ -23,7 +23,7 @@ SYMBOLS = [
     "b200tsdf_keyframe_meta_words", "b200tsdf_keyframe_meta", "b200tsdf_integrate_keyframes_pull",
     "b200tsdf_ipc_open", "b200tsdf_ipc_close", "b200tsdf_peer_alloc", "b200tsdf_peer_free", "b200tsdf_counters", "b200tsdf_stats",
     "b200tsdf_query", "b200tsdf_export_voxels", "b200tsdf_export_blocks",
-    "b200tsdf_extract_mesh", "b200tsdf_extract_mesh_async", "b200tsdf_extract_mesh_indexed", "b200tsdf_weld_mesh",
+    "b200tsdf_extract_mesh", "b200tsdf_extract_mesh_async", "b200tsdf_extract_mesh_static", "b200tsdf_extract_mesh_indexed", "b200tsdf_weld_mesh",
     "b200tsdf_export_seam_blocks", "b200tsdf_import_halo_blocks",
     "b200tsdf_export_block_data", "b200tsdf_import_blocks",
     "b200tsdf_local_dims", "b200tsdf_local_build",
@@ -122,6 +122,7 @@ def lib():
     L.b200tsdf_export_blocks.argtypes = [vp, vp, i64, vp, vp]
     L.b200tsdf_extract_mesh.argtypes = [vp, C.c_int, vp, i64, vp, vp]
     L.b200tsdf_extract_mesh_async.argtypes = [vp, C.c_int, vp, i64, vp, vp]
+    L.b200tsdf_extract_mesh_static.argtypes = [vp, C.c_int, vp, i64, vp, vp]
     L.b200tsdf_extract_mesh_indexed.argtypes = [vp, C.c_int, vp, i64, vp, i64, vp, vp, vp]
     L.b200tsdf_weld_mesh.argtypes = [i32, vp, i64, vp, i64, vp, vp, vp]
     L.b200tsdf_export_seam_blocks.argtypes = [vp, vp, vp, vp, i64, vp, vp]

@@ -12,6 +12,8 @@
 #include <math.h>
 #include <stdlib.h>
 
+#include <mutex>
+
 #include "common.cuh"
 
 #define MC_TABLE_QUAL __device__ __align__(16) const
@@ -514,5 +516,84 @@ extern "C" int b200tsdf_extract_mesh(b200tsdf_t *h, int which, float *verts_dev,
   B200_CUDA(cudaMemcpyAsync(&n, h->scratch, 8, cudaMemcpyDeviceToHost, st));
   B200_CUDA(cudaStreamSynchronize(st));
   *n_tris_host = (int64_t)n;
+  return B200TSDF_OK;
+}
+
+// ---------------------------------------------------------------------------
+// b200tsdf_extract_mesh_static: the extraction pass for callers that may not
+// allocate (CUDA graph capture, tight serving loops).  No counterpart in the
+// reference.
+// b200tsdf_extract_mesh[_async] allocates the neighbour table of the pass lazily
+// (cudaMalloc of 32 bytes per hash slot on the first call).  Here the table and
+// the block ticket of mc_kernel3 live in a file-scope device array of a fixed
+// size, so the entry calls no cudaMalloc / cudaFree at all; volumes with more
+// than B200TSDF_STATIC_MESH_MAX_SLOTS hash slots are rejected.  Every GPU that
+// loads the library holds the array (2 MB + 256 B) until the process exits.
+// All calls on a device share it: two calls that overlap on the GPU (different
+// streams, or different volumes) race on the table.  Nothing in it has to
+// survive a call: the neighbour pass rewrites the table rows it uses and zeroes
+// the ticket and the caller's triangle counter.
+#define MC_STATIC_HEAD 256 // bytes in front of the table: [0] block ticket
+static __device__ __align__(256) unsigned char
+    mc_static_scratch[MC_STATIC_HEAD + (size_t)B200TSDF_STATIC_MESH_MAX_SLOTS * 8 * sizeof(uint32_t)];
+
+#define MC_STATIC_MAX_DEVICES 64
+// Device address of mc_static_scratch per device.  In host code the array's name is only a
+// stand-in for the symbol: it must never be handed to a kernel.
+static void *mc_static_ptr[MC_STATIC_MAX_DEVICES];
+static std::mutex mc_static_mu;
+
+// Set-up, once per device, with that device current.
+static int mc_static_setup(int device, void **out) {
+  if (device < 0 || device >= MC_STATIC_MAX_DEVICES) {
+    b200_set_error("b200tsdf_extract_mesh_static: device %d out of range", device);
+    return B200TSDF_E_INVALID;
+  }
+  std::lock_guard<std::mutex> lk(mc_static_mu);
+  if (!mc_static_ptr[device]) {
+    void *p = nullptr;
+    B200_CUDA(cudaGetSymbolAddress(&p, mc_static_scratch));
+    B200_CUDA(cudaFuncSetAttribute(mc_kernel3<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                   (int)sizeof(Mc3Smem)));
+    B200_CUDA(cudaFuncSetAttribute(mc_kernel3<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                   (int)sizeof(Mc3Smem)));
+    mc_static_ptr[device] = p;
+  }
+  *out = mc_static_ptr[device];
+  return B200TSDF_OK;
+}
+
+extern "C" int b200tsdf_extract_mesh_static(b200tsdf_t *h, int which, float *verts_dev,
+                                            int64_t tri_cap, uint64_t *n_tris_dev, void *stream) {
+  B200_NVTX("b200tsdf_extract_mesh_static");
+  if (!h || !n_tris_dev || (which != 0 && which != 1) || tri_cap < 0) {
+    b200_set_error("b200tsdf_extract_mesh_static: invalid argument");
+    return B200TSDF_E_INVALID;
+  }
+  if ((uint64_t)h->cap > (uint64_t)B200TSDF_STATIC_MESH_MAX_SLOTS) {
+    b200_set_error("b200tsdf_extract_mesh_static: the volume has %llu hash slots, the static "
+                   "neighbour table holds %d (capacity_log2 <= 16); use b200tsdf_extract_mesh",
+                   (unsigned long long)h->cap, B200TSDF_STATIC_MESH_MAX_SLOTS);
+    return B200TSDF_E_INVALID;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  B200_CUDA(cudaSetDevice(h->cfg.device));
+  void *base = nullptr;
+  int rc = mc_static_setup(h->cfg.device, &base);
+  if (rc) return rc;
+  uint32_t *sched = reinterpret_cast<uint32_t *>(base);
+  uint32_t *nbr = reinterpret_cast<uint32_t *>(static_cast<unsigned char *>(base) + MC_STATIC_HEAD);
+  unsigned long long *n_tris = reinterpret_cast<unsigned long long *>(n_tris_dev);
+  const float vs = (float)h->cfg.voxel_size;
+  const unsigned sms = (unsigned)(h->sm_count > 0 ? h->sm_count : 148);
+  mc_neighbors_kernel<<<sms * 8, 256, 0, st>>>(h->d, nbr, n_tris, sched);
+  const unsigned g3 = sms * MC3_CTAS_PER_SM;
+  if (verts_dev && tri_cap > 0)
+    mc_kernel3<true><<<g3, MC3_WARPS * 32, sizeof(Mc3Smem), st>>>(h->d, nbr, which, vs, verts_dev,
+                                                                 (long long)tri_cap, n_tris, sched);
+  else
+    mc_kernel3<false><<<g3, MC3_WARPS * 32, sizeof(Mc3Smem), st>>>(h->d, nbr, which, vs, nullptr, 0,
+                                                                  n_tris, sched);
+  B200_CUDA(cudaGetLastError());
   return B200TSDF_OK;
 }
