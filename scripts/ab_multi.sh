@@ -11,6 +11,7 @@ try:
 except Exception as e: print('$name failed', e)"
 }
 run pull X=1
+AB_ARGS="--no-pipeline" run pull_serial X=1
 AB_ARGS="--ingest gather" run gather X=1
 run pull_nofast B200TSDF_NO_FAST=1
 for f in build/variants/lib_*.so; do [ -e "$f" ] || continue; n=$(basename $f .so); run pull_$n B200TSDF_LIB=$PWD/$f; done
