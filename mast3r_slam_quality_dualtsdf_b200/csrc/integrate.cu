@@ -845,10 +845,15 @@ static MarchConst make_consts(const b200tsdf *h, int cell_h = 1, int cell_w = 1)
 static FastConst make_fast_consts(const b200tsdf *h, double step_d) {
   FastConst fc;
   memset(&fc, 0, sizeof(fc));
-  static const int off = [] {
-    const char *e = getenv("B200TSDF_NO_FAST"); // A/B knob: 1 = always the generic march
-    return e ? atoi(e) : 0;
+  static const int knob = [] {
+    // A/B knob: 1 = always the generic march, 0 = the fast march wherever it applies;
+    // unset: the fast march for single volumes only -- on a z-slab rank the generic march is
+    // 3.5 % faster (N = 2: 0.481 vs 0.499 ms per launch, profiles/r02z_ab_n2.txt): its
+    // per-sample slab test costs more in the fast loop than the one-FMA keys save
+    const char *e = getenv("B200TSDF_NO_FAST");
+    return e ? atoi(e) : -1;
   }();
+  const bool off = knob == 1 || (knob < 0 && h->d.slab_count > 1);
   const VolumeDev &d = h->d;
   const double vs = (double)(float)h->cfg.voxel_size, tr = (double)(float)h->cfg.truncation;
   bool ok = !off && d.bounded && d.dir_on && h->cfg.capacity_log2 <= 23 && step_d > 1.0e-6 &&

@@ -1,7 +1,7 @@
 #!/bin/bash
-# bench at N = 1, 2, 4, 8 on one box (what the driver does at round end)
+# bench at N = 1, 2, 4, 8 (or the list given as \$1) on one box (what the driver does at round end)
 mkdir -p gpurun_out
-for n in 1 2 4 8; do
+for n in ${1:-1 2 4 8}; do
   if [ $n -eq 1 ]; then
     timeout 900 python bench.py --gpus 1 --steps 6 --warmup 2 --no-cpu-baseline > gpurun_out/scale_n$n.json 2> gpurun_out/scale_n$n.err
   else

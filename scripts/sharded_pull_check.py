@@ -52,15 +52,18 @@ def main():
     torch.cuda.synchronize()
     dist.barrier()
     t0 = time.perf_counter()
-    for s in range(SLOTS):
-        sv.integrate_slot(peers, s, 0.05)
+    if os.environ.get("PULL_SERIAL") == "1":
+        for s in range(SLOTS):
+            sv.integrate_slot(peers, s, 0.05)
+    else:  # software-pipelined: meta pass + all-gather of slot s+1 behind the fuse of slot s
+        sv.integrate_slots(peers, range(SLOTS), 0.05)
     c = sv.counters()
     dt = time.perf_counter() - t0
     bk, vox, cnt = sv.vol.export_block_data()
     parts = [None] * world
     dist.all_gather_object(parts, (bk.cpu().numpy(), vox.cpu().numpy(), cnt.cpu().numpy()))
     ok = True
-    res = {"world": world, "slab_width": width, "keyframes": N_KF * SLOTS, "seconds": dt}
+    res = {"world": world, "pipelined": os.environ.get("PULL_SERIAL") != "1", "slab_width": width, "keyframes": N_KF * SLOTS, "seconds": dt}
     if rank == 0:
         merged = TSDFVolume(VOXEL, TRUNC, capacity_log2=16, bounds=(lo, hi), device=dev)
         for pb, pv, pc in parts:
