@@ -61,6 +61,9 @@ def parse():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--kf-per-launch", type=int, default=KF_PER_LAUNCH)
     ap.add_argument("--launches-per-step", type=int, default=ORBIT_TOTAL // KF_PER_LAUNCH)
+    ap.add_argument("--passes-per-step", type=int, default=4,
+                    help="passes over the 600-keyframe orbit per step (every pass fuses all "
+                         "launches again): keeps the timed region >= 0.2 s at 8 ranks")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--ingest", default="pull", choices=["pull", "gather"],
                     help="N > 1: how a launch's keyframes reach the ranks -- pull: ONE small "
@@ -199,7 +202,7 @@ def run_reference(args):
     orc.build()
     threads = host_threads()
     sample_kf = max(2, threads // 2)
-    per_step = args.kf_per_launch * args.launches_per_step
+    per_step = args.kf_per_launch * args.launches_per_step * args.passes_per_step
     ev_total, t_total = 0, 0.0
     for s in range(args.warmup + args.steps):
         # a different launch of the pass every step, so the sample walks the orbit
@@ -229,14 +232,17 @@ def workload_config(args):
     """The SAME dict on both arms and at every N (the partition of the volume over the
     ranks is reported under `partition`, outside `config`)."""
     return {
-        "workload": ("north_star Target: TUM fr1_room-shaped synthetic orbit, "
-                     f"{args.kf_per_launch * args.launches_per_step} keyframes 512x384 per step, "
+        "workload": ("north_star Target: TUM fr1_room-shaped synthetic orbit of "
+                     f"{args.kf_per_launch * args.launches_per_step} keyframes 512x384, fused "
+                     f"{args.passes_per_step} times per step, "
                      "dual TSDF (primary + quality-weighted), 1024^3 @ 5 mm, trunc 20 mm"),
-        "keyframes_per_step": args.kf_per_launch * args.launches_per_step,
-        "keyframes_per_launch": args.kf_per_launch, "launches_per_step": args.launches_per_step,
+        "keyframes_per_step": args.kf_per_launch * args.launches_per_step * args.passes_per_step,
+        "keyframes_per_launch": args.kf_per_launch,
+        "launches_per_step": args.launches_per_step * args.passes_per_step,
+        "passes_per_step": args.passes_per_step,
         "volume_dim": TARGET["dim"], "voxel_size": VOXEL, "truncation": TRUNC,
         "orbit_keyframes": ORBIT_TOTAL,
-        "l2": "every launch reads a fresh 126 MB keyframe batch and a step 1.9 GB "
+        "l2": "every launch reads a fresh 126 MB keyframe batch and a pass 1.9 GB "
               "(L2 = 126 MB): inputs larger than L2, no flush needed",
     }
 
@@ -273,7 +279,7 @@ def run_b200(args):
     vol = TSDFVolume(VOXEL, TRUNC, capacity_log2=wl["cap_log2"], bounds=bounds, slabs=slabs,
                      device=dev)
     scratch = TSDFVolume(VOXEL, TRUNC, capacity_log2=16, bounds=bounds, slabs=slabs, device=dev)
-    B, L = args.kf_per_launch, args.launches_per_step
+    B, L, P = args.kf_per_launch, args.launches_per_step, max(1, args.passes_per_step)
     if B % world:
         raise SystemExit(f"bench.py: --kf-per-launch {B} must be a multiple of the {world} ranks")
     share = B // world
@@ -422,6 +428,9 @@ def run_b200(args):
 
     def timed(step_fn, v, steps, warmup, sample_clocks=True):
         v.reset()
+        def step_fn(vv, one_pass=step_fn):
+            for _ in range(P):
+                one_pass(vv)
         for _ in range(warmup):
             step_fn(v)
         # started BEFORE the barrier: its start-up (NVML + a thread) on rank 0 would otherwise
@@ -455,7 +464,7 @@ def run_b200(args):
     e2e_ms, e2e_updates, _, _, _ = timed(step_e2e, vol, args.steps, args.warmup,
                                          sample_clocks=False)
     e2e_value = e2e_updates / (e2e_ms * 1e-3)
-    n_kf_step = B * L
+    n_kf_step = B * L * P
 
     # ---- algorithmic bytes per launch: voxels / blocks a launch's batch touches on this
     # rank (fused into an empty scratch volume)
@@ -480,7 +489,7 @@ def run_b200(args):
         frac = 1.0 - ctr["culled_rays"] / max(1, ctr["rays"])
         kf_read = share * KF_BYTES + world * words * 4 + frac * B * KF_BYTES
     alg_bytes_launch = kf_read + (touched_v * 32 + touched_b * 8) / L
-    launch_ms = float(np.mean(step_ms)) / L
+    launch_ms = float(np.mean(step_ms)) / (L * P)
     peaks = {}
     try:
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
@@ -500,7 +509,7 @@ def run_b200(args):
                 issue = {"warp_inst_per_launch": k["warp_inst_per_launch"],
                          "issue_active_pct": k.get("issue_active_pct"),
                          "inst_per_update": k["warp_inst_per_launch"] * 32.0 /
-                         (updates / (args.steps * L)),
+                         (updates / (args.steps * L * P)),
                          "source": k.get("source")}
     except Exception:
         pass
@@ -531,21 +540,21 @@ def run_b200(args):
          f"ONE packed NCCL all-gather (= {world} broadcasts over NVLink) per launch inside the "
          "timed region, double-buffered against the fuse"),
         "e2e": {"value": e2e_value, "unit": "voxel updates/s",
-                "h2d_bytes_per_step": n_kf_step * KF_BYTES, "d2h_bytes_per_step": 64,
+                "h2d_bytes_per_step": n_kf_step * KF_BYTES, "d2h_bytes_per_step": 64 * P,
                 "keyframes_per_s": n_kf_step * args.steps / (e2e_ms * 1e-3),
                 "ms_per_step": e2e_ms / args.steps,
                 "ingest": ("b200tsdf_integrate_keyframes_host per launch (chunked H2D overlapped "
                            "with the fuse), one counters read per step" if world == 1 else
                            ("per launch ONE packed H2D of the rank's share into its ring slot, "
                             "meta record + ONE small all-gather, fuse pulling its tiles from the "
-                            "owners' slots; one counters read + one barrier per step" if pull else
+                            "owners' slots; one counters read + one barrier per pass" if pull else
                             "per launch ONE packed H2D of the rank's share, ONE all-gather, one "
                             "fuse (classify + listed-tile march); copy / gather / fuse of "
                             "consecutive launches overlap on three streams; one counters read "
                             "per step"))},
         # kernels of this library inside the timed `value` region, all ranks: one fused launch
         # per 40 keyframes and rank; from 3 ranks up the classify pass + the listed-tile fuse
-        "gpu_launches": args.steps * L * world * (3 if pull else 2 if world > 2 else 1),
+        "gpu_launches": args.steps * L * P * world * (3 if pull else 2 if world > 2 else 1),
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": traffic,
                      "kernel": "integrate_keyframes_kernel" if world <= 2 and not pull else

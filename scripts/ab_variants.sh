@@ -5,7 +5,7 @@
 mkdir -p gpurun_out
 run() { # name, env...
   local name=$1; shift
-  env "$@" timeout 600 python bench.py --steps 6 --warmup 2 --launches-per-step 5 --no-cpu-baseline --no-sections 2>gpurun_out/ab_$name.err | python -c "
+  env "$@" timeout 600 python bench.py --steps 6 --warmup 2 --launches-per-step 5 --passes-per-step 1 --no-cpu-baseline --no-sections 2>gpurun_out/ab_$name.err | python -c "
 import sys,json
 try:
     d=json.loads(sys.stdin.read()); print('$name', 'launch_ms', round(d['roofline']['launch_ms'],4), 'value %.4e'%d['value'], 'e2e_ms', round(d['e2e']['ms_per_step'],3), d['clocks']['sm_mhz'])

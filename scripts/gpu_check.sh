@@ -15,7 +15,7 @@ try:
         print(k, json.dumps(d.get(k))[:600])
 except Exception as e: print('parse failed', e); print(open('gpurun_out/${tag}_bench_n1.err').read()[-3000:])
 P
-PROF="python bench.py --steps 1 --warmup 1 --no-cpu-baseline --no-sections"
+PROF="python bench.py --steps 1 --warmup 1 --passes-per-step 1 --no-cpu-baseline --no-sections"
 $PROF > gpurun_out/${tag}_plain.log 2>&1 && \
 ncu --metrics gpu__time_duration.sum --clock-control none -c 200 --csv --log-file gpurun_out/${tag}_launches.csv $PROF > gpurun_out/${tag}_ncu1.log 2>&1
 echo "ncu launches rc=$?"

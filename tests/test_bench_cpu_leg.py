@@ -22,8 +22,8 @@ def test_both_arms_share_one_config_dict():
     reference arm (`same_config`): it must not depend on N or on the arm."""
     import argparse
 
-    a = argparse.Namespace(kf_per_launch=40, launches_per_step=15, gpus=1)
-    b = argparse.Namespace(kf_per_launch=40, launches_per_step=15, gpus=8)
+    a = argparse.Namespace(kf_per_launch=40, launches_per_step=15, passes_per_step=4, gpus=1)
+    b = argparse.Namespace(kf_per_launch=40, launches_per_step=15, passes_per_step=4, gpus=8)
     assert bench.workload_config(a) == bench.workload_config(b)
     assert "1024^3 @ 5 mm" in bench.workload_config(a)["workload"]
 
