@@ -9,6 +9,7 @@
 // voxel with ONE 128-bit vector reduction (red.global.add.v4.f32) plus one
 // 64-bit reduction for the two hit counters.  The fold is commutative
 // (DESIGN.md "the fold"), so no ordering between rays is needed.
+#include <cooperative_groups.h>
 #include <stdlib.h>
 #include <string.h>
 
@@ -554,8 +555,8 @@ __device__ __forceinline__ void tile_consume(const VolumeDev &v, WarpCache &wc, 
                                              const float *sC, uint32_t bar, uint32_t phase,
                                              int bx, int by, int kf, Tally &tl) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int tx = (warp & 3) * 8 + (lane & 7), ty = (warp >> 2) * 4 + (lane >> 3);
-  const int px = bx * TILE_W + tx, py = by * TILE_H + ty;
+  int tx = (warp & 3) * 8 + (lane & 7), ty = (warp >> 2) * 4 + (lane >> 3);
+  int px = bx * TILE_W + tx, py = by * TILE_H + ty;
   float c = 0.f, x0 = 0.f, x1 = 0.f, x2 = 0.f;
   bool in_img = true;
   const KfPtrs k = kf_ptrs(a, kf);
@@ -575,7 +576,45 @@ __device__ __forceinline__ void tile_consume(const VolumeDev &v, WarpCache &wc, 
       }
     }
   }
-  const bool take = in_img && c > a.min_conf && sub_take(a, kf, py * a.W + px);
+  bool take = in_img && c > a.min_conf && sub_take(a, kf, py * a.W + px);
+  if (a.sub) {
+    // tsdf_global.max_points_per_kf is active (launch-uniform): about max_points / (H W)
+    // of the tile's pixels survive (20 % at the reference's defaults), which would leave
+    // every warp marching with mostly idle lanes.  Compact the survivors onto the first
+    // warps of the CTA (order: warp sub-tile, then lane -- neighbours stay neighbours); the
+    // other warps find no ray and leave.  Which rays are fused does not change, and the
+    // fold is commutative, so the volume is the same up to float32 summation order.
+    __shared__ unsigned char s_sel[TILE_W * TILE_H];
+    __shared__ int s_cnt[8];
+    const unsigned bal = __ballot_sync(0xFFFFFFFFu, take);
+    if (lane == 0) s_cnt[warp] = __popc(bal);
+    __syncthreads();
+    int base = 0, total = 0;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) {
+      const int cw = s_cnt[w];
+      base += w < warp ? cw : 0;
+      total += cw;
+    }
+    if (take) s_sel[base + __popc(bal & ((1u << lane) - 1u))] = (unsigned char)(ty * TILE_W + tx);
+    __syncthreads(); // (the next tile's s_cnt writes come after the caller's loop barrier)
+    take = (int)threadIdx.x < total;
+    if (take) {
+      const int t = s_sel[threadIdx.x];
+      tx = t & (TILE_W - 1), ty = t >> 5;
+      px = bx * TILE_W + tx, py = by * TILE_H + ty;
+      if (TMA) {
+        c = sC[ty * SC_ROW + tx];
+        x0 = sX[ty * SX_ROW + tx * 3], x1 = sX[ty * SX_ROW + tx * 3 + 1],
+        x2 = sX[ty * SX_ROW + tx * 3 + 2];
+      } else {
+        const long long pix = (long long)py * a.W + px;
+        c = k.C[pix];
+        const float *x = k.X + pix * 3;
+        x0 = x[0], x1 = x[1], x2 = x[2];
+      }
+    }
+  }
   if (BOUNDED && DIR && fc.enabled) { // commits its own tally
     fuse_pixels_warp_fast(v, mc, fc, k.P, take, c, x0, x1, x2, a.step, k.qg, a.gh, a.gw, px, py,
                           d_sh);
@@ -754,55 +793,90 @@ __global__ void __launch_bounds__(256, FUSE_MINB_LISTED)
   }
 }
 
-// ---- tsdf_global.max_points_per_kf (global_manager.py:94-99): one CTA per keyframe
-// finds the hash threshold that keeps exactly min(n_valid, max_points) valid pixels
-// -- the max_points smallest hashes -- by a three-pass radix select (11 + 11 + 10
-// bits) over shared-memory histograms.  C stays L2-resident between the passes.
-__global__ void __launch_bounds__(1024)
+// ---- tsdf_global.max_points_per_kf (global_manager.py:94-99): a thread-block cluster
+// of SUB_SPLIT CTAs per keyframe finds the hash threshold that keeps exactly
+// min(n_valid, max_points) valid pixels -- the max_points smallest hashes -- by a
+// three-pass radix select (11 + 11 + 10 bits).  Every CTA histograms its share of the
+// pixels in its own shared memory; CTA 0 of the cluster sums the SUB_SPLIT histograms
+// through distributed shared memory, finds the bin of the need-th hash with one block
+// scan and publishes it to the cluster.  C stays L2-resident between the passes.
+#define SUB_SPLIT 8
+#define SUB_THREADS 1024
+__global__ void __cluster_dims__(SUB_SPLIT, 1, 1) __launch_bounds__(SUB_THREADS)
     subsample_threshold_kernel(KfArgs a, int max_points, unsigned long long seed,
                                const long long *__restrict__ kf_ids, uint2 *__restrict__ out) {
-  __shared__ unsigned int hist[2048];
-  __shared__ unsigned int s_need, s_bin;
-  const int kf = blockIdx.x, npix = a.H * a.W;
+  namespace cg = cooperative_groups;
+  cg::cluster_group cl = cg::this_cluster();
+  __shared__ __align__(8) unsigned int hist[2048];
+  __shared__ unsigned int s_warp[SUB_THREADS / 32];
+  __shared__ unsigned int s_need, s_bin;  // CTA 0 publishes, the others read them remotely
+  const int kf = blockIdx.y, npix = a.H * a.W;
+  const unsigned int part = cl.block_rank();
+  const int chunk = (npix + SUB_SPLIT - 1) / SUB_SPLIT;
+  const int p_lo = (int)part * chunk, p_hi = min(npix, p_lo + chunk);
   const KfPtrs k = kf_ptrs(a, kf);
   const uint32_t salt = sub_salt(seed, kf_ids ? (unsigned long long)kf_ids[kf] : (unsigned long long)kf);
+  const unsigned int *const bin0 = cl.map_shared_rank(&s_bin, 0);
+  const unsigned int *const need0 = cl.map_shared_rank(&s_need, 0);
   unsigned int prefix = 0, need = (unsigned int)max_points; // hashes < prefix region are all kept
   // pass p fixes the next `bits` bits of the threshold below the already fixed ones
   const int shifts[3] = {21, 10, 0}, nbins[3] = {2048, 2048, 1024};
   unsigned int fixed_mask = 0;
   bool all = false;
   for (int p = 0; p < 3; ++p) {
-    for (int i = threadIdx.x; i < 2048; i += blockDim.x) hist[i] = 0;
+    for (int i = threadIdx.x; i < 2048; i += SUB_THREADS) hist[i] = 0;
     __syncthreads();
-    for (int i = threadIdx.x; i < npix; i += blockDim.x) {
+    for (int i = p_lo + (int)threadIdx.x; i < p_hi; i += SUB_THREADS) {
       if (k.C[i] > a.min_conf) {
         const uint32_t h = sub_hash((uint32_t)i, salt);
         if ((h & fixed_mask) == prefix) atomicAdd(&hist[(h >> shifts[p]) & (nbins[p] - 1)], 1u);
       }
     }
-    __syncthreads();
-    if (threadIdx.x == 0) { // 2048 bins: a serial scan costs ~2 us per pass
-      unsigned int acc = 0, b = 0;
-      for (; b < (unsigned int)nbins[p]; ++b) {
-        if (acc + hist[b] >= need) break;
-        acc += hist[b];
+    cl.sync(); // every CTA's histogram is complete
+    if (part == 0) {
+      // thread t owns bins 2t and 2t + 1 of the cluster's histogram
+      unsigned int v0 = 0, v1 = 0;
+#pragma unroll
+      for (int r = 0; r < SUB_SPLIT; ++r) {
+        const uint2 hv = *reinterpret_cast<const uint2 *>(cl.map_shared_rank(hist, r) + 2 * threadIdx.x);
+        v0 += hv.x, v1 += hv.y;
       }
-      s_bin = b; // == nbins[p]: fewer than `need` pixels match -> keep them all
-      s_need = need - acc;
+      if (2 * (int)threadIdx.x >= nbins[p]) v0 = v1 = 0;
+      // block-wide exclusive scan of v0 + v1
+      const unsigned int v = v0 + v1;
+      unsigned int inc = v;
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        const unsigned int n = __shfl_up_sync(0xFFFFFFFFu, inc, d);
+        if ((int)(threadIdx.x & 31) >= d) inc += n;
+      }
+      if ((threadIdx.x & 31) == 31) s_warp[threadIdx.x >> 5] = inc;
+      if (threadIdx.x == 0) s_bin = (unsigned int)nbins[p]; // fewer than `need` match: keep them all
+      __syncthreads();
+      unsigned int ex = inc - v;
+      for (int w = 0; w < (int)(threadIdx.x >> 5); ++w) ex += s_warp[w];
+      // the one thread whose bins hold the need-th smallest hash of the candidates
+      if (ex < need && need <= ex + v) {
+        const bool first = ex + v0 >= need;
+        s_bin = 2 * threadIdx.x + (first ? 0 : 1);
+        s_need = need - (first ? ex : ex + v0);
+      }
     }
-    __syncthreads();
-    if (s_bin >= (unsigned int)nbins[p]) {
+    cl.sync(); // s_bin / s_need of CTA 0 are final; nobody reads a remote histogram any more
+    const unsigned int bin = *bin0;
+    if (bin >= (unsigned int)nbins[p]) {
       all = true;
       break;
     }
-    prefix |= s_bin << shifts[p];
+    prefix |= bin << shifts[p];
     fixed_mask |= (unsigned int)(nbins[p] - 1) << shifts[p];
-    need = s_need;
-    __syncthreads();
+    need = *need0;
+    // (CTA 0 rewrites s_bin only after the next pass's first cluster barrier)
   }
   // after three passes `prefix` is the hash of the need-th smallest kept pixel
   // (hashes are distinct), so h <= prefix selects exactly max_points pixels
-  if (threadIdx.x == 0) out[kf] = make_uint2(all ? 0xFFFFFFFFu : prefix, salt);
+  if (part == 0 && threadIdx.x == 0) out[kf] = make_uint2(all ? 0xFFFFFFFFu : prefix, salt);
+  cl.sync(); // CTA 0's shared memory stays alive until every CTA has read it
 }
 
 // ------------------------------------------------------------------ C ABI
@@ -986,7 +1060,7 @@ static int fuse_keyframes(b200tsdf_t *h, const b200tsdf_kf_batch *kb, void *stre
       B200_CUDA(cudaMalloc(&h->sub_thr, (size_t)B * sizeof(uint2)));
       h->sub_cap = (size_t)B;
     }
-    subsample_threshold_kernel<<<(unsigned)B, 1024, 0, st>>>(ka, kb->max_points, kb->seed,
+    subsample_threshold_kernel<<<dim3(SUB_SPLIT, (unsigned)B), SUB_THREADS, 0, st>>>(ka, kb->max_points, kb->seed,
                                                              (const long long *)kb->kf_ids_dev,
                                                              (uint2 *)h->sub_thr);
     ka.sub = (const uint2 *)h->sub_thr;

@@ -527,6 +527,18 @@ def bench_manager(wl, device, n_kf, H, W, gh, gw, voxel, trunc, min_conf, gen_ba
         out[name] = {"keyframes_per_s": (n_kf - 40) / dt, "seconds": dt,
                      "launches": mgr.integrator.launches - 1,
                      "updates": c["updates_primary"] + c["updates_quality"]}
+        # the launches themselves on the device (CUDA events): the orbit's 40-keyframe
+        # batches through TSDFVolume.integrate_keyframes with the same cap
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+        n_l = n_kf // 40
+        ev[0].record()
+        for l in range(n_l):
+            sl = slice(40 * l, 40 * l + 40)
+            mgr.volume.integrate_keyframes(X[sl], Cf[sl], pose[sl], None, min_conf, H, W,
+                                           max_points=cap, seed=0)
+        ev[1].record()
+        torch.cuda.synchronize()
+        out[name]["device_ms_per_launch"] = ev[0].elapsed_time(ev[1]) / n_l
         del mgr
     out["what"] = ("TSDFGlobalIntegrator.step(): snapshot under the keyframe lock (one device "
                    "gather per array) + one fused launch per 40 keyframes + one overflow check; "

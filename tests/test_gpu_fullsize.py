@@ -89,6 +89,27 @@ def test_full_size_subsample_matches_oracle(cuda_device, kf):
     assert_volume_matches(vol.export(1), oq.export(), "40k sub-sample quality")
 
 
+def test_full_size_keyframe_cap_matches_oracle(cuda_device, kf):
+    """config/base.yaml:116 through the keyframe entry: max_points_per_kf = 40 000 of
+    ~196 608 valid pixels per 512x384 keyframe (TMA-staged tiles, survivors compacted
+    inside the CTA) against the sequential oracle fed the same seeded choice."""
+    from tests.util import oracle_dual
+
+    sub = {k: (v[:2] if isinstance(v, np.ndarray) and v.shape[:1] == kf["X"].shape[:1] else v)
+           for k, v in kf.items()}
+    vp, vq, rays = oracle_dual(sub, VOXEL, TRUNC, max_points=40000, seed=7)
+    assert rays == 80000
+    vol = _vol(cuda_device)
+    t = {k: torch.from_numpy(np.ascontiguousarray(sub[k])).to(cuda_device)
+         for k in ("X", "C", "pose", "q")}
+    vol.integrate_keyframes(t["X"], t["C"], t["pose"], t["q"], 0.05, H, W, max_points=40000, seed=7)
+    c = vol.counters()
+    assert c["rays"] == rays and c["updates_primary"] == vp.events
+    assert c["updates_quality"] == vq.events and c["dropped"] == 0
+    assert_volume_matches(vol.export(0), vp.export(), "capped full-size primary")
+    assert_volume_matches(vol.export(1), vq.export(), "capped full-size quality")
+
+
 def _oracle_dual_threaded(kf, voxel, trunc):
     """tests.util.oracle_dual with the two volumes on one thread each (the C
     oracle releases the GIL): full-resolution keyframes take ~0.2 s each."""

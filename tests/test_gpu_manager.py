@@ -399,6 +399,50 @@ def test_max_points_per_kf_is_honoured(cuda_device, bounded):
     assert ka.shape != kb.shape or not np.array_equal(ka, kb)
 
 
+@pytest.mark.parametrize("ranks", [1, 2, 4])
+def test_capped_rays_are_compacted_ragged_and_sharded(cuda_device, ranks):
+    """The max_points_per_kf survivors of a tile are compacted onto the CTA's first
+    warps (csrc/integrate.cu tile_consume).  Ragged image (45x60: partial tiles, the
+    non-TMA loads), degenerate rays among the survivors, one volume and the z-slab
+    paths (2 ranks: direct launch; 4 ranks: classify pass + listed tiles): the same
+    rays as the oracle's seeded choice are fused, counters add up, union bit-exact."""
+    from mast3r_slam_quality_dualtsdf_b200 import synth
+    from mast3r_slam_quality_dualtsdf_b200.tsdf import TSDFVolume
+
+    H, W = 45, 60
+    kf = synth.make_keyframes(synth.SCENES["sphere"], 3, H=H, W=W, seed=21, f=50.0, total=8,
+                              gh=9, gw=12)
+    X = kf["X"].reshape(3, H * W, 3)
+    Cf = kf["C"].reshape(3, H * W)
+    X[0, np.nonzero(Cf[0] > 0.05)[0][::7]] = 0.0          # len 0: skipped (global_volume.py:56)
+    X[1, np.nonzero(Cf[1] > 0.05)[0][3::11], 2] = np.inf  # non-finite: skipped
+    kf["X"] = X.reshape(kf["X"].shape)
+    cap, seed, ids = 500, 99, [5, 17, 2]
+    assert ((kf["C"] > 0.05).reshape(3, -1).sum(axis=1) > cap).all()
+    vp, vq, rays = oracle_dual(kf, 0.02, 0.08, max_points=cap, seed=seed, kf_ids=ids)
+    assert 0 < rays < 3 * cap  # some of the chosen pixels are not rays
+    t = {k: torch.from_numpy(kf[k]).to(cuda_device) for k in ("X", "C", "pose", "q")}
+    kid = torch.tensor(ids, dtype=torch.int64, device=cuda_device)
+    parts, partsq, ev_p, ev_q = [], [], 0, 0
+    for r in range(ranks):
+        kw = {"slabs": (ranks, r, 8)} if ranks > 1 else {}
+        vol = TSDFVolume(0.02, 0.08, device=cuda_device, **kw)
+        vol.integrate_keyframes(t["X"], t["C"], t["pose"], t["q"], 0.05, H, W, max_points=cap,
+                                seed=seed, kf_ids=kid)
+        c = vol.counters()
+        assert c["rays"] == rays
+        ev_p += c["updates_primary"]
+        ev_q += c["updates_quality"]
+        parts.append(vol.export(0))
+        partsq.append(vol.export(1))
+    assert ev_p == vp.events and ev_q == vq.events
+    for ps, want in ((parts, vp), (partsq, vq)):
+        gk = np.concatenate([p[0] for p in ps])
+        order = np.lexsort((gk[:, 2], gk[:, 1], gk[:, 0]))
+        got = tuple(np.concatenate([p[i] for p in ps])[order] for i in range(4))
+        assert_volume_matches(got, want.export(), f"capped, {ranks} rank(s)")
+
+
 def test_hash_overflow_is_an_error(cuda_device):
     """B200TSDF_E_CAPACITY is returned, and the drop-in
     integrator raises instead of losing updates silently."""
