@@ -461,6 +461,9 @@ __device__ __forceinline__ void fuse_pixels_warp_fast(const VolumeDev &v, const 
 #ifndef FUSE_KF_ORDER
 #define FUSE_KF_ORDER 1
 #endif
+#ifndef FUSE_TMA_PAR
+#define FUSE_TMA_PAR 0 // 1: the tile's row copies issued by 16 lanes at once (A/B)
+#endif
 struct KfArgs { // one keyframe batch (device pointers)
   const float *X, *C, *qg, *poses; // bases of segment 0
   // packed multi-GPU ingest: the batch is n segments (one per source rank) of
@@ -640,14 +643,146 @@ __global__ void __launch_bounds__(256, FUSE_MINB)
   const uint32_t bar = smem_u32(&s_bar);
   int bx = blockIdx.x, kf = blockIdx.z;
   if (a.order > 1) kf = kf * a.order + bx % a.order, bx /= a.order;
+#if FUSE_TMA_PAR
+  if (TMA && threadIdx.x < 32) { // A/B: 16 lanes issue one row copy each instead of thread 0 all 16
+    const int lane = threadIdx.x;
+    if (lane == 0) {
+      mbar_init(bar, 1);
+      mbar_expect_tx(bar, TILE_H * (TILE_W * 12 + TILE_W * 4));
+    }
+    __syncwarp();
+    if (lane < 2 * TILE_H) {
+      const KfPtrs k = kf_ptrs(a, kf);
+      const int row = lane >> 1;
+      const long long p = (long long)(blockIdx.y * TILE_H + row) * a.W + bx * TILE_W;
+      if (lane & 1) bulk_g2s(smem_u32(sC + row * SC_ROW), k.C + p, TILE_W * 4, bar);
+      else bulk_g2s(smem_u32(sX + row * SX_ROW), k.X + p * 3, TILE_W * 12, bar);
+    }
+  }
+#else
   if (TMA && threadIdx.x == 0) {
     mbar_init(bar, 1);
     tile_issue(a, sX, sC, bar, bx, blockIdx.y, kf);
   }
+#endif
   if (!DIR) warp_cache_init(wc);
   if (TMA) __syncthreads(); // mbarrier init visible to the waiters
   Tally tl = {0, 0, 0, 0, 0, 0, 0};
   tile_consume<BOUNDED, DIR, TMA>(v, wc, a, mc, fc, d_sh, sX, sC, bar, 0, bx, blockIdx.y, kf, tl);
+  commit_tally(v, tl);
+}
+
+// ---- tsdf_global.max_points_per_kf on one volume: CTA = CAP_G vertically adjacent tiles
+// (a 32 x 32 pixel block).  With the reference's default cap (40 000 of 196 608 pixels)
+// a 32 x 8 tile keeps ~52 rays: compacted onto the first warps of a one-tile CTA that
+// is two marching warps out of eight, and the SM runs latency-bound (0.32 ms for 22 %
+// of the uncapped launch's samples).  Four tiles keep ~208 rays = 6.5 full warps: all
+// tiles are staged by TMA at once, the survivors of the block are compacted into one
+// list (order: tile, warp sub-tile, lane -- neighbours stay neighbours) and the warps
+// take 32-ray chunks of it round robin.  Which rays are fused is decided by sub_take
+// alone, so the volume equals the one-tile path's up to float32 summation order.
+#define CAP_G 4
+template <bool BOUNDED, bool DIR, bool TMA>
+__global__ void __launch_bounds__(256, FUSE_MINB)
+    integrate_keyframes_capped_kernel(const __grid_constant__ VolumeDev v,
+                                      const __grid_constant__ KfArgs a,
+                                      const __grid_constant__ MarchConst mc,
+                                      const __grid_constant__ FastConst fc) {
+  __shared__ WarpCache wcs[DIR ? 1 : 8];
+  __shared__ float d_shs[(BOUNDED && DIR) ? 8 * 96 : 1];
+  __shared__ __align__(128) float sX[TMA ? CAP_G * TILE_H * SX_ROW : 4];
+  __shared__ __align__(128) float sC[TMA ? CAP_G * TILE_H * SC_ROW : 4];
+  __shared__ __align__(8) unsigned long long s_bar;
+  __shared__ unsigned short s_sel[CAP_G * TILE_H * TILE_W];
+  __shared__ int s_cnt[CAP_G * 8];
+  WarpCache &wc = wcs[DIR ? 0 : (threadIdx.x >> 5)];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int bx = blockIdx.x, kf = blockIdx.z;
+  const int row0 = blockIdx.y * (CAP_G * TILE_H);
+  const int rows = min(CAP_G * TILE_H, a.H - row0); // TMA: a multiple of TILE_H
+  const KfPtrs k = kf_ptrs(a, kf);
+  const uint32_t bar = smem_u32(&s_bar);
+  if (TMA && warp == 0) {
+    // the block's 2 x 32 row copies are issued by the 32 lanes of warp 0 at once (one
+    // thread issuing them in turn costs more than the copies take); lane 0 arms the
+    // barrier first: the phase cannot complete before its arrival
+    if (lane == 0) {
+      mbar_init(bar, 1);
+      mbar_expect_tx(bar, (uint32_t)rows * (TILE_W * 12 + TILE_W * 4));
+    }
+    __syncwarp();
+    if (lane < rows) {
+      const long long p = (long long)(row0 + lane) * a.W + bx * TILE_W;
+      bulk_g2s(smem_u32(sX + lane * SX_ROW), k.X + p * 3, TILE_W * 12, bar);
+      bulk_g2s(smem_u32(sC + lane * SC_ROW), k.C + p, TILE_W * 4, bar);
+    }
+  }
+  if (!DIR) warp_cache_init(wc);
+  if (TMA) {
+    __syncthreads(); // mbarrier init visible to the waiters
+    mbar_wait(bar, 0);
+  }
+  // which of this thread's CAP_G pixels (one per tile) survive the filter and the cap
+  const int tx = (warp & 3) * 8 + (lane & 7), ty = (warp >> 2) * 4 + (lane >> 3);
+  const int px0 = bx * TILE_W + tx;
+  unsigned bal[CAP_G];
+#pragma unroll
+  for (int t = 0; t < CAP_G; ++t) {
+    const int r = t * TILE_H + ty, py = row0 + r;
+    bool take = false;
+    if (r < rows && (TMA || px0 < a.W)) {
+      const float c = TMA ? sC[r * SC_ROW + tx] : k.C[(long long)py * a.W + px0];
+      take = c > a.min_conf && sub_take(a, kf, py * a.W + px0);
+    }
+    bal[t] = __ballot_sync(0xFFFFFFFFu, take);
+    if (lane == 0) s_cnt[t * 8 + warp] = __popc(bal[t]);
+  }
+  __syncthreads();
+  // every warp scans the 32 (tile, warp) counts itself
+  const int mine = s_cnt[lane];
+  int inc = mine;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const int n = __shfl_up_sync(0xFFFFFFFFu, inc, d);
+    if (lane >= d) inc += n;
+  }
+  const int total = __shfl_sync(0xFFFFFFFFu, inc, 31);
+#pragma unroll
+  for (int t = 0; t < CAP_G; ++t) {
+    const int base = __shfl_sync(0xFFFFFFFFu, inc - mine, t * 8 + warp);
+    if ((bal[t] >> lane) & 1u)
+      s_sel[base + __popc(bal[t] & ((1u << lane) - 1u))] =
+          (unsigned short)((t * TILE_H + ty) * TILE_W + tx);
+  }
+  __syncthreads();
+  Tally tl = {0, 0, 0, 0, 0, 0, 0};
+#pragma unroll 1
+  for (int j0 = warp * 32; j0 < total; j0 += 256) { // warp-uniform
+    const bool take = j0 + lane < total;
+    float c = 0.f, x0 = 0.f, x1 = 0.f, x2 = 0.f;
+    int px = 0, py = 0;
+    if (take) {
+      const int e = s_sel[j0 + lane], r = e >> 5, ex = e & (TILE_W - 1);
+      px = bx * TILE_W + ex, py = row0 + r;
+      if (TMA) {
+        c = sC[r * SC_ROW + ex];
+        x0 = sX[r * SX_ROW + ex * 3], x1 = sX[r * SX_ROW + ex * 3 + 1],
+        x2 = sX[r * SX_ROW + ex * 3 + 2];
+      } else {
+        const long long pix = (long long)py * a.W + px;
+        c = k.C[pix];
+        const float *x = k.X + pix * 3;
+        x0 = x[0], x1 = x[1], x2 = x[2];
+      }
+    }
+    if (BOUNDED && DIR && fc.enabled) { // commits its own tally
+      fuse_pixels_warp_fast(v, mc, fc, k.P, take, c, x0, x1, x2, a.step, k.qg, a.gh, a.gw, px, py,
+                            d_shs);
+    } else {
+      fuse_pixels_warp<BOUNDED, DIR>(v, wc, mc, k.P, take, c, x0, x1, x2, a.step, k.qg, 0, a.gh,
+                                     a.gw, px, py, tl);
+    }
+  }
   commit_tally(v, tl);
 }
 
@@ -801,13 +936,13 @@ __global__ void __launch_bounds__(256, FUSE_MINB_LISTED)
 // through distributed shared memory, finds the bin of the need-th hash with one block
 // scan and publishes it to the cluster.  C stays L2-resident between the passes.
 #define SUB_SPLIT 8
-#define SUB_THREADS 1024
+#define SUB_THREADS 512 // 40 keyframes x 8 CTAs = 320 CTAs, four per SM: one wave of clusters
 __global__ void __cluster_dims__(SUB_SPLIT, 1, 1) __launch_bounds__(SUB_THREADS)
     subsample_threshold_kernel(KfArgs a, int max_points, unsigned long long seed,
                                const long long *__restrict__ kf_ids, uint2 *__restrict__ out) {
   namespace cg = cooperative_groups;
   cg::cluster_group cl = cg::this_cluster();
-  __shared__ __align__(8) unsigned int hist[2048];
+  __shared__ __align__(16) unsigned int hist[2048];
   __shared__ unsigned int s_warp[SUB_THREADS / 32];
   __shared__ unsigned int s_need, s_bin;  // CTA 0 publishes, the others read them remotely
   const int kf = blockIdx.y, npix = a.H * a.W;
@@ -826,24 +961,33 @@ __global__ void __cluster_dims__(SUB_SPLIT, 1, 1) __launch_bounds__(SUB_THREADS)
   for (int p = 0; p < 3; ++p) {
     for (int i = threadIdx.x; i < 2048; i += SUB_THREADS) hist[i] = 0;
     __syncthreads();
-    for (int i = p_lo + (int)threadIdx.x; i < p_hi; i += SUB_THREADS) {
-      if (k.C[i] > a.min_conf) {
-        const uint32_t h = sub_hash((uint32_t)i, salt);
-        if ((h & fixed_mask) == prefix) atomicAdd(&hist[(h >> shifts[p]) & (nbins[p] - 1)], 1u);
+    for (int i0 = p_lo + (int)threadIdx.x; i0 < p_hi; i0 += 8 * SUB_THREADS) {
+      float cv[8]; // eight coalesced loads in flight per thread: a pass is one or two L2 round trips
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int i = i0 + u * SUB_THREADS;
+        cv[u] = i < p_hi ? __ldg(k.C + i) : a.min_conf;
+      }
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        if (cv[u] > a.min_conf) {
+          const uint32_t h = sub_hash((uint32_t)(i0 + u * SUB_THREADS), salt);
+          if ((h & fixed_mask) == prefix) atomicAdd(&hist[(h >> shifts[p]) & (nbins[p] - 1)], 1u);
+        }
       }
     }
     cl.sync(); // every CTA's histogram is complete
     if (part == 0) {
-      // thread t owns bins 2t and 2t + 1 of the cluster's histogram
-      unsigned int v0 = 0, v1 = 0;
+      // thread t owns bins 4t .. 4t + 3 of the cluster's histogram
+      unsigned int b0 = 0, b1 = 0, b2 = 0, b3 = 0;
 #pragma unroll
       for (int r = 0; r < SUB_SPLIT; ++r) {
-        const uint2 hv = *reinterpret_cast<const uint2 *>(cl.map_shared_rank(hist, r) + 2 * threadIdx.x);
-        v0 += hv.x, v1 += hv.y;
+        const uint4 hv = *reinterpret_cast<const uint4 *>(cl.map_shared_rank(hist, r) + 4 * threadIdx.x);
+        b0 += hv.x, b1 += hv.y, b2 += hv.z, b3 += hv.w;
       }
-      if (2 * (int)threadIdx.x >= nbins[p]) v0 = v1 = 0;
-      // block-wide exclusive scan of v0 + v1
-      const unsigned int v = v0 + v1;
+      if (4 * (int)threadIdx.x >= nbins[p]) b0 = b1 = b2 = b3 = 0;
+      // block-wide exclusive scan of the threads' sums
+      const unsigned int v = b0 + b1 + b2 + b3;
       unsigned int inc = v;
 #pragma unroll
       for (int d = 1; d < 32; d <<= 1) {
@@ -857,9 +1001,16 @@ __global__ void __cluster_dims__(SUB_SPLIT, 1, 1) __launch_bounds__(SUB_THREADS)
       for (int w = 0; w < (int)(threadIdx.x >> 5); ++w) ex += s_warp[w];
       // the one thread whose bins hold the need-th smallest hash of the candidates
       if (ex < need && need <= ex + v) {
-        const bool first = ex + v0 >= need;
-        s_bin = 2 * threadIdx.x + (first ? 0 : 1);
-        s_need = need - (first ? ex : ex + v0);
+        unsigned int bin = 4 * threadIdx.x, acc = ex;
+        if (acc + b0 < need) {
+          acc += b0, ++bin;
+          if (acc + b1 < need) {
+            acc += b1, ++bin;
+            if (acc + b2 < need) acc += b2, ++bin;
+          }
+        }
+        s_bin = bin;
+        s_need = need - acc;
       }
     }
     cl.sync(); // s_bin / s_need of CTA 0 are final; nobody reads a remote histogram any more
@@ -1107,11 +1258,23 @@ static int fuse_keyframes(b200tsdf_t *h, const b200tsdf_kf_batch *kb, void *stre
     }();
     int order = kf_order < 1 ? 1 : kf_order;
     while (order > 1 && (B % order) != 0) --order; // largest divisor of the batch <= the knob
-    ka.order = order;
-    const dim3 ogrid(grid.x * (unsigned)order, grid.y, (unsigned)(B / order));
+    static const int cap_group = [] {
+      const char *e = getenv("B200TSDF_CAP_GROUP"); // A/B knob: 0 = one tile per CTA also under the cap
+      return e ? atoi(e) : 1;
+    }();
+    if (ka.sub && cap_group) {
+      // max_points_per_kf: CAP_G tiles per CTA, survivors compacted across them
+      const dim3 cgrid(grid.x, (grid.y + CAP_G - 1) / CAP_G, (unsigned)B);
+#define LAUNCH_CAP(BD, DR, TM) integrate_keyframes_capped_kernel<BD, DR, TM><<<cgrid, 256, 0, st>>>(h->d, ka, mc, fc)
+      DISPATCH_KF(LAUNCH_CAP)
+#undef LAUNCH_CAP
+    } else {
+      ka.order = order;
+      const dim3 ogrid(grid.x * (unsigned)order, grid.y, (unsigned)(B / order));
 #define LAUNCH_KF(BD, DR, TM) integrate_keyframes_kernel<BD, DR, TM><<<ogrid, 256, 0, st>>>(h->d, ka, mc, fc)
-    DISPATCH_KF(LAUNCH_KF)
+      DISPATCH_KF(LAUNCH_KF)
 #undef LAUNCH_KF
+    }
   }
 #undef DISPATCH_KF
   B200_CUDA(cudaGetLastError());
