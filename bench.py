@@ -73,6 +73,8 @@ def parse():
     ap.add_argument("--no-pipeline", action="store_true",
                     help="N > 1, pull ingest: meta pass, all-gather and fuse of a launch in series "
                          "on one stream (A/B against the default software pipeline)")
+    ap.add_argument("--e2e-per-launch", action="store_true",
+                    help="N = 1: one *_host call per 40-keyframe launch instead of one per pass (A/B)")
     ap.add_argument("--no-sections", action="store_true",
                     help="skip the secondary sections (config2, extract, sweep, quality, manager, "
                          "reintegrate): headline value / e2e / roofline only")
@@ -297,8 +299,15 @@ def run_b200(args):
         host_seg.append(seg)
         res_seg.append(seg.to(dev, non_blocking=True))
         if world == 1:
-            host_sep.append({k: torch.from_numpy(kf[k]).pin_memory()
-                             for k in ("X", "C", "pose", "q")})
+            # the four separate arrays the reference-facing host entry takes: the whole pass
+            # in one pinned allocation per array, host_sep[l] = the views of launch l
+            if not host_sep:
+                host_all = {k: torch.empty((L * B,) + tuple(kf[k].shape[1:]),
+                                           dtype=torch.float32).pin_memory()
+                            for k in ("X", "C", "pose", "q")}
+            for k in ("X", "C", "pose", "q"):
+                host_all[k][l * B:(l + 1) * B].copy_(torch.from_numpy(kf[k]))
+            host_sep.append({k: host_all[k][l * B:(l + 1) * B] for k in ("X", "C", "pose", "q")})
     torch.cuda.synchronize()
 
     main = torch.cuda.current_stream(dev)
@@ -374,10 +383,16 @@ def run_b200(args):
 
     def step_e2e(v):
         """The same pass from pinned HOST buffers."""
-        if world == 1:
-            for l in range(L):  # *_host entry: chunked H2D inside the C ABI call
+        if world == 1 and args.e2e_per_launch:
+            for l in range(L):  # one *_host call per 40-keyframe launch (A/B)
                 t = host_sep[l]
                 v.integrate_keyframes(t["X"], t["C"], t["pose"], t["q"], MIN_CONF, H, W)
+        elif world == 1:
+            # ONE *_host call for the pass: inside the C ABI call the pointmaps cross PCIe in
+            # 40-keyframe chunks through a ring of staging slots, each chunk fused by its own
+            # launch while the next one is copied; the call returns when the copies are done
+            t = host_all
+            v.integrate_keyframes(t["X"], t["C"], t["pose"], t["q"], MIN_CONF, H, W)
         elif pull:  # one H2D of my share per launch into its ring slot, then as step_value
             sv = pull_volume(v)
             if args.no_pipeline:
@@ -543,8 +558,12 @@ def run_b200(args):
                 "h2d_bytes_per_step": n_kf_step * KF_BYTES, "d2h_bytes_per_step": 64 * P,
                 "keyframes_per_s": n_kf_step * args.steps / (e2e_ms * 1e-3),
                 "ms_per_step": e2e_ms / args.steps,
-                "ingest": ("b200tsdf_integrate_keyframes_host per launch (chunked H2D overlapped "
-                           "with the fuse), one counters read per step" if world == 1 else
+                "ingest": (("b200tsdf_integrate_keyframes_host per launch (chunked H2D overlapped "
+                            "with the fuse), one counters read per step" if args.e2e_per_launch else
+                            "ONE b200tsdf_integrate_keyframes_host call per 600-keyframe pass: "
+                            "inside it 40-keyframe chunks cross PCIe through a ring of three "
+                            "staging slots, each fused by its own launch behind the next copy; "
+                            "one counters read per step") if world == 1 else
                            ("per launch ONE packed H2D of the rank's share into its ring slot, "
                             "meta record + ONE small all-gather, fuse pulling its tiles from the "
                             "owners' slots; one counters read + one barrier per pass" if pull else

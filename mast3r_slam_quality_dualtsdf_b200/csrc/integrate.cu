@@ -1337,50 +1337,74 @@ extern "C" int b200tsdf_integrate_keyframes_host(b200tsdf_t *h, const float *X_h
   if (B == 0) return B200TSDF_OK;
   cudaStream_t st = (cudaStream_t)stream;
   B200_CUDA(cudaSetDevice(h->cfg.device));
-  size_t npix = (size_t)H * W;
-  size_t bx = (size_t)B * npix * 3 * sizeof(float), bc = (size_t)B * npix * sizeof(float);
-  size_t bq = q_grid_host ? (size_t)B * gh * gw * sizeof(float) : 0;
-  size_t bp = (size_t)B * 8 * sizeof(float);
+  const size_t npix = (size_t)H * W;
+  const size_t bq = q_grid_host ? (size_t)B * gh * gw * sizeof(float) : 0;
+  const size_t bp = (size_t)B * 8 * sizeof(float);
   auto al = [](size_t x) { return (x + 255) & ~(size_t)255; };
-  size_t total = al(bx) + al(bc) + al(bq) + al(bp);
+  // Chunked pipeline: the H2D copy of chunk c+1 (copy stream) overlaps the fuse of
+  // chunk c (caller's stream); the call stays stream-ordered on `st`.  PCIe pays per
+  // copy -- this box moves 55.4 GB/s in 64 MiB copies, 52.6 in 4 MiB ones and loses
+  // ~2 us on every tiny one (scripts/h2d_probe.py) -- and per call (the final wait for
+  // the copies is a bubble on the link).  So: quality grids and poses of the whole
+  // batch first, one copy each; pointmaps / confidences in chunks of up to
+  // `chunk_kf` keyframes (one fuse launch each, at least 4 chunks so that the fuse
+  // nothing overlaps is a quarter of the batch); and the chunks go through a ring of
+  // three staging slots, so a caller may hand over a whole trajectory in one call
+  // without the staging area growing with it.
+  static const int chunk_kf_knob = [] {
+    const char *e = getenv("B200TSDF_H2D_CHUNK_KF"); // A/B knob: keyframes per chunk (default 40)
+    const int n = e ? atoi(e) : 40;
+    return n < 1 ? 1 : n;
+  }();
+  const size_t kf_bytes = npix * 4 * sizeof(float);
+  int chunk_kf = chunk_kf_knob;
+  if ((size_t)chunk_kf * kf_bytes > ((size_t)256 << 20)) // a slot holds at most 256 MiB
+    chunk_kf = (int)(((size_t)256 << 20) / kf_bytes) > 1 ? (int)(((size_t)256 << 20) / kf_bytes) : 1;
+  int nchunk = (B + chunk_kf - 1) / chunk_kf;
+  if (nchunk < 4) nchunk = B < 4 ? B : 4;
+  const int slot_kf = (B + nchunk - 1) / nchunk; // chunks differ by at most one keyframe
+  const size_t slot_x = al((size_t)slot_kf * npix * 3 * sizeof(float));
+  const size_t slot_c = al((size_t)slot_kf * npix * sizeof(float));
+  const int nslot = nchunk < 3 ? nchunk : 3;
+  const size_t total = al(bq) + al(bp) + (size_t)nslot * (slot_x + slot_c);
   int rc = b200_ensure_stage(h, total);
   if (rc) return rc;
   char *base = (char *)h->stage_dev;
-  float *dX = (float *)base;
-  float *dC = (float *)(base + al(bx));
-  float *dQ = (float *)(base + al(bx) + al(bc));
-  float *dP = (float *)(base + al(bx) + al(bc) + al(bq));
-  // Chunked pipeline: the H2D copy of chunk k+1 (copy stream) overlaps the fuse
-  // of chunk k (caller's stream); the call stays stream-ordered on `st`.
-  const int nchunk = B < B200_H2D_CHUNKS ? B : B200_H2D_CHUNKS;
+  float *dQ = (float *)base;
+  float *dP = (float *)(base + al(bq));
+  char *slots = base + al(bq) + al(bp);
   if (!h->copy_stream) {
     B200_CUDA(cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
     for (int i = 0; i <= B200_H2D_CHUNKS; ++i)
       B200_CUDA(cudaEventCreateWithFlags(&h->copy_ev[i], cudaEventDisableTiming));
   }
+  // events: [0] "chunk copied" (re-recorded per chunk: a stream wait refers to the record
+  // that precedes it), [1..3] "slot fused", [B200_H2D_CHUNKS] "staging area free"
+  cudaStream_t cs = h->copy_stream;
   // the staging area may still be read by kernels queued on `st` earlier
   B200_CUDA(cudaEventRecord(h->copy_ev[B200_H2D_CHUNKS], st));
-  B200_CUDA(cudaStreamWaitEvent(h->copy_stream, h->copy_ev[B200_H2D_CHUNKS], 0));
+  B200_CUDA(cudaStreamWaitEvent(cs, h->copy_ev[B200_H2D_CHUNKS], 0));
   const size_t qsz = (size_t)gh * gw;
+  if (bq) B200_CUDA(cudaMemcpyAsync(dQ, q_grid_host, bq, cudaMemcpyHostToDevice, cs));
+  B200_CUDA(cudaMemcpyAsync(dP, pose_host, bp, cudaMemcpyHostToDevice, cs));
   for (int c = 0; c < nchunk; ++c) {
     const int b0 = (int)((long long)B * c / nchunk), b1 = (int)((long long)B * (c + 1) / nchunk);
     const size_t nb = (size_t)(b1 - b0);
-    cudaStream_t cs = h->copy_stream;
-    B200_CUDA(cudaMemcpyAsync(dX + (size_t)b0 * npix * 3, X_host + (size_t)b0 * npix * 3,
-                              nb * npix * 3 * sizeof(float), cudaMemcpyHostToDevice, cs));
-    B200_CUDA(cudaMemcpyAsync(dC + (size_t)b0 * npix, C_host + (size_t)b0 * npix,
-                              nb * npix * sizeof(float), cudaMemcpyHostToDevice, cs));
-    if (bq)
-      B200_CUDA(cudaMemcpyAsync(dQ + (size_t)b0 * qsz, q_grid_host + (size_t)b0 * qsz,
-                                nb * qsz * sizeof(float), cudaMemcpyHostToDevice, cs));
-    B200_CUDA(cudaMemcpyAsync(dP + (size_t)b0 * 8, pose_host + (size_t)b0 * 8,
-                              nb * 8 * sizeof(float), cudaMemcpyHostToDevice, cs));
-    B200_CUDA(cudaEventRecord(h->copy_ev[c], cs));
-    B200_CUDA(cudaStreamWaitEvent(st, h->copy_ev[c], 0));
-    rc = b200tsdf_integrate_keyframes(h, dX + (size_t)b0 * npix * 3, dC + (size_t)b0 * npix,
-                                      bq ? dQ + (size_t)b0 * qsz : nullptr, dP + (size_t)b0 * 8,
-                                      (int32_t)nb, H, W, gh, gw, min_conf, step_scale, st);
+    const int slot = c % nslot;
+    float *dX = (float *)(slots + (size_t)slot * (slot_x + slot_c));
+    float *dC = (float *)(slots + (size_t)slot * (slot_x + slot_c) + slot_x);
+    if (c >= nslot) B200_CUDA(cudaStreamWaitEvent(cs, h->copy_ev[1 + slot], 0)); // chunk c - 3 fused
+    B200_CUDA(cudaMemcpyAsync(dX, X_host + (size_t)b0 * npix * 3, nb * npix * 3 * sizeof(float),
+                              cudaMemcpyHostToDevice, cs));
+    B200_CUDA(cudaMemcpyAsync(dC, C_host + (size_t)b0 * npix, nb * npix * sizeof(float),
+                              cudaMemcpyHostToDevice, cs));
+    B200_CUDA(cudaEventRecord(h->copy_ev[0], cs));
+    B200_CUDA(cudaStreamWaitEvent(st, h->copy_ev[0], 0));
+    rc = b200tsdf_integrate_keyframes(h, dX, dC, bq ? dQ + (size_t)b0 * qsz : nullptr,
+                                      dP + (size_t)b0 * 8, (int32_t)nb, H, W, gh, gw, min_conf,
+                                      step_scale, st);
     if (rc) return rc;
+    if (c + nslot < nchunk) B200_CUDA(cudaEventRecord(h->copy_ev[1 + slot], st));
   }
   // the host buffers are the caller's again when this returns: wait for the copies
   // (not for the fuse, which stays queued on `stream`)

@@ -42,14 +42,23 @@ def test_keyframes_match_oracle(cuda_device, scene, voxel, n_kf):
     assert vol.stats(0) == vp.stats() and vol.stats(1) == vq.stats()
 
 
-def test_host_entry_matches_device_entry(cuda_device):
-    kf = synth.make_keyframes(synth.SCENES["sphere"], 2, H=48, W=64, seed=3, f=50.0)
+@pytest.mark.parametrize("n_kf,pinned", [(2, True), (9, True), (7, False), (1, True)])
+def test_host_entry_matches_device_entry(cuda_device, n_kf, pinned):
+    """b200tsdf_integrate_keyframes_host: the batch crosses PCIe in chunks through a ring
+    of three staging slots (9 and 7 keyframes = 4 chunks of unequal size, the fourth reuses
+    slot 0 behind the fuse of the first), quality grids and poses in one copy each; twice
+    in a row on the same handle (the second call waits for the first call's kernels before
+    it overwrites the slots).  Equal to the device entry fed the same tensors."""
+    kf = synth.make_keyframes(synth.SCENES["sphere"], n_kf, H=48, W=64, seed=3, f=50.0,
+                              total=max(n_kf, 8))
     a, b = _vol(cuda_device, 0.02, 0.08), _vol(cuda_device, 0.02, 0.08)
     t = {k: torch.from_numpy(kf[k]) for k in ("X", "C", "pose", "q")}
-    a.integrate_keyframes(t["X"].pin_memory(), t["C"].pin_memory(), t["pose"].pin_memory(),
-                          t["q"].pin_memory(), 0.05, 48, 64)
-    b.integrate_keyframes(*(t[k].to(cuda_device) for k in ("X", "C", "pose")),
-                          t["q"].to(cuda_device), 0.05, 48, 64)
+    th = {k: (v.pin_memory() if pinned else v) for k, v in t.items()}
+    for _ in range(2):
+        a.integrate_keyframes(th["X"], th["C"], th["pose"], th["q"], 0.05, 48, 64)
+        b.integrate_keyframes(*(t[k].to(cuda_device) for k in ("X", "C", "pose")),
+                              t["q"].to(cuda_device), 0.05, 48, 64)
+    assert a.counters()["rays"] == b.counters()["rays"] > 0
     for which in (0, 1):
         assert_volume_matches(a.export(which), tuple(np.asarray(x, np.float64) if x.dtype.kind == "f"
                                                      else x for x in b.export(which)), "host")
