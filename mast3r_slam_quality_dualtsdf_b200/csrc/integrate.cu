@@ -930,21 +930,31 @@ __global__ void __launch_bounds__(256, FUSE_MINB_LISTED)
 
 // ---- tsdf_global.max_points_per_kf (global_manager.py:94-99): a thread-block cluster
 // of SUB_SPLIT CTAs per keyframe finds the hash threshold that keeps exactly
-// min(n_valid, max_points) valid pixels -- the max_points smallest hashes -- by a
-// three-pass radix select (11 + 11 + 10 bits).  Every CTA histograms its share of the
-// pixels in its own shared memory; CTA 0 of the cluster sums the SUB_SPLIT histograms
-// through distributed shared memory, finds the bin of the need-th hash with one block
-// scan and publishes it to the cluster.  C stays L2-resident between the passes.
+// min(n_valid, max_points) valid pixels -- the max_points smallest hashes.
+//   pass 1: every CTA histograms the top 11 hash bits of its share of the pixels in
+//     its own shared memory; CTA 0 sums the SUB_SPLIT histograms through distributed
+//     shared memory, finds the bin of the need-th hash with one block scan and
+//     publishes bin, remaining need and the bin's population to the cluster;
+//   pass 2: the bin holds n_valid / 2048 hashes (~96 of a 512x384 keyframe): every
+//     CTA appends the hashes of its pixels that fall into it to ONE list in CTA 0's
+//     shared memory (remote atomicAdd + remote store), and CTA 0 picks the need-th
+//     smallest by rank counting -- exact, hashes are distinct;
+//   a bin of more than `list_cap` hashes (images of > 2 M valid pixels, or the test
+//     knob) takes two more radix passes (11 + 10 bits) instead.
+// C stays L2-resident between the passes; the pass is bound by the hash evaluations.
 #define SUB_SPLIT 8
 #define SUB_THREADS 512 // 40 keyframes x 8 CTAs = 320 CTAs, four per SM: one wave of clusters
+#define SUB_LIST_CAP 1024
 __global__ void __cluster_dims__(SUB_SPLIT, 1, 1) __launch_bounds__(SUB_THREADS)
     subsample_threshold_kernel(KfArgs a, int max_points, unsigned long long seed,
-                               const long long *__restrict__ kf_ids, uint2 *__restrict__ out) {
+                               const long long *__restrict__ kf_ids, uint2 *__restrict__ out,
+                               int list_cap) {
   namespace cg = cooperative_groups;
   cg::cluster_group cl = cg::this_cluster();
   __shared__ __align__(16) unsigned int hist[2048];
   __shared__ unsigned int s_warp[SUB_THREADS / 32];
-  __shared__ unsigned int s_need, s_bin;  // CTA 0 publishes, the others read them remotely
+  __shared__ unsigned int s_need, s_bin, s_pop; // CTA 0 publishes, the others read them remotely
+  __shared__ unsigned int s_list[SUB_LIST_CAP], s_nlist; // CTA 0: the threshold bin's hashes
   const int kf = blockIdx.y, npix = a.H * a.W;
   const unsigned int part = cl.block_rank();
   const int chunk = (npix + SUB_SPLIT - 1) / SUB_SPLIT;
@@ -953,11 +963,13 @@ __global__ void __cluster_dims__(SUB_SPLIT, 1, 1) __launch_bounds__(SUB_THREADS)
   const uint32_t salt = sub_salt(seed, kf_ids ? (unsigned long long)kf_ids[kf] : (unsigned long long)kf);
   const unsigned int *const bin0 = cl.map_shared_rank(&s_bin, 0);
   const unsigned int *const need0 = cl.map_shared_rank(&s_need, 0);
+  const unsigned int *const pop0 = cl.map_shared_rank(&s_pop, 0);
   unsigned int prefix = 0, need = (unsigned int)max_points; // hashes < prefix region are all kept
   // pass p fixes the next `bits` bits of the threshold below the already fixed ones
   const int shifts[3] = {21, 10, 0}, nbins[3] = {2048, 2048, 1024};
   unsigned int fixed_mask = 0;
-  bool all = false;
+  bool all = false, listed = false;
+  if (threadIdx.x == 0) s_nlist = 0;
   for (int p = 0; p < 3; ++p) {
     for (int i = threadIdx.x; i < 2048; i += SUB_THREADS) hist[i] = 0;
     __syncthreads();
@@ -1001,19 +1013,20 @@ __global__ void __cluster_dims__(SUB_SPLIT, 1, 1) __launch_bounds__(SUB_THREADS)
       for (int w = 0; w < (int)(threadIdx.x >> 5); ++w) ex += s_warp[w];
       // the one thread whose bins hold the need-th smallest hash of the candidates
       if (ex < need && need <= ex + v) {
-        unsigned int bin = 4 * threadIdx.x, acc = ex;
+        unsigned int bin = 4 * threadIdx.x, acc = ex, pop = b0;
         if (acc + b0 < need) {
-          acc += b0, ++bin;
+          acc += b0, ++bin, pop = b1;
           if (acc + b1 < need) {
-            acc += b1, ++bin;
-            if (acc + b2 < need) acc += b2, ++bin;
+            acc += b1, ++bin, pop = b2;
+            if (acc + b2 < need) acc += b2, ++bin, pop = b3;
           }
         }
         s_bin = bin;
         s_need = need - acc;
+        s_pop = pop;
       }
     }
-    cl.sync(); // s_bin / s_need of CTA 0 are final; nobody reads a remote histogram any more
+    cl.sync(); // s_bin / s_need / s_pop of CTA 0 are final; nobody reads a remote histogram any more
     const unsigned int bin = *bin0;
     if (bin >= (unsigned int)nbins[p]) {
       all = true;
@@ -1022,7 +1035,41 @@ __global__ void __cluster_dims__(SUB_SPLIT, 1, 1) __launch_bounds__(SUB_THREADS)
     prefix |= bin << shifts[p];
     fixed_mask |= (unsigned int)(nbins[p] - 1) << shifts[p];
     need = *need0;
+    if (p == 0 && *pop0 <= (unsigned int)list_cap) { // cluster-uniform
+      listed = true;
+      break;
+    }
     // (CTA 0 rewrites s_bin only after the next pass's first cluster barrier)
+  }
+  if (listed) {
+    unsigned int *const list0 = cl.map_shared_rank(s_list, 0);
+    unsigned int *const nlist0 = cl.map_shared_rank(&s_nlist, 0);
+    for (int i0 = p_lo + (int)threadIdx.x; i0 < p_hi; i0 += 8 * SUB_THREADS) {
+      float cv[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int i = i0 + u * SUB_THREADS;
+        cv[u] = i < p_hi ? __ldg(k.C + i) : a.min_conf;
+      }
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        if (cv[u] > a.min_conf) {
+          const uint32_t h = sub_hash((uint32_t)(i0 + u * SUB_THREADS), salt);
+          if ((h & fixed_mask) == prefix) list0[atomicAdd(nlist0, 1u)] = h; // <= s_pop entries
+        }
+      }
+    }
+    cl.sync(); // the list is complete (and nobody touches CTA 0's memory after this)
+    if (part == 0) {
+      const unsigned int n = s_nlist; // == s_pop
+      for (unsigned int i = threadIdx.x; i < n; i += SUB_THREADS) {
+        const unsigned int mine = s_list[i];
+        unsigned int below = 0;
+        for (unsigned int j = 0; j < n; ++j) below += s_list[j] < mine ? 1u : 0u;
+        if (below + 1 == need) out[kf] = make_uint2(mine, salt); // exactly one (distinct hashes)
+      }
+    }
+    return;
   }
   // after three passes `prefix` is the hash of the need-th smallest kept pixel
   // (hashes are distinct), so h <= prefix selects exactly max_points pixels
@@ -1211,9 +1258,13 @@ static int fuse_keyframes(b200tsdf_t *h, const b200tsdf_kf_batch *kb, void *stre
       B200_CUDA(cudaMalloc(&h->sub_thr, (size_t)B * sizeof(uint2)));
       h->sub_cap = (size_t)B;
     }
-    subsample_threshold_kernel<<<dim3(SUB_SPLIT, (unsigned)B), SUB_THREADS, 0, st>>>(ka, kb->max_points, kb->seed,
-                                                             (const long long *)kb->kf_ids_dev,
-                                                             (uint2 *)h->sub_thr);
+    int list_cap = SUB_LIST_CAP;
+    if (const char *e = getenv("B200TSDF_SUB_LIST_CAP")) { // test knob, read per call: 0 = radix passes only
+      const int n = atoi(e);
+      list_cap = n < 0 ? 0 : (n > SUB_LIST_CAP ? SUB_LIST_CAP : n);
+    }
+    subsample_threshold_kernel<<<dim3(SUB_SPLIT, (unsigned)B), SUB_THREADS, 0, st>>>(
+        ka, kb->max_points, kb->seed, (const long long *)kb->kf_ids_dev, (uint2 *)h->sub_thr, list_cap);
     ka.sub = (const uint2 *)h->sub_thr;
   }
 #define DISPATCH_KF(LAUNCH)                                                                    \

@@ -443,6 +443,35 @@ def test_capped_rays_are_compacted_ragged_and_sharded(cuda_device, ranks):
         assert_volume_matches(got, want.export(), f"capped, {ranks} rank(s)")
 
 
+def test_threshold_select_list_and_radix_paths_agree(cuda_device, monkeypatch):
+    """subsample_threshold_kernel picks the need-th smallest hash either from the list of
+    the threshold bin's hashes (default) or, for bins larger than the list, by two more
+    radix passes; B200TSDF_SUB_LIST_CAP = 0 forces the latter.  Same selection either way:
+    equal to the oracle's argsort choice, on small and on full-size keyframes."""
+    from mast3r_slam_quality_dualtsdf_b200 import synth
+    from mast3r_slam_quality_dualtsdf_b200.tsdf import TSDFVolume
+
+    for (H, W, voxel, cap) in ((48, 64, 0.03, 700), (384, 512, 0.02, 40000)):
+        scene = synth.SCENES["sphere"] if H == 48 else synth.SCENES["room"]
+        kw = {"f": 50.0} if H == 48 else {"orbit_radius": 0.6, "gh": 24, "gw": 32}
+        kf = synth.make_keyframes(scene, 2, H=H, W=W, seed=8, total=9, **kw)
+        vp, vq, rays = oracle_dual(kf, voxel, 4 * voxel, max_points=cap, seed=5)
+        assert rays == 2 * cap
+        t = {k: torch.from_numpy(kf[k]).to(cuda_device) for k in ("X", "C", "pose", "q")}
+        for knob in (None, "0", "3"):
+            if knob is None:
+                monkeypatch.delenv("B200TSDF_SUB_LIST_CAP", raising=False)
+            else:
+                monkeypatch.setenv("B200TSDF_SUB_LIST_CAP", knob)
+            vol = TSDFVolume(voxel, 4 * voxel, capacity_log2=17, device=cuda_device)
+            vol.integrate_keyframes(t["X"], t["C"], t["pose"], t["q"], 0.05, H, W, max_points=cap,
+                                    seed=5)
+            c = vol.counters()
+            assert c["rays"] == rays and c["updates_primary"] == vp.events, f"list cap {knob}"
+            assert_volume_matches(vol.export(0), vp.export(), f"{H}x{W}, list cap {knob}")
+            assert_volume_matches(vol.export(1), vq.export(), f"{H}x{W} quality, list cap {knob}")
+
+
 def test_hash_overflow_is_an_error(cuda_device):
     """B200TSDF_E_CAPACITY is returned, and the drop-in
     integrator raises instead of losing updates silently."""
