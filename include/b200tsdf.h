@@ -209,7 +209,12 @@ int b200tsdf_ipc_close(int32_t device, void *ptr, int64_t offset_bytes);
  * fused on `stream`.  Returns once every copy has completed -- the host buffers
  * may be reused or freed right away -- while the fuse itself stays queued on
  * `stream`.  This is the entry the reference-facing plugin uses when keyframes
- * live on the host. */
+ * live on the host.  B may be a whole trajectory: quality grids and poses cross
+ * in one copy each, pointmaps / confidences in chunks of 40 keyframes (env
+ * B200TSDF_H2D_CHUNK_KF; at least 4 chunks) through a ring of three staging
+ * slots, one fuse launch per chunk, so the staging area does not grow with B.
+ * One call per pass keeps the link busy (54 GB/s of this box's 55.4); a call per
+ * 40 keyframes idles it during each call's final wait (50 GB/s). */
 int b200tsdf_integrate_keyframes_host(b200tsdf_t *h, const float *X_host,
                                       const float *C_host,
                                       const float *q_grid_host,

@@ -54,7 +54,7 @@ extern "C" int b200tsdf_stats(b200tsdf_t *h, int which, int64_t *valid_host, int
   cudaStream_t st = (cudaStream_t)stream;
   B200_CUDA(cudaSetDevice(h->cfg.device));
   B200_CUDA(cudaMemsetAsync(h->scratch, 0, 16, st));
-  stats_kernel<<<148 * 8, 128, 0, st>>>(h->d, which, h->scratch);
+  stats_kernel<<<(unsigned)(h->sm_count > 0 ? h->sm_count : 148) * 8, 128, 0, st>>>(h->d, which, h->scratch);
   B200_CUDA(cudaGetLastError());
   unsigned long long r[2];
   B200_CUDA(cudaMemcpyAsync(r, h->scratch, 16, cudaMemcpyDeviceToHost, st));
@@ -122,7 +122,7 @@ extern "C" int b200tsdf_export_voxels(b200tsdf_t *h, int which, int64_t *keys_de
   cudaStream_t st = (cudaStream_t)stream;
   B200_CUDA(cudaSetDevice(h->cfg.device));
   B200_CUDA(cudaMemsetAsync(h->scratch, 0, 8, st));
-  export_kernel<<<148 * 8, 128, 0, st>>>(h->d, which, cap > 0 ? (long long *)keys_dev : nullptr,
+  export_kernel<<<(unsigned)(h->sm_count > 0 ? h->sm_count : 148) * 8, 128, 0, st>>>(h->d, which, cap > 0 ? (long long *)keys_dev : nullptr,
                                          tsdf_dev, weight_dev, count_dev, (long long)cap,
                                          h->scratch);
   B200_CUDA(cudaGetLastError());
@@ -790,7 +790,7 @@ static int export_block_payload(b200tsdf_t *h, int64_t *bkeys_dev, float *vox_de
   cudaStream_t st = (cudaStream_t)stream;
   B200_CUDA(cudaSetDevice(h->cfg.device));
   B200_CUDA(cudaMemsetAsync(h->scratch, 0, 8, st));
-  export_seam_kernel<<<148 * 8, 128, 0, st>>>(h->d, (long long *)bkeys_dev, (float4 *)vox_dev,
+  export_seam_kernel<<<(unsigned)(h->sm_count > 0 ? h->sm_count : 148) * 8, 128, 0, st>>>(h->d, (long long *)bkeys_dev, (float4 *)vox_dev,
                                               (unsigned long long *)cnt_dev, (long long)cap,
                                               h->scratch, all_blocks);
   B200_CUDA(cudaGetLastError());
