@@ -215,10 +215,16 @@ class ShardedTSDFVolume:
             ids = [int(i) for i in ids]
             if len(ids) != int(X.shape[0]):
                 raise ValueError("ids must name every keyframe of the batch")
+            # one clone of the batch (not one per keyframe); the entries are views of it and
+            # remember their run, so that re-integration of a stored run needs no re-stacking
+            # (the batch's memory is released when its last keyframe is forgotten)
+            run = {"X": X.clone(), "C": Cf.clone(),
+                   "q": None if q_grid is None else q_grid.clone()}
+            pc = poses.reshape(-1, 8).clone()
             for b, i in enumerate(ids):
                 self._store[i] = {
-                    "X": X[b].clone(), "C": Cf[b].clone(), "pose": poses[b].reshape(8).clone(),
-                    "q": None if q_grid is None else q_grid[b].clone(),
+                    "X": run["X"][b], "C": run["C"][b], "pose": pc[b].clone(),
+                    "q": None if q_grid is None else run["q"][b], "run": (run, b),
                     "args": (float(min_conf), int(H), int(W), float(step_scale))}
 
     def integrate_slot(self, peers, i, min_conf=0.05, step_scale=0.5, meta_bufs=None):
@@ -349,9 +355,16 @@ class ShardedTSDFVolume:
             for a in range(0, len(members), batch):
                 part = members[a:a + batch]
                 es = [self._store[i] for _, i in part]
-                X = torch.stack([e["X"] for e in es])
-                Cf = torch.stack([e["C"] for e in es])
-                Q = None if qshape is None else torch.stack([e["q"] for e in es])
+                run, b0 = es[0].get("run", (None, 0))
+                if run is not None and all(e.get("run", (None, 0))[0] is run and
+                                           e["run"][1] == b0 + j for j, e in enumerate(es)):
+                    # consecutive keyframes of one stored batch: zero-copy slices
+                    X, Cf = run["X"][b0:b0 + len(es)], run["C"][b0:b0 + len(es)]
+                    Q = None if qshape is None else run["q"][b0:b0 + len(es)]
+                else:
+                    X = torch.stack([e["X"] for e in es])
+                    Cf = torch.stack([e["C"] for e in es])
+                    Q = None if qshape is None else torch.stack([e["q"] for e in es])
                 if mode == "replace":
                     old = torch.stack([e["pose"] for e in es])
                     self.vol.deintegrate_keyframes(X, Cf, old, Q, min_conf, H, W, step_scale)
