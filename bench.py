@@ -785,7 +785,7 @@ def reintegrate_section(args, dev, rank, world, bounds, slabs, dev_ms):
 def local_section(args, dev, dev_ms):
     """the refiner's per-ROI dense TSDF (tsdf_refine.py:837-1064) --
     `build_tsdf_robust` + `extract_surface_safe` for 64x64-pixel blocks of one full-size
-    Target keyframe (ROI = the block's world points + 2 truncation distances, 2 cm voxels,
+    Target keyframe (ROI = the block's points + the refiner's 4 cm margin, 2 cm voxels,
     <= 64^3 grid, 100 ray-cast pixels per block as the reference).  Latency-bound by
     construction: reported as blocks/s through the Python mirror."""
     import numpy as np
@@ -800,14 +800,17 @@ def local_section(args, dev, dev_ms):
     kf = gen_batch(TARGET, 3, 1)
     X = torch.from_numpy(kf["X"][0]).to(dev)
     Cf = torch.from_numpy(kf["C"][0]).to(dev)
-    pose = torch.from_numpy(kf["pose"][0]).to(dev)
+    # the refiner takes the ROI from the block's camera-frame points (+ margin,
+    # tsdf_refine.py:715-716) and hands the kernels the keyframe's pose; with the identity
+    # pose the two frames coincide and every block has its surface inside its ROI
+    pose = torch.tensor([0, 0, 0, 0, 0, 0, 1, 1], dtype=torch.float32, device=dev)
     Xw = sim3.act(pose, X).reshape(H, W, 3)
     T = type("Pose", (), {"data": pose.reshape(1, 8).cpu()})()
     blocks = []
     for y0 in range(32, H - 64, 96):
         for x0 in range(32, W - 64, 96):
             pts = Xw[y0:y0 + 64, x0:x0 + 64].reshape(-1, 3)
-            lo, hi = pts.min(0).values - 0.16, pts.max(0).values + 0.16
+            lo, hi = pts.min(0).values - 0.04, pts.max(0).values + 0.04
             mask = torch.zeros(H, W, dtype=torch.bool, device=dev)
             mask[y0:y0 + 64, x0:x0 + 64] = True
             blocks.append((lo.cpu(), hi.cpu(), mask.reshape(-1)))
