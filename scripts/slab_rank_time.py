@@ -24,22 +24,23 @@ def main():
     ap.add_argument("--steps", type=int, default=4)
     ap.add_argument("--warmup", type=int, default=2)
     ap.add_argument("--ranks", default="1,2,4,8")
-    ap.add_argument("--width", type=int, default=0, help="0: bench.slab_width_for(R)")
+    ap.add_argument("--width", default="0", help="slab widths to try, comma separated; 0: bench.slab_width_for(R)")
     ap.add_argument("--only-rank", type=int, default=-1)
     a = ap.parse_args()
     dev = torch.device("cuda:0")
-    scene, dim, orbit_r = bench.scene_for(8)
-    lo, hi = synth.bounds_for(scene, bench.VOXEL, dim)
+    wl = bench.TARGET
+    dim = wl["dim"]
+    lo, hi = synth.bounds_for(wl["scene"], bench.VOXEL, dim)
     batches = []
     for s in range(a.warmup + a.steps):
-        kf = bench.gen_batch(scene, orbit_r, s, a.kf, up_axis="z")
+        kf = bench.gen_batch(wl, 3 * s, a.kf)  # spread over the orbit
         batches.append(tuple(torch.from_numpy(kf[k]).to(dev) for k in ("X", "C", "pose", "q")))
     out = {}
-    for R in (int(x) for x in a.ranks.split(",")):
+    for R, width in ((int(x), int(w)) for x in a.ranks.split(",") for w in a.width.split(",")):
         per_rank = []
         for r in (range(R) if a.only_rank < 0 else [a.only_rank % R]):
-            slabs = (R, r, a.width or bench.slab_width_for(R, dim)) if R > 1 else None
-            vol = TSDFVolume(bench.VOXEL, bench.TRUNC, capacity_log2=18, bounds=(lo, hi),
+            slabs = (R, r, width or bench.slab_width_for(R, dim)) if R > 1 else None
+            vol = TSDFVolume(bench.VOXEL, bench.TRUNC, capacity_log2=wl["cap_log2"], bounds=(lo, hi),
                              slabs=slabs, device=dev)
             evs = []
             for i, (X, C, P, q) in enumerate(batches):
@@ -56,12 +57,12 @@ def main():
             del vol
         ms = [p[0] for p in per_rank]
         upd = sum(p[1] for p in per_rank)
-        out[R] = {"max_ms": max(ms), "mean_ms": sum(ms) / len(ms), "ms": [round(m, 4) for m in ms],
+        out[(R, width)] = {"width": width or bench.slab_width_for(R, dim), "max_ms": max(ms), "mean_ms": sum(ms) / len(ms), "ms": [round(m, 4) for m in ms],
                   "updates": upd,
                   # share of the rays a rank marches / share of the updates it applies
                   "marched": [round(p[2], 4) for p in per_rank],
                   "applied": [round(p[1] / max(1, upd), 4) for p in per_rank]}
-        print(R, json.dumps(out[R]), flush=True)
+        print(R, json.dumps(out[(R, width)]), flush=True)
 
 
 if __name__ == "__main__":
