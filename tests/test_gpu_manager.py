@@ -61,6 +61,56 @@ def test_pose_optimizer_matches_reference_golden(cuda_device, case):
     assert np.allclose(got, _canon_q(ref), rtol=tol, atol=tol * 0.1)
 
 
+def test_tsdf_factor_blocks_match_oracle_and_optimizer_step(cuda_device):
+    """SURVEY 8(f) rank 4 / roadmap 9.3.2 (MASt3R_SLAM_TSDF_Integration.md:240-252): the
+    unary TSDF factor's 7x7 block and gradient per keyframe equal the oracle's normal
+    equations of tsdf_optimizer.py:94-116 at the same pose and sample choice; scattered
+    into a two-keyframe system (variable order as unique_kf_idx[pin:]) and solved with
+    the optimiser's damping, the update of a keyframe is the optimiser's own first
+    Gauss-Newton step (:82-86)."""
+    from mast3r_slam_quality_dualtsdf_b200.tsdf import TSDFFactor, TSDFPoseOptimizer, TSDFVolume
+    from mast3r_slam_quality_dualtsdf_b200.tsdf import sim3
+    from oracle.opt_oracle import _act_f32, normal_equations
+
+    kf, bad = mg.scene()
+    vol = TSDFVolume(mg.VOXEL, mg.TRUNC, device=cuda_device)
+    vol.integrate_keyframes(*(torch.from_numpy(kf[k]).to(cuda_device) for k in ("X", "C", "pose")),
+                            None, mg.CFG["min_confidence"], mg.H, mg.W)
+    ovol = oracle_volume(kf)
+    poses = [kf["pose"][0], bad, kf["pose"][2]]
+    kfs = _keyframes(kf, poses, cuda_device)
+    cfg = dict(mg.CFG, damping=1.0e-4)
+    fac = TSDFFactor(vol, kfs, cfg, cuda_device)
+    choice = {1: G["choice"], 2: G["choice"]}
+    blocks = fac.linearize([1, 2, 7], choices=choice)  # 7: not a keyframe, skipped
+    assert sorted(blocks) == [1, 2]
+    for idx in (1, 2):
+        pts = kf["X"][idx].reshape(-1, 3)[G["choice"]].astype(np.float32)
+        conf = kf["C"][idx].reshape(-1)[G["choice"]]
+        Ho, bo, uo = normal_equations(ovol, _act_f32(np.asarray(poses[idx], np.float32), pts), conf,
+                                      cfg["lambda"])
+        H, b, used = blocks[idx]
+        # the probe set may differ by the few points whose gradient presence flips between
+        # float32 sums and the reference's float64 dict (DESIGN.md 3): same bound as the
+        # optimiser's golden test
+        assert abs(used - uo) <= max(2, uo // 200)
+        assert np.allclose(H, Ho, rtol=2e-3, atol=2e-3 * np.abs(Ho).max())
+        assert np.allclose(b, bo, rtol=2e-3, atol=2e-3 * np.abs(bo).max())
+        assert np.allclose(H, H.T)
+    # variable order [2, 1] with keyframe 0 pinned: blocks land on the diagonal
+    Hf, bf = np.zeros((14, 14)), np.zeros(14)
+    assert TSDFFactor.add_to(Hf, bf, blocks, order=[2, 1]) == 2
+    assert np.array_equal(Hf[:7, :7], blocks[2][0]) and np.array_equal(Hf[7:, 7:], blocks[1][0])
+    assert not Hf[:7, 7:].any() and np.array_equal(bf[7:], blocks[1][1])
+    delta = np.linalg.solve(Hf + cfg["damping"] * np.eye(14), -bf)
+    want = sim3.mul(sim3.exp(torch.from_numpy(delta[7:]).to(torch.float32).to(torch.float64)),
+                    torch.from_numpy(np.asarray(bad, np.float64))).numpy()
+    opt = TSDFPoseOptimizer(vol, kfs, dict(cfg, device_solve=False), False, cuda_device)
+    opt._optimize_single(1, iterations=1, choice=G["choice"])
+    got = kfs.T_WC[1].cpu().numpy().reshape(8).astype(np.float64)
+    assert np.allclose(_canon_q(got), _canon_q(want), rtol=1e-6, atol=1e-7)
+
+
 def test_device_gauss_newton_equals_host_solve(cuda_device):
     """the whole loop of _optimize_single on the device
     (b200tsdf_pose_optimize: one launch per iteration -- linearise, 7x7 solve,
@@ -273,6 +323,9 @@ def test_checkpoint_round_trip_and_merge(cuda_device, tmp_path):
     path = str(tmp_path / "vol.npz")
     nblk = whole.save_checkpoint(path)
     assert nblk == whole.counters()["blocks"] > 0
+    # the oracle is the checker of what comes back from disk, not only the volume that
+    # wrote it: the reference dict fused with the same keyframes
+    vp, vq, _ = oracle_dual(kf, 0.02, 0.08)
     for kw in ({}, {"bounds": ((-64, -64, 0), (64, 64, 128))}):  # hash-only and directory volumes
         back = TSDFVolume(0.02, 0.08, device=cuda_device, **kw)
         assert back.load_checkpoint(path) == nblk
@@ -280,6 +333,10 @@ def test_checkpoint_round_trip_and_merge(cuda_device, tmp_path):
             a, b = whole.export(which), back.export(which)
             assert all(np.array_equal(x, y) for x, y in zip(a, b))
         assert back.stats() == whole.stats()
+        assert_volume_matches(back.export(0), vp.export(), "restored primary vs oracle")
+        assert_volume_matches(back.export(1), vq.export(), "restored quality vs oracle")
+        assert back.stats(0) == vp.stats() and back.stats(1) == vq.stats()
+        assert np.array_equal(back.block_keys(), np.unique(vp.export()[0] >> 3, axis=0))
         # the restored volume keeps fusing like the original
         back.integrate_keyframes(t["X"][:1], t["C"][:1], t["pose"][:1], t["q"][:1], 0.05, 48, 64)
         assert back.counters()["blocks"] >= nblk
@@ -291,6 +348,15 @@ def test_checkpoint_round_trip_and_merge(cuda_device, tmp_path):
         wk, wt, ww, wc = whole.export(which)
         assert np.array_equal(gk, wk) and np.array_equal(gc, wc)
         assert np.abs(gt - wt).max() <= 1e-5 and np.abs(gw - ww).max() <= 1e-4 * max(1.0, ww.max())
+    assert_volume_matches(left.export(0), vp.export(), "merged primary vs oracle")
+    assert_volume_matches(left.export(1), vq.export(), "merged quality vs oracle")
+    # a checkpoint loaded on top of a fused volume = the reference fusing both sets
+    # (additive sums): {0,1} from disk onto {2,3}
+    half = str(tmp_path / "half.npz")
+    fused(slice(0, 2)).save_checkpoint(half)
+    onto = fused(slice(2, 4))
+    onto.load_checkpoint(half)
+    assert_volume_matches(onto.export(0), vp.export(), "checkpoint merged onto a volume vs oracle")
     with pytest.raises(ValueError):
         TSDFVolume(0.03, 0.08, device=cuda_device).load_checkpoint(path)
 
