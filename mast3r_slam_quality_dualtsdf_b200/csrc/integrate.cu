@@ -682,8 +682,13 @@ __global__ void __launch_bounds__(256, FUSE_MINB)
 // take 32-ray chunks of it round robin.  Which rays are fused is decided by sub_take
 // alone, so the volume equals the one-tile path's up to float32 summation order.
 #define CAP_G 4
+#ifndef CAP_WARPS
+#define CAP_WARPS 4 // warps per CTA (8, 4 or 2).  4: eight CTAs per SM, a warp takes one or two chunks, and a CTA waits less
+                    // for its slowest warp (0.254 -> 0.245 ms at cap 40 000, 0.194 -> 0.144 at 10 000; 2 warps: 0.295)
+#endif
+#define CAP_THREADS (CAP_WARPS * 32)
 template <bool BOUNDED, bool DIR, bool TMA>
-__global__ void __launch_bounds__(256, FUSE_MINB)
+__global__ void __launch_bounds__(CAP_THREADS, FUSE_MINB * 8 / CAP_WARPS)
     integrate_keyframes_capped_kernel(const __grid_constant__ VolumeDev v,
                                       const __grid_constant__ KfArgs a,
                                       const __grid_constant__ MarchConst mc,
@@ -722,20 +727,26 @@ __global__ void __launch_bounds__(256, FUSE_MINB)
     __syncthreads(); // mbarrier init visible to the waiters
     mbar_wait(bar, 0);
   }
-  // which of this thread's CAP_G pixels (one per tile) survive the filter and the cap
-  const int tx = (warp & 3) * 8 + (lane & 7), ty = (warp >> 2) * 4 + (lane >> 3);
-  const int px0 = bx * TILE_W + tx;
-  unsigned bal[CAP_G];
+  // which pixels survive the filter and the cap: warp w tests the 8 x 4 sub-tiles
+  // w, w + CAP_WARPS, ... of every tile, one pixel per lane
+  constexpr int SUBS = 8 / CAP_WARPS; // sub-tiles of a tile per warp
+  unsigned bal[CAP_G * SUBS];
 #pragma unroll
   for (int t = 0; t < CAP_G; ++t) {
-    const int r = t * TILE_H + ty, py = row0 + r;
-    bool take = false;
-    if (r < rows && (TMA || px0 < a.W)) {
-      const float c = TMA ? sC[r * SC_ROW + tx] : k.C[(long long)py * a.W + px0];
-      take = c > a.min_conf && sub_take(a, kf, py * a.W + px0);
+#pragma unroll
+    for (int u = 0; u < SUBS; ++u) {
+      const int sub = warp + u * CAP_WARPS;
+      const int tx = (sub & 3) * 8 + (lane & 7), ty = (sub >> 2) * 4 + (lane >> 3);
+      const int px0 = bx * TILE_W + tx;
+      const int r = t * TILE_H + ty, py = row0 + r;
+      bool take = false;
+      if (r < rows && (TMA || px0 < a.W)) {
+        const float c = TMA ? sC[r * SC_ROW + tx] : k.C[(long long)py * a.W + px0];
+        take = c > a.min_conf && sub_take(a, kf, py * a.W + px0);
+      }
+      bal[t * SUBS + u] = __ballot_sync(0xFFFFFFFFu, take);
+      if (lane == 0) s_cnt[t * 8 + sub] = __popc(bal[t * SUBS + u]);
     }
-    bal[t] = __ballot_sync(0xFFFFFFFFu, take);
-    if (lane == 0) s_cnt[t * 8 + warp] = __popc(bal[t]);
   }
   __syncthreads();
   // every warp scans the 32 (tile, warp) counts itself
@@ -749,15 +760,21 @@ __global__ void __launch_bounds__(256, FUSE_MINB)
   const int total = __shfl_sync(0xFFFFFFFFu, inc, 31);
 #pragma unroll
   for (int t = 0; t < CAP_G; ++t) {
-    const int base = __shfl_sync(0xFFFFFFFFu, inc - mine, t * 8 + warp);
-    if ((bal[t] >> lane) & 1u)
-      s_sel[base + __popc(bal[t] & ((1u << lane) - 1u))] =
-          (unsigned short)((t * TILE_H + ty) * TILE_W + tx);
+#pragma unroll
+    for (int u = 0; u < SUBS; ++u) {
+      const int sub = warp + u * CAP_WARPS;
+      const int tx = (sub & 3) * 8 + (lane & 7), ty = (sub >> 2) * 4 + (lane >> 3);
+      const unsigned bl = bal[t * SUBS + u];
+      const int base = __shfl_sync(0xFFFFFFFFu, inc - mine, t * 8 + sub);
+      if ((bl >> lane) & 1u)
+        s_sel[base + __popc(bl & ((1u << lane) - 1u))] =
+            (unsigned short)((t * TILE_H + ty) * TILE_W + tx);
+    }
   }
   __syncthreads();
   Tally tl = {0, 0, 0, 0, 0, 0, 0};
 #pragma unroll 1
-  for (int j0 = warp * 32; j0 < total; j0 += 256) { // warp-uniform
+  for (int j0 = warp * 32; j0 < total; j0 += CAP_THREADS) { // warp-uniform
     const bool take = j0 + lane < total;
     float c = 0.f, x0 = 0.f, x1 = 0.f, x2 = 0.f;
     int px = 0, py = 0;
@@ -1316,7 +1333,7 @@ static int fuse_keyframes(b200tsdf_t *h, const b200tsdf_kf_batch *kb, void *stre
     if (ka.sub && cap_group) {
       // max_points_per_kf: CAP_G tiles per CTA, survivors compacted across them
       const dim3 cgrid(grid.x, (grid.y + CAP_G - 1) / CAP_G, (unsigned)B);
-#define LAUNCH_CAP(BD, DR, TM) integrate_keyframes_capped_kernel<BD, DR, TM><<<cgrid, 256, 0, st>>>(h->d, ka, mc, fc)
+#define LAUNCH_CAP(BD, DR, TM) integrate_keyframes_capped_kernel<BD, DR, TM><<<cgrid, CAP_THREADS, 0, st>>>(h->d, ka, mc, fc)
       DISPATCH_KF(LAUNCH_CAP)
 #undef LAUNCH_CAP
     } else {
