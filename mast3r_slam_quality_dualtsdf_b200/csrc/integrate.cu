@@ -1072,13 +1072,16 @@ __global__ void __cluster_dims__(SUB_SPLIT, 1, 1) __launch_bounds__(SUB_THREADS)
       for (int u = 0; u < 8; ++u) {
         if (cv[u] > a.min_conf) {
           const uint32_t h = sub_hash((uint32_t)(i0 + u * SUB_THREADS), salt);
-          if ((h & fixed_mask) == prefix) list0[atomicAdd(nlist0, 1u)] = h; // <= s_pop entries
+          if ((h & fixed_mask) == prefix) { // s_pop entries, unless the caller rewrites C under us
+            const unsigned int at = atomicAdd(nlist0, 1u);
+            if (at < SUB_LIST_CAP) list0[at] = h;
+          }
         }
       }
     }
     cl.sync(); // the list is complete (and nobody touches CTA 0's memory after this)
     if (part == 0) {
-      const unsigned int n = s_nlist; // == s_pop
+      const unsigned int n = min(s_nlist, (unsigned int)SUB_LIST_CAP); // == s_pop
       for (unsigned int i = threadIdx.x; i < n; i += SUB_THREADS) {
         const unsigned int mine = s_list[i];
         unsigned int below = 0;
