@@ -681,7 +681,9 @@ __global__ void __launch_bounds__(256, FUSE_MINB)
 // list (order: tile, warp sub-tile, lane -- neighbours stay neighbours) and the warps
 // take 32-ray chunks of it round robin.  Which rays are fused is decided by sub_take
 // alone, so the volume equals the one-tile path's up to float32 summation order.
-#define CAP_G 4
+#ifndef CAP_G
+#define CAP_G 4 // tiles per CTA: 1, 2 or 4 (the compaction scans CAP_G * 8 <= 32 counts with one warp)
+#endif
 #ifndef CAP_WARPS
 #define CAP_WARPS 4 // warps per CTA (8, 4 or 2).  4: eight CTAs per SM, a warp takes one or two chunks, and a CTA waits less
                     // for its slowest warp (0.254 -> 0.245 ms at cap 40 000, 0.194 -> 0.144 at 10 000; 2 warps: 0.295)
@@ -750,7 +752,7 @@ __global__ void __launch_bounds__(CAP_THREADS, FUSE_MINB * 8 / CAP_WARPS)
   }
   __syncthreads();
   // every warp scans the 32 (tile, warp) counts itself
-  const int mine = s_cnt[lane];
+  const int mine = lane < CAP_G * 8 ? s_cnt[lane] : 0;
   int inc = mine;
 #pragma unroll
   for (int d = 1; d < 32; d <<= 1) {
