@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """SASS evidence for profiles/: per kernel the count of the mnemonics that prove the
 bulk-copy (UBLKCP), mbarrier (SYNCS), cp.async (LDGSTS), vector reduction (REDG ... F32x4)
-and warp-collective instructions, plus an excerpt of the fast march loop of
+and warp-collective instructions and the cluster barrier (UCGABAR_*), plus an excerpt of the fast march loop of
 integrate_keyframes_kernel<true, true, true>.
 usage: python scripts/sass_counts.py [lib] > profiles/sass_counts.txt"""
 import collections
@@ -16,8 +16,8 @@ lib = sys.argv[1] if len(sys.argv) > 1 else os.path.join(
 txt = subprocess.run(["cuobjdump", "-sass", lib], capture_output=True, text=True, check=True).stdout
 funcs = re.split(r"\n\s*Function : ", txt)[1:]
 KEEP = ("UBLKCP", "SYNCS", "LDGSTS", "RED", "ATOM", "REDUX", "MUFU", "BAR", "STL", "LDL", "UTMA",
-        "MATCH", "VOTE", "SHFL", "LDGDEPBAR", "DEPBAR")
-INS = re.compile(r"/\*[0-9a-f]{4}\*/\s+(?:@!?U?P\d+\s+)?([A-Za-z0-9_.]+)")
+        "MATCH", "VOTE", "SHFL", "LDGDEPBAR", "DEPBAR", "UCGABAR", "MEMBAR")
+INS = re.compile(r"/\*[0-9a-f]{4,6}\*/\s+(?:@!?U?P\d+\s+)?([A-Za-z0-9_.]+)")
 
 
 def demangle(n):
@@ -28,7 +28,7 @@ print("# cuobjdump -sass of", os.path.relpath(lib, ROOT), "(sm_100a); written by
 excerpt = None
 for f in funcs:
     name = demangle(f.split("\n", 1)[0].strip())
-    lines = [l for l in f.split("\n") if re.search(r"/\*[0-9a-f]{4}\*/", l)]
+    lines = [l for l in f.split("\n") if re.search(r"/\*[0-9a-f]{4,6}\*/", l)]
     ops = collections.Counter()
     for l in lines:
         m = INS.search(l)
