@@ -311,7 +311,9 @@ class ShardedTSDFVolume:
     def forget(self, ids=None):
         """Drop keyframes from the store (all of them with ids=None): their
         contribution stays in the volume, they can no longer be re-fused.
-        Returns the bytes released on this rank."""
+        Returns the bytes the dropped entries held on this rank (entries are views
+        of one clone per ingested batch: the allocator gets the memory back when
+        the last keyframe of a batch is forgotten)."""
         ids = list(self._store) if ids is None else [int(i) for i in ids]
         freed = 0
         for i in ids:
